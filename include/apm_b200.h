@@ -1,0 +1,227 @@
+/*
+ * apm_b200.h - C ABI of libapm_b200.so: the B200-native replacement for the
+ * arithmetic of APMBackend's two hot stream stages,
+ *     stream_calc_stats.js   (per-interval transaction-timing aggregation)
+ *     stream_calc_z_score.js (rolling baseline / signal)
+ * All "replaces" citations are file:line in the reference tree.
+ *
+ * Conventions
+ *   - plain C types only; every call returns apm_status (0 = OK) and never
+ *     throws or aborts.  apm_last_error(ctx) gives the text of the last failure.
+ *   - one caller thread per context (the reference stages are single-threaded
+ *     event loops, stream_calc_stats.js:331-371).
+ *   - the context owns all device and pinned memory; output buffers passed to
+ *     apm_fetch_* are caller-owned host memory.
+ *   - there is no CPU fallback: without a CUDA device every compute entry
+ *     point fails with APM_E_DEVICE.
+ */
+#ifndef APM_B200_H
+#define APM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define APM_ABI_VERSION 1
+
+typedef int32_t apm_status;
+enum {
+    APM_OK = 0,
+    APM_E_INVALID = 1,    /* bad argument / bad config                                  */
+    APM_E_DEVICE = 2,     /* CUDA error (sticky: destroy the context, state_load again) */
+    APM_E_CAPACITY = 3,   /* a configured capacity would be exceeded; nothing was lost  */
+    APM_E_WOULDBLOCK = 4, /* output ring full: fetch results, then retry                */
+    APM_E_STATE = 5,      /* call order violated (e.g. commit without acquire)          */
+    APM_E_IO = 6,         /* state file could not be read / written                     */
+    APM_E_COMM = 7        /* NCCL failure                                               */
+};
+
+#define APM_MAX_PCT 4
+#define APM_MAX_LAGS 4
+#define APM_NUM_SERIES 3 /* average + two percentiles, as FullStatEntry has (entries.js:86-108) */
+
+/* apm_config.flags */
+#define APM_F_PERCENTILES 1u /* keep per-bucket value logs and compute percentiles */
+#define APM_F_ZSCORE 2u      /* run the rolling-baseline stage                      */
+#define APM_F_KEEP_STATS 4u  /* retain apm_stat_record per tick for apm_fetch_stats */
+#define APM_F_KEEP_FS 8u     /* retain apm_fs_record per tick for apm_fetch_fs      */
+#define APM_F_ALERTS 16u     /* compact signalled fs records for apm_fetch_alerts / all-gather */
+
+/* apm_config.sd_mode */
+#define APM_SD_REFERENCE 0 /* "stddev" = sqrt(mean), as util_methods.js:26-50 computes it */
+#define APM_SD_TRUE 1      /* extension: population stddev of the valid ring entries       */
+
+/*
+ * Replaces the resolved numeric settings both stages read from
+ * config/apm_config.json:105-107 (interval, window, buffer) and :126-172
+ * (LAG / THRESHOLD / INFLUENCE defaults).  Per-key overrides are resolved by
+ * the host with the reference's own logic (stream_calc_z_score.js:106-150)
+ * and pushed with apm_set_key_params.
+ */
+typedef struct apm_config {
+    uint32_t struct_size;  /* sizeof(apm_config), for ABI checking                         */
+    int32_t device;        /* CUDA device ordinal                                           */
+    uint32_t num_services; /* capacity of service ids                                       */
+    uint32_t num_jvms;     /* capacity of JVM (server) ids; key = jvm*num_services+service  */
+    int64_t bucket_ms;     /* 10000 in the reference (generateBucketLabel, :89-91)          */
+    int32_t window_buckets; /* 30: windowSizeInIntervals                                    */
+    int32_t buffer_buckets; /* 6:  bufferSizeInIntervals                                    */
+    int32_t num_percentiles;           /* 0..APM_MAX_PCT; the reference has {75, 95}        */
+    int32_t z_series_pct[2];           /* which percentiles feed z-series 1 and 2 ({0,1})   */
+    double percentiles[APM_MAX_PCT];
+    int32_t num_lags;                  /* 0..APM_MAX_LAGS; the reference has {360, 8640}    */
+    int32_t lags[APM_MAX_LAGS];        /* ascending                                         */
+    double default_threshold[APM_MAX_LAGS];
+    double default_influence[APM_MAX_LAGS];
+    int32_t sd_mode;                   /* APM_SD_*                                          */
+    uint32_t flags;                    /* APM_F_*                                           */
+    uint64_t max_tx_per_bucket;        /* capacity of one bucket's value log (tx)           */
+    uint64_t max_batch;                /* capacity of the pinned ingest ring (tx)           */
+    uint32_t out_ticks;                /* ticks of retained records before WOULDBLOCK       */
+    uint32_t max_alerts_per_tick;      /* capacity of the compact alert block               */
+} apm_config;
+
+/* Columnar transaction batch: the fields of TxEntry (entries.js:1-21) that feed
+ * statistics - server (as jvm_id), service (as service_id), endTs, elapsed.
+ * Preconditions (checked on the device, violations are counted and skipped):
+ * service_id < num_services, jvm_id < num_jvms, elapsed_ms >= 0, end_ts_ms >= 0. */
+typedef struct apm_tx_columns {
+    uint32_t* service_id;
+    uint32_t* jvm_id;
+    int64_t* end_ts_ms;
+    int32_t* elapsed_ms;
+} apm_tx_columns;
+
+/* One per (key, tick): what generateAllStatsToQueue (stream_calc_stats.js:157-203)
+ * puts into a StatEntry, un-rounded, plus the extension fields. 96 bytes. */
+typedef struct apm_stat_record {
+    int64_t tick_ts;  /* edgeTs = (latest - buffer - 1) * bucket_ms (:356)             */
+    uint32_t key;
+    uint32_t flags;   /* bit0: key has been seen (record valid); bit1: window non-empty */
+    uint64_t count;   /* windowCntSum                                                   */
+    uint64_t sum;     /* windowRtTotalSum (exact)                                       */
+    double tpm;       /* count / (window * interval_s / 60)                             */
+    double avg;       /* sum / count, NaN when the window is empty ("undefined")        */
+    double pct[APM_MAX_PCT]; /* calcPercentile results, NaN when empty / not configured */
+    int32_t min;      /* extension (0 when empty)                                       */
+    int32_t max;      /* extension                                                      */
+    double stddev;    /* extension: population stddev of the window, NaN when empty     */
+} apm_stat_record;
+
+/* One per (key, lag, tick): the numeric content of a FullStatEntry
+ * (entries.js:86-118) as processData builds it (stream_calc_z_score.js:195-311).
+ * NaN stands for JS `undefined`. 128 bytes. */
+typedef struct apm_fs_record {
+    int64_t tick_ts;
+    uint32_t key;
+    uint32_t lag;
+    double tpm;                  /* parseFloat(tpm.toFixed(2))                           */
+    double val[APM_NUM_SERIES];  /* parseFloat(x.toFixed(1)) of average, pctA, pctB       */
+    double avg[APM_NUM_SERIES];  /* rolling mean of the lag list                          */
+    double lb[APM_NUM_SERIES];
+    double ub[APM_NUM_SERIES];
+    int8_t signal[APM_NUM_SERIES];
+    uint8_t flags;               /* bit0: record valid                                    */
+    uint8_t pad_[4];
+} apm_fs_record;
+
+typedef struct apm_tick_result {
+    uint64_t ticks;        /* ticks run by this call                        */
+    uint64_t tx_ingested;  /* transactions reduced into buckets             */
+    uint64_t tx_dropped;   /* older than the retained buckets (evicted)     */
+    uint64_t tx_invalid;   /* failed the apm_tx_columns preconditions       */
+    int64_t latest_bucket; /* latestBucket after the call                   */
+} apm_tick_result;
+
+typedef struct apm_counters {
+    uint64_t tx_ingested, tx_dropped, tx_invalid;
+    uint64_t ticks, stat_records, fs_records, alerts;
+    uint64_t h2d_bytes, d2h_bytes;
+    uint64_t kernel_launches;
+    uint64_t keys_seen;
+} apm_counters;
+
+typedef struct apm_ctx apm_ctx;
+
+/* ---- lifecycle (replaces `new StatParser()` / `new ZScoreParser()`,
+ *      stream_calc_stats.js:225, stream_calc_z_score.js:367) ---- */
+apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out);
+void apm_ctx_destroy(apm_ctx* ctx);
+const char* apm_last_error(const apm_ctx* ctx); /* ctx may be NULL (create failures) */
+uint32_t apm_abi_version(void);
+
+/* ---- ingest: replaces addData (stream_calc_stats.js:115-134) ----
+ * acquire/commit: zero-copy pinned SoA slices the host parser fills; commit
+ * copies them to the device on the copy stream and reduces them into their
+ * (key, bucket) accumulators.  All n transactions belong to the current
+ * segment: the caller has already run apm_tick for any larger bucket label,
+ * exactly as consumeMsg does (:348-370). */
+apm_status apm_ingest_acquire(apm_ctx* ctx, uint64_t n, apm_tx_columns* out_pinned);
+apm_status apm_ingest_commit(apm_ctx* ctx, uint64_t n);
+
+/* ---- tick: replaces the body of `if (bucketLabel > data.latestBucket)`
+ * (stream_calc_stats.js:348-367: removeOldBuckets + generateAllStatsToQueue)
+ * and, fused behind it, processData for every emitted StatEntry
+ * (stream_calc_z_score.js:195-311). latest_bucket must exceed the current one. */
+apm_status apm_tick(apm_ctx* ctx, int64_t latest_bucket, apm_tick_result* res);
+
+/* ---- stream chunk: replaces a run of consumeMsg calls (:331-371) over n
+ * transactions in arrival order, ticks found on the device.  *_host takes
+ * host columns (pageable or pinned) and includes the H2D copies; *_device
+ * takes device-resident columns. res may be NULL. */
+apm_status apm_process_host(apm_ctx* ctx, const apm_tx_columns* host_cols, uint64_t n, apm_tick_result* res);
+apm_status apm_process_device(apm_ctx* ctx, const apm_tx_columns* dev_cols, uint64_t n, apm_tick_result* res);
+
+/* ---- per-key z-score settings: replaces updateServiceSettings
+ * (stream_calc_z_score.js:134-150); thr/infl hold n values for keys
+ * [key_lo, key_lo+n) of lag index lag_idx. */
+apm_status apm_set_key_params(apm_ctx* ctx, uint32_t key_lo, uint32_t n, int32_t lag_idx,
+                              const double* thr, const double* infl);
+/* replaces removeStaleLagData (:170-193) for one lag: forget its lists. */
+apm_status apm_drop_lag(apm_ctx* ctx, int32_t lag_idx);
+
+/* ---- results.  Records of the ticks run since the last fetch, tick-major,
+ * key-ascending inside a tick (the host re-orders to first-seen order, the
+ * order Object.entries gives the reference, :159-160).  Only valid records
+ * are returned. Fetching drains the retained ticks. */
+apm_status apm_fetch_stats(apm_ctx* ctx, apm_stat_record* out, uint64_t cap, uint64_t* n);
+apm_status apm_fetch_fs(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
+apm_status apm_fetch_alerts(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
+/* wait for all queued device work (for timing) */
+apm_status apm_sync(apm_ctx* ctx);
+
+/* ---- lag lists: replaces the avgList/per75List/per95List arrays a resume
+ * file carries (stream_calc_z_score.js:37-64).  values holds `len` entries,
+ * oldest first, NaN for null; len <= lag. */
+apm_status apm_ring_load(apm_ctx* ctx, uint32_t key, int32_t lag_idx, int32_t series,
+                         const double* values, uint32_t len);
+apm_status apm_ring_read(apm_ctx* ctx, uint32_t key, int32_t lag_idx, int32_t series,
+                         double* values, uint32_t cap, uint32_t* len);
+
+/* ---- checkpoint: replaces saveToResumeFile / resumeFromFileIfExists
+ * (stream_calc_stats.js:54-87, stream_calc_z_score.js:37-64) with a compact
+ * binary image of the same state. */
+apm_status apm_state_save(apm_ctx* ctx, const char* path);
+apm_status apm_state_load(apm_ctx* ctx, const char* path);
+
+apm_status apm_get_counters(apm_ctx* ctx, apm_counters* out);
+apm_status apm_reset_counters(apm_ctx* ctx);
+
+/* ---- exact helpers the host formatter needs (replace Number.prototype.toFixed
+ * as used by nf(), entries.js:65-69): parseFloat(x.toFixed(digits)), digits in {1,2}. */
+double apm_quantize(double x, int32_t digits);
+
+/* ---- multi-GPU: keys are hash-sharded by the host; each rank owns its keys.
+ * The only exchange is an all-gather of the compact alert block per tick. */
+uint32_t apm_owner_of_key(uint64_t global_key, uint32_t nranks);
+apm_status apm_comm_unique_id(void* out128);                 /* ncclGetUniqueId */
+apm_status apm_comm_init(apm_ctx* ctx, int32_t rank, int32_t nranks, const void* unique_id128);
+/* all ranks' alerts of the ticks since the last call; out holds up to cap records. */
+apm_status apm_gather_alerts(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* APM_B200_H */
