@@ -15,7 +15,7 @@ CASES = [
          pcts=(75.0, 95.0), gap=(20, 31)),
     dict(seed=3, n=2500, S=9, J=2, bucket_ms=60000, window=1, buffer=0, span=40, lags=(6, 12), thr=(1.2, 3.0),
          infl=(0.0, 0.3), pcts=(50.0, 95.0), gap=None),
-    dict(seed=4, n=800, S=3, J=1, bucket_ms=10000, window=30, buffer=6, span=400, lags=(360,), thr=(3.0,),
+    dict(seed=4, n=1500, S=3, J=1, bucket_ms=10000, window=30, buffer=6, span=520, lags=(360,), thr=(3.0,),
          infl=(0.1,), pcts=(75.0, 95.0), gap=(100, 150)),
 ]
 
