@@ -1,0 +1,158 @@
+"""ctypes binding of libapm_b200.so (include/apm_b200.h).  Fails loudly when the
+CUDA library is missing - there is deliberately no other implementation to fall
+back to."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libapm_b200.so")
+SYNTH_PATH = os.path.join(_HERE, "libapm_synth.so")
+
+OK, E_INVALID, E_DEVICE, E_CAPACITY, E_WOULDBLOCK, E_STATE, E_IO, E_COMM = range(8)
+F_PERCENTILES, F_ZSCORE, F_KEEP_STATS, F_KEEP_FS, F_ALERTS = 1, 2, 4, 8, 16
+MAX_PCT, MAX_LAGS, NUM_SERIES = 4, 4, 3
+
+STAT_DTYPE = np.dtype([
+    ("tick_ts", "<i8"), ("key", "<u4"), ("flags", "<u4"), ("count", "<u8"), ("sum", "<u8"),
+    ("tpm", "<f8"), ("avg", "<f8"), ("pct", "<f8", (4,)), ("min", "<i4"), ("max", "<i4"), ("stddev", "<f8"),
+])
+FS_DTYPE = np.dtype([
+    ("tick_ts", "<i8"), ("key", "<u4"), ("lag", "<u4"), ("tpm", "<f8"),
+    ("val", "<f8", (3,)), ("avg", "<f8", (3,)), ("lb", "<f8", (3,)), ("ub", "<f8", (3,)),
+    ("signal", "i1", (3,)), ("flags", "u1"), ("pad", "u1", (4,)),
+])
+assert STAT_DTYPE.itemsize == 96 and FS_DTYPE.itemsize == 128
+
+
+class ApmConfig(C.Structure):
+    _fields_ = [
+        ("struct_size", C.c_uint32), ("device", C.c_int32),
+        ("num_services", C.c_uint32), ("num_jvms", C.c_uint32),
+        ("bucket_ms", C.c_int64),
+        ("window_buckets", C.c_int32), ("buffer_buckets", C.c_int32),
+        ("num_percentiles", C.c_int32), ("z_series_pct", C.c_int32 * 2),
+        ("percentiles", C.c_double * 4),
+        ("num_lags", C.c_int32), ("lags", C.c_int32 * 4),
+        ("default_threshold", C.c_double * 4), ("default_influence", C.c_double * 4),
+        ("sd_mode", C.c_int32), ("flags", C.c_uint32),
+        ("max_tx_per_bucket", C.c_uint64), ("max_batch", C.c_uint64),
+        ("out_ticks", C.c_uint32), ("max_alerts_per_tick", C.c_uint32),
+    ]
+
+
+class TxColumns(C.Structure):
+    _fields_ = [("service_id", C.c_void_p), ("jvm_id", C.c_void_p), ("end_ts_ms", C.c_void_p),
+                ("elapsed_ms", C.c_void_p)]
+
+
+class TickResult(C.Structure):
+    _fields_ = [("ticks", C.c_uint64), ("tx_ingested", C.c_uint64), ("tx_dropped", C.c_uint64),
+                ("tx_invalid", C.c_uint64), ("latest_bucket", C.c_int64)]
+
+
+class Counters(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in (
+        "tx_ingested", "tx_dropped", "tx_invalid", "ticks", "stat_records", "fs_records", "alerts",
+        "h2d_bytes", "d2h_bytes", "kernel_launches", "keys_seen")]
+
+
+class ApmError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"apm_b200 status {status}: {msg}")
+        self.status = status
+
+
+_lib = None
+_synth = None
+
+# every symbol include/apm_b200.h declares (tests check the library exports them all)
+SYMBOLS = {
+    "apm_abi_version": (C.c_uint32, []),
+    "apm_ctx_create": (C.c_int32, [C.POINTER(ApmConfig), C.POINTER(C.c_void_p)]),
+    "apm_ctx_destroy": (None, [C.c_void_p]),
+    "apm_last_error": (C.c_char_p, [C.c_void_p]),
+    "apm_ingest_acquire": (C.c_int32, [C.c_void_p, C.c_uint64, C.POINTER(TxColumns)]),
+    "apm_ingest_commit": (C.c_int32, [C.c_void_p, C.c_uint64]),
+    "apm_tick": (C.c_int32, [C.c_void_p, C.c_int64, C.POINTER(TickResult)]),
+    "apm_process_host": (C.c_int32, [C.c_void_p, C.POINTER(TxColumns), C.c_uint64, C.POINTER(TickResult)]),
+    "apm_process_device": (C.c_int32, [C.c_void_p, C.POINTER(TxColumns), C.c_uint64, C.POINTER(TickResult)]),
+    "apm_set_key_params": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "apm_drop_lag": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "apm_fetch_stats": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "apm_fetch_fs": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "apm_fetch_alerts": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "apm_release_ticks": (C.c_int32, [C.c_void_p]),
+    "apm_ticks_buffered": (C.c_uint32, [C.c_void_p]),
+    "apm_sync": (C.c_int32, [C.c_void_p]),
+    "apm_ring_load": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint32]),
+    "apm_ring_read": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint32,
+                                  C.POINTER(C.c_uint32)]),
+    "apm_ring_load_all": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_uint32, C.c_int32]),
+    "apm_state_save": (C.c_int32, [C.c_void_p, C.c_char_p]),
+    "apm_state_load": (C.c_int32, [C.c_void_p, C.c_char_p]),
+    "apm_get_counters": (C.c_int32, [C.c_void_p, C.POINTER(Counters)]),
+    "apm_reset_counters": (C.c_int32, [C.c_void_p]),
+    "apm_quantize": (C.c_double, [C.c_double, C.c_int32]),
+    "apm_owner_of_key": (C.c_uint32, [C.c_uint64, C.c_uint32]),
+    "apm_comm_unique_id": (C.c_int32, [C.c_void_p]),
+    "apm_comm_init": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "apm_gather_alerts": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+}
+
+
+def lib():
+    """The CUDA library.  Raises if it has not been built - never substitutes anything."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "or `make -C apmbackend_b200/csrc`.  apmbackend_b200 has no CPU fallback.")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)  # AttributeError here = library out of date
+            fn.restype = res
+            fn.argtypes = args
+        if L.apm_abi_version() != 1:
+            raise ImportError("libapm_b200.so ABI version mismatch")
+        _lib = L
+    return _lib
+
+
+def synth():
+    """Bench / test support library (synthetic streams, raw device buffers)."""
+    global _synth
+    if _synth is None:
+        if not os.path.exists(SYNTH_PATH):
+            raise ImportError(f"{SYNTH_PATH} is missing: run `make -C apmbackend_b200/csrc`")
+        S = C.CDLL(SYNTH_PATH)
+        S.synth_device_count.restype = C.c_int
+        S.synth_malloc.argtypes = [C.POINTER(C.c_void_p), C.c_uint64]
+        S.synth_malloc_host.argtypes = [C.POINTER(C.c_void_p), C.c_uint64]
+        S.synth_free.argtypes = [C.c_void_p]
+        S.synth_free_host.argtypes = [C.c_void_p]
+        S.synth_h2d.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+        S.synth_d2h.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+        S.synth_memset.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
+        S.synth_error_string.restype = C.c_char_p
+        S.synth_error_string.argtypes = [C.c_int]
+        S.synth_generate_device.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(TxColumns)]
+        S.synth_generate_host.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(TxColumns)]
+        S.synth_generate_host.restype = None
+        S.synth_ring_fill_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32]
+        S.synth_ring_fill_host.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32,
+                                           C.c_void_p, C.c_uint64]
+        S.synth_ring_fill_host.restype = None
+        _synth = S
+    return _synth
+
+
+def device_count() -> int:
+    try:
+        return int(synth().synth_device_count())
+    except Exception:
+        return 0

@@ -1,0 +1,585 @@
+// extern "C" surface of libapm_b200.so (include/apm_b200.h) and the host-side tick logic.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "ctx.h"
+
+static thread_local std::string g_create_error;
+
+apm_status apm_fail(apm_ctx* ctx, apm_status st, const std::string& msg) {
+    if (ctx) ctx->err = msg; else g_create_error = msg;
+    return st;
+}
+
+apm_status apm_fail_cuda(apm_ctx* ctx, cudaError_t e, const char* what, const char* file, int line) {
+    char buf[512];
+    snprintf(buf, sizeof buf, "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    if (ctx) { ctx->err = buf; ctx->device_error = true; } else g_create_error = buf;
+    return APM_E_DEVICE;
+}
+
+namespace {
+
+template <typename T>
+cudaError_t dalloc(T** p, size_t n) {
+    *p = nullptr;
+    if (n == 0) return cudaSuccess;
+    return cudaMalloc((void**)p, n * sizeof(T));
+}
+
+apm_status alloc_columns_device(apm_ctx* c, apm_tx_columns* d, uint64_t n) {
+    CUDA_TRY(c, dalloc(&d->service_id, n));
+    CUDA_TRY(c, dalloc(&d->jvm_id, n));
+    CUDA_TRY(c, dalloc(&d->end_ts_ms, n));
+    CUDA_TRY(c, dalloc(&d->elapsed_ms, n));
+    return APM_OK;
+}
+
+void free_columns_device(apm_tx_columns* d) {
+    cudaFree(d->service_id); cudaFree(d->jvm_id); cudaFree(d->end_ts_ms); cudaFree(d->elapsed_ms);
+    *d = {nullptr, nullptr, nullptr, nullptr};
+}
+
+apm_status validate(const apm_config* cfg) {
+    if (!cfg) return apm_fail(nullptr, APM_E_INVALID, "cfg is NULL");
+    if (cfg->struct_size != sizeof(apm_config)) return apm_fail(nullptr, APM_E_INVALID, "apm_config.struct_size mismatch");
+    if (cfg->num_services == 0 || cfg->num_jvms == 0) return apm_fail(nullptr, APM_E_INVALID, "num_services/num_jvms must be > 0");
+    if ((uint64_t)cfg->num_services * cfg->num_jvms > (1ull << 28)) return apm_fail(nullptr, APM_E_INVALID, "too many keys (limit 2^28)");
+    if (cfg->bucket_ms <= 0) return apm_fail(nullptr, APM_E_INVALID, "bucket_ms must be > 0");
+    if (cfg->window_buckets < 1 || cfg->buffer_buckets < 0 || cfg->window_buckets + cfg->buffer_buckets + 1 > APM_MAX_SLOTS)
+        return apm_fail(nullptr, APM_E_INVALID, "window/buffer out of range (window >= 1, window+buffer+1 <= 64)");
+    if (cfg->num_percentiles < 0 || cfg->num_percentiles > APM_MAX_PCT) return apm_fail(nullptr, APM_E_INVALID, "num_percentiles out of range");
+    for (int i = 0; i < cfg->num_percentiles; ++i)
+        if (!(cfg->percentiles[i] >= 0.0 && cfg->percentiles[i] <= 100.0)) return apm_fail(nullptr, APM_E_INVALID, "percentile out of [0,100]");
+    if (cfg->num_lags < 0 || cfg->num_lags > APM_MAX_LAGS) return apm_fail(nullptr, APM_E_INVALID, "num_lags out of range");
+    for (int i = 0; i < cfg->num_lags; ++i) {
+        if (cfg->lags[i] < 1) return apm_fail(nullptr, APM_E_INVALID, "lag must be >= 1");
+        if (i && cfg->lags[i] <= cfg->lags[i - 1]) return apm_fail(nullptr, APM_E_INVALID, "lags must be ascending");
+    }
+    if (cfg->max_batch == 0) return apm_fail(nullptr, APM_E_INVALID, "max_batch must be > 0");
+    if (cfg->out_ticks == 0) return apm_fail(nullptr, APM_E_INVALID, "out_ticks must be > 0");
+    if ((cfg->flags & APM_F_PERCENTILES) && cfg->num_percentiles > 0 && cfg->max_tx_per_bucket == 0)
+        return apm_fail(nullptr, APM_E_INVALID, "max_tx_per_bucket must be > 0 with percentiles");
+    return APM_OK;
+}
+
+bool with_pct(const apm_ctx* c) { return (c->cfg.flags & APM_F_PERCENTILES) && c->cfg.num_percentiles > 0; }
+bool with_z(const apm_ctx* c) { return (c->cfg.flags & APM_F_ZSCORE) && c->cfg.num_lags > 0; }
+
+apm_status refresh_counters(apm_ctx* c) {
+    CUDA_TRY(c, cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    c->counters.tx_ingested = c->h_counters->ingested;
+    c->counters.tx_dropped = c->h_counters->dropped;
+    c->counters.tx_invalid = c->h_counters->invalid + c->h_counters->future;
+    c->counters.kernel_launches = c->launches;
+    if (c->h_counters->log_overflow)
+        return apm_fail(c, APM_E_CAPACITY, "a bucket's value log overflowed max_tx_per_bucket; percentiles of that bucket are incomplete - recreate the context with a larger capacity");
+    return APM_OK;
+}
+
+// The tick itself: everything consumeMsg does inside `if (bucketLabel > latestBucket)`
+// (stream_calc_stats.js:348-367) and, behind it, processData for each emitted StatEntry.
+apm_status do_tick(apm_ctx* c, int64_t new_latest) {
+    if (new_latest <= c->latest) return apm_fail(c, APM_E_INVALID, "tick label must exceed latestBucket");
+    const bool keep_any = c->cfg.flags & (APM_F_KEEP_STATS | APM_F_KEEP_FS | APM_F_ALERTS);
+    if (keep_any && c->ticks_buffered >= c->cfg.out_ticks) return apm_fail(c, APM_E_WOULDBLOCK, "output ring full: fetch results first");
+    const int64_t old_latest = c->latest;
+    c->latest = new_latest;  // :351
+    // removeOldBuckets (:103-113): labels below latest - keep are dropped; their slots take the new labels
+    uint64_t mask = 0;
+    const int64_t first_new = std::max(old_latest + 1, new_latest - c->S + 1);
+    for (int64_t lab = first_new; lab <= new_latest; ++lab) {
+        if (lab < 0) continue;
+        const int slot = (int)(lab % c->S);
+        mask |= 1ull << slot;
+        c->slot_label[slot] = lab;
+    }
+    apm_status st = apm_launch_clear_slots(c, mask);
+    if (st) return st;
+
+    // window = labels in [latest - keep, latest - buffer] (:172)
+    WindowSlots w;
+    w.n = 0;
+    for (int64_t lab = new_latest - c->keep; lab <= new_latest - c->cfg.buffer_buckets; ++lab) {
+        if (lab < 0) continue;
+        const int slot = (int)(lab % c->S);
+        if (c->slot_label[slot] != lab) continue;  // never filled
+        w.slot[w.n++] = slot;
+    }
+    if (with_pct(c)) {
+        // sort the window's value logs that grew since their last sort
+        std::vector<SlotMeta> meta(c->S);
+        CUDA_TRY(c, cudaMemcpyAsync(meta.data(), c->slot_meta, sizeof(SlotMeta) * c->S, cudaMemcpyDeviceToHost, c->s_main));
+        CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+        c->counters.d2h_bytes += sizeof(SlotMeta) * c->S;
+        for (int i = 0; i < w.n; ++i) {
+            const int slot = w.slot[i];
+            SlotMeta& m = meta[slot];
+            if (m.count > c->log_cap) return apm_fail(c, APM_E_CAPACITY, "a bucket's value log overflowed max_tx_per_bucket");
+            if (m.count != m.sorted) {
+                st = apm_sort_slot_n(c, slot, m.count, m.max_value);
+                if (st) return st;
+                m.sorted = m.count;
+                CUDA_TRY(c, cudaMemcpyAsync(&c->slot_meta[slot].sorted, &m.sorted, sizeof(m.sorted), cudaMemcpyHostToDevice, c->s_main));
+            }
+        }
+    }
+    const int64_t tick_ts = (new_latest - c->cfg.buffer_buckets - 1) * c->cfg.bucket_ms;  // edgeTs (:356)
+    const uint32_t tslot = keep_any ? c->ticks_buffered : 0;
+    st = apm_launch_tick_stats(c, w, tick_ts, (c->cfg.flags & APM_F_KEEP_STATS) ? tslot : 0);
+    if (st) return st;
+    if (with_z(c)) {
+        const uint32_t fslot = (c->cfg.flags & APM_F_KEEP_FS) ? tslot : 0;
+        for (int l = 0; l < c->cfg.num_lags; ++l) {  // Object.entries(lags): ascending (:217)
+            st = apm_launch_baseline(c, l, tick_ts, fslot);
+            if (st) return st;
+        }
+        if (c->cfg.flags & APM_F_ALERTS) {
+            st = apm_launch_compact_alerts(c, fslot, tslot);
+            if (st) return st;
+        }
+    }
+    if (keep_any) c->ticks_buffered++;
+    c->counters.ticks++;
+    return APM_OK;
+}
+
+apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n, apm_tick_result* res) {
+    unsigned int nt = 0;
+    apm_status st = apm_launch_find_ticks(c, d.end_ts_ms, n, &nt);
+    if (st) return st;
+    const bool keep_any = c->cfg.flags & (APM_F_KEEP_STATS | APM_F_KEEP_FS | APM_F_ALERTS);
+    if (keep_any && c->ticks_buffered + nt > c->cfg.out_ticks)
+        return apm_fail(c, APM_E_WOULDBLOCK, "chunk holds more ticks than the output ring has room for: fetch results or raise out_ticks");
+    std::sort(c->h_ticks, c->h_ticks + nt, [](const TickMark& a, const TickMark& b) { return a.pos < b.pos; });
+    uint64_t pos = 0;
+    for (unsigned int i = 0; i < nt; ++i) {
+        const TickMark tm = c->h_ticks[i];
+        st = apm_launch_reduce(c, d, pos, tm.pos);  // everything that arrived before the trigger
+        if (st) return st;
+        st = do_tick(c, tm.label);  // tick BEFORE the triggering transaction is added (:348-370)
+        if (st) return st;
+        pos = tm.pos;
+    }
+    st = apm_launch_reduce(c, d, pos, n);
+    if (st) return st;
+    if (res) res->ticks += nt;
+    return APM_OK;
+}
+
+// Copies the valid records of the buffered ticks to the caller, tick-major / key-ascending.
+template <typename R>
+static apm_status fetch_dense(apm_ctx* c, const R* d_src, size_t per_tick, R* out, uint64_t cap, uint64_t* n_out) {
+    *n_out = 0;
+    const size_t total = (size_t)c->ticks_buffered * per_tick;
+    if (total == 0) return APM_OK;
+    if (cap < total) return apm_fail(c, APM_E_CAPACITY, "output buffer smaller than ticks_buffered * records per tick");
+    CUDA_TRY(c, cudaMemcpyAsync(out, d_src, total * sizeof(R), cudaMemcpyDeviceToHost, c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    c->counters.d2h_bytes += total * sizeof(R);
+    size_t w = 0;
+    for (size_t i = 0; i < total; ++i) {
+        if (out[i].flags & 1) {
+            if (w != i) out[w] = out[i];
+            ++w;
+        }
+    }
+    *n_out = w;
+    return APM_OK;
+}
+
+// fills the transaction counts of a finished call from the device counters (one sync) and
+// surfaces a value-log overflow as APM_E_CAPACITY
+static apm_status finish_result(apm_ctx* c, const apm_counters& before, apm_tick_result* res) {
+    apm_status st = refresh_counters(c);
+    if (res) {
+        res->tx_ingested = c->counters.tx_ingested - before.tx_ingested;
+        res->tx_dropped = c->counters.tx_dropped - before.tx_dropped;
+        res->tx_invalid = c->counters.tx_invalid - before.tx_invalid;
+        res->latest_bucket = c->latest;
+    }
+    return st;
+}
+
+}  // namespace
+
+extern "C" {
+
+uint32_t apm_abi_version(void) { return APM_ABI_VERSION; }
+
+const char* apm_last_error(const apm_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+double apm_quantize(double x, int32_t digits) { return apm_quantize_fixed(x, digits == 2 ? 2 : 1); }
+
+void apm_ctx_destroy(apm_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->cfg.device);
+    if (c->s_main) cudaStreamSynchronize(c->s_main);
+    if (c->s_copy) cudaStreamSynchronize(c->s_copy);
+    cudaFree(c->acc); cudaFree(c->seen); cudaFree(c->slot_meta);
+    for (int i = 0; i <= c->S && i <= APM_MAX_SLOTS; ++i) cudaFree(c->log_buf[i]);
+    cudaFree(c->d_log_ptrs); cudaFree(c->sort_hist); cudaFree(c->sort_base);
+    cudaFree(c->tf_tile_max); cudaFree(c->tf_tile_prefix); cudaFree(c->d_ticks); cudaFree(c->d_nticks);
+    cudaFreeHost(c->h_ticks); cudaFreeHost(c->h_nticks);
+    cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
+    free_columns_device(&c->dev[0]); free_columns_device(&c->dev[1]);
+    cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->zin);
+    for (int l = 0; l < APM_MAX_LAGS; ++l) { cudaFree(c->ring[l]); cudaFree(c->ring_len[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
+    cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->d_gather);
+    for (int i = 0; i < 2; ++i) { if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); if (c->ev_consumed[i]) cudaEventDestroy(c->ev_consumed[i]); }
+    if (c->s_main) cudaStreamDestroy(c->s_main);
+    if (c->s_copy) cudaStreamDestroy(c->s_copy);
+    apm_comm_destroy_internal(c);
+    delete c;
+}
+
+apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
+    if (!out) return apm_fail(nullptr, APM_E_INVALID, "out is NULL");
+    *out = nullptr;
+    apm_status st = validate(cfg);
+    if (st) return st;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return apm_fail(nullptr, APM_E_DEVICE, std::string("no CUDA device available (there is no CPU fallback): ") + cudaGetErrorString(e));
+    if (cfg->device < 0 || cfg->device >= ndev) return apm_fail(nullptr, APM_E_INVALID, "device ordinal out of range");
+    apm_ctx* c = new apm_ctx();
+    c->cfg = *cfg;
+    memset(&c->counters, 0, sizeof c->counters);
+    for (int i = 0; i <= APM_MAX_SLOTS; ++i) c->log_buf[i] = nullptr;
+    for (int i = 0; i < APM_MAX_SLOTS; ++i) c->slot_label[i] = -1;
+    c->K = cfg->num_services * cfg->num_jvms;
+    c->keep = cfg->window_buckets + cfg->buffer_buckets;
+    c->S = c->keep + 1;
+    c->inv_bucket = 1.0 / (double)cfg->bucket_ms;
+    // windowSz * intervalLengthSec / 60.0 (stream_calc_stats.js:186)
+    c->tpm_div = (double)cfg->window_buckets * ((double)cfg->bucket_ms / 1000.0) / 60.0;
+    for (int i = 0; i < cfg->num_percentiles; ++i) c->pfrac[i] = cfg->percentiles[i] / 100.0;  // util_methods.js:129
+    auto fail = [&](apm_status s) { g_create_error = c->err; apm_ctx_destroy(c); return s; };
+#define TRY_CREATE(expr) do { cudaError_t e2_ = (expr); if (e2_ != cudaSuccess) { apm_fail_cuda(c, e2_, #expr, __FILE__, __LINE__); return fail(APM_E_DEVICE); } } while (0)
+    TRY_CREATE(cudaSetDevice(cfg->device));
+    TRY_CREATE(cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking));
+    TRY_CREATE(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        TRY_CREATE(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
+        TRY_CREATE(cudaEventCreateWithFlags(&c->ev_consumed[i], cudaEventDisableTiming));
+    }
+    const size_t K = c->K;
+    TRY_CREATE(dalloc(&c->acc, (size_t)c->S * K));
+    TRY_CREATE(dalloc(&c->seen, K));
+    TRY_CREATE(cudaMemsetAsync(c->seen, 0, K, c->s_main));
+    TRY_CREATE(dalloc(&c->slot_meta, (size_t)c->S));
+    TRY_CREATE(cudaMemsetAsync(c->slot_meta, 0, sizeof(SlotMeta) * c->S, c->s_main));
+    TRY_CREATE(dalloc(&c->d_log_ptrs, (size_t)APM_MAX_SLOTS));
+    if (with_pct(c)) {
+        c->log_cap = cfg->max_tx_per_bucket;
+        for (int i = 0; i <= c->S; ++i) TRY_CREATE(dalloc(&c->log_buf[i], (size_t)c->log_cap));
+        c->sort_tiles_cap = (c->log_cap + 4095) / 4096;
+        TRY_CREATE(dalloc(&c->sort_hist, (size_t)256 * c->sort_tiles_cap));
+        TRY_CREATE(dalloc(&c->sort_base, (size_t)256));
+    }
+    TRY_CREATE(cudaMemcpyAsync(c->d_log_ptrs, c->log_buf, sizeof(uint64_t*) * APM_MAX_SLOTS, cudaMemcpyHostToDevice, c->s_main));
+    c->tf_tiles_cap = (cfg->max_batch + 4095) / 4096;
+    TRY_CREATE(dalloc(&c->tf_tile_max, (size_t)c->tf_tiles_cap));
+    TRY_CREATE(dalloc(&c->tf_tile_prefix, (size_t)c->tf_tiles_cap));
+    TRY_CREATE(dalloc(&c->d_ticks, (size_t)c->max_ticks_per_chunk));
+    TRY_CREATE(dalloc(&c->d_nticks, (size_t)1));
+    TRY_CREATE(cudaMallocHost((void**)&c->h_ticks, sizeof(TickMark) * c->max_ticks_per_chunk));
+    TRY_CREATE(cudaMallocHost((void**)&c->h_nticks, sizeof(unsigned int)));
+    TRY_CREATE(dalloc(&c->zin, 4 * K));
+    if (cfg->flags & APM_F_KEEP_STATS) TRY_CREATE(dalloc(&c->d_stats, (size_t)cfg->out_ticks * K));
+    if (with_z(c)) {
+        const size_t fs_ticks = (cfg->flags & APM_F_KEEP_FS) ? cfg->out_ticks : 1;
+        TRY_CREATE(dalloc(&c->d_fs, fs_ticks * cfg->num_lags * K));
+        if (cfg->flags & APM_F_ALERTS) {
+            if (cfg->max_alerts_per_tick == 0) { c->err = "max_alerts_per_tick must be > 0 with APM_F_ALERTS"; return fail(APM_E_INVALID); }
+            TRY_CREATE(dalloc(&c->d_alerts, (size_t)cfg->out_ticks * cfg->max_alerts_per_tick));
+            TRY_CREATE(dalloc(&c->d_alert_count, (size_t)cfg->out_ticks));
+            TRY_CREATE(cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * cfg->out_ticks, c->s_main));
+        }
+        for (int l = 0; l < cfg->num_lags; ++l) {
+            const size_t L = (size_t)cfg->lags[l];
+            TRY_CREATE(dalloc(&c->ring[l], L * 3 * K));
+            TRY_CREATE(dalloc(&c->ring_len[l], 3 * K));
+            TRY_CREATE(cudaMemsetAsync(c->ring_len[l], 0, sizeof(uint32_t) * 3 * K, c->s_main));
+            TRY_CREATE(dalloc(&c->thr[l], K));
+            TRY_CREATE(dalloc(&c->infl[l], K));
+            std::vector<double> t(K, cfg->default_threshold[l]), f(K, cfg->default_influence[l]);
+            TRY_CREATE(cudaMemcpy(c->thr[l], t.data(), K * sizeof(double), cudaMemcpyHostToDevice));
+            TRY_CREATE(cudaMemcpy(c->infl[l], f.data(), K * sizeof(double), cudaMemcpyHostToDevice));
+        }
+    }
+    TRY_CREATE(dalloc(&c->d_counters, (size_t)1));
+    TRY_CREATE(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->s_main));
+    TRY_CREATE(cudaMallocHost((void**)&c->h_counters, sizeof(DevCounters)));
+    for (int i = 0; i < 2; ++i) {
+        st = alloc_columns_device(c, &c->dev[i], cfg->max_batch);
+        if (st) return fail(st);
+    }
+    TRY_CREATE(cudaMallocHost((void**)&c->pin.service_id, cfg->max_batch * sizeof(uint32_t)));
+    TRY_CREATE(cudaMallocHost((void**)&c->pin.jvm_id, cfg->max_batch * sizeof(uint32_t)));
+    TRY_CREATE(cudaMallocHost((void**)&c->pin.end_ts_ms, cfg->max_batch * sizeof(int64_t)));
+    TRY_CREATE(cudaMallocHost((void**)&c->pin.elapsed_ms, cfg->max_batch * sizeof(int32_t)));
+    TRY_CREATE(cudaStreamSynchronize(c->s_main));
+#undef TRY_CREATE
+    *out = c;
+    return APM_OK;
+}
+
+apm_status apm_sync(apm_ctx* c) {
+    if (!c) return APM_E_INVALID;
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    return APM_OK;
+}
+
+apm_status apm_ingest_acquire(apm_ctx* c, uint64_t n, apm_tx_columns* out) {
+    if (!c || !out) return APM_E_INVALID;
+    if (n > c->cfg.max_batch) return apm_fail(c, APM_E_CAPACITY, "acquire larger than max_batch");
+    // the previous commit's copy must have left the pinned slices
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
+    *out = c->pin;
+    c->acquired = n;
+    return APM_OK;
+}
+
+apm_status apm_ingest_commit(apm_ctx* c, uint64_t n) {
+    if (!c) return APM_E_INVALID;
+    if (n > c->acquired) return apm_fail(c, APM_E_STATE, "commit without a matching acquire");
+    c->acquired = 0;
+    if (n == 0) return APM_OK;
+    if (c->latest == 0) return apm_fail(c, APM_E_STATE, "commit before the first tick: run apm_tick for the first bucket label");
+    apm_tx_columns& d = c->dev[0];
+    CUDA_TRY(c, cudaStreamWaitEvent(c->s_copy, c->ev_consumed[0], 0));
+    CUDA_TRY(c, cudaMemcpyAsync(d.service_id, c->pin.service_id, n * 4, cudaMemcpyHostToDevice, c->s_copy));
+    CUDA_TRY(c, cudaMemcpyAsync(d.jvm_id, c->pin.jvm_id, n * 4, cudaMemcpyHostToDevice, c->s_copy));
+    CUDA_TRY(c, cudaMemcpyAsync(d.end_ts_ms, c->pin.end_ts_ms, n * 8, cudaMemcpyHostToDevice, c->s_copy));
+    CUDA_TRY(c, cudaMemcpyAsync(d.elapsed_ms, c->pin.elapsed_ms, n * 4, cudaMemcpyHostToDevice, c->s_copy));
+    CUDA_TRY(c, cudaEventRecord(c->ev_copied[0], c->s_copy));
+    CUDA_TRY(c, cudaStreamWaitEvent(c->s_main, c->ev_copied[0], 0));
+    c->counters.h2d_bytes += n * 20;
+    apm_status st = apm_launch_reduce(c, d, 0, n);
+    if (st) return st;
+    CUDA_TRY(c, cudaEventRecord(c->ev_consumed[0], c->s_main));
+    return APM_OK;
+}
+
+apm_status apm_tick(apm_ctx* c, int64_t latest_bucket, apm_tick_result* res) {
+    if (!c) return APM_E_INVALID;
+    apm_status st = do_tick(c, latest_bucket);
+    if (st) return st;
+    if (res) {
+        memset(res, 0, sizeof *res);
+        res->ticks = 1;
+        res->latest_bucket = c->latest;
+    }
+    return APM_OK;
+}
+
+apm_status apm_process_device(apm_ctx* c, const apm_tx_columns* cols, uint64_t n, apm_tick_result* res) {
+    if (!c || !cols) return APM_E_INVALID;
+    if (res) memset(res, 0, sizeof *res);
+    const apm_counters before = c->counters;
+    uint64_t off = 0;
+    while (off < n) {
+        const uint64_t m = std::min<uint64_t>(n - off, c->cfg.max_batch);
+        apm_tx_columns d = {cols->service_id + off, cols->jvm_id + off, cols->end_ts_ms + off, cols->elapsed_ms + off};
+        apm_status st = process_chunk_device(c, d, m, res);
+        if (st) return st;
+        off += m;
+    }
+    return finish_result(c, before, res);
+}
+
+apm_status apm_process_host(apm_ctx* c, const apm_tx_columns* h, uint64_t n, apm_tick_result* res) {
+    if (!c || !h) return APM_E_INVALID;
+    if (res) memset(res, 0, sizeof *res);
+    const apm_counters before = c->counters;
+    const uint64_t B = c->cfg.max_batch;
+    const uint64_t nchunks = (n + B - 1) / B;
+    auto enqueue_copy = [&](uint64_t ci) -> apm_status {
+        const int b = (int)(ci & 1);
+        const uint64_t off = ci * B, m = std::min<uint64_t>(n - off, B);
+        apm_tx_columns& d = c->dev[b];
+        CUDA_TRY(c, cudaStreamWaitEvent(c->s_copy, c->ev_consumed[b], 0));
+        CUDA_TRY(c, cudaMemcpyAsync(d.service_id, h->service_id + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
+        CUDA_TRY(c, cudaMemcpyAsync(d.jvm_id, h->jvm_id + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
+        CUDA_TRY(c, cudaMemcpyAsync(d.end_ts_ms, h->end_ts_ms + off, m * 8, cudaMemcpyHostToDevice, c->s_copy));
+        CUDA_TRY(c, cudaMemcpyAsync(d.elapsed_ms, h->elapsed_ms + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
+        CUDA_TRY(c, cudaEventRecord(c->ev_copied[b], c->s_copy));
+        c->counters.h2d_bytes += m * 20;
+        return APM_OK;
+    };
+    if (nchunks) { apm_status st = enqueue_copy(0); if (st) return st; }
+    for (uint64_t ci = 0; ci < nchunks; ++ci) {
+        const int b = (int)(ci & 1);
+        const uint64_t off = ci * B, m = std::min<uint64_t>(n - off, B);
+        // the next chunk's copy overlaps this chunk's kernels
+        if (ci + 1 < nchunks) { apm_status st = enqueue_copy(ci + 1); if (st) return st; }
+        CUDA_TRY(c, cudaStreamWaitEvent(c->s_main, c->ev_copied[b], 0));
+        apm_status st = process_chunk_device(c, c->dev[b], m, res);
+        if (st) return st;
+        CUDA_TRY(c, cudaEventRecord(c->ev_consumed[b], c->s_main));
+    }
+    return finish_result(c, before, res);
+}
+
+apm_status apm_set_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, int32_t l, const double* thr, const double* infl) {
+    if (!c || !thr || !infl) return APM_E_INVALID;
+    if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || (uint64_t)key_lo + n > c->K) return apm_fail(c, APM_E_INVALID, "set_key_params: range");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    CUDA_TRY(c, cudaMemcpy(c->thr[l] + key_lo, thr, n * sizeof(double), cudaMemcpyHostToDevice));
+    CUDA_TRY(c, cudaMemcpy(c->infl[l] + key_lo, infl, n * sizeof(double), cudaMemcpyHostToDevice));
+    return APM_OK;
+}
+
+apm_status apm_drop_lag(apm_ctx* c, int32_t l) {
+    if (!c) return APM_E_INVALID;
+    if (!with_z(c) || l < 0 || l >= c->cfg.num_lags) return apm_fail(c, APM_E_INVALID, "drop_lag: index");
+    CUDA_TRY(c, cudaMemsetAsync(c->ring_len[l], 0, sizeof(uint32_t) * 3 * c->K, c->s_main));
+    return APM_OK;
+}
+
+apm_status apm_fetch_stats(apm_ctx* c, apm_stat_record* out, uint64_t cap, uint64_t* n) {
+    if (!c || !n) return APM_E_INVALID;
+    if (!(c->cfg.flags & APM_F_KEEP_STATS)) return apm_fail(c, APM_E_STATE, "stat records are not retained (APM_F_KEEP_STATS)");
+    apm_status st = fetch_dense(c, c->d_stats, c->K, out, cap, n);
+    if (!st) c->counters.stat_records += *n;
+    return st;
+}
+
+apm_status apm_fetch_fs(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64_t* n) {
+    if (!c || !n) return APM_E_INVALID;
+    if (!(c->cfg.flags & APM_F_KEEP_FS) || !with_z(c)) return apm_fail(c, APM_E_STATE, "fs records are not retained (APM_F_KEEP_FS | APM_F_ZSCORE)");
+    apm_status st = fetch_dense(c, c->d_fs, (size_t)c->K * c->cfg.num_lags, out, cap, n);
+    if (!st) c->counters.fs_records += *n;
+    return st;
+}
+
+apm_status apm_fetch_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64_t* n) {
+    if (!c || !n) return APM_E_INVALID;
+    *n = 0;
+    if (!c->d_alerts) return apm_fail(c, APM_E_STATE, "alerts are not compacted (APM_F_ALERTS | APM_F_ZSCORE)");
+    if (c->ticks_buffered == 0) return APM_OK;
+    std::vector<unsigned int> counts(c->ticks_buffered);
+    CUDA_TRY(c, cudaMemcpyAsync(counts.data(), c->d_alert_count, sizeof(unsigned int) * c->ticks_buffered, cudaMemcpyDeviceToHost, c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    uint64_t total = 0;
+    for (unsigned int k : counts) {
+        if (k > c->cfg.max_alerts_per_tick) return apm_fail(c, APM_E_CAPACITY, "more alerts in one tick than max_alerts_per_tick");
+        total += k;
+    }
+    if (total > cap) return apm_fail(c, APM_E_CAPACITY, "alert output buffer too small");
+    uint64_t w = 0;
+    for (uint32_t t = 0; t < c->ticks_buffered; ++t) {
+        if (!counts[t]) continue;
+        CUDA_TRY(c, cudaMemcpyAsync(out + w, c->d_alerts + (size_t)t * c->cfg.max_alerts_per_tick, counts[t] * sizeof(apm_fs_record), cudaMemcpyDeviceToHost, c->s_main));
+        // atomics append in arbitrary order: present each tick's alerts (lag, key)-ascending
+        CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+        std::sort(out + w, out + w + counts[t], [](const apm_fs_record& a, const apm_fs_record& b) { return a.lag != b.lag ? a.lag < b.lag : a.key < b.key; });
+        w += counts[t];
+    }
+    c->counters.d2h_bytes += total * sizeof(apm_fs_record) + counts.size() * 4;
+    c->counters.alerts += total;
+    *n = total;
+    return APM_OK;
+}
+
+apm_status apm_release_ticks(apm_ctx* c) {
+    if (!c) return APM_E_INVALID;
+    if (c->d_alert_count) CUDA_TRY(c, cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * c->cfg.out_ticks, c->s_main));
+    c->ticks_buffered = 0;
+    return APM_OK;
+}
+
+apm_status apm_ring_load(apm_ctx* c, uint32_t key, int32_t l, int32_t series, const double* values, uint32_t len) {
+    if (!c || (!values && len)) return APM_E_INVALID;
+    if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || series < 0 || series >= APM_NUM_SERIES || key >= c->K) return apm_fail(c, APM_E_INVALID, "ring_load: index");
+    const uint32_t L = (uint32_t)c->cfg.lags[l];
+    if (len > L) return apm_fail(c, APM_E_INVALID, "ring_load: list longer than its lag");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    const size_t ncol = 3 * (size_t)c->K, col = (size_t)series * c->K + key;
+    const uint32_t head = c->ring_head[l];
+    // the list ends just before `head`: element i (oldest first) lives at slot head - len + i
+    std::vector<double> tmp(values, values + len);
+    const uint32_t first = (head + L - len) % L;
+    const uint32_t n1 = std::min(len, L - first);
+    if (n1) CUDA_TRY(c, cudaMemcpy2D(c->ring[l] + (size_t)first * ncol + col, ncol * sizeof(double), tmp.data(), sizeof(double), sizeof(double), n1, cudaMemcpyHostToDevice));
+    if (len > n1) CUDA_TRY(c, cudaMemcpy2D(c->ring[l] + col, ncol * sizeof(double), tmp.data() + n1, sizeof(double), sizeof(double), len - n1, cudaMemcpyHostToDevice));
+    CUDA_TRY(c, cudaMemcpy(c->ring_len[l] + col, &len, sizeof(uint32_t), cudaMemcpyHostToDevice));
+    return APM_OK;
+}
+
+apm_status apm_ring_load_all(apm_ctx* c, int32_t l, const double* values, uint32_t len, int32_t on_device) {
+    if (!c || (!values && len)) return APM_E_INVALID;
+    if (!with_z(c) || l < 0 || l >= c->cfg.num_lags) return apm_fail(c, APM_E_INVALID, "ring_load_all: index");
+    const uint32_t L = (uint32_t)c->cfg.lags[l];
+    if (len > L) return apm_fail(c, APM_E_INVALID, "ring_load_all: lists longer than the lag");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    const size_t ncol = 3 * (size_t)c->K, row = ncol * sizeof(double);
+    const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    const uint32_t head = c->ring_head[l], first = (head + L - len) % L, n1 = std::min(len, L - first);
+    if (n1) CUDA_TRY(c, cudaMemcpy(c->ring[l] + (size_t)first * ncol, values, n1 * row, kind));
+    if (len > n1) CUDA_TRY(c, cudaMemcpy(c->ring[l], values + (size_t)n1 * ncol, (len - n1) * row, kind));
+    std::vector<uint32_t> lens(ncol, len);
+    CUDA_TRY(c, cudaMemcpy(c->ring_len[l], lens.data(), ncol * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    return APM_OK;
+}
+
+apm_status apm_ring_read(apm_ctx* c, uint32_t key, int32_t l, int32_t series, double* values, uint32_t cap, uint32_t* len_out) {
+    if (!c || !len_out) return APM_E_INVALID;
+    if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || series < 0 || series >= APM_NUM_SERIES || key >= c->K) return apm_fail(c, APM_E_INVALID, "ring_read: index");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    const uint32_t L = (uint32_t)c->cfg.lags[l];
+    const size_t ncol = 3 * (size_t)c->K, col = (size_t)series * c->K + key;
+    uint32_t len = 0;
+    CUDA_TRY(c, cudaMemcpy(&len, c->ring_len[l] + col, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    *len_out = len;
+    if (len == 0) return APM_OK;
+    if (!values || cap < len) return apm_fail(c, APM_E_CAPACITY, "ring_read: buffer too small");
+    const uint32_t head = c->ring_head[l];
+    const uint32_t first = (head + L - len) % L;
+    const uint32_t n1 = std::min(len, L - first);
+    CUDA_TRY(c, cudaMemcpy2D(values, sizeof(double), c->ring[l] + (size_t)first * ncol + col, ncol * sizeof(double), sizeof(double), n1, cudaMemcpyDeviceToHost));
+    if (len > n1) CUDA_TRY(c, cudaMemcpy2D(values + n1, sizeof(double), c->ring[l] + col, ncol * sizeof(double), sizeof(double), len - n1, cudaMemcpyDeviceToHost));
+    return APM_OK;
+}
+
+apm_status apm_get_counters(apm_ctx* c, apm_counters* out) {
+    if (!c || !out) return APM_E_INVALID;
+    apm_status st = refresh_counters(c);
+    // keys_seen: count on the host (called rarely)
+    std::vector<uint8_t> seen(c->K);
+    CUDA_TRY(c, cudaMemcpy(seen.data(), c->seen, c->K, cudaMemcpyDeviceToHost));
+    uint64_t ks = 0;
+    for (uint8_t s : seen) ks += s;
+    c->counters.keys_seen = ks;
+    *out = c->counters;
+    return st;
+}
+
+apm_status apm_reset_counters(apm_ctx* c) {
+    if (!c) return APM_E_INVALID;
+    CUDA_TRY(c, cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->s_main));
+    memset(&c->counters, 0, sizeof c->counters);
+    c->launches = 0;
+    return APM_OK;
+}
+
+uint32_t apm_owner_of_key(uint64_t k, uint32_t nranks) {
+    // splitmix64 finaliser
+    k += 0x9E3779B97F4A7C15ull;
+    k = (k ^ (k >> 30)) * 0xBF58476D1CE4E5B9ull;
+    k = (k ^ (k >> 27)) * 0x94D049BB133111EBull;
+    k ^= k >> 31;
+    return nranks ? (uint32_t)(k % nranks) : 0;
+}
+
+}  // extern "C"
+
+extern "C" uint32_t apm_ticks_buffered(const apm_ctx* c) { return c ? c->ticks_buffered : 0; }

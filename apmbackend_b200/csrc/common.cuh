@@ -1,0 +1,112 @@
+// Shared device/host definitions of libapm_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/apm_b200.h"
+
+#define APM_MAX_SLOTS 64  // window + buffer + 1 must not exceed this
+#define APM_NUM_SMS 148   // B200
+
+// One (key, bucket-slot) accumulator: everything addData (stream_calc_stats.js:115-134)
+// would have appended to buckets[label], reduced to order-independent integers.
+struct __align__(32) Acc {
+    uint32_t count;
+    uint32_t vmin;      // 0xFFFFFFFF when empty
+    uint32_t vmax;
+    uint32_t sumsq_hi;  // bits 64..95 of the sum of squares
+    uint64_t sum;
+    uint64_t sumsq_lo;
+};
+static_assert(sizeof(Acc) == 32, "Acc must be one 32-byte sector");
+
+// Per bucket-slot bookkeeping of the value log (device resident).
+struct SlotMeta {
+    unsigned long long count;   // entries appended
+    unsigned long long sorted;  // entries covered by the last sort
+    uint32_t max_value;         // largest elapsed appended (bounds the radix passes)
+    uint32_t pad_;
+};
+
+// Device counters, one cache line.
+struct DevCounters {
+    unsigned long long ingested, dropped, invalid, future, log_overflow;
+};
+
+struct WindowSlots {
+    int n;
+    int slot[APM_MAX_SLOTS];
+};
+
+#define CUDA_TRY(ctx, expr)                                                                       \
+    do {                                                                                          \
+        cudaError_t e_ = (expr);                                                                  \
+        if (e_ != cudaSuccess) return apm_fail_cuda((ctx), e_, #expr, __FILE__, __LINE__);        \
+    } while (0)
+
+struct apm_ctx;
+apm_status apm_fail_cuda(apm_ctx* ctx, cudaError_t e, const char* what, const char* file, int line);
+apm_status apm_fail(apm_ctx* ctx, apm_status st, const std::string& msg);
+
+// ---------------------------------------------------------------------------------------------
+// Exact helpers shared by host and device
+// ---------------------------------------------------------------------------------------------
+
+// generateBucketLabel (stream_calc_stats.js:89-91): floor(ts / bucket_ms) for ts >= 0.
+__host__ __device__ __forceinline__ int64_t apm_label(int64_t ts, int64_t bucket_ms, double inv_bucket) {
+#ifdef __CUDA_ARCH__
+    // ts < 2^53: one multiply and a one-step fix-up is exact and avoids the 64-bit divide sequence
+    int64_t q = (int64_t)(__dmul_rn((double)ts, inv_bucket));
+    int64_t r = ts - q * bucket_ms;
+    if (r < 0) { q -= 1; r += bucket_ms; }
+    if (r >= bucket_ms) { q += 1; }
+    return q;
+#else
+    (void)inv_bucket;
+    return ts / bucket_ms;
+#endif
+}
+
+// parseFloat(x.toFixed(digits)) for x >= 0 or NaN, digits in {1, 2}: what the next stage reads
+// after the CSV hop (entries.js:65-73 -> 58-61).  toFixed picks the integer n closest to
+// x * 10^digits on the EXACT binary value of x, the larger n on a tie; strtod of the decimal
+// string is the correctly rounded n / 10^digits, which one IEEE division reproduces
+// (n < 2^53).  Negative inputs (never produced by the stats stage) take the mirrored path.
+__host__ __device__ __forceinline__ double apm_quantize_fixed(double x, int digits) {
+    if (x != x) return x;
+    const bool neg = x < 0;
+    if (neg) x = -x;
+    if (x >= 4.0e15) return neg ? -x : x;  // already an integer multiple far above 0.01
+    unsigned long long bits;
+#ifdef __CUDA_ARCH__
+    bits = (unsigned long long)__double_as_longlong(x);
+#else
+    __builtin_memcpy(&bits, &x, 8);
+#endif
+    const int be = (int)((bits >> 52) & 0x7FF);
+    unsigned long long m = bits & 0xFFFFFFFFFFFFFull;
+    int e;
+    if (be == 0) { e = -1074; } else { m |= 1ull << 52; e = be - 1075; }  // x = m * 2^e
+    const unsigned long long p = digits == 1 ? 10ull : 100ull;
+    unsigned long long v = m * p;  // < 2^60
+    unsigned long long n;
+    if (e >= 0) {
+        n = v << e;  // x < 4e15 keeps this below 2^63
+    } else if (-e >= 64) {
+        n = 0;
+    } else {
+        const int s = -e;
+        const unsigned long long q = v >> s;
+        const unsigned long long r = v - (q << s);
+        n = q + ((r >= (1ull << (s - 1))) ? 1ull : 0ull);
+    }
+    const double d = digits == 1 ? 10.0 : 100.0;
+#ifdef __CUDA_ARCH__
+    const double y = __ddiv_rn((double)n, d);
+#else
+    const double y = (double)n / d;
+#endif
+    return neg ? -y : y;
+}

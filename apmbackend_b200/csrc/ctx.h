@@ -1,0 +1,95 @@
+// Context layout and the host-side launchers of each kernel group.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+struct TickMark {
+    unsigned long long pos;  // index in the chunk of the transaction that triggers the tick
+    long long label;         // its bucket label (the new latestBucket)
+};
+
+struct apm_ctx {
+    apm_config cfg;
+    uint32_t K = 0;       // keys = num_services * num_jvms
+    int S = 0;            // bucket slots = window + buffer + 1 (labels latest-keep .. latest)
+    int keep = 0;         // NUM_KEEP_INTERVALS = window + buffer (stream_calc_stats.js:233)
+    int64_t latest = 0;   // latestBucket (:42)
+    double inv_bucket = 0, tpm_div = 1;
+    double pfrac[APM_MAX_PCT] = {0, 0, 0, 0};  // percentile / 100.0 (util_methods.js:129)
+
+    cudaStream_t s_main = nullptr, s_copy = nullptr;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
+
+    // --- bucket accumulators and value logs
+    Acc* acc = nullptr;          // [S][K]
+    uint8_t* seen = nullptr;     // [K] key has ever been ingested
+    SlotMeta* slot_meta = nullptr;  // [S]
+    int64_t slot_label[APM_MAX_SLOTS];
+    uint64_t* log_buf[APM_MAX_SLOTS + 1];  // S value logs + 1 spare for the sort ping-pong
+    uint64_t** d_log_ptrs = nullptr;       // device copy of log_buf[0..S)
+    uint64_t log_cap = 0;
+    // radix sort scratch
+    uint32_t* sort_hist = nullptr;  // [256][tiles]
+    uint32_t* sort_base = nullptr;  // [256]
+    uint64_t sort_tiles_cap = 0;
+
+    // --- tick finder scratch
+    long long* tf_tile_max = nullptr;
+    long long* tf_tile_prefix = nullptr;
+    uint64_t tf_tiles_cap = 0;
+    TickMark* d_ticks = nullptr;
+    unsigned int* d_nticks = nullptr;
+    TickMark* h_ticks = nullptr;       // pinned
+    unsigned int* h_nticks = nullptr;  // pinned
+    uint32_t max_ticks_per_chunk = 4096;
+
+    // --- staging of host batches: pinned SoA ring (acquire/commit) + two device buffers
+    apm_tx_columns pin = {nullptr, nullptr, nullptr, nullptr};
+    apm_tx_columns dev[2] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
+    uint64_t acquired = 0;
+
+    // --- tick outputs
+    apm_stat_record* d_stats = nullptr;  // [out_ticks][K]
+    apm_fs_record* d_fs = nullptr;       // [out_ticks][num_lags][K]
+    apm_fs_record* d_alerts = nullptr;   // [out_ticks][max_alerts_per_tick]
+    unsigned int* d_alert_count = nullptr;  // [out_ticks]
+    double* zin = nullptr;               // [4][K]: tpm', val0, val1, val2 (quantised)
+    uint32_t ticks_buffered = 0;
+    uint32_t alerts_gather_from = 0;     // first buffered tick not yet all-gathered
+
+    // --- rolling baseline
+    double* ring[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};        // [L][3][K]
+    uint32_t* ring_len[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};  // [3][K]
+    uint32_t ring_head[APM_MAX_LAGS] = {0, 0, 0, 0};                          // slot the next push writes
+    double* thr[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};         // [K]
+    double* infl[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};        // [K]
+
+    DevCounters* d_counters = nullptr;
+    DevCounters* h_counters = nullptr;  // pinned mirror
+    apm_counters counters;
+    uint64_t launches = 0;
+
+    // multi-GPU
+    void* nccl_comm = nullptr;
+    int rank = 0, nranks = 1;
+    apm_fs_record* d_gather = nullptr;  // [nranks][1 + max_alerts_per_tick * out_ticks] blocks
+
+    bool device_error = false;
+    std::string err;
+};
+
+// k1_ingest.cu
+apm_status apm_launch_find_ticks(apm_ctx* c, const int64_t* d_ts, uint64_t n, unsigned int* n_ticks_out);
+apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin, uint64_t end);
+// k3_sort.cu
+apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value);
+// k2_tick.cu
+apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask);
+apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot);
+// k4_baseline.cu
+apm_status apm_launch_baseline(apm_ctx* c, int lag_idx, int64_t tick_ts, uint32_t tick_slot);
+apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot);
+// comm.cu
+void apm_comm_destroy_internal(apm_ctx* c);

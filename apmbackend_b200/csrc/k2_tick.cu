@@ -1,0 +1,234 @@
+// K2 + K3b: per-key window combine, percentile selection and the toFixed hop.
+//
+// Replaces removeOldBuckets (stream_calc_stats.js:103-113) with a slot clear and
+// generateAllStatsToQueue (:157-203) + calcPercentile (util_methods.js:112-142) +
+// StatEntry.toCSVString / re-parse (entries.js:52-73, 179-180) with one thread per key.
+#include "ctx.h"
+
+namespace {
+
+__global__ void __launch_bounds__(256) clear_slots_kernel(Acc* __restrict__ acc, SlotMeta* __restrict__ meta, uint32_t K,
+                                                          int S, unsigned long long slot_mask) {
+    // grid.y = slot; 32-byte accumulators are written as two 16-byte stores
+    const int slot = blockIdx.y;
+    if (!((slot_mask >> slot) & 1ull)) return;
+    uint4* a = reinterpret_cast<uint4*>(acc + (size_t)slot * K);
+    const uint4 lo = make_uint4(0u, 0xFFFFFFFFu, 0u, 0u), hi = make_uint4(0u, 0u, 0u, 0u);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)K; i += (size_t)gridDim.x * blockDim.x) {
+        a[2 * i] = lo;
+        a[2 * i + 1] = hi;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        meta[slot].count = 0;
+        meta[slot].sorted = 0;
+        meta[slot].max_value = 0;
+    }
+}
+
+struct Run {
+    const uint64_t* p;  // first word of this key's ascending run inside a sorted bucket log
+    uint32_t n;
+};
+
+// first index in [0, n) whose word is >= x
+__device__ __forceinline__ uint64_t lower_bound_u64(const uint64_t* a, uint64_t n, uint64_t x) {
+    uint64_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint64_t mid = (lo + hi) >> 1;
+        if (__ldg(a + mid) < x) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// number of values <= v in an ascending run (values are the low 32 bits)
+__device__ __forceinline__ uint32_t count_le(const Run& r, uint32_t v) {
+    uint32_t lo = 0, hi = r.n;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if ((uint32_t)__ldg(r.p + mid) <= v) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// k-th smallest (0-based) of the union of the runs; also returns how many values are <= it
+__device__ uint32_t select_kth(const Run* runs, int nruns, uint64_t k, uint32_t vmin, uint32_t vmax, uint64_t* n_le) {
+    uint32_t lo = vmin, hi = vmax;  // invariant: answer in [lo, hi]
+    while (lo < hi) {
+        const uint32_t mid = lo + ((hi - lo) >> 1);
+        uint64_t c = 0;
+        for (int r = 0; r < nruns; ++r) c += count_le(runs[r], mid);
+        if (c >= k + 1) hi = mid; else lo = mid + 1;
+    }
+    uint64_t c = 0;
+    for (int r = 0; r < nruns; ++r) c += count_le(runs[r], lo);
+    *n_le = c;
+    return lo;
+}
+
+// smallest value strictly greater than v over all runs (caller guarantees one exists)
+__device__ uint32_t next_above(const Run* runs, int nruns, uint32_t v) {
+    uint32_t best = 0xFFFFFFFFu;
+    for (int r = 0; r < nruns; ++r) {
+        const uint32_t i = count_le(runs[r], v);
+        if (i < runs[r].n) {
+            const uint32_t x = (uint32_t)__ldg(runs[r].p + i);
+            best = x < best ? x : best;
+        }
+    }
+    return best;
+}
+
+struct TickParams {
+    const Acc* acc;
+    const uint8_t* seen;
+    uint64_t* const* logs;
+    const SlotMeta* slot_meta;
+    uint32_t K;
+    WindowSlots win;
+    int npct;
+    double pfrac[APM_MAX_PCT];
+    int zpct[2];
+    double tpm_div;
+    int64_t tick_ts;
+    apm_stat_record* stats;  // nullptr when stat records are not retained
+    double* zin;             // [4][K]
+    int with_pct;
+    uint64_t log_cap;
+};
+
+__global__ void __launch_bounds__(128) tick_stats_kernel(const TickParams p) {
+    const uint32_t key = blockIdx.x * blockDim.x + threadIdx.x;
+    if (key >= p.K) return;
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    if (!p.seen[key]) {
+        if (p.stats) p.stats[key].flags = 0;
+        return;
+    }
+    // ---- window combine (:171-178): exact integer moments
+    uint64_t cnt = 0, sum = 0, sq_lo = 0, sq_hi = 0;
+    uint32_t vmin = 0xFFFFFFFFu, vmax = 0;
+    Run runs[APM_MAX_SLOTS];
+    int nruns = 0;
+    for (int w = 0; w < p.win.n; ++w) {
+        const int slot = p.win.slot[w];
+        const uint4* a4 = reinterpret_cast<const uint4*>(p.acc + (size_t)slot * p.K + key);
+        const uint4 lo = __ldg(a4), hi = __ldg(a4 + 1);
+        const uint32_t c = lo.x;
+        if (c == 0) continue;
+        cnt += c;
+        vmin = lo.y < vmin ? lo.y : vmin;
+        vmax = lo.z > vmax ? lo.z : vmax;
+        sum += ((uint64_t)hi.y << 32) | hi.x;
+        const uint64_t add = ((uint64_t)hi.w << 32) | hi.z;
+        const uint64_t t = sq_lo + add;
+        sq_hi += (uint64_t)lo.w + (t < sq_lo ? 1u : 0u);
+        sq_lo = t;
+        if (p.with_pct) {
+            const uint64_t* lg = p.logs[slot];
+            uint64_t ln = p.slot_meta[slot].count;
+            ln = ln < p.log_cap ? ln : p.log_cap;
+            const uint64_t s = lower_bound_u64(lg, ln, (uint64_t)key << 32);
+            runs[nruns].p = lg + s;
+            runs[nruns].n = c;
+            ++nruns;
+        }
+    }
+    double avg = nan, sd = nan, pct[APM_MAX_PCT] = {nan, nan, nan, nan};
+    if (cnt != 0) {
+        avg = __ddiv_rn((double)sum, (double)cnt);  // :181, one correctly rounded divide of exact integers
+        // extension: population stddev from exact moments, var = (cnt*sumsq - sum^2) / cnt^2
+        {
+            // 128-bit: cnt * (sq_hi:sq_lo) - sum * sum   (domain: result < 2^128)
+            const uint64_t a_lo = cnt * sq_lo, a_hi = __umul64hi(cnt, sq_lo) + cnt * sq_hi;
+            const uint64_t b_lo = sum * sum, b_hi = __umul64hi(sum, sum);
+            const uint64_t d_lo = a_lo - b_lo, d_hi = a_hi - b_hi - (a_lo < b_lo ? 1u : 0u);
+            const double num = __dadd_rn(__dmul_rn((double)d_hi, 18446744073709551616.0), (double)d_lo);
+            sd = __ddiv_rn(__dsqrt_rn(num), (double)cnt);
+        }
+        for (int q = 0; q < (p.with_pct ? p.npct : 0); ++q) {
+            // calcPercentile (util_methods.js:112-142), double index arithmetic without contraction
+            const double n = (double)cnt;
+            double index = __dsub_rn(__dmul_rn(p.pfrac[q], n), 1.0);
+            uint64_t i0;
+            bool pair = false;
+            if (p.pfrac[q] == 0.0) {
+                i0 = 0;
+            } else if (p.pfrac[q] == 1.0) {
+                i0 = cnt - 1;
+            } else if (cnt == 1 || index == trunc(index)) {
+                i0 = index < 0 ? 0 : (uint64_t)index;
+            } else {
+                const double ci = ceil(index);
+                i0 = ci < 0 ? 0 : (uint64_t)ci;
+                pair = i0 != cnt - 1;
+            }
+            uint32_t v0, v1;
+            if (nruns == 1) {
+                v0 = (uint32_t)__ldg(runs[0].p + i0);
+                v1 = pair ? (uint32_t)__ldg(runs[0].p + i0 + 1) : v0;
+            } else {
+                uint64_t n_le;
+                v0 = select_kth(runs, nruns, i0, vmin, vmax, &n_le);
+                v1 = v0;
+                if (pair && n_le < i0 + 2) v1 = next_above(runs, nruns, v0);
+            }
+            pct[q] = pair ? __dmul_rn(__dadd_rn((double)v0, (double)v1), 0.5) : (double)v0;
+        }
+    }
+    const double tpm = __ddiv_rn((double)cnt, p.tpm_div);  // :186
+    if (p.stats) {
+        apm_stat_record r;
+        r.tick_ts = p.tick_ts;
+        r.key = key;
+        r.flags = 1u | (cnt ? 2u : 0u);
+        r.count = cnt;
+        r.sum = sum;
+        r.tpm = tpm;
+        r.avg = avg;
+#pragma unroll
+        for (int q = 0; q < APM_MAX_PCT; ++q) r.pct[q] = pct[q];
+        r.min = cnt ? (int32_t)vmin : 0;
+        r.max = (int32_t)vmax;
+        r.stddev = sd;
+        p.stats[key] = r;
+    }
+    // ---- what the z-score stage parses out of the `st` line (entries.js:71-73 -> 58-61)
+    p.zin[key] = apm_quantize_fixed(tpm, 2);
+    p.zin[(size_t)p.K + key] = apm_quantize_fixed(avg, 1);
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+        const int q = p.zpct[s];
+        p.zin[(size_t)(2 + s) * p.K + key] = (q >= 0 && q < p.npct) ? apm_quantize_fixed(pct[q], 1) : nan;
+    }
+}
+
+}  // namespace
+
+apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask) {
+    if (!slot_mask) return APM_OK;
+    unsigned gx = (c->K + 255) / 256;
+    if (gx > APM_NUM_SMS * 4) gx = APM_NUM_SMS * 4;
+    clear_slots_kernel<<<dim3(gx, c->S), 256, 0, c->s_main>>>(c->acc, c->slot_meta, c->K, c->S, slot_mask);
+    c->launches += 1;
+    CUDA_TRY(c, cudaGetLastError());
+    return APM_OK;
+}
+
+apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot) {
+    TickParams p;
+    p.acc = c->acc; p.seen = c->seen; p.logs = c->d_log_ptrs; p.slot_meta = c->slot_meta; p.K = c->K;
+    p.win = w;
+    p.npct = c->cfg.num_percentiles;
+    for (int i = 0; i < APM_MAX_PCT; ++i) p.pfrac[i] = c->pfrac[i];
+    p.zpct[0] = c->cfg.z_series_pct[0]; p.zpct[1] = c->cfg.z_series_pct[1];
+    p.tpm_div = c->tpm_div;
+    p.tick_ts = tick_ts;
+    p.stats = (c->cfg.flags & APM_F_KEEP_STATS) ? c->d_stats + (size_t)tick_slot * c->K : nullptr;
+    p.zin = c->zin;
+    p.with_pct = (c->cfg.flags & APM_F_PERCENTILES) && c->cfg.num_percentiles > 0;
+    p.log_cap = c->log_cap;
+    tick_stats_kernel<<<(c->K + 127) / 128, 128, 0, c->s_main>>>(p);
+    c->launches += 1;
+    CUDA_TRY(c, cudaGetLastError());
+    return APM_OK;
+}

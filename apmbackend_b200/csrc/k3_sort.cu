@@ -1,0 +1,225 @@
+// K3a: hand-written LSD radix sort of one bucket's value log.
+//
+// The log holds (key << 32 | elapsed) words in arrival order; after the sort every key's
+// elapsed values form one ascending run, which is the array binaryConcat builds per window
+// (stream_calc_stats.js:176 -> util_methods.js:84-106) without its O(W^2) splices.
+// Only the significant bits are sorted: the low bits(max elapsed) of the value field and the
+// low bits(K-1) of the key field, 8 bits per pass, stable.
+#include "ctx.h"
+
+namespace {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;  // 4096 words = 32 KB staged in shared memory
+
+__device__ __forceinline__ uint32_t digit_of(uint64_t x, int shift) { return (uint32_t)(x >> shift) & 0xFFu; }
+
+// lanes of the warp holding the same 8-bit digit (8 ballots)
+__device__ __forceinline__ uint32_t match_digit(uint32_t d) {
+    uint32_t peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        const uint32_t bal = __ballot_sync(0xffffffffu, (d >> b) & 1u);
+        peers &= ((d >> b) & 1u) ? bal : ~bal;
+    }
+    return peers;
+}
+
+// ---- per-tile digit histogram -> hist[digit][tile] --------------------------------------------
+__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint64_t* __restrict__ src, uint64_t n, int shift,
+                                                             uint32_t* __restrict__ hist, uint32_t ntiles) {
+    __shared__ uint32_t s_hist[RS_WARPS][256];
+    for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&s_hist[0][0])[i] = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint64_t base = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)w * (32 * RS_ITEMS);
+#pragma unroll 4
+    for (int i = 0; i < RS_ITEMS; ++i) {
+        const uint64_t idx = base + (uint64_t)i * 32 + lane;
+        const bool ok = idx < n;
+        const uint32_t d = ok ? digit_of(__ldg(src + idx), shift) : 0xFFFFFFFFu;
+        // warp-aggregate equal digits so a skewed digit costs one shared atomic, not 32
+        const uint32_t peers = match_digit(d & 0xFFu) & __ballot_sync(0xffffffffu, ok);
+        if (ok && lane == (__ffs(peers) - 1)) atomicAdd(&s_hist[w][d], __popc(peers));
+    }
+    __syncthreads();
+    uint32_t t = 0;
+#pragma unroll
+    for (int j = 0; j < RS_WARPS; ++j) t += s_hist[j][threadIdx.x];
+    hist[(size_t)threadIdx.x * ntiles + blockIdx.x] = t;
+}
+
+// ---- exclusive scan of every digit row over the tiles; row totals ------------------------------
+__global__ void __launch_bounds__(256) rs_scan_rows_kernel(uint32_t* __restrict__ hist, uint32_t ntiles,
+                                                           uint32_t* __restrict__ totals) {
+    __shared__ uint32_t s_warp[8];
+    uint32_t* row = hist + (size_t)blockIdx.x * ntiles;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < ntiles; base += 256) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t x = i < ntiles ? row[i] : 0;
+        uint32_t v = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += y;
+        }
+        if (lane == 31) s_warp[w] = v;
+        __syncthreads();
+        uint32_t woff = 0, tot = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (j < w) woff += s_warp[j];
+            tot += s_warp[j];
+        }
+        if (i < ntiles) row[i] = carry + woff + v - x;
+        carry += tot;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) totals[blockIdx.x] = carry;
+}
+
+// ---- stable scatter of one tile ------------------------------------------------------------------
+__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint64_t* __restrict__ src, uint64_t* __restrict__ dst,
+                                                                uint64_t n, int shift, const uint32_t* __restrict__ hist,
+                                                                const uint32_t* __restrict__ totals, uint32_t ntiles) {
+    __shared__ uint64_t s_items[RS_TILE];
+    __shared__ uint32_t s_cnt[RS_WARPS][256];  // per-warp digit counts, then per-warp digit offsets
+    __shared__ uint32_t s_start[256];          // first local position of each digit
+    __shared__ uint32_t s_gbase[256];          // global position of the tile's first item of each digit
+    __shared__ uint32_t s_scan[RS_WARPS];
+
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&s_cnt[0][0])[i] = 0;
+    __syncthreads();
+
+    const uint64_t tile_base = (uint64_t)blockIdx.x * RS_TILE;
+    const uint64_t base = tile_base + (uint64_t)w * (32 * RS_ITEMS);
+    uint64_t item[RS_ITEMS];
+    uint32_t rank[RS_ITEMS];
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; ++i) {
+        const uint64_t idx = base + (uint64_t)i * 32 + lane;
+        item[i] = idx < n ? __ldg(src + idx) : ~0ull;
+    }
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; ++i) {
+        const uint64_t idx = base + (uint64_t)i * 32 + lane;
+        const bool ok = idx < n;
+        // out-of-range lanes take a private pseudo digit so they never join a peer group
+        const uint32_t d = digit_of(item[i], shift);
+        const uint32_t okmask = __ballot_sync(0xffffffffu, ok);
+        const uint32_t peers = match_digit(d) & okmask;
+        uint32_t before = 0;
+        if (ok) before = s_cnt[w][d];
+        __syncwarp();
+        if (ok && lane == (__ffs(peers) - 1)) s_cnt[w][d] = before + __popc(peers);
+        __syncwarp();
+        rank[i] = before + __popc(peers & ((1u << lane) - 1u));
+    }
+    __syncthreads();
+
+    // thread d owns digit d: offsets of each warp inside the digit, digit total
+    {
+        const int d = threadIdx.x;
+        uint32_t run = 0;
+#pragma unroll
+        for (int j = 0; j < RS_WARPS; ++j) {
+            const uint32_t c = s_cnt[j][d];
+            s_cnt[j][d] = run;
+            run += c;
+        }
+        // exclusive scan of the digit totals over the block -> s_start
+        uint32_t v = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += y;
+        }
+        if (lane == 31) s_scan[w] = v;
+        __syncthreads();
+        uint32_t woff = 0;
+#pragma unroll
+        for (int j = 0; j < RS_WARPS; ++j)
+            if (j < w) woff += s_scan[j];
+        s_start[d] = woff + v - run;
+        // global base of digit d = sum of totals of smaller digits + this tile's row prefix
+        uint32_t tv = totals[d];
+        uint32_t tincl = tv;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, tincl, o);
+            if (lane >= o) tincl += y;
+        }
+        __syncthreads();
+        if (lane == 31) s_scan[w] = tincl;
+        __syncthreads();
+        uint32_t toff = 0;
+#pragma unroll
+        for (int j = 0; j < RS_WARPS; ++j)
+            if (j < w) toff += s_scan[j];
+        s_gbase[d] = toff + tincl - tv + hist[(size_t)d * ntiles + blockIdx.x];
+    }
+    __syncthreads();
+
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; ++i) {
+        const uint64_t idx = base + (uint64_t)i * 32 + lane;
+        if (idx < n) {
+            const uint32_t d = digit_of(item[i], shift);
+            s_items[s_start[d] + s_cnt[w][d] + rank[i]] = item[i];
+        }
+    }
+    __syncthreads();
+
+    const uint32_t in_tile = (uint32_t)((n - tile_base) < (uint64_t)RS_TILE ? (n - tile_base) : RS_TILE);
+    for (uint32_t j = threadIdx.x; j < in_tile; j += RS_THREADS) {
+        const uint64_t x = s_items[j];
+        const uint32_t d = digit_of(x, shift);
+        dst[(uint64_t)s_gbase[d] + (j - s_start[d])] = x;
+    }
+}
+
+int bits_of(uint64_t v) {
+    int b = 0;
+    while (v) { ++b; v >>= 1; }
+    return b;
+}
+
+}  // namespace
+
+// Sorts log slot `slot` if entries were appended since its last sort.  Host reads the slot
+// bookkeeping first (the caller has synchronised c->s_main and refreshed h-side copies).
+apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value) {
+    if (n < 2) return APM_OK;
+    if (n > 0xFFFFFFFFull) return apm_fail(c, APM_E_CAPACITY, "value log above 2^32 entries");
+    const uint32_t ntiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
+    if (ntiles > c->sort_tiles_cap) return apm_fail(c, APM_E_CAPACITY, "sort scratch too small");
+    const int vbits = bits_of(max_value), kbits = bits_of(c->K > 1 ? c->K - 1 : 0);
+    uint64_t* src = c->log_buf[slot];
+    uint64_t* dst = c->log_buf[c->S];
+    int passes = 0;
+    for (int field = 0; field < 2; ++field) {
+        const int lo = field == 0 ? 0 : 32, nb = field == 0 ? vbits : kbits;
+        for (int b = 0; b < nb; b += 8) {
+            const int shift = lo + b;
+            rs_hist_kernel<<<ntiles, RS_THREADS, 0, c->s_main>>>(src, n, shift, c->sort_hist, ntiles);
+            rs_scan_rows_kernel<<<256, 256, 0, c->s_main>>>(c->sort_hist, ntiles, c->sort_base);
+            rs_scatter_kernel<<<ntiles, RS_THREADS, 0, c->s_main>>>(src, dst, n, shift, c->sort_hist, c->sort_base, ntiles);
+            c->launches += 3;
+            uint64_t* t = src; src = dst; dst = t;
+            ++passes;
+        }
+    }
+    CUDA_TRY(c, cudaGetLastError());
+    if (passes & 1) {  // result sits in the spare buffer: swap roles
+        c->log_buf[c->S] = c->log_buf[slot];
+        c->log_buf[slot] = src;
+        CUDA_TRY(c, cudaMemcpyAsync(c->d_log_ptrs + slot, &c->log_buf[slot], sizeof(uint64_t*), cudaMemcpyHostToDevice,
+                                    c->s_main));
+    }
+    return APM_OK;
+}

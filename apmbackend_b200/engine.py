@@ -1,0 +1,230 @@
+"""Thin object wrapper over the C ABI (include/apm_b200.h): one Engine == one apm_ctx."""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _capi
+from ._capi import ApmConfig, ApmError, Counters, TickResult, TxColumns
+
+
+@dataclass
+class EngineConfig:
+    """Resolved numeric settings of both stages (config/apm_config.json:105-107, 126-172).
+    Defaults are the reference's: 10 s buckets, window 30, buffer 6, p75/p95, lags 360 and 8640."""
+    num_services: int
+    num_jvms: int = 1
+    bucket_ms: int = 10000
+    window: int = 30
+    buffer: int = 6
+    percentiles: Sequence[float] = (75.0, 95.0)
+    z_series_pct: Sequence[int] = (0, 1)
+    lags: Sequence[int] = (360, 8640)
+    thresholds: Sequence[float] = (20.0, 15.0)
+    influences: Sequence[float] = (0.1, 0.0)
+    flags: int = _capi.F_PERCENTILES | _capi.F_ZSCORE | _capi.F_KEEP_STATS | _capi.F_KEEP_FS | _capi.F_ALERTS
+    sd_mode: int = 0
+    max_tx_per_bucket: int = 1 << 20
+    max_batch: int = 1 << 20
+    out_ticks: int = 64
+    max_alerts_per_tick: int = 4096
+    device: int = 0
+
+    def to_c(self) -> ApmConfig:
+        c = ApmConfig()
+        c.struct_size = C.sizeof(ApmConfig)
+        c.device = self.device
+        c.num_services, c.num_jvms = self.num_services, self.num_jvms
+        c.bucket_ms, c.window_buckets, c.buffer_buckets = self.bucket_ms, self.window, self.buffer
+        c.num_percentiles = len(self.percentiles)
+        for i, p in enumerate(self.percentiles):
+            c.percentiles[i] = p
+        c.z_series_pct[0], c.z_series_pct[1] = self.z_series_pct
+        c.num_lags = len(self.lags)
+        for i, l in enumerate(self.lags):
+            c.lags[i] = l
+            c.default_threshold[i] = self.thresholds[i]
+            c.default_influence[i] = self.influences[i]
+        c.sd_mode, c.flags = self.sd_mode, self.flags
+        c.max_tx_per_bucket, c.max_batch = self.max_tx_per_bucket, self.max_batch
+        c.out_ticks, c.max_alerts_per_tick = self.out_ticks, self.max_alerts_per_tick
+        return c
+
+
+def _cols(service_id, jvm_id, end_ts_ms, elapsed_ms):
+    s = np.ascontiguousarray(service_id, dtype=np.uint32)
+    j = np.ascontiguousarray(jvm_id, dtype=np.uint32)
+    t = np.ascontiguousarray(end_ts_ms, dtype=np.int64)
+    e = np.ascontiguousarray(elapsed_ms, dtype=np.int32)
+    if not (s.size == j.size == t.size == e.size):
+        raise ValueError("columns differ in length")
+    return s, j, t, e
+
+
+class Engine:
+    def __init__(self, cfg: EngineConfig):
+        self.cfg = cfg
+        self._lib = _capi.lib()
+        self._c = cfg.to_c()
+        h = C.c_void_p()
+        st = self._lib.apm_ctx_create(C.byref(self._c), C.byref(h))
+        if st != _capi.OK:
+            raise ApmError(st, (self._lib.apm_last_error(None) or b"").decode())
+        self._h = h
+        self.K = cfg.num_services * cfg.num_jvms
+
+    # ---- lifecycle
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.apm_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, st):
+        if st != _capi.OK:
+            raise ApmError(st, (self._lib.apm_last_error(self._h) or b"").decode())
+
+    @property
+    def handle(self):
+        return self._h
+
+    # ---- ingest / tick
+    def process_host(self, service_id, jvm_id, end_ts_ms, elapsed_ms) -> TickResult:
+        """A run of consumeMsg calls (stream_calc_stats.js:331-371) over host columns in arrival order."""
+        s, j, t, e = _cols(service_id, jvm_id, end_ts_ms, elapsed_ms)
+        cols = TxColumns(s.ctypes.data, j.ctypes.data, t.ctypes.data, e.ctypes.data)
+        res = TickResult()
+        self._check(self._lib.apm_process_host(self._h, C.byref(cols), s.size, C.byref(res)))
+        return res
+
+    def process_device(self, cols: TxColumns, n: int) -> TickResult:
+        res = TickResult()
+        self._check(self._lib.apm_process_device(self._h, C.byref(cols), n, C.byref(res)))
+        return res
+
+    def add_batch(self, service_id, jvm_id, end_ts_ms, elapsed_ms):
+        """addData (:115-134) for a batch that contains no tick (the caller ticks first, as consumeMsg does)."""
+        s, j, t, e = _cols(service_id, jvm_id, end_ts_ms, elapsed_ms)
+        off = 0
+        while off < s.size:
+            m = min(s.size - off, self.cfg.max_batch)
+            pin = TxColumns()
+            self._check(self._lib.apm_ingest_acquire(self._h, m, C.byref(pin)))
+            for ptr, arr, dt in ((pin.service_id, s, np.uint32), (pin.jvm_id, j, np.uint32),
+                                 (pin.end_ts_ms, t, np.int64), (pin.elapsed_ms, e, np.int32)):
+                dst = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(np.ctypeslib.as_ctypes_type(dt))), shape=(m,))
+                dst[:] = arr[off:off + m]
+            self._check(self._lib.apm_ingest_commit(self._h, m))
+            off += m
+
+    def tick(self, latest_bucket: int) -> TickResult:
+        res = TickResult()
+        self._check(self._lib.apm_tick(self._h, int(latest_bucket), C.byref(res)))
+        return res
+
+    def sync(self):
+        self._check(self._lib.apm_sync(self._h))
+
+    # ---- results
+    @property
+    def ticks_buffered(self) -> int:
+        return int(self._lib.apm_ticks_buffered(self._h))
+
+    def fetch_stats(self) -> np.ndarray:
+        cap = self.ticks_buffered * self.K
+        out = np.zeros(max(cap, 1), dtype=_capi.STAT_DTYPE)
+        n = C.c_uint64(0)
+        self._check(self._lib.apm_fetch_stats(self._h, out.ctypes.data, cap, C.byref(n)))
+        return out[:n.value]
+
+    def fetch_fs(self) -> np.ndarray:
+        cap = self.ticks_buffered * self.K * len(self.cfg.lags)
+        out = np.zeros(max(cap, 1), dtype=_capi.FS_DTYPE)
+        n = C.c_uint64(0)
+        self._check(self._lib.apm_fetch_fs(self._h, out.ctypes.data, cap, C.byref(n)))
+        return out[:n.value]
+
+    def fetch_alerts(self) -> np.ndarray:
+        cap = self.ticks_buffered * self.cfg.max_alerts_per_tick
+        out = np.zeros(max(cap, 1), dtype=_capi.FS_DTYPE)
+        n = C.c_uint64(0)
+        self._check(self._lib.apm_fetch_alerts(self._h, out.ctypes.data, cap, C.byref(n)))
+        return out[:n.value]
+
+    def release_ticks(self):
+        self._check(self._lib.apm_release_ticks(self._h))
+
+    # ---- z-score settings and lag lists
+    def set_key_params(self, key_lo: int, lag_idx: int, thr, infl):
+        t = np.ascontiguousarray(thr, dtype=np.float64)
+        f = np.ascontiguousarray(infl, dtype=np.float64)
+        self._check(self._lib.apm_set_key_params(self._h, key_lo, t.size, lag_idx, t.ctypes.data, f.ctypes.data))
+
+    def drop_lag(self, lag_idx: int):
+        self._check(self._lib.apm_drop_lag(self._h, lag_idx))
+
+    def ring_load(self, key: int, lag_idx: int, series: int, values):
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        self._check(self._lib.apm_ring_load(self._h, key, lag_idx, series, v.ctypes.data, v.size))
+
+    def ring_load_all(self, lag_idx: int, values=None, length: int = 0, device_ptr: Optional[int] = None):
+        if device_ptr is not None:
+            self._check(self._lib.apm_ring_load_all(self._h, lag_idx, C.c_void_p(device_ptr), length, 1))
+        else:
+            v = np.ascontiguousarray(values, dtype=np.float64)
+            assert v.shape[1:] == (3, self.K)
+            self._check(self._lib.apm_ring_load_all(self._h, lag_idx, v.ctypes.data, v.shape[0], 0))
+
+    def ring_read(self, key: int, lag_idx: int, series: int) -> np.ndarray:
+        cap = int(self.cfg.lags[lag_idx])
+        out = np.empty(cap, dtype=np.float64)
+        n = C.c_uint32(0)
+        self._check(self._lib.apm_ring_read(self._h, key, lag_idx, series, out.ctypes.data, cap, C.byref(n)))
+        return out[:n.value].copy()
+
+    # ---- checkpoint
+    def state_save(self, path: str):
+        self._check(self._lib.apm_state_save(self._h, path.encode()))
+
+    def state_load(self, path: str):
+        self._check(self._lib.apm_state_load(self._h, path.encode()))
+
+    def counters(self) -> Counters:
+        c = Counters()
+        self._check(self._lib.apm_get_counters(self._h, C.byref(c)))
+        return c
+
+    def reset_counters(self):
+        self._check(self._lib.apm_reset_counters(self._h))
+
+    # ---- multi-GPU
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        st = _capi.lib().apm_comm_unique_id(buf)
+        if st != _capi.OK:
+            raise ApmError(st, (_capi.lib().apm_last_error(None) or b"").decode())
+        return buf.raw
+
+    def comm_init(self, rank: int, nranks: int, unique_id: bytes):
+        self._check(self._lib.apm_comm_init(self._h, rank, nranks, unique_id))
+
+    def gather_alerts(self, cap: int) -> np.ndarray:
+        out = np.zeros(max(cap, 1), dtype=_capi.FS_DTYPE)
+        n = C.c_uint64(0)
+        self._check(self._lib.apm_gather_alerts(self._h, out.ctypes.data, cap, C.byref(n)))
+        return out[:n.value]

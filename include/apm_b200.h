@@ -31,7 +31,7 @@ enum {
     APM_OK = 0,
     APM_E_INVALID = 1,    /* bad argument / bad config                                  */
     APM_E_DEVICE = 2,     /* CUDA error (sticky: destroy the context, state_load again) */
-    APM_E_CAPACITY = 3,   /* a configured capacity would be exceeded; nothing was lost  */
+    APM_E_CAPACITY = 3,   /* a configured capacity was exceeded (see apm_last_error)     */
     APM_E_WOULDBLOCK = 4, /* output ring full: fetch results, then retry                */
     APM_E_STATE = 5,      /* call order violated (e.g. commit without acquire)          */
     APM_E_IO = 6,         /* state file could not be read / written                     */
@@ -182,13 +182,20 @@ apm_status apm_set_key_params(apm_ctx* ctx, uint32_t key_lo, uint32_t n, int32_t
 /* replaces removeStaleLagData (:170-193) for one lag: forget its lists. */
 apm_status apm_drop_lag(apm_ctx* ctx, int32_t lag_idx);
 
-/* ---- results.  Records of the ticks run since the last fetch, tick-major,
- * key-ascending inside a tick (the host re-orders to first-seen order, the
- * order Object.entries gives the reference, :159-160).  Only valid records
- * are returned. Fetching drains the retained ticks. */
+/* ---- results: replace the outQueue.writeLineToQueue calls (stream_calc_stats.js:200,
+ * stream_calc_z_score.js:473) with binary records.  The records of the ticks
+ * run since the last apm_release_ticks are retained on the device (up to
+ * out_ticks ticks); a fetch copies the valid ones, tick-major, key-ascending
+ * inside a tick (fs: lag-major then key; the host re-orders to first-seen
+ * order, the order Object.entries gives the reference, :159-160).  cap must
+ * hold every retained record slot: ticks * keys (* lags for fs).  Alerts are
+ * the fs records with a non-zero signal, (lag, key)-ascending inside a tick.
+ * apm_release_ticks frees the retained ticks for reuse. */
 apm_status apm_fetch_stats(apm_ctx* ctx, apm_stat_record* out, uint64_t cap, uint64_t* n);
 apm_status apm_fetch_fs(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
 apm_status apm_fetch_alerts(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
+apm_status apm_release_ticks(apm_ctx* ctx);
+uint32_t apm_ticks_buffered(const apm_ctx* ctx);
 /* wait for all queued device work (for timing) */
 apm_status apm_sync(apm_ctx* ctx);
 
@@ -199,6 +206,8 @@ apm_status apm_ring_load(apm_ctx* ctx, uint32_t key, int32_t lag_idx, int32_t se
                          const double* values, uint32_t len);
 apm_status apm_ring_read(apm_ctx* ctx, uint32_t key, int32_t lag_idx, int32_t series,
                          double* values, uint32_t cap, uint32_t* len);
+/* all keys at once: values[len][APM_NUM_SERIES][keys], oldest row first, host or device memory. */
+apm_status apm_ring_load_all(apm_ctx* ctx, int32_t lag_idx, const double* values, uint32_t len, int32_t on_device);
 
 /* ---- checkpoint: replaces saveToResumeFile / resumeFromFileIfExists
  * (stream_calc_stats.js:54-87, stream_calc_z_score.js:37-64) with a compact
@@ -218,7 +227,9 @@ double apm_quantize(double x, int32_t digits);
 uint32_t apm_owner_of_key(uint64_t global_key, uint32_t nranks);
 apm_status apm_comm_unique_id(void* out128);                 /* ncclGetUniqueId */
 apm_status apm_comm_init(apm_ctx* ctx, int32_t rank, int32_t nranks, const void* unique_id128);
-/* all ranks' alerts of the ticks since the last call; out holds up to cap records. */
+/* Collective: every rank calls it at the same point of the stream.  Gathers the
+ * alerts of this rank's retained ticks from all ranks (rank-major, then
+ * tick, lag, key); at most max_alerts_per_tick records per rank per call. */
 apm_status apm_gather_alerts(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
 
 #ifdef __cplusplus
