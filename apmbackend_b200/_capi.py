@@ -60,6 +60,14 @@ class Counters(C.Structure):
         "h2d_bytes", "d2h_bytes", "kernel_launches", "keys_seen")]
 
 
+class KernelTimes(C.Structure):
+    _fields_ = [("ms", C.c_double * 8), ("spans", C.c_uint64 * 8)]
+
+
+KERNEL_GROUPS = ("tick_finder", "keyed_reduce", "slot_clear", "radix_sort", "window_percentiles", "rolling_baseline",
+                 "alert_compaction")
+
+
 class ApmError(RuntimeError):
     def __init__(self, status: int, msg: str):
         super().__init__(f"apm_b200 status {status}: {msg}")
@@ -94,6 +102,10 @@ SYMBOLS = {
     "apm_ring_load_all": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_uint32, C.c_int32]),
     "apm_state_save": (C.c_int32, [C.c_void_p, C.c_char_p]),
     "apm_state_load": (C.c_int32, [C.c_void_p, C.c_char_p]),
+    "apm_profile_enable": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "apm_profile_read": (C.c_int32, [C.c_void_p, C.POINTER(KernelTimes)]),
+    "apm_timer_start": (C.c_int32, [C.c_void_p]),
+    "apm_timer_stop": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "apm_get_counters": (C.c_int32, [C.c_void_p, C.POINTER(Counters)]),
     "apm_reset_counters": (C.c_int32, [C.c_void_p]),
     "apm_quantize": (C.c_double, [C.c_double, C.c_int32]),

@@ -235,6 +235,9 @@ void apm_ctx_destroy(apm_ctx* c) {
     if (c->s_main) cudaStreamDestroy(c->s_main);
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
     apm_comm_destroy_internal(c);
+    for (auto& sp : c->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+    for (auto e : c->prof_pool) cudaEventDestroy(e);
+    for (int i = 0; i < 2; ++i) if (c->timer[i]) cudaEventDestroy(c->timer[i]);
     delete c;
 }
 
@@ -581,5 +584,49 @@ uint32_t apm_owner_of_key(uint64_t k, uint32_t nranks) {
 }
 
 }  // extern "C"
+
+// Device-side stopwatch on the context's stream (what bench.py brackets its timed region with).
+extern "C" apm_status apm_timer_start(apm_ctx* c) {
+    if (!c) return APM_E_INVALID;
+    if (!c->timer[0]) { CUDA_TRY(c, cudaEventCreate(&c->timer[0])); CUDA_TRY(c, cudaEventCreate(&c->timer[1])); }
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
+    CUDA_TRY(c, cudaEventRecord(c->timer[0], c->s_main));
+    return APM_OK;
+}
+
+extern "C" apm_status apm_timer_stop(apm_ctx* c, double* ms) {
+    if (!c || !ms) return APM_E_INVALID;
+    if (!c->timer[0]) return apm_fail(c, APM_E_STATE, "timer_stop without timer_start");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
+    CUDA_TRY(c, cudaEventRecord(c->timer[1], c->s_main));
+    CUDA_TRY(c, cudaEventSynchronize(c->timer[1]));
+    float f = 0;
+    CUDA_TRY(c, cudaEventElapsedTime(&f, c->timer[0], c->timer[1]));
+    *ms = f;
+    return APM_OK;
+}
+
+extern "C" apm_status apm_profile_enable(apm_ctx* c, int32_t on) {
+    if (!c) return APM_E_INVALID;
+    c->prof_on = on != 0;
+    return APM_OK;
+}
+
+extern "C" apm_status apm_profile_read(apm_ctx* c, apm_kernel_times* out) {
+    if (!c || !out) return APM_E_INVALID;
+    memset(out, 0, sizeof *out);
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    for (auto& sp : c->prof_spans) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess && sp.group < APM_KT_GROUPS) {
+            out->ms[sp.group] += ms;
+            out->spans[sp.group] += 1;
+        }
+        c->prof_pool.push_back(sp.a);
+        c->prof_pool.push_back(sp.b);
+    }
+    c->prof_spans.clear();
+    return APM_OK;
+}
 
 extern "C" uint32_t apm_ticks_buffered(const apm_ctx* c) { return c ? c->ticks_buffered : 0; }

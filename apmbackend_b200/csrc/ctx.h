@@ -76,8 +76,34 @@ struct apm_ctx {
     int rank = 0, nranks = 1;
     apm_fs_record* d_gather = nullptr;  // [nranks][1 + max_alerts_per_tick * out_ticks] blocks
 
+    // optional per-kernel-group timing (CUDA events on s_main around each launch)
+    bool prof_on = false;
+    struct ProfSpan { int group; cudaEvent_t a, b; };
+    std::vector<ProfSpan> prof_spans;
+    std::vector<cudaEvent_t> prof_pool;
+    cudaEvent_t timer[2] = {nullptr, nullptr};
+
     bool device_error = false;
     std::string err;
+};
+
+enum { APM_PG_TICKFIND = 0, APM_PG_REDUCE, APM_PG_CLEAR, APM_PG_SORT, APM_PG_TICKSTATS, APM_PG_BASELINE, APM_PG_ALERTS, APM_PG_COUNT };
+
+// Brackets the launches issued during its lifetime with an event pair when profiling is on.
+struct ProfScope {
+    apm_ctx* c; int idx = -1;
+    ProfScope(apm_ctx* ctx, int group) : c(ctx) {
+        if (!c->prof_on) return;
+        cudaEvent_t ev[2];
+        for (int i = 0; i < 2; ++i) {
+            if (!c->prof_pool.empty()) { ev[i] = c->prof_pool.back(); c->prof_pool.pop_back(); }
+            else if (cudaEventCreate(&ev[i]) != cudaSuccess) return;
+        }
+        cudaEventRecord(ev[0], c->s_main);
+        c->prof_spans.push_back({group, ev[0], ev[1]});
+        idx = (int)c->prof_spans.size() - 1;
+    }
+    ~ProfScope() { if (idx >= 0) cudaEventRecord(c->prof_spans[idx].b, c->s_main); }
 };
 
 // k1_ingest.cu

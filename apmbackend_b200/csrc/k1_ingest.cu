@@ -211,6 +211,7 @@ __global__ void __launch_bounds__(256) reduce_kernel_v1(const ReduceParams p) {
 }  // namespace
 
 apm_status apm_launch_find_ticks(apm_ctx* c, const int64_t* d_ts, uint64_t n, unsigned int* n_ticks_out) {
+    ProfScope prof_scope_(c, APM_PG_TICKFIND);
     *n_ticks_out = 0;
     if (n == 0) return APM_OK;
     const uint64_t ntiles = (n + TF_TILE - 1) / TF_TILE;
@@ -239,6 +240,7 @@ apm_status apm_launch_find_ticks(apm_ctx* c, const int64_t* d_ts, uint64_t n, un
 }
 
 apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin, uint64_t end) {
+    ProfScope prof_scope_(c, APM_PG_REDUCE);
     if (end <= begin) return APM_OK;
     ReduceParams p;
     p.svc = d.service_id; p.jvm = d.jvm_id; p.ts = d.end_ts_ms; p.el = d.elapsed_ms;

@@ -205,6 +205,7 @@ __global__ void __launch_bounds__(128) tick_stats_kernel(const TickParams p) {
 }  // namespace
 
 apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask) {
+    ProfScope prof_scope_(c, APM_PG_CLEAR);
     if (!slot_mask) return APM_OK;
     unsigned gx = (c->K + 255) / 256;
     if (gx > APM_NUM_SMS * 4) gx = APM_NUM_SMS * 4;
@@ -215,6 +216,7 @@ apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask) {
 }
 
 apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot) {
+    ProfScope prof_scope_(c, APM_PG_TICKSTATS);
     TickParams p;
     p.acc = c->acc; p.seen = c->seen; p.logs = c->d_log_ptrs; p.slot_meta = c->slot_meta; p.K = c->K;
     p.win = w;

@@ -194,6 +194,7 @@ int bits_of(uint64_t v) {
 // Sorts log slot `slot` if entries were appended since its last sort.  Host reads the slot
 // bookkeeping first (the caller has synchronised c->s_main and refreshed h-side copies).
 apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value) {
+    ProfScope prof_scope_(c, APM_PG_SORT);
     if (n < 2) return APM_OK;
     if (n > 0xFFFFFFFFull) return apm_fail(c, APM_E_CAPACITY, "value log above 2^32 entries");
     const uint32_t ntiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);

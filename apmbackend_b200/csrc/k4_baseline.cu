@@ -157,6 +157,7 @@ __global__ void __launch_bounds__(256) compact_alerts_kernel(const apm_fs_record
 }  // namespace
 
 apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick_slot) {
+    ProfScope prof_scope_(c, APM_PG_BASELINE);
     BaselineParams p;
     p.ring = c->ring[l]; p.ring_len = c->ring_len[l]; p.zin = c->zin; p.thr = c->thr[l]; p.infl = c->infl[l];
     p.seen = c->seen;
@@ -173,6 +174,7 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
 }
 
 apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot) {
+    ProfScope prof_scope_(c, APM_PG_ALERTS);
     if (!c->d_alerts || !c->d_fs) return APM_OK;
     const uint32_t n = c->K * (uint32_t)c->cfg.num_lags;
     compact_alerts_kernel<<<(n + 255) / 256, 256, 0, c->s_main>>>(

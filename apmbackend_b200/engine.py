@@ -208,6 +208,22 @@ class Engine:
         self._check(self._lib.apm_get_counters(self._h, C.byref(c)))
         return c
 
+    def timer_start(self):
+        self._check(self._lib.apm_timer_start(self._h))
+
+    def timer_stop(self) -> float:
+        ms = C.c_double(0)
+        self._check(self._lib.apm_timer_stop(self._h, C.byref(ms)))
+        return ms.value
+
+    def profile_enable(self, on: bool = True):
+        self._check(self._lib.apm_profile_enable(self._h, 1 if on else 0))
+
+    def profile_read(self) -> dict:
+        kt = _capi.KernelTimes()
+        self._check(self._lib.apm_profile_read(self._h, C.byref(kt)))
+        return {g: {"ms": kt.ms[i], "spans": int(kt.spans[i])} for i, g in enumerate(_capi.KERNEL_GROUPS)}
+
     def reset_counters(self):
         self._check(self._lib.apm_reset_counters(self._h))
 

@@ -1,0 +1,221 @@
+"""Synthetic transaction streams for bench.py and the tests: Zipf service
+popularity, lognormal-shaped durations, near-sorted event time.  The generator is
+counter-based and integer-only (csrc/synth_common.h), so the device and the host twin give
+identical columns.  Bench/test support - not part of the drop-in API."""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _capi
+from ._capi import TxColumns
+
+
+class SynthParams(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("n", C.c_uint64), ("first", C.c_uint64),
+                ("num_services", C.c_uint32), ("num_jvms", C.c_uint32),
+                ("t0_ms", C.c_int64), ("span_ms", C.c_int64),
+                ("jitter_ms", C.c_uint32), ("elapsed_max", C.c_uint32),
+                ("shift_mod", C.c_uint32), ("shift_mul", C.c_uint32),
+                ("q_size", C.c_uint32), ("pad_", C.c_uint32),
+                ("cdf", C.c_void_p), ("base", C.c_void_p), ("q", C.c_void_p)]
+
+
+def _chk(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"{what}: CUDA error {rc}: {_capi.synth().synth_error_string(rc).decode()}")
+
+
+class DeviceBuffer:
+    def __init__(self, nbytes: int):
+        self.nbytes = int(nbytes)
+        p = C.c_void_p()
+        _chk(_capi.synth().synth_malloc(C.byref(p), max(self.nbytes, 1)), "cudaMalloc")
+        self.ptr = p.value
+
+    def upload(self, arr: np.ndarray):
+        a = np.ascontiguousarray(arr)
+        assert a.nbytes <= self.nbytes
+        _chk(_capi.synth().synth_h2d(self.ptr, a.ctypes.data, a.nbytes), "H2D")
+        return self
+
+    def download(self, dtype, count, offset_bytes=0) -> np.ndarray:
+        out = np.empty(count, dtype=dtype)
+        _chk(_capi.synth().synth_d2h(out.ctypes.data, self.ptr + offset_bytes, out.nbytes), "D2H")
+        return out
+
+    def free(self):
+        if self.ptr:
+            _capi.synth().synth_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class PinnedArray:
+    """numpy view over cudaMallocHost memory."""
+
+    def __init__(self, dtype, count):
+        self.dtype = np.dtype(dtype)
+        self.count = int(count)
+        p = C.c_void_p()
+        _chk(_capi.synth().synth_malloc_host(C.byref(p), max(self.count * self.dtype.itemsize, 1)), "cudaMallocHost")
+        self.ptr = p.value
+        buf = (C.c_char * (self.count * self.dtype.itemsize)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=self.count)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            _capi.synth().synth_free_host(self.ptr)
+            self.ptr = None
+
+
+class DeviceColumns:
+    def __init__(self, n: int):
+        self.n = int(n)
+        self.bufs = [DeviceBuffer(self.n * 4), DeviceBuffer(self.n * 4), DeviceBuffer(self.n * 8), DeviceBuffer(self.n * 4)]
+
+    def columns(self, offset=0) -> TxColumns:
+        b = self.bufs
+        return TxColumns(b[0].ptr + 4 * offset, b[1].ptr + 4 * offset, b[2].ptr + 8 * offset, b[3].ptr + 4 * offset)
+
+    def to_host(self):
+        b = self.bufs
+        return (b[0].download(np.uint32, self.n), b[1].download(np.uint32, self.n), b[2].download(np.int64, self.n),
+                b[3].download(np.int32, self.n))
+
+    def free(self):
+        for b in self.bufs:
+            b.free()
+
+
+def zipf_cdf(num_services: int, s: float = 1.0, hot=None) -> np.ndarray:
+    """P(service <= k) * 2^32 as uint32.  hot=(h, mass): the first h services share `mass` of
+    the traffic equally, the rest is Zipf over the remaining services (cfg5's two-tier skew)."""
+    w = 1.0 / np.arange(1, num_services + 1, dtype=np.float64) ** s
+    if hot:
+        h, mass = hot
+        w[:h] = mass / h
+        w[h:] *= (1.0 - mass) / w[h:].sum()
+    c = np.cumsum(w / w.sum())
+    cdf = np.minimum(np.floor(c * 4294967296.0), 4294967295.0).astype(np.uint64).astype(np.uint32)
+    cdf[-1] = 0xFFFFFFFF
+    return cdf
+
+
+def duration_tables(num_services: int, seed: int = 0, q_size: int = 4096, sigma: float = 0.5):
+    rng = np.random.default_rng(seed ^ 0x5EED)
+    base = rng.integers(20, 420, size=num_services).astype(np.uint32)
+    # lognormal(0, sigma) quantiles * 1024 via the rational approximation of the probit (Acklam)
+    p = (np.arange(q_size) + 0.5) / q_size
+    z = _probit(p)
+    q = np.rint(np.exp(sigma * z) * 1024.0).astype(np.uint32)
+    perm = np.random.default_rng(seed ^ 0xBEEF).permutation(q_size)
+    return base, q[perm]
+
+
+def _probit(p):
+    a = [-3.969683028665376e+01, 2.209460984245205e+02, -2.759285104469687e+02, 1.383577518672690e+02,
+         -3.066479806614716e+01, 2.506628277459239e+00]
+    b = [-5.447609879822406e+01, 1.615858368580409e+02, -1.556989798598866e+02, 6.680131188771972e+01,
+         -1.328068155288572e+01]
+    c = [-7.784894002430293e-03, -3.223964580411365e-01, -2.400758277161838e+00, -2.549732539343734e+00,
+         4.374664141464968e+00, 2.938163982698783e+00]
+    d = [7.784695709041462e-03, 3.224671290700398e-01, 2.445134137142996e+00, 3.754408661907416e+00]
+    p = np.asarray(p, dtype=np.float64)
+    out = np.empty_like(p)
+    lo, hi = p < 0.02425, p > 1 - 0.02425
+    mid = ~(lo | hi)
+    q = np.sqrt(-2 * np.log(p[lo]))
+    out[lo] = (((((c[0] * q + c[1]) * q + c[2]) * q + c[3]) * q + c[4]) * q + c[5]) / \
+              ((((d[0] * q + d[1]) * q + d[2]) * q + d[3]) * q + 1)
+    q = np.sqrt(-2 * np.log(1 - p[hi]))
+    out[hi] = -(((((c[0] * q + c[1]) * q + c[2]) * q + c[3]) * q + c[4]) * q + c[5]) / \
+               ((((d[0] * q + d[1]) * q + d[2]) * q + d[3]) * q + 1)
+    q = p[mid] - 0.5
+    r = q * q
+    out[mid] = (((((a[0] * r + a[1]) * r + a[2]) * r + a[3]) * r + a[4]) * r + a[5]) * q / \
+               (((((b[0] * r + b[1]) * r + b[2]) * r + b[3]) * r + b[4]) * r + 1)
+    return out
+
+
+@dataclass
+class StreamSpec:
+    seed: int
+    n: int
+    num_services: int
+    num_jvms: int = 1
+    t0_ms: int = 1578409200000
+    span_ms: int = 3_600_000
+    jitter_ms: int = 2000
+    elapsed_max: int = 60000
+    shift_mod: int = 0
+    shift_mul: int = 5
+    zipf_s: float = 1.0
+    hot: tuple = None
+
+
+class SynthStream:
+    """One synthetic stream; chunks of it can be generated on the device or on the host."""
+
+    def __init__(self, spec: StreamSpec, device: bool = True):
+        self.spec = spec
+        self.cdf = zipf_cdf(spec.num_services, spec.zipf_s, spec.hot)
+        self.base, self.q = duration_tables(spec.num_services, spec.seed)
+        self._dev = None
+        if device:
+            self._dev = [DeviceBuffer(self.cdf.nbytes).upload(self.cdf), DeviceBuffer(self.base.nbytes).upload(self.base),
+                         DeviceBuffer(self.q.nbytes).upload(self.q)]
+
+    def _params(self, first, device, t0_ms=None, seed=None) -> SynthParams:
+        s = self.spec
+        p = SynthParams()
+        p.seed, p.n, p.first = (s.seed if seed is None else seed), s.n, first
+        p.num_services, p.num_jvms = s.num_services, s.num_jvms
+        p.t0_ms, p.span_ms = (s.t0_ms if t0_ms is None else t0_ms), s.span_ms
+        p.jitter_ms, p.elapsed_max = s.jitter_ms, s.elapsed_max
+        p.shift_mod, p.shift_mul = s.shift_mod, s.shift_mul
+        p.q_size = self.q.size
+        if device:
+            p.cdf, p.base, p.q = (b.ptr for b in self._dev)
+        else:
+            p.cdf, p.base, p.q = self.cdf.ctypes.data, self.base.ctypes.data, self.q.ctypes.data
+        return p
+
+    def generate_device(self, cols: DeviceColumns, first=0, count=None, t0_ms=None, seed=None, offset=0):
+        count = self.spec.n - first if count is None else count
+        p = self._params(first, True, t0_ms, seed)
+        c = cols.columns(offset)
+        _chk(_capi.synth().synth_generate_device(C.byref(p), count, C.byref(c)), "synth_generate_device")
+
+    def generate_host(self, first=0, count=None, t0_ms=None, seed=None):
+        count = self.spec.n - first if count is None else count
+        svc, jvm = np.empty(count, np.uint32), np.empty(count, np.uint32)
+        ts, el = np.empty(count, np.int64), np.empty(count, np.int32)
+        p = self._params(first, False, t0_ms, seed)
+        c = TxColumns(svc.ctypes.data, jvm.ctypes.data, ts.ctypes.data, el.ctypes.data)
+        _capi.synth().synth_generate_host(C.byref(p), count, C.byref(c))
+        return svc, jvm, ts, el
+
+    def free(self):
+        for b in self._dev or []:
+            b.free()
+
+
+def ring_fill_device(buf: DeviceBuffer, rows: int, ncol: int, seed: int, level_lo=20, level_span=400):
+    _chk(_capi.synth().synth_ring_fill_device(buf.ptr, rows, ncol, seed, level_lo, level_span), "ring_fill")
+
+
+def ring_fill_host(rows: int, ncol: int, seed: int, cols, level_lo=20, level_span=400) -> np.ndarray:
+    """The same values for a selection of columns, as [rows][len(cols)]."""
+    cols = np.ascontiguousarray(cols, dtype=np.uint64)
+    out = np.empty((rows, cols.size), dtype=np.float64)
+    _capi.synth().synth_ring_fill_host(out.ctypes.data, rows, ncol, seed, level_lo, level_span, cols.ctypes.data, cols.size)
+    return out

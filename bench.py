@@ -1,0 +1,433 @@
+#!/usr/bin/env python
+"""
+bench.py - the hot path on BASELINE.json's metric: transactions/sec aggregated + z-scored.
+
+A step is one pass of the hot path over one batch of synthetic input: the whole workload's
+transaction stream (cfg3: 100 M transactions, 10 k service keys, 1-min buckets, p50/p95/p99
+and z-score against a pre-filled 10 080-bucket baseline), i.e. 60 ticks.  Every step gets its
+own pre-generated stream one hour later than the previous one, resident in HBM (`value`) or
+in pinned host memory (`e2e`) before the timed region starts; inputs are 2 GB per step, far
+above the 126 MB L2, so no L2 flush is needed between steps.
+
+  python bench.py --gpus N --steps K --warmup W            # this repository's CUDA path
+  python bench.py --impl reference ...                      # the reference's algorithm on the host cores
+
+N > 1 (launched by torchrun, one rank per GPU): weak scaling - every rank owns its own hash
+shard of the key space (10 k keys and 100 M transactions per rank), and the only exchange is
+the NCCL all-gather of the compact alert records after each step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # BASELINE.json configs[2]: the configuration the metric ("aggregated+z-scored") is quoted on
+    "cfg3": dict(n=100_000_000, services=10_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
+                 percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
+                 influences=(0.0,), zscore=True, pct=True, seed=2,
+                 desc="100M transactions, 10k service keys, 1-min buckets, p50/p95/p99 + z-score vs 7-day "
+                      "rolling baseline (10080 buckets/key, pre-filled), exact-order baseline"),
+    # BASELINE.json configs[1]
+    "cfg2": dict(n=100_000_000, services=10_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
+                 percentiles=(), z_series_pct=(0, 1), lags=(), thresholds=(), influences=(), zscore=False, pct=False,
+                 seed=1, desc="100M transactions, 10k service keys, 1-min buckets, stats-only"),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink n (debug only; the line says so)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks: sampled DURING the timed region
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# the reference's algorithm on the host cores (oracle port; test/baseline infrastructure)
+# ---------------------------------------------------------------------------------------------
+def cpu_reference_run(wl, cols, ring_seed, threads, prefill=True):
+    """Times the reference-structure CPU port (oracle fast=0: sorted insert per element, four
+    list passes per statistic, shift() memmove) on the given columns.  Keys are independent,
+    so the host threads each own key % threads of them while all of them walk the whole
+    stream for the ticks - the reference itself runs each stage as one single-threaded process."""
+    from oracle import capi as ocapi
+    from apmbackend_b200 import synthetic as syn
+
+    svc, jvm, ts, el = cols
+    K = wl["services"] * wl["jvms"]
+    flags = ocapi.F_KEEP_FS | (ocapi.F_ZSCORE if wl["zscore"] else 0) | (ocapi.F_PERCENTILES if wl["pct"] else 0)
+    cfg = ocapi.make_config(wl["services"], wl["jvms"], wl["bucket_ms"], wl["window"], wl["buffer"], wl["percentiles"],
+                            wl["z_series_pct"], wl["lags"], wl["thresholds"], wl["influences"], flags=flags)
+    pipes = []
+    for t in range(threads):
+        p = ocapi.Pipeline(cfg, fast=False)
+        keep = np.zeros(K, dtype=np.uint8)
+        keep[t::threads] = 1
+        p.set_filter(keep)
+        p.keep_outputs(False)
+        if prefill and wl["zscore"]:
+            L = wl["lags"][0]
+            mine = np.arange(t, K, threads)
+            for s in range(3):
+                vals = syn.ring_fill_host(L, 3 * K, ring_seed, s * K + mine)
+                for j, key in enumerate(mine):
+                    p.ring_load(int(key), 0, s, vals[:, j])
+        pipes.append(p)
+    t0 = time.perf_counter()
+    th = [threading.Thread(target=p.consume, args=(svc, jvm, ts, el)) for p in pipes]
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    dt = time.perf_counter() - t0
+    ticks = pipes[0].ticks
+    for p in pipes:
+        p.close()
+    return dt, ticks
+
+
+def sample_for_cpu(wl, stream, ticks=2):
+    """A bounded sample of the same workload: the first `ticks` buckets' worth of the stream
+    (all 10 k keys, same rates), plus one transaction of the next bucket to close the last tick."""
+    per_bucket = wl["n"] // wl["span_buckets"]
+    n = int(per_bucket * ticks + per_bucket // 50)
+    return stream.generate_host(first=0, count=n), n
+
+
+# ---------------------------------------------------------------------------------------------
+def main():
+    args = parse_args()
+    wl = dict(WORKLOADS[args.workload])
+    if args.scale != 1.0:
+        wl["n"] = int(wl["n"] * args.scale)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != max(args.gpus, 1) and world > 1:
+        print(f"WORLD_SIZE={world} but --gpus {args.gpus}", file=sys.stderr)
+    span_ms = wl["span_buckets"] * wl["bucket_ms"]
+    config = {"workload": f"{args.workload}: {wl['desc']}", "transactions_per_step_per_gpu": wl["n"],
+              "keys_per_gpu": wl["services"] * wl["jvms"], "ticks_per_step": wl["span_buckets"],
+              "l2_policy": "inputs (2 GB/step) larger than L2, fresh stream each step",
+              "sharding": "none" if world == 1 else f"key-hash sharded, {world} ranks, NCCL alert all-gather per step"}
+    if args.scale != 1.0:
+        config["scaled_down"] = args.scale
+
+    from apmbackend_b200 import synthetic as syn
+
+    if args.impl == "reference":
+        return run_reference(args, wl, rank, world, config, span_ms)
+
+    from apmbackend_b200 import Engine, EngineConfig, _capi
+    if _capi.device_count() == 0:
+        raise SystemExit("bench.py needs a CUDA device: apmbackend_b200 has no CPU fallback")
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    _capi.synth().synth_set_device(local_rank)
+
+    K = wl["services"] * wl["jvms"]
+    per_bucket = wl["n"] // wl["span_buckets"]
+    flags = _capi.F_KEEP_FS | _capi.F_ALERTS if wl["zscore"] else _capi.F_KEEP_STATS
+    if wl["zscore"]:
+        flags |= _capi.F_ZSCORE
+    if wl["pct"]:
+        flags |= _capi.F_PERCENTILES
+    ecfg = EngineConfig(num_services=wl["services"], num_jvms=wl["jvms"], bucket_ms=wl["bucket_ms"], window=wl["window"],
+                        buffer=wl["buffer"], percentiles=wl["percentiles"], z_series_pct=wl["z_series_pct"],
+                        lags=wl["lags"], thresholds=wl["thresholds"], influences=wl["influences"], flags=flags,
+                        max_tx_per_bucket=int(per_bucket * 1.5) + 4096, max_batch=min(wl["n"], 1 << 24),
+                        out_ticks=wl["span_buckets"] + 12, max_alerts_per_tick=max(K * max(len(wl["lags"]), 1), 1024),
+                        device=local_rank)
+    eng = Engine(ecfg)
+    if world > 1:
+        import torch
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid = torch.frombuffer(bytearray(Engine.comm_unique_id()), dtype=torch.uint8).cuda()
+        dist.broadcast(uid, 0)
+        eng.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
+
+    ring_seed = 77 + rank
+    if wl["zscore"]:
+        L = wl["lags"][0]
+        buf = syn.DeviceBuffer(L * 3 * K * 8)
+        syn.ring_fill_device(buf, L, 3 * K, ring_seed)
+        eng.ring_load_all(0, length=L, device_ptr=buf.ptr)
+        buf.free()
+
+    nsteps = args.warmup + args.steps
+    spec = syn.StreamSpec(seed=wl["seed"] + 1000 * rank, n=wl["n"], num_services=wl["services"], num_jvms=wl["jvms"],
+                          span_ms=span_ms, shift_mod=97)
+    stream = syn.SynthStream(spec, device=True)
+    t0 = spec.t0_ms
+
+    def step_t0(s):
+        return t0 + s * span_ms
+
+    # ---- value: inputs resident in HBM before the timed region
+    dev_steps = []
+    for s in range(nsteps):
+        dc = syn.DeviceColumns(wl["n"])
+        stream.generate_device(dc, t0_ms=step_t0(s), seed=spec.seed + s)
+        dev_steps.append(dc)
+
+    def run_step_device(s):
+        eng.process_device(dev_steps[s].columns(), wl["n"])
+        if world > 1 and wl["zscore"]:
+            eng.gather_alerts(ecfg.max_alerts_per_tick * world)
+        eng.release_ticks()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        eng.sync()
+
+    for s in range(args.warmup):
+        run_step_device(s)
+    eng.profile_read()
+    eng.profile_enable(True)
+    c0 = eng.counters()
+    launches0 = c0.kernel_launches
+    clocks = ClockSampler(local_rank)
+    barrier()
+    clocks.start()
+    eng.timer_start()
+    w0 = time.perf_counter()
+    for s in range(args.warmup, nsteps):
+        run_step_device(s)
+    ms = eng.timer_stop()
+    barrier()
+    wall_ms = (time.perf_counter() - w0) * 1e3
+    clk = clocks.stop()
+    prof = eng.profile_read()
+    eng.profile_enable(False)
+    c1 = eng.counters()
+    launches = c1.kernel_launches - launches0
+    ticks = c1.ticks - c0.ticks
+    for dc in dev_steps:
+        dc.free()
+    if dist is not None:
+        import torch
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    total_tx = wl["n"] * args.steps * world
+    value = total_tx / (ms / 1e3)
+
+    # ---- e2e: host buffers, H2D inside the timed region, fs + alert records read back
+    e2e = None
+    if not args.no_e2e:
+        host_steps = []
+        tmp = syn.DeviceColumns(wl["n"])
+        for s in range(nsteps):
+            # time keeps moving forward after the device-resident steps
+            stream.generate_device(tmp, t0_ms=step_t0(nsteps + s), seed=spec.seed + 100 + s)
+            pins = [syn.PinnedArray(np.uint32, wl["n"]), syn.PinnedArray(np.uint32, wl["n"]),
+                    syn.PinnedArray(np.int64, wl["n"]), syn.PinnedArray(np.int32, wl["n"])]
+            for pa, b, dt in zip(pins, tmp.bufs, (np.uint32, np.uint32, np.int64, np.int32)):
+                _capi.synth().synth_d2h(pa.ptr, b.ptr, wl["n"] * np.dtype(dt).itemsize)
+            host_steps.append(pins)
+        tmp.free()
+        out_bytes = [0]
+
+        def run_step_host(s):
+            p = host_steps[s]
+            eng.process_host(p[0].array, p[1].array, p[2].array, p[3].array)
+            if wl["zscore"]:
+                fs = eng.fetch_fs()
+                al = eng.fetch_alerts()
+                out_bytes[0] = fs.nbytes + al.nbytes
+                if world > 1:
+                    eng.gather_alerts(ecfg.max_alerts_per_tick * world)
+            else:
+                st = eng.fetch_stats()
+                out_bytes[0] = st.nbytes
+            eng.release_ticks()
+
+        for s in range(args.warmup):
+            run_step_host(s)
+        ce0 = eng.counters()
+        barrier()
+        eng.timer_start()
+        for s in range(args.warmup, nsteps):
+            run_step_host(s)
+        ems = eng.timer_stop()
+        barrier()
+        ce1 = eng.counters()
+        if dist is not None:
+            import torch
+            t = torch.tensor([ems], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ems = float(t.item())
+        e2e = {"value": total_tx / (ems / 1e3), "unit": "transactions/s",
+               "h2d_bytes_per_step": int((ce1.h2d_bytes - ce0.h2d_bytes) // args.steps),
+               "d2h_bytes_per_step": int((ce1.d2h_bytes - ce0.d2h_bytes) // args.steps),
+               "ms_per_step": ems / args.steps, "records_bytes_per_step": int(out_bytes[0])}
+        for pins in host_steps:
+            for pa in pins:
+                pa.free()
+
+    # ---- roofline of the dominant kernel (live CUDA-event spans recorded inside the timed region)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+    dom = max(prof, key=lambda g: prof[g]["ms"])
+    if dom == "rolling_baseline":
+        L = wl["lags"][0]
+        alg = K * L * 3 * 8 + K * 3 * 8 + K * 128  # ring read + push + fs record, per launch
+    elif dom == "keyed_reduce":
+        alg = 20 * wl["n"] * args.steps / max(prof[dom]["spans"], 1)
+    elif dom == "radix_sort":
+        alg = 16 * wl["n"] * args.steps / max(prof[dom]["spans"], 1)
+    else:
+        alg = 0
+    avg_ms = prof[dom]["ms"] / max(prof[dom]["spans"], 1)
+    achieved = alg / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg, "avg_launch_ms": avg_ms, "launches_timed": prof[dom]["spans"],
+                "share_of_step": prof[dom]["ms"] / ms if ms else None,
+                "kernel_ms": {g: round(v["ms"], 3) for g, v in prof.items()}}
+    prof_json = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof_json):
+        try:
+            roofline["traffic"] = json.load(open(prof_json)).get(dom)
+        except Exception:
+            pass
+
+    line = {"metric": "transactions/sec aggregated+z-scored", "value": value, "unit": "transactions/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32/u64 + f64",
+            "data": "synthetic", "config": config, "clocks": clk, "gpu_launches": int(launches),
+            "ticks": int(ticks), "wall_ms_per_step": wall_ms / args.steps, "roofline": roofline}
+    if e2e:
+        line["e2e"] = e2e
+
+    # ---- CPU baseline: the reference-structure port on a bounded sample, rank 0 at N = 1 only
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        hs = syn.SynthStream(spec, device=False)
+        cols, n_s = sample_for_cpu(wl, hs, ticks=1)
+        threads = 1
+        dt, tks = cpu_reference_run(wl, cols, ring_seed, threads)
+        line["cpu_baseline"] = {"value": n_s / dt, "unit": "transactions/s", "cores": threads, "kind": "port",
+                                "sample": f"first {n_s} transactions of the same stream (1 bucket + the tick that "
+                                          f"closes it, all {K} keys, rings pre-filled): {tks} ticks in {dt:.1f} s, "
+                                          "reference-structure C++ port, 1 thread (each reference stage is one "
+                                          "single-threaded Node process; Node itself is absent on this box)"}
+    eng.close()
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def run_reference(args, wl, rank, world, config, span_ms):
+    """--impl reference: the reference's own algorithm (oracle port, fast=0) on the host cores."""
+    if rank != 0:
+        return
+    from apmbackend_b200 import synthetic as syn
+    spec = syn.StreamSpec(seed=wl["seed"], n=wl["n"], num_services=wl["services"], num_jvms=wl["jvms"], span_ms=span_ms,
+                          shift_mod=97)
+    hs = syn.SynthStream(spec, device=False)
+    threads = os.cpu_count() or 1
+    (svc, jvm, ts, el), n_s = sample_for_cpu(wl, hs, ticks=1)
+    times, ticks = [], 0
+    for s in range(args.warmup + args.steps):
+        # prefill only matters for the z stage's cost; it is rebuilt each step so every step does the same work
+        dt, tk = cpu_reference_run(wl, (svc, jvm, ts + s * span_ms, el), 77, threads)
+        if s >= args.warmup:
+            times.append(dt); ticks += tk
+    total = float(np.sum(times))
+    v = n_s * args.steps / total
+    sample = (f"each step = the first {n_s} transactions of the workload's stream (1 of its {wl['span_buckets']} buckets + "
+              f"the tick that closes it, all keys, rings pre-filled), reference-structure C++ port of "
+              f"stream_calc_stats.js + stream_calc_z_score.js, keys partitioned over {threads} host threads")
+    line = {"impl": "reference", "metric": "transactions/sec aggregated+z-scored", "value": v, "unit": "transactions/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 (JS numbers)",
+            "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": v, "unit": "transactions/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "transactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "Node.js is absent on this box (node --version: not found), so the reference's own JS cannot be "
+                    "timed; this is its CPU restatement"}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

@@ -215,6 +215,22 @@ apm_status apm_ring_load_all(apm_ctx* ctx, int32_t lag_idx, const double* values
 apm_status apm_state_save(apm_ctx* ctx, const char* path);
 apm_status apm_state_load(apm_ctx* ctx, const char* path);
 
+/* ---- optional device timing (no reference counterpart; the reference only times its DB
+ * inserts, stream_insert_db.js:295-308).  When enabled, every launch group is bracketed by
+ * CUDA events on the context's stream; read sums them per group and resets.
+ * groups: 0 tick finder, 1 keyed reduce, 2 slot clear, 3 radix sort, 4 window/percentiles,
+ *         5 rolling baseline, 6 alert compaction. */
+#define APM_KT_GROUPS 8
+typedef struct apm_kernel_times {
+    double ms[APM_KT_GROUPS];
+    uint64_t spans[APM_KT_GROUPS]; /* event-bracketed launch groups (one per tick and kernel group) */
+} apm_kernel_times;
+apm_status apm_profile_enable(apm_ctx* ctx, int32_t on);
+/* stopwatch: CUDA events on the context's stream; stop waits for the queued work and returns ms. */
+apm_status apm_timer_start(apm_ctx* ctx);
+apm_status apm_timer_stop(apm_ctx* ctx, double* ms);
+apm_status apm_profile_read(apm_ctx* ctx, apm_kernel_times* out);
+
 apm_status apm_get_counters(apm_ctx* ctx, apm_counters* out);
 apm_status apm_reset_counters(apm_ctx* ctx);
 
