@@ -48,7 +48,7 @@ apm_status validate(const apm_config* cfg) {
     if (!cfg) return apm_fail(nullptr, APM_E_INVALID, "cfg is NULL");
     if (cfg->struct_size != sizeof(apm_config)) return apm_fail(nullptr, APM_E_INVALID, "apm_config.struct_size mismatch");
     if (cfg->num_services == 0 || cfg->num_jvms == 0) return apm_fail(nullptr, APM_E_INVALID, "num_services/num_jvms must be > 0");
-    if ((uint64_t)cfg->num_services * cfg->num_jvms > (1ull << 28)) return apm_fail(nullptr, APM_E_INVALID, "too many keys (limit 2^28)");
+    if ((uint64_t)cfg->num_services * cfg->num_jvms > (1ull << 26)) return apm_fail(nullptr, APM_E_INVALID, "too many keys (limit 2^26 per GPU)");
     if (cfg->bucket_ms <= 0) return apm_fail(nullptr, APM_E_INVALID, "bucket_ms must be > 0");
     if (cfg->window_buckets < 1 || cfg->buffer_buckets < 0 || cfg->window_buckets + cfg->buffer_buckets + 1 > APM_MAX_SLOTS)
         return apm_fail(nullptr, APM_E_INVALID, "window/buffer out of range (window >= 1, window+buffer+1 <= 64)");
@@ -115,14 +115,16 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
         // sort the window's value logs that grew since their last sort
         std::vector<SlotMeta> meta(c->S);
         CUDA_TRY(c, cudaMemcpyAsync(meta.data(), c->slot_meta, sizeof(SlotMeta) * c->S, cudaMemcpyDeviceToHost, c->s_main));
+        CUDA_TRY(c, cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->s_main));
         CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-        c->counters.d2h_bytes += sizeof(SlotMeta) * c->S;
+        c->counters.d2h_bytes += sizeof(SlotMeta) * c->S + sizeof(DevCounters);
+        const uint32_t max_value = c->h_counters->max_value;
         for (int i = 0; i < w.n; ++i) {
             const int slot = w.slot[i];
             SlotMeta& m = meta[slot];
             if (m.count > c->log_cap) return apm_fail(c, APM_E_CAPACITY, "a bucket's value log overflowed max_tx_per_bucket");
             if (m.count != m.sorted) {
-                st = apm_sort_slot_n(c, slot, m.count, m.max_value);
+                st = apm_sort_slot_n(c, slot, m.count, max_value);
                 if (st) return st;
                 m.sorted = m.count;
                 CUDA_TRY(c, cudaMemcpyAsync(&c->slot_meta[slot].sorted, &m.sorted, sizeof(m.sorted), cudaMemcpyHostToDevice, c->s_main));
@@ -221,7 +223,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaSetDevice(c->cfg.device);
     if (c->s_main) cudaStreamSynchronize(c->s_main);
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
-    cudaFree(c->acc); cudaFree(c->seen); cudaFree(c->slot_meta);
+    cudaFree(c->acc_raw); cudaFree(c->seen); cudaFree(c->slot_meta);
     for (int i = 0; i <= c->S && i <= APM_MAX_SLOTS; ++i) cudaFree(c->log_buf[i]);
     cudaFree(c->d_log_ptrs); cudaFree(c->sort_hist); cudaFree(c->sort_base);
     cudaFree(c->tf_tile_max); cudaFree(c->tf_tile_prefix); cudaFree(c->d_ticks); cudaFree(c->d_nticks);
@@ -260,6 +262,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     c->keep = cfg->window_buckets + cfg->buffer_buckets;
     c->S = c->keep + 1;
     c->inv_bucket = 1.0 / (double)cfg->bucket_ms;
+    if (const char* e = getenv("APM_K1_TPC")) { int v = atoi(e); if (v > 0) c->k1_tiles_per_cta = (uint32_t)v; }
     // windowSz * intervalLengthSec / 60.0 (stream_calc_stats.js:186)
     c->tpm_div = (double)cfg->window_buckets * ((double)cfg->bucket_ms / 1000.0) / 60.0;
     for (int i = 0; i < cfg->num_percentiles; ++i) c->pfrac[i] = cfg->percentiles[i] / 100.0;  // util_methods.js:129
@@ -273,7 +276,17 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_consumed[i], cudaEventDisableTiming));
     }
     const size_t K = c->K;
-    TRY_CREATE(dalloc(&c->acc, (size_t)c->S * K));
+    {
+        const size_t n = (size_t)c->S * K;
+        TRY_CREATE(cudaMalloc(&c->acc_raw, n * APM_ACC_BYTES_PER_ENTRY));
+        char* b = (char*)c->acc_raw;
+        c->acc.sum = (unsigned long long*)b;
+        c->acc.sq_lo = c->acc.sum + n;
+        c->acc.sq_hi = c->acc.sq_lo + n;
+        c->acc.cnt = (uint32_t*)(c->acc.sq_hi + n);
+        c->acc.vmin = c->acc.cnt + n;
+        c->acc.vmax = c->acc.vmin + n;
+    }
     TRY_CREATE(dalloc(&c->seen, K));
     TRY_CREATE(cudaMemsetAsync(c->seen, 0, K, c->s_main));
     TRY_CREATE(dalloc(&c->slot_meta, (size_t)c->S));

@@ -10,17 +10,23 @@
 #define APM_MAX_SLOTS 64  // window + buffer + 1 must not exceed this
 #define APM_NUM_SMS 148   // B200
 
-// One (key, bucket-slot) accumulator: everything addData (stream_calc_stats.js:115-134)
-// would have appended to buckets[label], reduced to order-independent integers.
-struct __align__(32) Acc {
-    uint32_t count;
-    uint32_t vmin;      // 0xFFFFFFFF when empty
-    uint32_t vmax;
-    uint32_t sumsq_hi;  // bits 64..95 of the sum of squares
-    uint64_t sum;
-    uint64_t sumsq_lo;
+// (key, bucket-slot) accumulators: everything addData (stream_calc_stats.js:115-134) would
+// have appended to buckets[label], reduced to order-independent integers.  Structure of
+// arrays, each [slot][key], so the per-key tick kernel reads them coalesced and every update
+// is a fire-and-forget L2 reduction:
+//   sum   = sum of elapsed                       (u64: < 2^32 values of < 2^31)
+//   sq_lo = sum of (elapsed^2 & 0xFFFFFFFF)      (u64: cannot overflow below 2^32 updates)
+//   sq_hi = sum of (elapsed^2 >> 32)             (u64; only durations >= 2^16 ms touch it)
+// so the exact sum of squares is sq_hi * 2^32 + sq_lo without any carry between atomics.
+struct AccSoA {
+    unsigned long long* sum;
+    unsigned long long* sq_lo;
+    unsigned long long* sq_hi;
+    uint32_t* cnt;
+    uint32_t* vmin;  // 0xFFFFFFFF when empty
+    uint32_t* vmax;
 };
-static_assert(sizeof(Acc) == 32, "Acc must be one 32-byte sector");
+#define APM_ACC_BYTES_PER_ENTRY 36
 
 // Per bucket-slot bookkeeping of the value log (device resident).
 struct SlotMeta {
@@ -33,6 +39,8 @@ struct SlotMeta {
 // Device counters, one cache line.
 struct DevCounters {
     unsigned long long ingested, dropped, invalid, future, log_overflow;
+    uint32_t max_value;  // largest elapsed ever ingested (bounds the radix passes)
+    uint32_t pad_;
 };
 
 struct WindowSlots {

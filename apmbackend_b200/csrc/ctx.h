@@ -23,7 +23,8 @@ struct apm_ctx {
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
 
     // --- bucket accumulators and value logs
-    Acc* acc = nullptr;          // [S][K]
+    void* acc_raw = nullptr;     // one allocation behind the six accumulator planes
+    AccSoA acc = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // each [S][K]
     uint8_t* seen = nullptr;     // [K] key has ever been ingested
     SlotMeta* slot_meta = nullptr;  // [S]
     int64_t slot_label[APM_MAX_SLOTS];
@@ -70,6 +71,7 @@ struct apm_ctx {
     DevCounters* h_counters = nullptr;  // pinned mirror
     apm_counters counters;
     uint64_t launches = 0;
+    uint32_t k1_tiles_per_cta = 3;  // tuning knob (APM_K1_TPC)
 
     // multi-GPU
     void* nccl_comm = nullptr;

@@ -136,7 +136,16 @@ __global__ void __launch_bounds__(TF_THREADS) tf_emit_kernel(const int64_t* __re
 }
 
 // ---- K1: keyed segmented reduction ------------------------------------------------------------
-// v1: one transaction per thread, accumulators updated with L2 reductions.
+// Each CTA keeps a hash table of (key, bucket-slot) partial accumulators in shared memory,
+// streams its tiles of the segment through it with 128-bit coalesced loads, and flushes the
+// table to the global accumulator planes with fire-and-forget L2 reductions.  Zipf-hot keys
+// therefore cost native 32-bit shared-memory atomics instead of serialising on one L2 address;
+// only table misses and durations >= 2^16 ms go to global memory directly.  All accumulators
+// are integers, so the result does not depend on the order of the updates.
+//
+// Table entry (24 B, 4096 entries = 96 KB, two CTAs per SM), valid for values < 2^16 and at most
+// 65535 updates between flushes:  tag | sum (u32, cannot overflow) | sq_lo (u32) |
+// cnt:16 sq_hi:16 (carry of sq_lo) | min | max.
 struct ReduceParams {
     const uint32_t* svc;
     const uint32_t* jvm;
@@ -148,63 +157,245 @@ struct ReduceParams {
     int64_t latest;
     int keep, S;
     uint32_t num_services, num_jvms, K;
-    Acc* acc;
+    AccSoA acc;
     uint8_t* seen;
     SlotMeta* slot_meta;
     uint64_t* const* logs;
     uint64_t log_cap;
     DevCounters* counters;
     int with_log;
+    int vec_ok;            // all four column pointers are 16-byte aligned
+    uint32_t tiles;        // tiles of K1_TILE transactions starting at (begin & ~3)
 };
 
-__global__ void __launch_bounds__(256) reduce_kernel_v1(const ReduceParams p) {
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+constexpr int K1_THREADS = 512;
+constexpr int K1_PER_THREAD = 4;
+constexpr int K1_TILE = K1_THREADS * K1_PER_THREAD;
+constexpr int K1_TABLE = 4096;
+constexpr int K1_PROBES = 4;
+constexpr int K1_FLUSH_TILES = 65535 / K1_TILE;  // 31: keeps cnt < 2^16 and sum < 2^32 per entry
+constexpr uint32_t K1_EMPTY = 0xFFFFFFFFu;
+constexpr int K1_SLOT_SHIFT = 26;         // tag = slot << 26 | key  (K <= 2^26)
+
+struct K1Smem {
+    uint32_t tag[K1_TABLE], sum[K1_TABLE], sq_lo[K1_TABLE], cnt_hi[K1_TABLE], mn[K1_TABLE], mx[K1_TABLE];
+    uint32_t warp_scan[K1_THREADS / 32];
+    unsigned long long base;  // reserved log position of the current (tile, slot) group
+    uint32_t pick;            // (first pending index << 8 | slot) of the current log group
+    uint32_t vmax;
+    unsigned long long c[5];
+};
+
+__device__ __forceinline__ uint32_t k1_hash(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+
+__device__ __forceinline__ void k1_minmax_global(const AccSoA& acc, size_t ai, uint32_t lo, uint32_t hi) {
+    // unconditional reductions: a read-then-update would stall on the load for no saving,
+    // because most flushed entries are the first of their bucket
+    atomicMin(&acc.vmin[ai], lo);
+    atomicMax(&acc.vmax[ai], hi);
+}
+
+// one transaction straight to the global planes (table miss or a duration >= 2^16 ms)
+__device__ __forceinline__ void k1_global_update(const ReduceParams& p, int slot, uint32_t key, uint32_t v) {
+    const size_t ai = (size_t)slot * p.K + key;
+    const unsigned long long sq = (unsigned long long)v * v;
+    atomicAdd(&p.acc.cnt[ai], 1u);
+    atomicAdd(&p.acc.sum[ai], (unsigned long long)v);
+    atomicAdd(&p.acc.sq_lo[ai], sq & 0xFFFFFFFFull);
+    if (sq >> 32) atomicAdd(&p.acc.sq_hi[ai], sq >> 32);
+    k1_minmax_global(p.acc, ai, v, v);
+    p.seen[key] = 1;
+}
+
+__device__ __forceinline__ void k1_table_init(K1Smem& sm, int tid) {
+    for (int i = tid; i < K1_TABLE; i += K1_THREADS) {
+        sm.tag[i] = K1_EMPTY; sm.sum[i] = 0; sm.sq_lo[i] = 0; sm.cnt_hi[i] = 0; sm.mn[i] = 0xFFFFFFFFu; sm.mx[i] = 0;
+    }
+}
+
+__device__ __forceinline__ void k1_table_flush(const ReduceParams& p, K1Smem& sm, int tid) {
+    for (int i = tid; i < K1_TABLE; i += K1_THREADS) {
+        const uint32_t tag = sm.tag[i];
+        if (tag == K1_EMPTY) continue;
+        const uint32_t k = tag & ((1u << K1_SLOT_SHIFT) - 1u);
+        const size_t ai = (size_t)(tag >> K1_SLOT_SHIFT) * p.K + k;
+        const uint32_t ch = sm.cnt_hi[i];
+        atomicAdd(&p.acc.cnt[ai], ch >> 16);
+        atomicAdd(&p.acc.sum[ai], (unsigned long long)sm.sum[i]);
+        atomicAdd(&p.acc.sq_lo[ai], (unsigned long long)sm.sq_lo[i]);
+        if (ch & 0xFFFFu) atomicAdd(&p.acc.sq_hi[ai], (unsigned long long)(ch & 0xFFFFu));
+        k1_minmax_global(p.acc, ai, sm.mn[i], sm.mx[i]);
+        p.seen[k] = 1;
+    }
+}
+
+__global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReduceParams p) {
+    extern __shared__ __align__(16) unsigned char k1_raw[];
+    K1Smem& sm = *reinterpret_cast<K1Smem*>(k1_raw);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    k1_table_init(sm, tid);
+    if (tid < 5) sm.c[tid] = 0;
+    if (tid == 0) sm.vmax = 0;
+    __syncthreads();
+
+    const uint64_t i0 = p.begin & ~3ull;
     unsigned long long n_ing = 0, n_drop = 0, n_inv = 0, n_fut = 0, n_ovf = 0;
-    for (uint64_t i = p.begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < p.end; i += stride) {
-        const uint32_t svc = __ldg(p.svc + i), jvm = __ldg(p.jvm + i);
-        const int64_t t = __ldg(p.ts + i);
-        const int32_t el = __ldg(p.el + i);
-        if (svc >= p.num_services || jvm >= p.num_jvms || el < 0 || t < 0) { n_inv++; continue; }
-        const int64_t lab = apm_label(t, p.bucket_ms, p.inv_bucket);
-        if (lab > p.latest) { n_fut++; continue; }
-        if (lab < p.latest - p.keep) { n_drop++; continue; }
-        const int slot = (int)(lab % p.S);
-        const uint32_t key = jvm * p.num_services + svc;
-        p.seen[key] = 1;
-        Acc* a = p.acc + (size_t)slot * p.K + key;
-        const uint32_t v = (uint32_t)el;
-        atomicAdd(&a->count, 1u);
-        atomicAdd((unsigned long long*)&a->sum, (unsigned long long)v);
-        const unsigned long long sq = (unsigned long long)v * v;
-        const unsigned long long old = atomicAdd((unsigned long long*)&a->sumsq_lo, sq);
-        if (old + sq < old) atomicAdd(&a->sumsq_hi, 1u);
-        atomicMin(&a->vmin, v);
-        atomicMax(&a->vmax, v);
-        n_ing++;
+    uint32_t my_max = 0;
+    int tiles_since_flush = 0;
+
+    for (uint32_t tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+        if (tiles_since_flush == K1_FLUSH_TILES) {
+            __syncthreads();
+            k1_table_flush(p, sm, tid);
+            __syncthreads();
+            k1_table_init(sm, tid);
+            __syncthreads();
+            tiles_since_flush = 0;
+        }
+        ++tiles_since_flush;
+        const uint64_t idx = i0 + (uint64_t)tile * K1_TILE + (uint64_t)tid * K1_PER_THREAD;
+        uint32_t svc[4], jvm[4];
+        int32_t el[4];
+        int64_t ts[4];
+        bool in[4];
+        if (p.vec_ok && idx >= p.begin && idx + 4 <= p.end) {
+            const uint4 s4 = __ldcs(reinterpret_cast<const uint4*>(p.svc + idx));
+            const uint4 j4 = __ldcs(reinterpret_cast<const uint4*>(p.jvm + idx));
+            const int4 e4 = __ldcs(reinterpret_cast<const int4*>(p.el + idx));
+            const longlong2 t01 = __ldcs(reinterpret_cast<const longlong2*>(p.ts + idx));
+            const longlong2 t23 = __ldcs(reinterpret_cast<const longlong2*>(p.ts + idx + 2));
+            svc[0] = s4.x; svc[1] = s4.y; svc[2] = s4.z; svc[3] = s4.w;
+            jvm[0] = j4.x; jvm[1] = j4.y; jvm[2] = j4.z; jvm[3] = j4.w;
+            el[0] = e4.x; el[1] = e4.y; el[2] = e4.z; el[3] = e4.w;
+            ts[0] = t01.x; ts[1] = t01.y; ts[2] = t23.x; ts[3] = t23.y;
+            in[0] = in[1] = in[2] = in[3] = true;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint64_t i = idx + j;
+                in[j] = i >= p.begin && i < p.end;
+                svc[j] = in[j] ? __ldg(p.svc + i) : 0;
+                jvm[j] = in[j] ? __ldg(p.jvm + i) : 0;
+                el[j] = in[j] ? __ldg(p.el + i) : 0;
+                ts[j] = in[j] ? __ldg(p.ts + i) : 0;
+            }
+        }
+        int slot[4];       // -1: nothing to log
+        uint32_t key[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            slot[j] = -1;
+            key[j] = 0;
+            if (!in[j]) continue;
+            if (svc[j] >= p.num_services || jvm[j] >= p.num_jvms || el[j] < 0 || ts[j] < 0) { n_inv++; continue; }
+            const int64_t lab = apm_label(ts[j], p.bucket_ms, p.inv_bucket);
+            if (lab > p.latest) { n_fut++; continue; }
+            if (lab < p.latest - p.keep) { n_drop++; continue; }
+            const int sl = (int)(lab % p.S);
+            const uint32_t k = jvm[j] * p.num_services + svc[j];
+            const uint32_t v = (uint32_t)el[j];
+            slot[j] = sl;
+            key[j] = k;
+            n_ing++;
+            my_max = v > my_max ? v : my_max;
+            bool done = false;
+            if (v < 65536u) {
+                const uint32_t tag = ((uint32_t)sl << K1_SLOT_SHIFT) | k;
+                uint32_t h = k1_hash(tag) & (K1_TABLE - 1);
+#pragma unroll 1
+                for (int pr = 0; pr < K1_PROBES; ++pr) {
+                    uint32_t cur = sm.tag[h];
+                    if (cur != tag) {
+                        if (cur == K1_EMPTY) cur = atomicCAS(&sm.tag[h], K1_EMPTY, tag);
+                        if (cur != K1_EMPTY && cur != tag) { h = (h + 1) & (K1_TABLE - 1); continue; }
+                    }
+                    atomicAdd(&sm.sum[h], v);
+                    const uint32_t q = v * v;
+                    const uint32_t o = atomicAdd(&sm.sq_lo[h], q);
+                    atomicAdd(&sm.cnt_hi[h], 0x10000u + ((o + q < o) ? 1u : 0u));
+                    if (v < sm.mn[h]) atomicMin(&sm.mn[h], v);
+                    if (v > sm.mx[h]) atomicMax(&sm.mx[h], v);
+                    done = true;
+                    break;
+                }
+            }
+            if (!done) k1_global_update(p, sl, k, v);
+        }
+
         if (p.with_log) {
-            SlotMeta* sm = p.slot_meta + slot;
-            const unsigned long long pos = atomicAdd(&sm->count, 1ull);
-            if (pos < p.log_cap) p.logs[slot][pos] = ((uint64_t)key << 32) | v;
-            else n_ovf++;
-            atomicMax(&sm->max_value, v);
+            // append (key, value) words to their bucket's log: one reservation per (tile, slot)
+            bool pending[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) pending[j] = slot[j] >= 0;
+            bool any = pending[0] | pending[1] | pending[2] | pending[3];
+            while (__syncthreads_or(any)) {
+                if (tid == 0) sm.pick = 0xFFFFFFFFu;
+                __syncthreads();
+                uint32_t mine = 0xFFFFFFFFu;
+#pragma unroll
+                for (int j = 3; j >= 0; --j)
+                    if (pending[j]) mine = ((uint32_t)(tid * 4 + j) << 8) | (uint32_t)slot[j];
+                const uint32_t wmin = __reduce_min_sync(0xffffffffu, mine);
+                if (lane == 0 && wmin != 0xFFFFFFFFu) atomicMin(&sm.pick, wmin);
+                __syncthreads();
+                const int gslot = (int)(sm.pick & 0xFFu);
+                uint32_t c = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) c += (pending[j] && slot[j] == gslot) ? 1u : 0u;
+                uint32_t incl = c;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += y;
+                }
+                if (lane == 31) sm.warp_scan[wid] = incl;
+                __syncthreads();
+                uint32_t woff = 0, total = 0;
+#pragma unroll
+                for (int w = 0; w < K1_THREADS / 32; ++w) {
+                    const uint32_t x = sm.warp_scan[w];
+                    if (w < wid) woff += x;
+                    total += x;
+                }
+                if (tid == 0) sm.base = atomicAdd(&p.slot_meta[gslot].count, (unsigned long long)total);
+                __syncthreads();
+                unsigned long long pos = sm.base + woff + incl - c;
+                uint64_t* lg = p.logs[gslot];
+                any = false;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (pending[j] && slot[j] == gslot) {
+                        if (pos < p.log_cap) lg[pos] = ((uint64_t)key[j] << 32) | (uint32_t)el[j];
+                        else n_ovf++;
+                        ++pos;
+                        pending[j] = false;
+                    }
+                    any |= pending[j];
+                }
+            }
         }
     }
-    // block-level counter aggregation
-    __shared__ unsigned long long s_c[5];
-    if (threadIdx.x < 5) s_c[threadIdx.x] = 0;
+
     __syncthreads();
-    if (n_ing) atomicAdd(&s_c[0], n_ing);
-    if (n_drop) atomicAdd(&s_c[1], n_drop);
-    if (n_inv) atomicAdd(&s_c[2], n_inv);
-    if (n_fut) atomicAdd(&s_c[3], n_fut);
-    if (n_ovf) atomicAdd(&s_c[4], n_ovf);
+    k1_table_flush(p, sm, tid);
+    my_max = __reduce_max_sync(0xffffffffu, my_max);
+    if (lane == 0 && my_max) atomicMax(&sm.vmax, my_max);
+    if (n_ing) atomicAdd(&sm.c[0], n_ing);
+    if (n_drop) atomicAdd(&sm.c[1], n_drop);
+    if (n_inv) atomicAdd(&sm.c[2], n_inv);
+    if (n_fut) atomicAdd(&sm.c[3], n_fut);
+    if (n_ovf) atomicAdd(&sm.c[4], n_ovf);
     __syncthreads();
-    if (threadIdx.x == 0) {
-        if (s_c[0]) atomicAdd(&p.counters->ingested, s_c[0]);
-        if (s_c[1]) atomicAdd(&p.counters->dropped, s_c[1]);
-        if (s_c[2]) atomicAdd(&p.counters->invalid, s_c[2]);
-        if (s_c[3]) atomicAdd(&p.counters->future, s_c[3]);
-        if (s_c[4]) atomicAdd(&p.counters->log_overflow, s_c[4]);
+    if (tid == 0) {
+        if (sm.c[0]) atomicAdd(&p.counters->ingested, sm.c[0]);
+        if (sm.c[1]) atomicAdd(&p.counters->dropped, sm.c[1]);
+        if (sm.c[2]) atomicAdd(&p.counters->invalid, sm.c[2]);
+        if (sm.c[3]) atomicAdd(&p.counters->future, sm.c[3]);
+        if (sm.c[4]) atomicAdd(&p.counters->log_overflow, sm.c[4]);
+        if (sm.vmax > p.counters->max_value) atomicMax(&p.counters->max_value, sm.vmax);
     }
 }
 
@@ -251,11 +442,23 @@ apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin
     p.acc = c->acc; p.seen = c->seen; p.slot_meta = c->slot_meta; p.logs = c->d_log_ptrs; p.log_cap = c->log_cap;
     p.counters = c->d_counters;
     p.with_log = (c->cfg.flags & APM_F_PERCENTILES) && c->cfg.num_percentiles > 0;
-    const uint64_t n = end - begin;
-    uint64_t blocks = (n + 255) / 256;
-    const uint64_t max_blocks = (uint64_t)APM_NUM_SMS * 8;
+    const uintptr_t align = (uintptr_t)d.service_id | (uintptr_t)d.jvm_id | (uintptr_t)d.end_ts_ms | (uintptr_t)d.elapsed_ms;
+    p.vec_ok = (align & 15) == 0;
+    const uint64_t i0 = begin & ~3ull;
+    const uint64_t tiles = (end - i0 + K1_TILE - 1) / K1_TILE;
+    if (tiles > 0xFFFFFFFFull) return apm_fail(c, APM_E_CAPACITY, "segment too large");
+    p.tiles = (uint32_t)tiles;
+    // every CTA flushes its table once: give each at least k1_tiles_per_cta tiles, cap at 2 CTAs per SM
+    uint64_t blocks = (tiles + c->k1_tiles_per_cta - 1) / c->k1_tiles_per_cta;
+    const uint64_t max_blocks = (uint64_t)APM_NUM_SMS * 2;
     if (blocks > max_blocks) blocks = max_blocks;
-    reduce_kernel_v1<<<(unsigned)blocks, 256, 0, c->s_main>>>(p);
+    if (blocks < 1) blocks = 1;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CUDA_TRY(c, cudaFuncSetAttribute(reduce_kernel_v3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem)));
+        attr_set = true;
+    }
+    reduce_kernel_v3<<<(unsigned)blocks, K1_THREADS, sizeof(K1Smem), c->s_main>>>(p);
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;

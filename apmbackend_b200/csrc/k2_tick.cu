@@ -7,16 +7,14 @@
 
 namespace {
 
-__global__ void __launch_bounds__(256) clear_slots_kernel(Acc* __restrict__ acc, SlotMeta* __restrict__ meta, uint32_t K,
-                                                          int S, unsigned long long slot_mask) {
-    // grid.y = slot; 32-byte accumulators are written as two 16-byte stores
-    const int slot = blockIdx.y;
+__global__ void __launch_bounds__(256) clear_slots_kernel(const AccSoA acc, SlotMeta* __restrict__ meta, uint32_t K,
+                                                          unsigned long long slot_mask) {
+    const int slot = blockIdx.y;  // grid.y = slot
     if (!((slot_mask >> slot) & 1ull)) return;
-    uint4* a = reinterpret_cast<uint4*>(acc + (size_t)slot * K);
-    const uint4 lo = make_uint4(0u, 0xFFFFFFFFu, 0u, 0u), hi = make_uint4(0u, 0u, 0u, 0u);
+    const size_t base = (size_t)slot * K;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)K; i += (size_t)gridDim.x * blockDim.x) {
-        a[2 * i] = lo;
-        a[2 * i + 1] = hi;
+        acc.sum[base + i] = 0; acc.sq_lo[base + i] = 0; acc.sq_hi[base + i] = 0;
+        acc.cnt[base + i] = 0; acc.vmin[base + i] = 0xFFFFFFFFu; acc.vmax[base + i] = 0;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         meta[slot].count = 0;
@@ -79,7 +77,7 @@ __device__ uint32_t next_above(const Run* runs, int nruns, uint32_t v) {
 }
 
 struct TickParams {
-    const Acc* acc;
+    AccSoA acc;
     const uint8_t* seen;
     uint64_t* const* logs;
     const SlotMeta* slot_meta;
@@ -111,17 +109,20 @@ __global__ void __launch_bounds__(128) tick_stats_kernel(const TickParams p) {
     int nruns = 0;
     for (int w = 0; w < p.win.n; ++w) {
         const int slot = p.win.slot[w];
-        const uint4* a4 = reinterpret_cast<const uint4*>(p.acc + (size_t)slot * p.K + key);
-        const uint4 lo = __ldg(a4), hi = __ldg(a4 + 1);
-        const uint32_t c = lo.x;
+        const size_t ai = (size_t)slot * p.K + key;
+        const uint32_t c = p.acc.cnt[ai];
         if (c == 0) continue;
         cnt += c;
-        vmin = lo.y < vmin ? lo.y : vmin;
-        vmax = lo.z > vmax ? lo.z : vmax;
-        sum += ((uint64_t)hi.y << 32) | hi.x;
-        const uint64_t add = ((uint64_t)hi.w << 32) | hi.z;
-        const uint64_t t = sq_lo + add;
-        sq_hi += (uint64_t)lo.w + (t < sq_lo ? 1u : 0u);
+        const uint32_t mn = p.acc.vmin[ai], mx = p.acc.vmax[ai];
+        vmin = mn < vmin ? mn : vmin;
+        vmax = mx > vmax ? mx : vmax;
+        sum += p.acc.sum[ai];
+        // sum of squares = sq_hi * 2^32 + sq_lo, accumulated as a 128-bit (hi:lo) pair
+        const uint64_t lo_part = p.acc.sq_lo[ai], hi_part = p.acc.sq_hi[ai];
+        const uint64_t add_lo = lo_part + (hi_part << 32);
+        const uint64_t add_hi = (hi_part >> 32) + (add_lo < lo_part ? 1u : 0u);
+        const uint64_t t = sq_lo + add_lo;
+        sq_hi += add_hi + (t < sq_lo ? 1u : 0u);
         sq_lo = t;
         if (p.with_pct) {
             const uint64_t* lg = p.logs[slot];
@@ -209,7 +210,7 @@ apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask) {
     if (!slot_mask) return APM_OK;
     unsigned gx = (c->K + 255) / 256;
     if (gx > APM_NUM_SMS * 4) gx = APM_NUM_SMS * 4;
-    clear_slots_kernel<<<dim3(gx, c->S), 256, 0, c->s_main>>>(c->acc, c->slot_meta, c->K, c->S, slot_mask);
+    clear_slots_kernel<<<dim3(gx, c->S), 256, 0, c->s_main>>>(c->acc, c->slot_meta, c->K, slot_mask);
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;

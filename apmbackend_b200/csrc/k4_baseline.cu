@@ -15,7 +15,7 @@
 namespace {
 
 constexpr int K4_THREADS = 128;
-constexpr int K4_UNROLL = 16;
+constexpr int K4_UNROLL = 32;
 
 struct BaselineParams {
     double* ring;          // [L][3K]
@@ -59,18 +59,27 @@ __global__ void __launch_bounds__(K4_THREADS) baseline_kernel(const BaselinePara
         double sum = 0.0, sumsq_dev = 0.0;
         uint32_t cnt = 0;
         const double* base = p.ring + col;
-        // two contiguous spans: [head, L) then [0, head)
-        for (int span = 0; span < 2; ++span) {
-            uint32_t s = span == 0 ? p.head : 0u;
-            const uint32_t e = span == 0 ? p.L : p.head;
-            for (; s + K4_UNROLL <= e; s += K4_UNROLL) {
-                double v[K4_UNROLL];
+        // Oldest first: element i of the list lives in slot (head + i) mod L.  The chain of
+        // additions is sequential by definition, so bandwidth comes from loads in flight: two
+        // register batches are software-pipelined (one being added while the other is loading).
+        // Reads past the end are replaced by NaN, which average() skips anyway.
+        auto load_elem = [&](uint32_t i) -> double {
+            uint32_t sl = p.head + i;
+            sl = sl >= p.L ? sl - p.L : sl;
+            return i < p.L ? __ldcs(base + (size_t)sl * ncol) : nan;
+        };
+        double va[K4_UNROLL], vb[K4_UNROLL];
 #pragma unroll
-                for (int u = 0; u < K4_UNROLL; ++u) v[u] = __ldcs(base + (size_t)(s + u) * ncol);
+        for (int u = 0; u < K4_UNROLL; ++u) va[u] = load_elem(u);
+        for (uint32_t i = 0; i < p.L; i += 2 * K4_UNROLL) {
 #pragma unroll
-                for (int u = 0; u < K4_UNROLL; ++u) accumulate(v[u], sum, cnt);
-            }
-            for (; s < e; ++s) accumulate(__ldcs(base + (size_t)s * ncol), sum, cnt);
+            for (int u = 0; u < K4_UNROLL; ++u) vb[u] = load_elem(i + K4_UNROLL + u);
+#pragma unroll
+            for (int u = 0; u < K4_UNROLL; ++u) accumulate(va[u], sum, cnt);
+#pragma unroll
+            for (int u = 0; u < K4_UNROLL; ++u) va[u] = load_elem(i + 2 * K4_UNROLL + u);
+#pragma unroll
+            for (int u = 0; u < K4_UNROLL; ++u) accumulate(vb[u], sum, cnt);
         }
         const double last = base[(size_t)((p.head + p.L - 1) % p.L) * ncol];
         bool avg_ok = cnt > 0, sd_ok = false;

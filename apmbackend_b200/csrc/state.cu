@@ -73,7 +73,7 @@ apm_status apm_state_save(apm_ctx* c, const char* path) {
     for (int s = 0; s < c->S; ++s) { h.slot_label[s] = c->slot_label[s]; h.log_count[s] = std::min<uint64_t>(meta[s].count, c->log_cap); }
     std::vector<char> tmp;
     bool ok = fwrite(&h, sizeof h, 1, fl.f) == 1;
-    ok = ok && put(fl.f, c->acc, sizeof(Acc) * (size_t)c->S * c->K, tmp);
+    ok = ok && put(fl.f, c->acc_raw, (size_t)APM_ACC_BYTES_PER_ENTRY * c->S * c->K, tmp);
     ok = ok && put(fl.f, c->seen, c->K, tmp);
     ok = ok && put(fl.f, c->slot_meta, sizeof(SlotMeta) * c->S, tmp);
     if (h.has_logs)
@@ -108,7 +108,7 @@ apm_status apm_state_load(apm_ctx* c, const char* path) {
     for (int s = 0; s < c->S; ++s)
         if (h.log_count[s] > c->log_cap) return apm_fail(c, APM_E_CAPACITY, "state file holds a value log above max_tx_per_bucket");
     std::vector<char> tmp;
-    bool ok = get(fl.f, c->acc, sizeof(Acc) * (size_t)c->S * c->K, tmp);
+    bool ok = get(fl.f, c->acc_raw, (size_t)APM_ACC_BYTES_PER_ENTRY * c->S * c->K, tmp);
     ok = ok && get(fl.f, c->seen, c->K, tmp);
     ok = ok && get(fl.f, c->slot_meta, sizeof(SlotMeta) * c->S, tmp);
     if (h.has_logs)
