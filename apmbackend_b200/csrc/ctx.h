@@ -113,6 +113,10 @@ apm_status apm_launch_find_ticks(apm_ctx* c, const int64_t* d_ts, uint64_t n, un
 apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin, uint64_t end);
 // k3_sort.cu
 apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value);
+uint64_t* apm_radix_sort_words(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t n, uint32_t* hist, uint32_t* totals,
+                               int vbits, int kbits, uint64_t* launches);
+uint64_t apm_radix_sort_tiles(uint64_t n);
+int apm_bits_of(uint64_t v);
 // k2_tick.cu
 apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask);
 apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot);

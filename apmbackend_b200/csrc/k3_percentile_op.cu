@@ -1,0 +1,137 @@
+// Stand-alone percentile operator: the Array.prototype pair binaryConcat + calcPercentile
+// (util_methods.js:102-106, 112-142) for one array of durations that already sits in device
+// memory - sort ascending (duplicates kept), then apply the reference's index rule.
+#include <mutex>
+
+#include "ctx.h"
+
+namespace {
+
+__global__ void __launch_bounds__(256) widen_kernel(const int32_t* __restrict__ v, uint64_t* __restrict__ w, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) w[i] = (uint64_t)(uint32_t)v[i];  // key field 0: only the value bits are sorted
+}
+
+// max over the values, for the number of radix passes
+__global__ void __launch_bounds__(256) max_kernel(const int32_t* __restrict__ v, uint32_t n, uint32_t* __restrict__ out) {
+    uint32_t m = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t x = (uint32_t)v[i];
+        m = x > m ? x : m;
+    }
+    m = __reduce_max_sync(0xffffffffu, m);
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
+}
+
+struct PctParams {
+    int npct;
+    double pfrac[APM_MAX_PCT];
+};
+
+// narrow the sorted words back to int32 and evaluate calcPercentile for each requested percentile
+__global__ void __launch_bounds__(256) narrow_pct_kernel(const uint64_t* __restrict__ w, uint32_t n, int32_t* __restrict__ sorted,
+                                                         const PctParams p, double* __restrict__ pct_out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && sorted) sorted[i] = (int32_t)(uint32_t)w[i];
+    if (blockIdx.x == 0 && (int)threadIdx.x < p.npct) {
+        const double nan = __longlong_as_double(0x7ff8000000000000ll);
+        double r = nan;
+        if (n > 0) {
+            const double f = p.pfrac[threadIdx.x];
+            const double index = __dsub_rn(__dmul_rn(f, (double)n), 1.0);  // (percentile / 100.0) * length - 1.0
+            uint32_t i0;
+            bool pair = false;
+            if (f == 0.0) i0 = 0;
+            else if (f == 1.0) i0 = n - 1;
+            else if (n == 1 || index == trunc(index)) i0 = index < 0 ? 0u : (uint32_t)index;
+            else {
+                const double ci = ceil(index);
+                i0 = ci < 0 ? 0u : (uint32_t)ci;
+                pair = i0 != n - 1;
+            }
+            const double v0 = (double)(uint32_t)w[i0];
+            r = pair ? __dmul_rn(__dadd_rn(v0, (double)(uint32_t)w[i0 + 1]), 0.5) : v0;
+        }
+        pct_out[threadIdx.x] = r;
+    }
+}
+
+// Scratch layout for n values (all offsets 256-byte aligned):
+//   words A [n] u64 | words B [n] u64 | hist [256 * tiles] u32 | totals [256] u32 | max u32 | pct [4] f64
+struct ScratchPlan {
+    size_t off_a, off_b, off_hist, off_totals, off_max, off_pct, bytes;
+};
+
+size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+ScratchPlan plan_for(uint64_t n) {
+    ScratchPlan s;
+    const uint64_t m = n ? n : 1;
+    s.off_a = 0;
+    s.off_b = align256(s.off_a + m * 8);
+    s.off_hist = align256(s.off_b + m * 8);
+    s.off_totals = align256(s.off_hist + 256 * apm_radix_sort_tiles(m) * 4);
+    s.off_max = align256(s.off_totals + 256 * 4);
+    s.off_pct = align256(s.off_max + 4);
+    s.bytes = align256(s.off_pct + APM_MAX_PCT * 8);
+    return s;
+}
+
+apm_status run_percentiles(unsigned char* scratch, const int32_t* d_values, uint32_t n, const double* pcts, int32_t npct,
+                           double* out_pct, int32_t* d_sorted) {
+    const ScratchPlan sp = plan_for(n);
+    uint64_t* a = (uint64_t*)(scratch + sp.off_a);
+    uint64_t* b = (uint64_t*)(scratch + sp.off_b);
+    uint32_t* hist = (uint32_t*)(scratch + sp.off_hist);
+    uint32_t* totals = (uint32_t*)(scratch + sp.off_totals);
+    uint32_t* dmax = (uint32_t*)(scratch + sp.off_max);
+    double* dpct = (double*)(scratch + sp.off_pct);
+    PctParams pp;
+    pp.npct = npct;
+    for (int i = 0; i < APM_MAX_PCT; ++i) pp.pfrac[i] = i < npct ? pcts[i] / 100.0 : 0.0;
+    cudaStream_t st = 0;
+    const uint64_t* sorted_words = a;
+    if (n > 0) {
+        // the scratch keeps the previous call's contents: the one word that is accumulated into is cleared
+        CUDA_TRY(nullptr, cudaMemsetAsync(dmax, 0, sizeof(uint32_t), st));
+        const unsigned g = (n + 255) / 256;
+        max_kernel<<<g < 1184 ? g : 1184, 256, 0, st>>>(d_values, n, dmax);
+        widen_kernel<<<g, 256, 0, st>>>(d_values, a, n);
+        uint32_t hmax = 0;
+        CUDA_TRY(nullptr, cudaMemcpyAsync(&hmax, dmax, sizeof hmax, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(nullptr, cudaStreamSynchronize(st));
+        if (hmax > 0x7FFFFFFFu) return apm_fail(nullptr, APM_E_INVALID, "percentiles: negative duration in the input");
+        sorted_words = apm_radix_sort_words(st, a, b, n, hist, totals, apm_bits_of(hmax), 0, nullptr);
+    }
+    narrow_pct_kernel<<<n ? (n + 255) / 256 : 1, 256, 0, st>>>(sorted_words, n, d_sorted, pp, dpct);
+    CUDA_TRY(nullptr, cudaGetLastError());
+    if (npct > 0) CUDA_TRY(nullptr, cudaMemcpyAsync(out_pct, dpct, npct * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(nullptr, cudaStreamSynchronize(st));
+    return APM_OK;
+}
+
+apm_status check_args(const int32_t* d_values, uint32_t n, const double* pcts, int32_t npct, double* out_pct) {
+    if ((!d_values && n) || npct < 0 || npct > APM_MAX_PCT || (npct && (!pcts || !out_pct)))
+        return apm_fail(nullptr, APM_E_INVALID, "percentiles: bad argument");
+    for (int i = 0; i < npct; ++i)
+        if (!(pcts[i] >= 0.0 && pcts[i] <= 100.0)) return apm_fail(nullptr, APM_E_INVALID, "percentiles: percentile out of [0,100]");
+    return APM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+apm_status apm_sorted_percentiles(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts, int32_t npct,
+                                  double* out_pct, int32_t* d_sorted) {
+    apm_status st = check_args(d_values, n, pcts, npct, out_pct);
+    if (st) return st;
+    CUDA_TRY(nullptr, cudaSetDevice(device));
+    unsigned char* scratch = nullptr;
+    CUDA_TRY(nullptr, cudaMalloc((void**)&scratch, plan_for(n).bytes));
+    st = run_percentiles(scratch, d_values, n, pcts, npct, out_pct, d_sorted);
+    cudaFree(scratch);
+    return st;
+}
+
+}  // extern "C"

@@ -191,34 +191,45 @@ int bits_of(uint64_t v) {
 
 }  // namespace
 
-// Sorts log slot `slot` if entries were appended since its last sort.  Host reads the slot
-// bookkeeping first (the caller has synchronised c->s_main and refreshed h-side copies).
+// Stable LSD sort of n words between two buffers on `st`; only the low `vbits` of the value
+// field and the low `kbits` of the key field are sorted.  hist needs 256 * tiles(n) entries,
+// totals 256.  Returns the buffer that holds the sorted words (a or b).
+uint64_t* apm_radix_sort_words(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t n, uint32_t* hist, uint32_t* totals,
+                               int vbits, int kbits, uint64_t* launches) {
+    const uint32_t ntiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
+    uint64_t* src = a;
+    uint64_t* dst = b;
+    for (int field = 0; field < 2; ++field) {
+        const int lo = field == 0 ? 0 : 32, nb = field == 0 ? vbits : kbits;
+        for (int bit = 0; bit < nb; bit += 8) {
+            const int shift = lo + bit;
+            rs_hist_kernel<<<ntiles, RS_THREADS, 0, st>>>(src, n, shift, hist, ntiles);
+            rs_scan_rows_kernel<<<256, 256, 0, st>>>(hist, ntiles, totals);
+            rs_scatter_kernel<<<ntiles, RS_THREADS, 0, st>>>(src, dst, n, shift, hist, totals, ntiles);
+            if (launches) *launches += 3;
+            uint64_t* t = src; src = dst; dst = t;
+        }
+    }
+    return src;
+}
+
+uint64_t apm_radix_sort_tiles(uint64_t n) { return (n + RS_TILE - 1) / RS_TILE; }
+
+int apm_bits_of(uint64_t v) { return bits_of(v); }
+
+// Sorts log slot `slot` (entries were appended since its last sort).
 apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value) {
     ProfScope prof_scope_(c, APM_PG_SORT);
     if (n < 2) return APM_OK;
     if (n > 0xFFFFFFFFull) return apm_fail(c, APM_E_CAPACITY, "value log above 2^32 entries");
-    const uint32_t ntiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
-    if (ntiles > c->sort_tiles_cap) return apm_fail(c, APM_E_CAPACITY, "sort scratch too small");
+    if (apm_radix_sort_tiles(n) > c->sort_tiles_cap) return apm_fail(c, APM_E_CAPACITY, "sort scratch too small");
     const int vbits = bits_of(max_value), kbits = bits_of(c->K > 1 ? c->K - 1 : 0);
-    uint64_t* src = c->log_buf[slot];
-    uint64_t* dst = c->log_buf[c->S];
-    int passes = 0;
-    for (int field = 0; field < 2; ++field) {
-        const int lo = field == 0 ? 0 : 32, nb = field == 0 ? vbits : kbits;
-        for (int b = 0; b < nb; b += 8) {
-            const int shift = lo + b;
-            rs_hist_kernel<<<ntiles, RS_THREADS, 0, c->s_main>>>(src, n, shift, c->sort_hist, ntiles);
-            rs_scan_rows_kernel<<<256, 256, 0, c->s_main>>>(c->sort_hist, ntiles, c->sort_base);
-            rs_scatter_kernel<<<ntiles, RS_THREADS, 0, c->s_main>>>(src, dst, n, shift, c->sort_hist, c->sort_base, ntiles);
-            c->launches += 3;
-            uint64_t* t = src; src = dst; dst = t;
-            ++passes;
-        }
-    }
+    uint64_t* res = apm_radix_sort_words(c->s_main, c->log_buf[slot], c->log_buf[c->S], n, c->sort_hist, c->sort_base, vbits,
+                                         kbits, &c->launches);
     CUDA_TRY(c, cudaGetLastError());
-    if (passes & 1) {  // result sits in the spare buffer: swap roles
+    if (res != c->log_buf[slot]) {  // result sits in the spare buffer: swap roles
         c->log_buf[c->S] = c->log_buf[slot];
-        c->log_buf[slot] = src;
+        c->log_buf[slot] = res;
         CUDA_TRY(c, cudaMemcpyAsync(c->d_log_ptrs + slot, &c->log_buf[slot], sizeof(uint64_t*), cudaMemcpyHostToDevice,
                                     c->s_main));
     }

@@ -238,6 +238,14 @@ apm_status apm_reset_counters(apm_ctx* ctx);
  * as used by nf(), entries.js:65-69): parseFloat(x.toFixed(digits)), digits in {1,2}. */
 double apm_quantize(double x, int32_t digits);
 
+/* ---- stand-alone operator: replaces Array.prototype.binaryConcat + calcPercentile
+ * (util_methods.js:102-106, 112-142) for one array of n durations (>= 0) in device memory
+ * on `device`: sorts them ascending into d_sorted (device, n entries, may be NULL) and writes
+ * the npct requested percentiles (NaN when n == 0) to out_pct (host).  Scratch memory is
+ * allocated and freed inside the call.  Errors are reported through apm_last_error(NULL). */
+apm_status apm_sorted_percentiles(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts, int32_t npct,
+                                  double* out_pct, int32_t* d_sorted);
+
 /* ---- multi-GPU: keys are hash-sharded by the host; each rank owns its keys.
  * The only exchange is an all-gather of the compact alert block per tick. */
 uint32_t apm_owner_of_key(uint64_t global_key, uint32_t nranks);
