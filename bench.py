@@ -382,12 +382,12 @@ def main():
     # ---- CPU baseline: the reference-structure port on a bounded sample, rank 0 at N = 1 only
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         hs = syn.SynthStream(spec, device=False)
-        cols, n_s = sample_for_cpu(wl, hs, ticks=1)
+        cols, n_s = sample_for_cpu(wl, hs, ticks=6)
         threads = 1
         dt, tks = cpu_reference_run(wl, cols, ring_seed, threads)
         line["cpu_baseline"] = {"value": n_s / dt, "unit": "transactions/s", "cores": threads, "kind": "port",
-                                "sample": f"first {n_s} transactions of the same stream (1 bucket + the tick that "
-                                          f"closes it, all {K} keys, rings pre-filled): {tks} ticks in {dt:.1f} s, "
+                                "sample": f"first {n_s} transactions of the same stream (6 of its buckets + the tick "
+                                          f"that closes the last, all {K} keys, rings pre-filled): {tks} ticks in {dt:.1f} s, "
                                           "reference-structure C++ port, 1 thread (each reference stage is one "
                                           "single-threaded Node process; Node itself is absent on this box)"}
     eng.close()
@@ -406,7 +406,7 @@ def run_reference(args, wl, rank, world, config, span_ms):
                           shift_mod=97)
     hs = syn.SynthStream(spec, device=False)
     threads = os.cpu_count() or 1
-    (svc, jvm, ts, el), n_s = sample_for_cpu(wl, hs, ticks=1)
+    (svc, jvm, ts, el), n_s = sample_for_cpu(wl, hs, ticks=6)
     times, ticks = [], 0
     for s in range(args.warmup + args.steps):
         # prefill only matters for the z stage's cost; it is rebuilt each step so every step does the same work
@@ -415,8 +415,8 @@ def run_reference(args, wl, rank, world, config, span_ms):
             times.append(dt); ticks += tk
     total = float(np.sum(times))
     v = n_s * args.steps / total
-    sample = (f"each step = the first {n_s} transactions of the workload's stream (1 of its {wl['span_buckets']} buckets + "
-              f"the tick that closes it, all keys, rings pre-filled), reference-structure C++ port of "
+    sample = (f"each step = the first {n_s} transactions of the workload's stream (6 of its {wl['span_buckets']} buckets + "
+              f"the tick that closes the last, all keys, rings pre-filled), reference-structure C++ port of "
               f"stream_calc_stats.js + stream_calc_z_score.js, keys partitioned over {threads} host threads")
     line = {"impl": "reference", "metric": "transactions/sec aggregated+z-scored", "value": v, "unit": "transactions/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3,
