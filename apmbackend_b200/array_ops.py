@@ -31,3 +31,17 @@ def _call(fn, device, values, percentiles, want_sorted=True):
 def sorted_percentiles(values, percentiles=(75.0, 95.0), device: int = 0):
     """Returns (percentile values, ascending copy of `values`)."""
     return _call(_capi.lib().apm_sorted_percentiles, device, values, percentiles)
+
+
+NOALLOC_MAX_VALUES = 262144
+
+
+def sorted_percentiles_noalloc(values, percentiles=(75.0, 95.0), device: int = 0):
+    """Same result as sorted_percentiles, for hosts that cannot allocate device memory when
+    they need it (all GPU memory already handed to the process's own pool, no room in the
+    latency budget for cudaMalloc's synchronisation, a no-allocation-after-start policy): the
+    operator's scratch is a fixed
+    array inside the library.  At most NOALLOC_MAX_VALUES values; calls must not overlap on
+    one GPU.  (This Python helper still stages `values` in device buffers of its own - only
+    the library call is allocation-free.)"""
+    return _call(_capi.lib().apm_sorted_percentiles_noalloc, device, values, percentiles)

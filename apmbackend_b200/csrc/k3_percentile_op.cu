@@ -2,6 +2,7 @@
 // (util_methods.js:102-106, 112-142) for one array of durations that already sits in device
 // memory - sort ascending (duplicates kept), then apply the reference's index rule.
 #include <mutex>
+#include <string>
 
 #include "ctx.h"
 
@@ -118,9 +119,50 @@ apm_status check_args(const int32_t* d_values, uint32_t n, const double* pcts, i
     return APM_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Scratch for apm_sorted_percentiles_noalloc: a fixed array inside the library image, so the
+// call never has to ask the CUDA allocator for memory.  Every GPU that loads the library
+// carries these bytes until the process exits.  In host code `g_noalloc_scratch` is only a
+// handle for the symbol - it is NOT a device address - so the address each device gave the
+// array is looked up once with cudaGetSymbolAddress and kept here.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kNoAllocMaxValues = APM_NOALLOC_MAX_VALUES;
+constexpr size_t kNoAllocScratchBytes = 2 * ((size_t)kNoAllocMaxValues * 8) + 256 * ((kNoAllocMaxValues + 4095) / 4096) * 4 +
+                                        256 * 4 + 4 + APM_MAX_PCT * 8 + 6 * 256 /* alignment slack */;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+constexpr int kMaxDevices = 64;
+unsigned char* g_noalloc_ptr[kMaxDevices];  // per device ordinal, nullptr until that device's set-up ran
+std::mutex g_noalloc_mutex;
+
 }  // namespace
 
 extern "C" {
+
+apm_status apm_sorted_percentiles_noalloc(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts,
+                                          int32_t npct, double* out_pct, int32_t* d_sorted) {
+    apm_status st = check_args(d_values, n, pcts, npct, out_pct);
+    if (st) return st;
+    if (n > kNoAllocMaxValues)
+        return apm_fail(nullptr, APM_E_CAPACITY,
+                        "apm_sorted_percentiles_noalloc: n exceeds APM_NOALLOC_MAX_VALUES (" + std::to_string(kNoAllocMaxValues) +
+                            "); use apm_sorted_percentiles for larger arrays");
+    if (device < 0 || device >= kMaxDevices) return apm_fail(nullptr, APM_E_INVALID, "apm_sorted_percentiles_noalloc: device ordinal");
+    CUDA_TRY(nullptr, cudaSetDevice(device));
+    unsigned char* scratch;
+    {
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (!g_noalloc_ptr[device]) {
+            // first call on this device: resolve the array's device address (this device is current)
+            void* p = nullptr;
+            CUDA_TRY(nullptr, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            g_noalloc_ptr[device] = (unsigned char*)p;
+        }
+        scratch = g_noalloc_ptr[device];
+    }
+    if (plan_for(n).bytes > kNoAllocScratchBytes) return apm_fail(nullptr, APM_E_CAPACITY, "apm_sorted_percentiles_noalloc: scratch plan exceeds the static array");
+    return run_percentiles(scratch, d_values, n, pcts, npct, out_pct, d_sorted);
+}
 
 apm_status apm_sorted_percentiles(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts, int32_t npct,
                                   double* out_pct, int32_t* d_sorted) {

@@ -246,6 +246,28 @@ double apm_quantize(double x, int32_t digits);
 apm_status apm_sorted_percentiles(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts, int32_t npct,
                                   double* out_pct, int32_t* d_sorted);
 
+/* ---- the same operator for callers that must not allocate.  It has no counterpart in the
+ * reference.  Some hosts of this library cannot call cudaMalloc at the point where they need
+ * a percentile: a stage whose process hands all of the GPU's memory to its own pool at
+ * start-up (a later cudaMalloc would simply fail), a message handler on a latency budget that
+ * cannot absorb the device-wide synchronisation cudaMalloc and cudaFree imply, or a
+ * deployment whose policy forbids device allocations after initialisation.  For them the scratch memory
+ * (two word buffers, histograms, a few scalars; about 4.3 MB) lives in a fixed array inside
+ * the library image, held by every GPU that loads the library until the process exits.
+ *   - n may be at most APM_NOALLOC_MAX_VALUES; larger arrays are refused with APM_E_CAPACITY
+ *     (use apm_sorted_percentiles).
+ *   - the call itself performs no cudaMalloc / cudaFree and calls no allocating library
+ *     routine; inputs (d_values) and outputs (d_sorted on the device, out_pct on the host)
+ *     are the caller's.
+ *   - the first call on each device looks the array's device address up
+ *     (cudaGetSymbolAddress); make that first call before any stream capture starts.
+ *   - all calls share the one array, which keeps the previous call's contents (the call
+ *     clears the single word it accumulates into).  Two calls that overlap on the same GPU
+ *     - from two host threads or processes sharing a context - race on it: serialise them. */
+#define APM_NOALLOC_MAX_VALUES 262144u
+apm_status apm_sorted_percentiles_noalloc(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts,
+                                          int32_t npct, double* out_pct, int32_t* d_sorted);
+
 /* ---- multi-GPU: keys are hash-sharded by the host; each rank owns its keys.
  * The only exchange is an all-gather of the compact alert block per tick. */
 uint32_t apm_owner_of_key(uint64_t global_key, uint32_t nranks);
