@@ -262,6 +262,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     c->keep = cfg->window_buckets + cfg->buffer_buckets;
     c->S = c->keep + 1;
     c->inv_bucket = 1.0 / (double)cfg->bucket_ms;
+    if (const char* e = getenv("APM_K4_LDG")) c->k4_force_ldg = atoi(e) != 0;
     if (const char* e = getenv("APM_K1_TPC")) { int v = atoi(e); if (v > 0) c->k1_tiles_per_cta = (uint32_t)v; }
     // windowSz * intervalLengthSec / 60.0 (stream_calc_stats.js:186)
     c->tpm_div = (double)cfg->window_buckets * ((double)cfg->bucket_ms / 1000.0) / 60.0;
@@ -318,9 +319,11 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
             TRY_CREATE(dalloc(&c->d_alert_count, (size_t)cfg->out_ticks));
             TRY_CREATE(cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * cfg->out_ticks, c->s_main));
         }
+        c->ring_pitch = (3 * K + 31) & ~(size_t)31;
         for (int l = 0; l < cfg->num_lags; ++l) {
             const size_t L = (size_t)cfg->lags[l];
-            TRY_CREATE(dalloc(&c->ring[l], L * 3 * K));
+            TRY_CREATE(dalloc(&c->ring[l], L * c->ring_pitch));
+            TRY_CREATE(cudaMemsetAsync(c->ring[l], 0, L * c->ring_pitch * sizeof(double), c->s_main));
             TRY_CREATE(dalloc(&c->ring_len[l], 3 * K));
             TRY_CREATE(cudaMemsetAsync(c->ring_len[l], 0, sizeof(uint32_t) * 3 * K, c->s_main));
             TRY_CREATE(dalloc(&c->thr[l], K));
@@ -330,6 +333,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
             TRY_CREATE(cudaMemcpy(c->infl[l], f.data(), K * sizeof(double), cudaMemcpyHostToDevice));
         }
     }
+    if (with_z(c)) { st = apm_baseline_make_tmaps(c); if (st) return fail(st); }
     TRY_CREATE(dalloc(&c->d_counters, (size_t)1));
     TRY_CREATE(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->s_main));
     TRY_CREATE(cudaMallocHost((void**)&c->h_counters, sizeof(DevCounters)));
@@ -519,7 +523,7 @@ apm_status apm_ring_load(apm_ctx* c, uint32_t key, int32_t l, int32_t series, co
     const uint32_t L = (uint32_t)c->cfg.lags[l];
     if (len > L) return apm_fail(c, APM_E_INVALID, "ring_load: list longer than its lag");
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-    const size_t ncol = 3 * (size_t)c->K, col = (size_t)series * c->K + key;
+    const size_t ncol = c->ring_pitch, col = (size_t)series * c->K + key;
     const uint32_t head = c->ring_head[l];
     // the list ends just before `head`: element i (oldest first) lives at slot head - len + i
     std::vector<double> tmp(values, values + len);
@@ -537,11 +541,11 @@ apm_status apm_ring_load_all(apm_ctx* c, int32_t l, const double* values, uint32
     const uint32_t L = (uint32_t)c->cfg.lags[l];
     if (len > L) return apm_fail(c, APM_E_INVALID, "ring_load_all: lists longer than the lag");
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-    const size_t ncol = 3 * (size_t)c->K, row = ncol * sizeof(double);
+    const size_t ncol = 3 * (size_t)c->K, row = ncol * sizeof(double), pitch = c->ring_pitch * sizeof(double);
     const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     const uint32_t head = c->ring_head[l], first = (head + L - len) % L, n1 = std::min(len, L - first);
-    if (n1) CUDA_TRY(c, cudaMemcpy(c->ring[l] + (size_t)first * ncol, values, n1 * row, kind));
-    if (len > n1) CUDA_TRY(c, cudaMemcpy(c->ring[l], values + (size_t)n1 * ncol, (len - n1) * row, kind));
+    if (n1) CUDA_TRY(c, cudaMemcpy2D(c->ring[l] + (size_t)first * c->ring_pitch, pitch, values, row, row, n1, kind));
+    if (len > n1) CUDA_TRY(c, cudaMemcpy2D(c->ring[l], pitch, values + (size_t)n1 * ncol, row, row, len - n1, kind));
     std::vector<uint32_t> lens(ncol, len);
     CUDA_TRY(c, cudaMemcpy(c->ring_len[l], lens.data(), ncol * sizeof(uint32_t), cudaMemcpyHostToDevice));
     return APM_OK;
@@ -552,7 +556,7 @@ apm_status apm_ring_read(apm_ctx* c, uint32_t key, int32_t l, int32_t series, do
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || series < 0 || series >= APM_NUM_SERIES || key >= c->K) return apm_fail(c, APM_E_INVALID, "ring_read: index");
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     const uint32_t L = (uint32_t)c->cfg.lags[l];
-    const size_t ncol = 3 * (size_t)c->K, col = (size_t)series * c->K + key;
+    const size_t ncol = c->ring_pitch, col = (size_t)series * c->K + key;
     uint32_t len = 0;
     CUDA_TRY(c, cudaMemcpy(&len, c->ring_len[l] + col, sizeof(uint32_t), cudaMemcpyDeviceToHost));
     *len_out = len;

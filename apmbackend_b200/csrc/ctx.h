@@ -3,6 +3,8 @@
 #include <string>
 #include <vector>
 
+#include <cuda.h>
+
 #include "common.cuh"
 
 struct TickMark {
@@ -61,8 +63,11 @@ struct apm_ctx {
     uint32_t alerts_gather_from = 0;     // first buffered tick not yet all-gathered
 
     // --- rolling baseline
-    double* ring[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};        // [L][3][K]
+    double* ring[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};        // [L][ring_pitch], column = series*K + key
     uint32_t* ring_len[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};  // [3][K]
+    size_t ring_pitch = 0;  // doubles per ring row: 3K rounded up to 32 (TMA box width, 256-byte rows)
+    CUtensorMap ring_tmap[APM_MAX_LAGS];  // 2-D view [L][ring_pitch] of each ring for the bulk-tensor loads
+    bool ring_tmap_ok = false;
     uint32_t ring_head[APM_MAX_LAGS] = {0, 0, 0, 0};                          // slot the next push writes
     double* thr[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};         // [K]
     double* infl[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};        // [K]
@@ -72,6 +77,7 @@ struct apm_ctx {
     apm_counters counters;
     uint64_t launches = 0;
     uint32_t k1_tiles_per_cta = 3;  // tuning knob (APM_K1_TPC)
+    bool k4_force_ldg = false;      // APM_K4_LDG=1: register-pipelined loads instead of TMA (A/B measurements)
 
     // multi-GPU
     void* nccl_comm = nullptr;
@@ -122,6 +128,7 @@ apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask);
 apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot);
 // k4_baseline.cu
 apm_status apm_launch_baseline(apm_ctx* c, int lag_idx, int64_t tick_ts, uint32_t tick_slot);
+apm_status apm_baseline_make_tmaps(apm_ctx* c);
 apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot);
 // comm.cu
 void apm_comm_destroy_internal(apm_ctx* c);

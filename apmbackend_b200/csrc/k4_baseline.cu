@@ -10,6 +10,8 @@
 // serves all keys: a list of length n occupies the n slots before `head`, the push goes to
 // `head`, and a full list is summed head, head+1, ... (oldest first) - the same left-to-right
 // order as Array.prototype.reduce, so the fp64 mean has the same bits as the reference's.
+#include <string>
+
 #include "ctx.h"
 
 namespace {
@@ -26,6 +28,7 @@ struct BaselineParams {
     const uint8_t* seen;   // [K]
     apm_fs_record* fs;     // [K] records of this (tick, lag); nullptr when not retained
     uint32_t K, L, head, lag_value;
+    uint32_t pitch;        // doubles per ring row
     int64_t tick_ts;
     int sd_mode;
 };
@@ -40,8 +43,8 @@ __device__ __forceinline__ void accumulate(double v, double& sum, uint32_t& cnt)
 
 __global__ void __launch_bounds__(K4_THREADS) baseline_kernel(const BaselineParams p) {
     const uint32_t col = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t ncol = 3u * p.K;
-    if (col >= ncol) return;
+    const uint32_t ncol = p.pitch;
+    if (col >= 3u * p.K) return;
     const uint32_t series = col / p.K, key = col - series * p.K;
     const double nan = __longlong_as_double(0x7ff8000000000000ll);
     apm_fs_record* rec = p.fs ? p.fs + key : nullptr;
@@ -144,6 +147,157 @@ __global__ void __launch_bounds__(K4_THREADS) baseline_kernel(const BaselinePara
     }
 }
 
+// ---- the same stage with the ring streamed by TMA --------------------------------------------
+// One warp per CTA owns 32 adjacent columns.  Lane 0 keeps K4T_STAGES bulk-tensor loads
+// (cp.async.bulk.tensor.2d, box = 32 columns x K4T_ROWS slots = 4 KB) in flight into shared
+// memory, each completing on its own mbarrier; the lanes then add their column's values in
+// slot order out of shared memory.  The additions of a column are sequential by definition
+// (that is what makes the mean bit-identical to the reference's), so all the bandwidth comes
+// from the depth of the load pipeline, which TMA provides without spending registers.
+constexpr int K4T_COLS = 32;
+constexpr int K4T_ROWS = 16;
+constexpr int K4T_STAGES = 6;
+constexpr uint32_t K4T_STAGE_BYTES = K4T_COLS * K4T_ROWS * sizeof(double);
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int r0, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(r0), "r"(smem_u32(bar)) : "memory");
+}
+
+struct __align__(128) K4TSmem {
+    double buf[K4T_STAGES][K4T_ROWS][K4T_COLS];
+    uint64_t bar[K4T_STAGES];
+};
+
+__global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant__ CUtensorMap tmap, const BaselineParams p) {
+    __shared__ K4TSmem sm;
+    const int lane = threadIdx.x;
+    const uint32_t col0 = blockIdx.x * K4T_COLS, col = col0 + lane;
+    const bool in_range = col < 3u * p.K;
+    const uint32_t series = in_range ? col / p.K : 0, key = in_range ? col - series * p.K : 0;
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    const bool seen = in_range && p.seen[key];
+    const uint32_t len = seen ? p.ring_len[col] : 0;
+    const bool full = seen && len >= p.L;  // prevValuesList.length >= lag (:75)
+
+    double sum = 0.0, last = nan;
+    uint32_t cnt = 0;
+    if (__any_sync(0xffffffffu, full)) {
+        // oldest first: rows head .. L-1, then 0 .. head-1, in chunks of K4T_ROWS slots
+        const uint32_t nA = (p.L - p.head + K4T_ROWS - 1) / K4T_ROWS, nB = (p.head + K4T_ROWS - 1) / K4T_ROWS;
+        const uint32_t n = nA + nB;
+        auto row0_of = [&](uint32_t c) { return c < nA ? p.head + c * K4T_ROWS : (c - nA) * K4T_ROWS; };
+        auto rows_of = [&](uint32_t c) {
+            const uint32_t r0 = row0_of(c), end = c < nA ? p.L : p.head;
+            return end - r0 < (uint32_t)K4T_ROWS ? end - r0 : (uint32_t)K4T_ROWS;
+        };
+        if (lane == 0) {
+#pragma unroll
+            for (int s = 0; s < K4T_STAGES; ++s) mbar_init(&sm.bar[s], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+        __syncwarp();
+        if (lane == 0) {
+            for (uint32_t c = 0; c < n && c < (uint32_t)K4T_STAGES; ++c) {
+                mbar_expect_tx(&sm.bar[c], K4T_STAGE_BYTES);  // rows past the end are zero-filled but still counted
+                tma_load_2d(&sm.buf[c][0][0], &tmap, (int)col0, (int)row0_of(c), &sm.bar[c]);
+            }
+        }
+        for (uint32_t c = 0; c < n; ++c) {
+            const uint32_t s = c % K4T_STAGES, parity = (c / K4T_STAGES) & 1u;
+            mbar_wait(&sm.bar[s], parity);
+            const uint32_t rows = rows_of(c);
+            if (rows == (uint32_t)K4T_ROWS) {
+                double v[K4T_ROWS];
+#pragma unroll
+                for (int r = 0; r < K4T_ROWS; ++r) v[r] = sm.buf[s][r][lane];
+                if (full) {
+#pragma unroll
+                    for (int r = 0; r < K4T_ROWS; ++r) accumulate(v[r], sum, cnt);
+                }
+                last = v[K4T_ROWS - 1];
+            } else {
+                for (uint32_t r = 0; r < rows; ++r) {
+                    const double v = sm.buf[s][r][lane];
+                    if (full) accumulate(v, sum, cnt);
+                    last = v;
+                }
+            }
+            __syncwarp();  // every lane holds its values in registers: the stage may be overwritten
+            if (lane == 0 && c + K4T_STAGES < n) {
+                mbar_expect_tx(&sm.bar[s], K4T_STAGE_BYTES);
+                tma_load_2d(&sm.buf[s][0][0], &tmap, (int)col0, (int)row0_of(c + K4T_STAGES), &sm.bar[s]);
+            }
+        }
+    }
+    if (!in_range) return;
+    apm_fs_record* rec = p.fs ? p.fs + key : nullptr;
+    if (!seen) {
+        if (rec && series == 0) rec->flags = 0;
+        return;
+    }
+    const double new_value = p.zin[(size_t)(1 + series) * p.K + key];
+    const double threshold = p.thr[key], influence = p.infl[key];
+    double infl_value = new_value, avg = nan, lb = nan, ub = nan;
+    int signal = 0;
+    if (full) {
+        if (cnt > 0) {
+            avg = __ddiv_rn(sum, (double)cnt);
+            // standardDeviation() == sqrt(mean): mean == 0 -> undefined, mean < 0 -> NaN (util_methods.js:41-49)
+            double sd = nan;
+            if (avg != 0.0) sd = __dsqrt_rn(avg);
+            if (sd == sd) {
+                const double band = __dmul_rn(threshold, sd);  // (:80-83), product rounded before the add
+                lb = __dsub_rn(avg, band);
+                ub = __dadd_rn(avg, band);
+                if (new_value == new_value && fabs(__dsub_rn(new_value, avg)) > band) {  // (:87-89) strict
+                    signal = new_value > avg ? 1 : -1;
+                    if (last == last)  // (:96-97)
+                        infl_value = __dadd_rn(__dmul_rn(influence, new_value), __dmul_rn(__dsub_rn(1.0, influence), last));
+                }
+            }
+        }
+    } else {
+        p.ring_len[col] = len + 1;
+    }
+    p.ring[(size_t)p.head * p.pitch + col] = infl_value;  // shift() + push() (:285-306)
+    if (rec) {
+        if (series == 0) {
+            rec->tick_ts = p.tick_ts;
+            rec->key = key;
+            rec->lag = p.lag_value;
+            rec->tpm = p.zin[key];
+            rec->flags = 1;
+            rec->pad_[0] = rec->pad_[1] = rec->pad_[2] = rec->pad_[3] = 0;
+        }
+        rec->val[series] = new_value;
+        rec->avg[series] = avg;
+        rec->lb[series] = lb;
+        rec->ub[series] = ub;
+        rec->signal[series] = (int8_t)signal;
+    }
+}
+
 // Copies the fs records that carry a signal into the tick's compact alert block.
 __global__ void __launch_bounds__(256) compact_alerts_kernel(const apm_fs_record* __restrict__ fs, uint32_t n,
                                                              apm_fs_record* __restrict__ alerts,
@@ -165,6 +319,30 @@ __global__ void __launch_bounds__(256) compact_alerts_kernel(const apm_fs_record
 
 }  // namespace
 
+apm_status apm_baseline_make_tmaps(apm_ctx* c) {
+    c->ring_tmap_ok = false;
+    typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn ||
+        qres != cudaDriverEntryPointSuccess)
+        return apm_fail(c, APM_E_DEVICE, "cuTensorMapEncodeTiled is not available in this driver");
+    for (int l = 0; l < c->cfg.num_lags; ++l) {
+        const cuuint64_t gdim[2] = {(cuuint64_t)c->ring_pitch, (cuuint64_t)c->cfg.lags[l]};
+        const cuuint64_t gstride[1] = {(cuuint64_t)(c->ring_pitch * sizeof(double))};
+        const cuuint32_t box[2] = {K4T_COLS, K4T_ROWS};
+        const cuuint32_t estr[2] = {1, 1};
+        CUresult r = ((EncodeTiled)fn)(&c->ring_tmap[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, c->ring[l], gdim, gstride, box, estr,
+                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return apm_fail(c, APM_E_DEVICE, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    }
+    c->ring_tmap_ok = true;
+    return APM_OK;
+}
+
 apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick_slot) {
     ProfScope prof_scope_(c, APM_PG_BASELINE);
     BaselineParams p;
@@ -172,10 +350,15 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
     p.seen = c->seen;
     p.fs = c->d_fs ? c->d_fs + ((size_t)tick_slot * c->cfg.num_lags + l) * c->K : nullptr;
     p.K = c->K; p.L = (uint32_t)c->cfg.lags[l]; p.head = c->ring_head[l]; p.lag_value = (uint32_t)c->cfg.lags[l];
+    p.pitch = (uint32_t)c->ring_pitch;
     p.tick_ts = tick_ts;
     p.sd_mode = c->cfg.sd_mode;
     const uint32_t ncol = 3u * c->K;
-    baseline_kernel<<<(ncol + K4_THREADS - 1) / K4_THREADS, K4_THREADS, 0, c->s_main>>>(p);
+    if (c->ring_tmap_ok && c->cfg.sd_mode == APM_SD_REFERENCE && !c->k4_force_ldg) {
+        baseline_tma_kernel<<<(ncol + K4T_COLS - 1) / K4T_COLS, 32, 0, c->s_main>>>(c->ring_tmap[l], p);
+    } else {
+        baseline_kernel<<<(ncol + K4_THREADS - 1) / K4_THREADS, K4_THREADS, 0, c->s_main>>>(p);
+    }
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
     c->ring_head[l] = (c->ring_head[l] + 1) % p.L;

@@ -80,7 +80,7 @@ apm_status apm_state_save(apm_ctx* c, const char* path) {
         for (int s = 0; s < c->S && ok; ++s) ok = put(fl.f, c->log_buf[s], h.log_count[s] * sizeof(uint64_t), tmp);
     if (rings)
         for (int l = 0; l < c->cfg.num_lags && ok; ++l) {
-            ok = put(fl.f, c->ring[l], sizeof(double) * (size_t)c->cfg.lags[l] * 3 * c->K, tmp);
+            ok = put(fl.f, c->ring[l], sizeof(double) * (size_t)c->cfg.lags[l] * c->ring_pitch, tmp);
             ok = ok && put(fl.f, c->ring_len[l], sizeof(uint32_t) * 3 * c->K, tmp);
             ok = ok && put(fl.f, c->thr[l], sizeof(double) * c->K, tmp);
             ok = ok && put(fl.f, c->infl[l], sizeof(double) * c->K, tmp);
@@ -115,7 +115,7 @@ apm_status apm_state_load(apm_ctx* c, const char* path) {
         for (int s = 0; s < c->S && ok; ++s) ok = get(fl.f, c->log_buf[s], h.log_count[s] * sizeof(uint64_t), tmp);
     if (rings)
         for (int l = 0; l < c->cfg.num_lags && ok; ++l) {
-            ok = get(fl.f, c->ring[l], sizeof(double) * (size_t)c->cfg.lags[l] * 3 * c->K, tmp);
+            ok = get(fl.f, c->ring[l], sizeof(double) * (size_t)c->cfg.lags[l] * c->ring_pitch, tmp);
             ok = ok && get(fl.f, c->ring_len[l], sizeof(uint32_t) * 3 * c->K, tmp);
             ok = ok && get(fl.f, c->thr[l], sizeof(double) * c->K, tmp);
             ok = ok && get(fl.f, c->infl[l], sizeof(double) * c->K, tmp);
