@@ -126,6 +126,8 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
             if (m.count != m.sorted) {
                 st = apm_sort_slot_n(c, slot, m.count, max_value);
                 if (st) return st;
+                st = apm_acc_from_sorted(c, slot, m.count);  // count / sum / sum of squares / min / max from the runs
+                if (st) return st;
                 m.sorted = m.count;
                 CUDA_TRY(c, cudaMemcpyAsync(&c->slot_meta[slot].sorted, &m.sorted, sizeof(m.sorted), cudaMemcpyHostToDevice, c->s_main));
             }

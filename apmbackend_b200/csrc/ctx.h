@@ -122,6 +122,7 @@ apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value)
 uint64_t* apm_radix_sort_words(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t n, uint32_t* hist, uint32_t* totals,
                                int vbits, int kbits, uint64_t* launches);
 uint64_t apm_radix_sort_tiles(uint64_t n);
+apm_status apm_acc_from_sorted(apm_ctx* c, int slot, uint64_t n);
 int apm_bits_of(uint64_t v);
 // k2_tick.cu
 apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask);

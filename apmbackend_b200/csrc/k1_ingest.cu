@@ -207,7 +207,6 @@ __device__ __forceinline__ void k1_global_update(const ReduceParams& p, int slot
     atomicAdd(&p.acc.sq_lo[ai], sq & 0xFFFFFFFFull);
     if (sq >> 32) atomicAdd(&p.acc.sq_hi[ai], sq >> 32);
     k1_minmax_global(p.acc, ai, v, v);
-    p.seen[key] = 1;
 }
 
 __device__ __forceinline__ void k1_table_init(K1Smem& sm, int tid) {
@@ -228,15 +227,15 @@ __device__ __forceinline__ void k1_table_flush(const ReduceParams& p, K1Smem& sm
         atomicAdd(&p.acc.sq_lo[ai], (unsigned long long)sm.sq_lo[i]);
         if (ch & 0xFFFFu) atomicAdd(&p.acc.sq_hi[ai], (unsigned long long)(ch & 0xFFFFu));
         k1_minmax_global(p.acc, ai, sm.mn[i], sm.mx[i]);
-        p.seen[k] = 1;
     }
 }
 
+template <bool TABLE>
 __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReduceParams p) {
     extern __shared__ __align__(16) unsigned char k1_raw[];
     K1Smem& sm = *reinterpret_cast<K1Smem*>(k1_raw);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    k1_table_init(sm, tid);
+    if (TABLE) k1_table_init(sm, tid);
     if (tid < 5) sm.c[tid] = 0;
     if (tid == 0) sm.vmax = 0;
     __syncthreads();
@@ -247,7 +246,7 @@ __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReducePa
     int tiles_since_flush = 0;
 
     for (uint32_t tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
-        if (tiles_since_flush == K1_FLUSH_TILES) {
+        if (TABLE && tiles_since_flush == K1_FLUSH_TILES) {
             __syncthreads();
             k1_table_flush(p, sm, tid);
             __syncthreads();
@@ -293,14 +292,18 @@ __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReducePa
             if (svc[j] >= p.num_services || jvm[j] >= p.num_jvms || el[j] < 0 || ts[j] < 0) { n_inv++; continue; }
             const int64_t lab = apm_label(ts[j], p.bucket_ms, p.inv_bucket);
             if (lab > p.latest) { n_fut++; continue; }
+            const uint32_t k = jvm[j] * p.num_services + svc[j];
+            // addData creates the (server, service) entry whatever the bucket's age (:125-126):
+            // the key is emitted from now on even if this transaction is too old to count
+            if (!p.seen[k]) p.seen[k] = 1;
             if (lab < p.latest - p.keep) { n_drop++; continue; }
             const int sl = (int)(lab % p.S);
-            const uint32_t k = jvm[j] * p.num_services + svc[j];
             const uint32_t v = (uint32_t)el[j];
             slot[j] = sl;
             key[j] = k;
             n_ing++;
             my_max = v > my_max ? v : my_max;
+            if (!TABLE) continue;  // percentile mode: the accumulators are rebuilt from the sorted log
             bool done = false;
             if (v < 65536u) {
                 const uint32_t tag = ((uint32_t)sl << K1_SLOT_SHIFT) | k;
@@ -380,7 +383,7 @@ __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReducePa
     }
 
     __syncthreads();
-    k1_table_flush(p, sm, tid);
+    if (TABLE) k1_table_flush(p, sm, tid);
     my_max = __reduce_max_sync(0xffffffffu, my_max);
     if (lane == 0 && my_max) atomicMax(&sm.vmax, my_max);
     if (n_ing) atomicAdd(&sm.c[0], n_ing);
@@ -455,10 +458,17 @@ apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin
     if (blocks < 1) blocks = 1;
     static bool attr_set = false;
     if (!attr_set) {
-        CUDA_TRY(c, cudaFuncSetAttribute(reduce_kernel_v3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem)));
+        CUDA_TRY(c, cudaFuncSetAttribute(reduce_kernel_v3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem)));
+        CUDA_TRY(c, cudaFuncSetAttribute(reduce_kernel_v3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem)));
         attr_set = true;
     }
-    reduce_kernel_v3<<<(unsigned)blocks, K1_THREADS, sizeof(K1Smem), c->s_main>>>(p);
+    if (p.with_log) {
+        // append-only: no per-CTA table to flush, so spread the tiles over every SM
+        uint64_t b2 = tiles < max_blocks ? tiles : max_blocks;
+        reduce_kernel_v3<false><<<(unsigned)b2, K1_THREADS, sizeof(K1Smem), c->s_main>>>(p);
+    } else {
+        reduce_kernel_v3<true><<<(unsigned)blocks, K1_THREADS, sizeof(K1Smem), c->s_main>>>(p);
+    }
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;

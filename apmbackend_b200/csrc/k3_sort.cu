@@ -183,6 +183,103 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint64_t* 
     }
 }
 
+// ---- accumulator planes of one bucket slot from its sorted log ----------------------------------
+// After the sort every key's values are one ascending run, so count / sum / sum of squares are
+// a segmented reduction over contiguous words and min / max are the run's first and last
+// value: no contended atomics at all.  Each thread walks 8 consecutive words; a warp whose
+// 256 words all belong to one key (the Zipf-hot keys) combines with shuffles and emits once.
+constexpr int AS_THREADS = 256;
+constexpr int AS_ITEMS = 8;
+
+struct Partial {
+    uint32_t cnt;
+    unsigned long long sum, sq_lo, sq_hi;
+};
+
+__device__ __forceinline__ void as_emit(const AccSoA& acc, size_t base, uint32_t key, const Partial& a) {
+    const size_t ai = base + key;
+    atomicAdd(&acc.cnt[ai], a.cnt);
+    atomicAdd(&acc.sum[ai], a.sum);
+    atomicAdd(&acc.sq_lo[ai], a.sq_lo);
+    if (a.sq_hi) atomicAdd(&acc.sq_hi[ai], a.sq_hi);
+}
+
+__global__ void __launch_bounds__(AS_THREADS) acc_from_sorted_kernel(const uint64_t* __restrict__ w, uint64_t n, const AccSoA acc,
+                                                                    uint32_t K, int slot) {
+    const size_t base = (size_t)slot * K;
+    const uint64_t i0 = ((uint64_t)blockIdx.x * AS_THREADS + threadIdx.x) * AS_ITEMS;
+    const bool any = i0 < n;
+    uint64_t x[AS_ITEMS];
+#pragma unroll
+    for (int j = 0; j < AS_ITEMS; ++j) x[j] = (i0 + j < n) ? __ldcs(w + i0 + j) : ~0ull;
+    const uint32_t cnt_here = any ? (uint32_t)((n - i0) < (uint64_t)AS_ITEMS ? (n - i0) : AS_ITEMS) : 0;
+    uint32_t first_key = 0xFFFFFFFFu, last_key = 0xFFFFFFFFu;
+    bool single = false;
+    Partial run = {0, 0, 0, 0};
+    if (any) {
+        first_key = (uint32_t)(x[0] >> 32);
+        last_key = (uint32_t)(x[cnt_here - 1] >> 32);
+        single = first_key == last_key && cnt_here == AS_ITEMS;
+        // run boundaries against the neighbouring words: first value of a run is its minimum, last its maximum
+        const uint32_t prev_key = i0 ? (uint32_t)(__ldg(w + i0 - 1) >> 32) : 0xFFFFFFFFu;
+        const uint32_t next_key = (i0 + cnt_here < n) ? (uint32_t)(__ldg(w + i0 + cnt_here) >> 32) : 0xFFFFFFFFu;
+        uint32_t pk = prev_key;
+#pragma unroll
+        for (int j = 0; j < AS_ITEMS; ++j) {
+            if ((uint32_t)j < cnt_here) {
+                const uint32_t k = (uint32_t)(x[j] >> 32), v = (uint32_t)x[j];
+                const uint32_t nk = ((uint32_t)(j + 1) < cnt_here) ? (uint32_t)(x[(j + 1) % AS_ITEMS] >> 32) : next_key;
+                if (k != pk || (i0 + j) == 0) acc.vmin[base + k] = v;
+                if (k != nk) acc.vmax[base + k] = v;
+                pk = k;
+            }
+        }
+    }
+    // hot-key fast path: the whole warp holds one key
+    const uint32_t k0 = __shfl_sync(0xffffffffu, first_key, 0);
+    if (__all_sync(0xffffffffu, single && first_key == k0)) {
+        Partial a = {AS_ITEMS, 0, 0, 0};
+#pragma unroll
+        for (int j = 0; j < AS_ITEMS; ++j) {
+            const unsigned long long v = (uint32_t)x[j], sq = v * v;
+            a.sum += v; a.sq_lo += sq & 0xFFFFFFFFull; a.sq_hi += sq >> 32;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a.cnt += __shfl_xor_sync(0xffffffffu, a.cnt, o);
+            a.sum += __shfl_xor_sync(0xffffffffu, a.sum, o);
+            a.sq_lo += __shfl_xor_sync(0xffffffffu, a.sq_lo, o);
+            a.sq_hi += __shfl_xor_sync(0xffffffffu, a.sq_hi, o);
+        }
+        if ((threadIdx.x & 31) == 0) as_emit(acc, base, k0, a);
+        return;
+    }
+    if (!any) return;
+    uint32_t cur = first_key;
+#pragma unroll
+    for (int j = 0; j < AS_ITEMS; ++j) {
+        if ((uint32_t)j < cnt_here) {
+            const uint32_t k = (uint32_t)(x[j] >> 32);
+            if (k != cur) {
+                as_emit(acc, base, cur, run);
+                run = {0, 0, 0, 0};
+                cur = k;
+            }
+            const unsigned long long v = (uint32_t)x[j], sq = v * v;
+            run.cnt += 1; run.sum += v; run.sq_lo += sq & 0xFFFFFFFFull; run.sq_hi += sq >> 32;
+        }
+    }
+    as_emit(acc, base, cur, run);
+}
+
+__global__ void __launch_bounds__(256) clear_planes_kernel(const AccSoA acc, uint32_t K, int slot) {
+    const size_t base = (size_t)slot * K;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)K; i += (size_t)gridDim.x * blockDim.x) {
+        acc.sum[base + i] = 0; acc.sq_lo[base + i] = 0; acc.sq_hi[base + i] = 0;
+        acc.cnt[base + i] = 0; acc.vmin[base + i] = 0xFFFFFFFFu; acc.vmax[base + i] = 0;
+    }
+}
+
 int bits_of(uint64_t v) {
     int b = 0;
     while (v) { ++b; v >>= 1; }
@@ -233,5 +330,21 @@ apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value)
         CUDA_TRY(c, cudaMemcpyAsync(c->d_log_ptrs + slot, &c->log_buf[slot], sizeof(uint64_t*), cudaMemcpyHostToDevice,
                                     c->s_main));
     }
+    return APM_OK;
+}
+
+// Rebuilds the accumulator planes of `slot` from its sorted log of n words.
+apm_status apm_acc_from_sorted(apm_ctx* c, int slot, uint64_t n) {
+    ProfScope prof_scope_(c, APM_PG_REDUCE);
+    unsigned g = (c->K + 255) / 256;
+    clear_planes_kernel<<<g < 592 ? g : 592, 256, 0, c->s_main>>>(c->acc, c->K, slot);
+    c->launches += 1;
+    if (n) {
+        const uint64_t per_block = (uint64_t)AS_THREADS * AS_ITEMS;
+        acc_from_sorted_kernel<<<(unsigned)((n + per_block - 1) / per_block), AS_THREADS, 0, c->s_main>>>(c->log_buf[slot], n, c->acc,
+                                                                                                      c->K, slot);
+        c->launches += 1;
+    }
+    CUDA_TRY(c, cudaGetLastError());
     return APM_OK;
 }

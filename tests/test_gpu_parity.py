@@ -46,6 +46,29 @@ def test_unsorted_and_late_arrivals():
     assert_fs_equal(fs, orc.fs())
 
 
+def test_key_first_seen_through_a_too_old_transaction_is_still_emitted():
+    """addData creates the (server, service) entry whatever the bucket's age
+    (stream_calc_stats.js:125-126): such a key is emitted with an empty window from then on."""
+    c = dict(CASES[1])
+    svc, jvm, ts, el = stream_for(c)
+    n = svc.size
+    mid = n // 2
+    svc = svc.copy(); ts = ts.copy()
+    new_key = c["S"] - 1
+    keep = svc != new_key                       # the key appears nowhere else ...
+    svc, jvm, ts, el = svc[keep], jvm[keep], ts[keep], el[keep]
+    mid = svc.size // 2
+    svc = np.insert(svc, mid, new_key); jvm = np.insert(jvm, mid, 0)
+    ts = np.insert(ts, mid, ts[mid] - 50 * c["bucket_ms"])  # ... except once, far older than the retained buckets
+    el = np.insert(el, mid, 7)
+    eng, orc, st, fs = run_both(c, (svc, jvm, ts, el))
+    assert_stats_equal(st, orc.stats())
+    assert_fs_equal(fs, orc.fs())
+    rows = st[st["key"] == new_key]
+    assert rows.size > 0 and np.all(rows["count"] == 0)
+    assert eng.counters().tx_dropped >= 1
+
+
 def test_empty_and_tiny_inputs():
     c = dict(CASES[0])
     z = np.zeros(0, dtype=np.int64)
