@@ -1,0 +1,100 @@
+"""Multi-rank host logic on CPU (gloo, world_size 2): key-hash partition, global ticks and the
+alert gather.  The per-rank arithmetic is stood in for by the oracle here - the GPU ranks are
+exercised by bench.py --gpus N on the box; what is checked is that sharded results, gathered,
+equal the unsharded run."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from apmbackend_b200 import _capi, sharding
+from oracle import capi as ocapi
+from tests.streams import make_stream
+
+CFG = dict(S=12, J=2, bucket_ms=10000, window=3, buffer=1, lags=(6, 15), thr=(1.5, 2.5), infl=(0.3, 0.0),
+           pcts=(75.0, 95.0))
+
+
+def _pipeline():
+    return ocapi.Pipeline(ocapi.make_config(CFG["S"], CFG["J"], CFG["bucket_ms"], CFG["window"], CFG["buffer"],
+                                            CFG["pcts"], (0, 1), CFG["lags"], CFG["thr"], CFG["infl"]), fast=True)
+
+
+def _stream():
+    return make_stream(31, 6000, CFG["S"], CFG["J"], CFG["bucket_ms"], 120, shift_services=(0, 1, 2, 3))
+
+
+def test_owner_function_matches_the_c_abi():
+    lib = _capi.lib()
+    keys = np.arange(5000, dtype=np.uint64) * 7919
+    for n in (1, 2, 3, 8):
+        want = np.array([lib.apm_owner_of_key(int(k), n) for k in keys], dtype=np.uint32)
+        assert np.array_equal(sharding.owner_of_keys(keys, n), want)
+
+
+def test_partition_is_a_disjoint_cover_in_arrival_order():
+    svc, jvm, ts, el = _stream()
+    parts = sharding.partition_columns(svc, jvm, ts, el, CFG["S"], 4)
+    assert sum(p[0].size for p in parts) == svc.size
+    seen = set()
+    for p in parts:
+        keys = set((p[1].astype(np.int64) * CFG["S"] + p[0]).tolist())
+        assert not (keys & seen)
+        seen |= keys
+        assert np.all(np.diff(np.flatnonzero(np.isin(ts, p[2]))) >= 0)
+
+
+def _run_rank(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    svc, jvm, ts, el = _stream()
+    mine = sharding.partition_columns(svc, jvm, ts, el, CFG["S"], world)[rank]
+    # ticks are global: replay the whole stream's tick positions, feeding only this rank's keys
+    keep = np.zeros(CFG["S"] * CFG["J"], np.uint8)
+    keys = np.arange(CFG["S"] * CFG["J"], dtype=np.uint64)
+    keep[sharding.owner_of_keys(keys, world) == rank] = 1
+    p = _pipeline()
+    p.set_filter(keep)
+    p.consume(svc, jvm, ts, el)
+    fs = p.fs()
+    alerts = fs[np.abs(fs["signal"]).sum(axis=1) > 0]
+    assert mine[0].size == p.ingested
+    gathered = [None] * world
+    dist.all_gather_object(gathered, alerts.tobytes())
+    merged = sharding.merge_alerts([np.frombuffer(b, dtype=ocapi.FS_DTYPE) for b in gathered])
+    if rank == 0:
+        q.put(merged.tobytes())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_ranks_gathered_alerts_equal_the_single_rank_run():
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_run_rank, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = np.frombuffer(q.get(timeout=120), dtype=ocapi.FS_DTYPE)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    full = _pipeline()
+    svc, jvm, ts, el = _stream()
+    full.consume(svc, jvm, ts, el)
+    fs = full.fs()
+    want = fs[np.abs(fs["signal"]).sum(axis=1) > 0]
+    assert want.size > 0 and got.size == want.size
+    key = lambda a: a[np.lexsort((a["key"], a["lag"], a["tick_ts"]))]  # noqa: E731
+    assert key(got).tobytes() == key(want).tobytes()
+
+
+def test_global_tick_labels():
+    svc, jvm, ts, el = _stream()
+    labs = sharding.tick_labels(ts, CFG["bucket_ms"])
+    p = _pipeline()
+    p.consume(svc, jvm, ts, el)
+    assert labs.size == p.ticks and labs[-1] == p.latest
