@@ -67,12 +67,21 @@ apm_status validate(const apm_config* cfg) {
     return APM_OK;
 }
 
+// waits for everything queued on the context (ingest/sort stream, baseline stream, copies)
+apm_status sync_all(apm_ctx* c) {
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
+    return APM_OK;
+}
+
 bool with_pct(const apm_ctx* c) { return (c->cfg.flags & APM_F_PERCENTILES) && c->cfg.num_percentiles > 0; }
 bool with_z(const apm_ctx* c) { return (c->cfg.flags & APM_F_ZSCORE) && c->cfg.num_lags > 0; }
 
 apm_status refresh_counters(apm_ctx* c) {
     CUDA_TRY(c, cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->s_main));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     c->counters.tx_ingested = c->h_counters->ingested;
     c->counters.tx_dropped = c->h_counters->dropped;
     c->counters.tx_invalid = c->h_counters->invalid + c->h_counters->future;
@@ -135,18 +144,29 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
     }
     const int64_t tick_ts = (new_latest - c->cfg.buffer_buckets - 1) * c->cfg.bucket_ms;  // edgeTs (:356)
     const uint32_t tslot = keep_any ? c->ticks_buffered : 0;
-    st = apm_launch_tick_stats(c, w, tick_ts, (c->cfg.flags & APM_F_KEEP_STATS) ? tslot : 0);
+    const uint64_t seq = c->tick_seq++;
+    const int buf = (int)(seq & 1), ev = (int)(seq & 3);
+    cudaStream_t sb = c->overlap ? c->s_base : c->s_main;
+    // the window kernel overwrites zin/emit[buf], last read by the baseline of two ticks ago
+    if (c->overlap && with_z(c) && seq >= 2) CUDA_TRY(c, cudaStreamWaitEvent(c->s_main, c->ev_base[(seq - 2) & 3], 0));
+    st = apm_launch_tick_stats(c, w, tick_ts, (c->cfg.flags & APM_F_KEEP_STATS) ? tslot : 0, buf);
     if (st) return st;
     if (with_z(c)) {
+        // the baseline of this tick runs on its own stream, under the ingest / sort of the next tick
+        if (c->overlap) {
+            CUDA_TRY(c, cudaEventRecord(c->ev_stats[ev], c->s_main));
+            CUDA_TRY(c, cudaStreamWaitEvent(sb, c->ev_stats[ev], 0));
+        }
         const uint32_t fslot = (c->cfg.flags & APM_F_KEEP_FS) ? tslot : 0;
         for (int l = 0; l < c->cfg.num_lags; ++l) {  // Object.entries(lags): ascending (:217)
-            st = apm_launch_baseline(c, l, tick_ts, fslot);
+            st = apm_launch_baseline(c, l, tick_ts, fslot, buf, sb);
             if (st) return st;
         }
         if (c->cfg.flags & APM_F_ALERTS) {
-            st = apm_launch_compact_alerts(c, fslot, tslot);
+            st = apm_launch_compact_alerts(c, fslot, tslot, sb);
             if (st) return st;
         }
+        if (c->overlap) CUDA_TRY(c, cudaEventRecord(c->ev_base[ev], sb));
     }
     if (keep_any) c->ticks_buffered++;
     c->counters.ticks++;
@@ -184,6 +204,7 @@ static apm_status fetch_dense(apm_ctx* c, const R* d_src, size_t per_tick, R* ou
     if (total == 0) return APM_OK;
     if (cap < total) return apm_fail(c, APM_E_CAPACITY, "output buffer smaller than ticks_buffered * records per tick");
     CUDA_TRY(c, cudaMemcpyAsync(out, d_src, total * sizeof(R), cudaMemcpyDeviceToHost, c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     c->counters.d2h_bytes += total * sizeof(R);
     size_t w = 0;
@@ -224,6 +245,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     if (c->s_main) cudaStreamSynchronize(c->s_main);
+    if (c->s_base) cudaStreamSynchronize(c->s_base);
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
     cudaFree(c->acc_raw); cudaFree(c->seen); cudaFree(c->slot_meta);
     for (int i = 0; i <= c->S && i <= APM_MAX_SLOTS; ++i) cudaFree(c->log_buf[i]);
@@ -232,10 +254,12 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFreeHost(c->h_ticks); cudaFreeHost(c->h_nticks);
     cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
     free_columns_device(&c->dev[0]); free_columns_device(&c->dev[1]);
-    cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->zin);
+    cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
     for (int l = 0; l < APM_MAX_LAGS; ++l) { cudaFree(c->ring[l]); cudaFree(c->ring_len[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
     cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->d_gather);
     for (int i = 0; i < 2; ++i) { if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); if (c->ev_consumed[i]) cudaEventDestroy(c->ev_consumed[i]); }
+    for (int i = 0; i < 4; ++i) { if (c->ev_stats[i]) cudaEventDestroy(c->ev_stats[i]); if (c->ev_base[i]) cudaEventDestroy(c->ev_base[i]); }
+    if (c->s_base) cudaStreamDestroy(c->s_base);
     if (c->s_main) cudaStreamDestroy(c->s_main);
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
     apm_comm_destroy_internal(c);
@@ -264,6 +288,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     c->keep = cfg->window_buckets + cfg->buffer_buckets;
     c->S = c->keep + 1;
     c->inv_bucket = 1.0 / (double)cfg->bucket_ms;
+    if (const char* e = getenv("APM_K4_STAGES")) c->k4_stages = atoi(e);
     if (const char* e = getenv("APM_K4_LDG")) c->k4_force_ldg = atoi(e) != 0;
     if (const char* e = getenv("APM_K1_TPC")) { int v = atoi(e); if (v > 0) c->k1_tiles_per_cta = (uint32_t)v; }
     // windowSz * intervalLengthSec / 60.0 (stream_calc_stats.js:186)
@@ -272,8 +297,19 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     auto fail = [&](apm_status s) { g_create_error = c->err; apm_ctx_destroy(c); return s; };
 #define TRY_CREATE(expr) do { cudaError_t e2_ = (expr); if (e2_ != cudaSuccess) { apm_fail_cuda(c, e2_, #expr, __FILE__, __LINE__); return fail(APM_E_DEVICE); } } while (0)
     TRY_CREATE(cudaSetDevice(cfg->device));
-    TRY_CREATE(cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking));
-    TRY_CREATE(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
+    {
+        // the ingest / sort chain is the latency-critical one: its CTAs go first when both streams have work
+        int prio_lo = 0, prio_hi = 0;
+        TRY_CREATE(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        TRY_CREATE(cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_hi));
+        TRY_CREATE(cudaStreamCreateWithPriority(&c->s_copy, cudaStreamNonBlocking, prio_hi));
+        TRY_CREATE(cudaStreamCreateWithPriority(&c->s_base, cudaStreamNonBlocking, prio_lo));
+    }
+    for (int i = 0; i < 4; ++i) {
+        TRY_CREATE(cudaEventCreateWithFlags(&c->ev_stats[i], cudaEventDisableTiming));
+        TRY_CREATE(cudaEventCreateWithFlags(&c->ev_base[i], cudaEventDisableTiming));
+    }
+    if (const char* e = getenv("APM_NO_OVERLAP")) c->overlap = atoi(e) == 0;
     for (int i = 0; i < 2; ++i) {
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_consumed[i], cudaEventDisableTiming));
@@ -310,7 +346,11 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     TRY_CREATE(dalloc(&c->d_nticks, (size_t)1));
     TRY_CREATE(cudaMallocHost((void**)&c->h_ticks, sizeof(TickMark) * c->max_ticks_per_chunk));
     TRY_CREATE(cudaMallocHost((void**)&c->h_nticks, sizeof(unsigned int)));
-    TRY_CREATE(dalloc(&c->zin, 4 * K));
+    for (int i = 0; i < 2; ++i) {
+        TRY_CREATE(dalloc(&c->zin[i], 4 * K));
+        TRY_CREATE(dalloc(&c->emit[i], K));
+        TRY_CREATE(cudaMemsetAsync(c->emit[i], 0, K, c->s_main));
+    }
     if (cfg->flags & APM_F_KEEP_STATS) TRY_CREATE(dalloc(&c->d_stats, (size_t)cfg->out_ticks * K));
     if (with_z(c)) {
         const size_t fs_ticks = (cfg->flags & APM_F_KEEP_FS) ? cfg->out_ticks : 1;
@@ -355,9 +395,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
 
 apm_status apm_sync(apm_ctx* c) {
     if (!c) return APM_E_INVALID;
-    CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
-    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-    return APM_OK;
+    return sync_all(c);
 }
 
 apm_status apm_ingest_acquire(apm_ctx* c, uint64_t n, apm_tx_columns* out) {
@@ -454,6 +492,7 @@ apm_status apm_process_host(apm_ctx* c, const apm_tx_columns* h, uint64_t n, apm
 apm_status apm_set_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, int32_t l, const double* thr, const double* infl) {
     if (!c || !thr || !infl) return APM_E_INVALID;
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || (uint64_t)key_lo + n > c->K) return apm_fail(c, APM_E_INVALID, "set_key_params: range");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     CUDA_TRY(c, cudaMemcpy(c->thr[l] + key_lo, thr, n * sizeof(double), cudaMemcpyHostToDevice));
     CUDA_TRY(c, cudaMemcpy(c->infl[l] + key_lo, infl, n * sizeof(double), cudaMemcpyHostToDevice));
@@ -463,7 +502,9 @@ apm_status apm_set_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, int32_t l
 apm_status apm_drop_lag(apm_ctx* c, int32_t l) {
     if (!c) return APM_E_INVALID;
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags) return apm_fail(c, APM_E_INVALID, "drop_lag: index");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaMemsetAsync(c->ring_len[l], 0, sizeof(uint32_t) * 3 * c->K, c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     return APM_OK;
 }
 
@@ -490,6 +531,7 @@ apm_status apm_fetch_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64
     if (c->ticks_buffered == 0) return APM_OK;
     std::vector<unsigned int> counts(c->ticks_buffered);
     CUDA_TRY(c, cudaMemcpyAsync(counts.data(), c->d_alert_count, sizeof(unsigned int) * c->ticks_buffered, cudaMemcpyDeviceToHost, c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     uint64_t total = 0;
     for (unsigned int k : counts) {
@@ -514,7 +556,11 @@ apm_status apm_fetch_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64
 
 apm_status apm_release_ticks(apm_ctx* c) {
     if (!c) return APM_E_INVALID;
-    if (c->d_alert_count) CUDA_TRY(c, cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * c->cfg.out_ticks, c->s_main));
+    if (c->d_alert_count) {
+        CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
+        CUDA_TRY(c, cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * c->cfg.out_ticks, c->s_main));
+        CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    }
     c->ticks_buffered = 0;
     return APM_OK;
 }
@@ -524,6 +570,7 @@ apm_status apm_ring_load(apm_ctx* c, uint32_t key, int32_t l, int32_t series, co
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || series < 0 || series >= APM_NUM_SERIES || key >= c->K) return apm_fail(c, APM_E_INVALID, "ring_load: index");
     const uint32_t L = (uint32_t)c->cfg.lags[l];
     if (len > L) return apm_fail(c, APM_E_INVALID, "ring_load: list longer than its lag");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     const size_t ncol = c->ring_pitch, col = (size_t)series * c->K + key;
     const uint32_t head = c->ring_head[l];
@@ -542,6 +589,7 @@ apm_status apm_ring_load_all(apm_ctx* c, int32_t l, const double* values, uint32
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags) return apm_fail(c, APM_E_INVALID, "ring_load_all: index");
     const uint32_t L = (uint32_t)c->cfg.lags[l];
     if (len > L) return apm_fail(c, APM_E_INVALID, "ring_load_all: lists longer than the lag");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     const size_t ncol = 3 * (size_t)c->K, row = ncol * sizeof(double), pitch = c->ring_pitch * sizeof(double);
     const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
@@ -556,6 +604,7 @@ apm_status apm_ring_load_all(apm_ctx* c, int32_t l, const double* values, uint32
 apm_status apm_ring_read(apm_ctx* c, uint32_t key, int32_t l, int32_t series, double* values, uint32_t cap, uint32_t* len_out) {
     if (!c || !len_out) return APM_E_INVALID;
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || series < 0 || series >= APM_NUM_SERIES || key >= c->K) return apm_fail(c, APM_E_INVALID, "ring_read: index");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     const uint32_t L = (uint32_t)c->cfg.lags[l];
     const size_t ncol = c->ring_pitch, col = (size_t)series * c->K + key;
@@ -609,6 +658,7 @@ extern "C" apm_status apm_timer_start(apm_ctx* c) {
     if (!c) return APM_E_INVALID;
     if (!c->timer[0]) { CUDA_TRY(c, cudaEventCreate(&c->timer[0])); CUDA_TRY(c, cudaEventCreate(&c->timer[1])); }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaEventRecord(c->timer[0], c->s_main));
     return APM_OK;
 }
@@ -617,6 +667,7 @@ extern "C" apm_status apm_timer_stop(apm_ctx* c, double* ms) {
     if (!c || !ms) return APM_E_INVALID;
     if (!c->timer[0]) return apm_fail(c, APM_E_STATE, "timer_stop without timer_start");
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));  // the stop event on s_main then follows all work of both streams
     CUDA_TRY(c, cudaEventRecord(c->timer[1], c->s_main));
     CUDA_TRY(c, cudaEventSynchronize(c->timer[1]));
     float f = 0;
@@ -634,6 +685,7 @@ extern "C" apm_status apm_profile_enable(apm_ctx* c, int32_t on) {
 extern "C" apm_status apm_profile_read(apm_ctx* c, apm_kernel_times* out) {
     if (!c || !out) return APM_E_INVALID;
     memset(out, 0, sizeof *out);
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     for (auto& sp : c->prof_spans) {
         float ms = 0;

@@ -101,6 +101,7 @@ apm_status apm_gather_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint6
     if (!c || !n) return APM_E_INVALID;
     *n = 0;
     if (!c->nccl_comm) return apm_fail(c, APM_E_STATE, "apm_comm_init has not been called");
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));  // the alert blocks are written on the baseline stream
     const size_t G = c->cfg.max_alerts_per_tick, block = 1 + G;
     apm_fs_record* send = c->d_gather;          // this rank's block
     apm_fs_record* recv = c->d_gather + block;  // nranks blocks

@@ -21,7 +21,12 @@ struct apm_ctx {
     double inv_bucket = 0, tpm_div = 1;
     double pfrac[APM_MAX_PCT] = {0, 0, 0, 0};  // percentile / 100.0 (util_methods.js:129)
 
-    cudaStream_t s_main = nullptr, s_copy = nullptr;
+    // s_main: ingest, sort, window statistics.  s_base: rolling baseline + alert compaction of tick i,
+    // which overlaps the ingest/sort of tick i+1 (linked by ev_stats / ev_base).  s_copy: H2D staging.
+    cudaStream_t s_main = nullptr, s_copy = nullptr, s_base = nullptr;
+    cudaEvent_t ev_stats[4] = {nullptr, nullptr, nullptr, nullptr}, ev_base[4] = {nullptr, nullptr, nullptr, nullptr};
+    uint64_t tick_seq = 0;        // ticks run so far (selects the zin / emit buffer and the events)
+    bool overlap = true;          // APM_NO_OVERLAP=1 runs the baseline on s_main (A/B measurements)
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
 
     // --- bucket accumulators and value logs
@@ -58,7 +63,8 @@ struct apm_ctx {
     apm_fs_record* d_fs = nullptr;       // [out_ticks][num_lags][K]
     apm_fs_record* d_alerts = nullptr;   // [out_ticks][max_alerts_per_tick]
     unsigned int* d_alert_count = nullptr;  // [out_ticks]
-    double* zin = nullptr;               // [4][K]: tpm', val0, val1, val2 (quantised)
+    double* zin[2] = {nullptr, nullptr};     // double-buffered [4][K]: tpm', val0, val1, val2 (quantised)
+    uint8_t* emit[2] = {nullptr, nullptr};   // [K] key emitted a StatEntry this tick (snapshot of `seen`)
     uint32_t ticks_buffered = 0;
     uint32_t alerts_gather_from = 0;     // first buffered tick not yet all-gathered
 
@@ -77,6 +83,7 @@ struct apm_ctx {
     apm_counters counters;
     uint64_t launches = 0;
     uint32_t k1_tiles_per_cta = 3;  // tuning knob (APM_K1_TPC)
+    int k4_stages = 4;              // APM_K4_STAGES: bulk-tensor loads kept in flight per CTA (2, 3, 4 or 6)
     bool k4_force_ldg = false;      // APM_K4_LDG=1: register-pipelined loads instead of TMA (A/B measurements)
 
     // multi-GPU
@@ -99,19 +106,19 @@ enum { APM_PG_TICKFIND = 0, APM_PG_REDUCE, APM_PG_CLEAR, APM_PG_SORT, APM_PG_TIC
 
 // Brackets the launches issued during its lifetime with an event pair when profiling is on.
 struct ProfScope {
-    apm_ctx* c; int idx = -1;
-    ProfScope(apm_ctx* ctx, int group) : c(ctx) {
+    apm_ctx* c; int idx = -1; cudaStream_t st;
+    ProfScope(apm_ctx* ctx, int group, cudaStream_t stream = nullptr) : c(ctx), st(stream ? stream : ctx->s_main) {
         if (!c->prof_on) return;
         cudaEvent_t ev[2];
         for (int i = 0; i < 2; ++i) {
             if (!c->prof_pool.empty()) { ev[i] = c->prof_pool.back(); c->prof_pool.pop_back(); }
             else if (cudaEventCreate(&ev[i]) != cudaSuccess) return;
         }
-        cudaEventRecord(ev[0], c->s_main);
+        cudaEventRecord(ev[0], st);
         c->prof_spans.push_back({group, ev[0], ev[1]});
         idx = (int)c->prof_spans.size() - 1;
     }
-    ~ProfScope() { if (idx >= 0) cudaEventRecord(c->prof_spans[idx].b, c->s_main); }
+    ~ProfScope() { if (idx >= 0) cudaEventRecord(c->prof_spans[idx].b, st); }
 };
 
 // k1_ingest.cu
@@ -126,10 +133,10 @@ apm_status apm_acc_from_sorted(apm_ctx* c, int slot, uint64_t n);
 int apm_bits_of(uint64_t v);
 // k2_tick.cu
 apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask);
-apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot);
+apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot, int buf);
 // k4_baseline.cu
-apm_status apm_launch_baseline(apm_ctx* c, int lag_idx, int64_t tick_ts, uint32_t tick_slot);
+apm_status apm_launch_baseline(apm_ctx* c, int lag_idx, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st);
 apm_status apm_baseline_make_tmaps(apm_ctx* c);
-apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot);
+apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot, cudaStream_t st);
 // comm.cu
 void apm_comm_destroy_internal(apm_ctx* c);

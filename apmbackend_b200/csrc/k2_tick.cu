@@ -90,6 +90,7 @@ struct TickParams {
     int64_t tick_ts;
     apm_stat_record* stats;  // nullptr when stat records are not retained
     double* zin;             // [4][K]
+    uint8_t* emit;           // [K]
     int with_pct;
     uint64_t log_cap;
 };
@@ -100,8 +101,10 @@ __global__ void __launch_bounds__(128) tick_stats_kernel(const TickParams p) {
     const double nan = __longlong_as_double(0x7ff8000000000000ll);
     if (!p.seen[key]) {
         if (p.stats) p.stats[key].flags = 0;
+        p.emit[key] = 0;
         return;
     }
+    p.emit[key] = 1;
     // ---- window combine (:171-178): exact integer moments
     uint64_t cnt = 0, sum = 0, sq_lo = 0, sq_hi = 0;
     uint32_t vmin = 0xFFFFFFFFu, vmax = 0;
@@ -216,7 +219,7 @@ apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask) {
     return APM_OK;
 }
 
-apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot) {
+apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot, int buf) {
     ProfScope prof_scope_(c, APM_PG_TICKSTATS);
     TickParams p;
     p.acc = c->acc; p.seen = c->seen; p.logs = c->d_log_ptrs; p.slot_meta = c->slot_meta; p.K = c->K;
@@ -227,7 +230,8 @@ apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_
     p.tpm_div = c->tpm_div;
     p.tick_ts = tick_ts;
     p.stats = (c->cfg.flags & APM_F_KEEP_STATS) ? c->d_stats + (size_t)tick_slot * c->K : nullptr;
-    p.zin = c->zin;
+    p.zin = c->zin[buf];
+    p.emit = c->emit[buf];
     p.with_pct = (c->cfg.flags & APM_F_PERCENTILES) && c->cfg.num_percentiles > 0;
     p.log_cap = c->log_cap;
     tick_stats_kernel<<<(c->K + 127) / 128, 128, 0, c->s_main>>>(p);

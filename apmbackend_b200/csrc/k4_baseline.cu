@@ -25,7 +25,7 @@ struct BaselineParams {
     const double* zin;     // [4][K]: tpm', val0..2
     const double* thr;     // [K]
     const double* infl;    // [K]
-    const uint8_t* seen;   // [K]
+    const uint8_t* seen;   // [K] snapshot taken by the tick's window kernel (emit flags)
     apm_fs_record* fs;     // [K] records of this (tick, lag); nullptr when not retained
     uint32_t K, L, head, lag_value;
     uint32_t pitch;        // doubles per ring row
@@ -156,7 +156,6 @@ __global__ void __launch_bounds__(K4_THREADS) baseline_kernel(const BaselinePara
 // from the depth of the load pipeline, which TMA provides without spending registers.
 constexpr int K4T_COLS = 32;
 constexpr int K4T_ROWS = 16;
-constexpr int K4T_STAGES = 6;
 constexpr uint32_t K4T_STAGE_BYTES = K4T_COLS * K4T_ROWS * sizeof(double);
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -183,13 +182,15 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
                  ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(r0), "r"(smem_u32(bar)) : "memory");
 }
 
+template <int K4T_STAGES>
 struct __align__(128) K4TSmem {
     double buf[K4T_STAGES][K4T_ROWS][K4T_COLS];
     uint64_t bar[K4T_STAGES];
 };
 
+template <int K4T_STAGES>
 __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant__ CUtensorMap tmap, const BaselineParams p) {
-    __shared__ K4TSmem sm;
+    __shared__ K4TSmem<K4T_STAGES> sm;
     const int lane = threadIdx.x;
     const uint32_t col0 = blockIdx.x * K4T_COLS, col = col0 + lane;
     const bool in_range = col < 3u * p.K;
@@ -343,11 +344,11 @@ apm_status apm_baseline_make_tmaps(apm_ctx* c) {
     return APM_OK;
 }
 
-apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick_slot) {
-    ProfScope prof_scope_(c, APM_PG_BASELINE);
+apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st) {
+    ProfScope prof_scope_(c, APM_PG_BASELINE, st);
     BaselineParams p;
-    p.ring = c->ring[l]; p.ring_len = c->ring_len[l]; p.zin = c->zin; p.thr = c->thr[l]; p.infl = c->infl[l];
-    p.seen = c->seen;
+    p.ring = c->ring[l]; p.ring_len = c->ring_len[l]; p.zin = c->zin[buf]; p.thr = c->thr[l]; p.infl = c->infl[l];
+    p.seen = c->emit[buf];
     p.fs = c->d_fs ? c->d_fs + ((size_t)tick_slot * c->cfg.num_lags + l) * c->K : nullptr;
     p.K = c->K; p.L = (uint32_t)c->cfg.lags[l]; p.head = c->ring_head[l]; p.lag_value = (uint32_t)c->cfg.lags[l];
     p.pitch = (uint32_t)c->ring_pitch;
@@ -355,9 +356,15 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
     p.sd_mode = c->cfg.sd_mode;
     const uint32_t ncol = 3u * c->K;
     if (c->ring_tmap_ok && c->cfg.sd_mode == APM_SD_REFERENCE && !c->k4_force_ldg) {
-        baseline_tma_kernel<<<(ncol + K4T_COLS - 1) / K4T_COLS, 32, 0, c->s_main>>>(c->ring_tmap[l], p);
+        const unsigned g = (ncol + K4T_COLS - 1) / K4T_COLS;
+        switch (c->k4_stages) {
+            case 2: baseline_tma_kernel<2><<<g, 32, 0, st>>>(c->ring_tmap[l], p); break;
+            case 3: baseline_tma_kernel<3><<<g, 32, 0, st>>>(c->ring_tmap[l], p); break;
+            case 6: baseline_tma_kernel<6><<<g, 32, 0, st>>>(c->ring_tmap[l], p); break;
+            default: baseline_tma_kernel<4><<<g, 32, 0, st>>>(c->ring_tmap[l], p); break;
+        }
     } else {
-        baseline_kernel<<<(ncol + K4_THREADS - 1) / K4_THREADS, K4_THREADS, 0, c->s_main>>>(p);
+        baseline_kernel<<<(ncol + K4_THREADS - 1) / K4_THREADS, K4_THREADS, 0, st>>>(p);
     }
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
@@ -365,11 +372,11 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
     return APM_OK;
 }
 
-apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot) {
-    ProfScope prof_scope_(c, APM_PG_ALERTS);
+apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot, cudaStream_t st) {
+    ProfScope prof_scope_(c, APM_PG_ALERTS, st);
     if (!c->d_alerts || !c->d_fs) return APM_OK;
     const uint32_t n = c->K * (uint32_t)c->cfg.num_lags;
-    compact_alerts_kernel<<<(n + 255) / 256, 256, 0, c->s_main>>>(
+    compact_alerts_kernel<<<(n + 255) / 256, 256, 0, st>>>(
         c->d_fs + (size_t)fs_slot * c->cfg.num_lags * c->K, n,
         c->d_alerts + (size_t)alert_slot * c->cfg.max_alerts_per_tick, c->d_alert_count + alert_slot,
         c->cfg.max_alerts_per_tick);

@@ -55,6 +55,7 @@ apm_status apm_state_save(apm_ctx* c, const char* path) {
     if (!c || !path) return APM_E_INVALID;
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     File fl;
     fl.f = fopen(path, "wb");
     if (!fl.f) return apm_fail(c, APM_E_IO, std::string("cannot open for writing: ") + path);
@@ -93,6 +94,7 @@ apm_status apm_state_load(apm_ctx* c, const char* path) {
     if (!c || !path) return APM_E_INVALID;
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     File fl;
     fl.f = fopen(path, "rb");
     if (!fl.f) return apm_fail(c, APM_E_IO, std::string("cannot open for reading: ") + path);
