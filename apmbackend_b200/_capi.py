@@ -95,6 +95,8 @@ SYMBOLS = {
     "apm_fetch_alerts": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "apm_release_ticks": (C.c_int32, [C.c_void_p]),
     "apm_ticks_buffered": (C.c_uint32, [C.c_void_p]),
+    "apm_host_alloc": (C.c_int32, [C.c_uint64, C.POINTER(C.c_void_p)]),
+    "apm_host_free": (None, [C.c_void_p]),
     "apm_sync": (C.c_int32, [C.c_void_p]),
     "apm_ring_load": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint32]),
     "apm_ring_read": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint32,
@@ -159,8 +161,8 @@ def synth():
         S.synth_generate_device.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(TxColumns)]
         S.synth_generate_host.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(TxColumns)]
         S.synth_generate_host.restype = None
-        S.synth_ring_fill_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32]
-        S.synth_ring_fill_host.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32,
+        S.synth_ring_fill_device.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint32, C.c_uint32]
+        S.synth_ring_fill_host.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint32, C.c_uint32,
                                            C.c_void_p, C.c_uint64]
         S.synth_ring_fill_host.restype = None
         _synth = S

@@ -249,7 +249,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
     cudaFree(c->acc_raw); cudaFree(c->seen); cudaFree(c->slot_meta);
     for (int i = 0; i <= c->S && i <= APM_MAX_SLOTS; ++i) cudaFree(c->log_buf[i]);
-    cudaFree(c->d_log_ptrs); cudaFree(c->sort_hist); cudaFree(c->sort_base);
+    cudaFree(c->d_log_ptrs); cudaFree(c->sort_hist); cudaFree(c->sort_base); cudaFree(c->sort_scratch);
     cudaFree(c->tf_tile_max); cudaFree(c->tf_tile_prefix); cudaFree(c->d_ticks); cudaFree(c->d_nticks);
     cudaFreeHost(c->h_ticks); cudaFreeHost(c->h_nticks);
     cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
@@ -337,6 +337,10 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
         c->sort_tiles_cap = (c->log_cap + 4095) / 4096;
         TRY_CREATE(dalloc(&c->sort_hist, (size_t)256 * c->sort_tiles_cap));
         TRY_CREATE(dalloc(&c->sort_base, (size_t)256));
+        c->sort_scratch_bytes = apm_onesweep_scratch_bytes(c->log_cap);
+        if (c->sort_scratch_bytes <= ((size_t)1 << 30)) TRY_CREATE(cudaMalloc((void**)&c->sort_scratch, c->sort_scratch_bytes));
+        else c->sort_scratch_bytes = 0;  // very large logs keep the three-kernel sort
+        if (const char* e = getenv("APM_SORT_LEGACY")) c->sort_legacy = atoi(e) != 0;
     }
     TRY_CREATE(cudaMemcpyAsync(c->d_log_ptrs, c->log_buf, sizeof(uint64_t*) * APM_MAX_SLOTS, cudaMemcpyHostToDevice, c->s_main));
     c->tf_tiles_cap = (cfg->max_batch + 4095) / 4096;
@@ -698,6 +702,19 @@ extern "C" apm_status apm_profile_read(apm_ctx* c, apm_kernel_times* out) {
     }
     c->prof_spans.clear();
     return APM_OK;
+}
+
+// Page-locked host buffers for results: a fetch into one of these is a plain DMA.
+extern "C" apm_status apm_host_alloc(uint64_t bytes, void** out) {
+    if (!out) return APM_E_INVALID;
+    *out = nullptr;
+    cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
+    if (e != cudaSuccess) return apm_fail_cuda(nullptr, e, "cudaMallocHost", __FILE__, __LINE__);
+    return APM_OK;
+}
+
+extern "C" void apm_host_free(void* p) {
+    if (p) cudaFreeHost(p);
 }
 
 extern "C" uint32_t apm_ticks_buffered(const apm_ctx* c) { return c ? c->ticks_buffered : 0; }

@@ -42,6 +42,9 @@ struct apm_ctx {
     uint32_t* sort_hist = nullptr;  // [256][tiles]
     uint32_t* sort_base = nullptr;  // [256]
     uint64_t sort_tiles_cap = 0;
+    unsigned char* sort_scratch = nullptr;  // onesweep: tickets, global histograms, per-tile look-back status
+    size_t sort_scratch_bytes = 0;
+    bool sort_legacy = false;               // APM_SORT_LEGACY=1: three-kernel-per-pass sort (A/B measurements)
 
     // --- tick finder scratch
     long long* tf_tile_max = nullptr;
@@ -129,6 +132,9 @@ apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value)
 uint64_t* apm_radix_sort_words(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t n, uint32_t* hist, uint32_t* totals,
                                int vbits, int kbits, uint64_t* launches);
 uint64_t apm_radix_sort_tiles(uint64_t n);
+size_t apm_onesweep_scratch_bytes(uint64_t max_n);
+uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t n, unsigned char* scratch, size_t scratch_bytes,
+                            int vbits, int kbits, uint64_t* launches, cudaError_t* err);
 apm_status apm_acc_from_sorted(apm_ctx* c, int slot, uint64_t n);
 int apm_bits_of(uint64_t v);
 // k2_tick.cu

@@ -1,0 +1,264 @@
+// K3a': single-pass-per-digit LSD radix sort ("onesweep": chained scan with decoupled look-back).
+//
+// Same job as k3_sort.cu - order one bucket's value log by (key, elapsed) so every key's
+// durations form one ascending run (what binaryConcat builds, util_methods.js:84-106) - with
+// less memory traffic and fewer launches: one histogram kernel reads the log once for all
+// digits, then each digit is ONE kernel that reads the words once and writes them once.  The
+// per-tile digit offsets that the three-kernel version gets from a global scan come from a
+// look-back over the predecessor tiles' published counts instead.
+//
+// Only the significant bits are sorted: the logical word is the low `vbits` of the value
+// field with the key field packed directly above it, cut into equal digits of <= 11 bits.
+#include "ctx.h"
+
+namespace {
+
+constexpr int OS_THREADS = 256;
+constexpr int OS_WARPS = OS_THREADS / 32;
+constexpr int OS_ITEMS = 16;
+constexpr int OS_TILE = OS_THREADS * OS_ITEMS;  // 4096 words
+constexpr int OS_MAX_BITS = 11;
+constexpr int OS_MAX_PASSES = 6;
+constexpr uint32_t OS_FLAG_AGG = 1u << 30, OS_FLAG_PREFIX = 1u << 31, OS_COUNT_MASK = (1u << 30) - 1u;
+
+struct OsPlan {
+    int npass;
+    int vbits;                  // significant bits of the value field
+    int shift[OS_MAX_PASSES];   // logical bit position of each digit
+    int bits[OS_MAX_PASSES];
+};
+
+__device__ __forceinline__ uint64_t os_logical(uint64_t x, int vbits) {
+    return vbits >= 32 ? x : ((x & ((1ull << vbits) - 1ull)) | ((x >> 32) << vbits));
+}
+__device__ __forceinline__ uint32_t os_digit(uint64_t x, int vbits, int shift, int bits) {
+    return (uint32_t)(os_logical(x, vbits) >> shift) & ((1u << bits) - 1u);
+}
+
+// lanes of the warp that hold the same digit
+__device__ __forceinline__ uint32_t os_match(uint32_t d, int bits) {
+    uint32_t peers = 0xffffffffu;
+    for (int b = 0; b < bits; ++b) {
+        const uint32_t bal = __ballot_sync(0xffffffffu, (d >> b) & 1u);
+        peers &= ((d >> b) & 1u) ? bal : ~bal;
+    }
+    return peers;
+}
+
+// ---- all digits' global histograms in one read ------------------------------------------------
+__global__ void __launch_bounds__(OS_THREADS) os_hist_kernel(const uint64_t* __restrict__ src, uint64_t n, const OsPlan plan,
+                                                             uint32_t* __restrict__ ghist /* [npass][2048] */) {
+    extern __shared__ uint32_t s_hist[];  // [npass][2048]
+    const int nb = plan.npass << OS_MAX_BITS;
+    for (int i = threadIdx.x; i < nb; i += OS_THREADS) s_hist[i] = 0;
+    __syncthreads();
+    const uint64_t stride = (uint64_t)gridDim.x * OS_THREADS;
+    for (uint64_t i = (uint64_t)blockIdx.x * OS_THREADS + threadIdx.x; i < n; i += stride) {
+        const uint64_t x = __ldg(src + i);
+        for (int p = 0; p < plan.npass; ++p)
+            atomicAdd(&s_hist[(p << OS_MAX_BITS) + os_digit(x, plan.vbits, plan.shift[p], plan.bits[p])], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < nb; i += OS_THREADS)
+        if (s_hist[i]) atomicAdd(&ghist[i], s_hist[i]);
+}
+
+// exclusive scan of each digit's bins -> first output position of every bin
+__global__ void __launch_bounds__(1024) os_scan_kernel(uint32_t* __restrict__ ghist) {
+    __shared__ uint32_t s_warp[32];
+    uint32_t* h = ghist + ((size_t)blockIdx.x << OS_MAX_BITS);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t a = h[2 * threadIdx.x], b = h[2 * threadIdx.x + 1];
+    uint32_t v = a + b;
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += y;
+    }
+    if (lane == 31) s_warp[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        uint32_t x = s_warp[lane];
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        s_warp[lane] = x;
+    }
+    __syncthreads();
+    const uint32_t excl = v - (a + b) + (w ? s_warp[w - 1] : 0u);
+    h[2 * threadIdx.x] = excl;
+    h[2 * threadIdx.x + 1] = excl + a;
+}
+
+// ---- one digit: rank, look back, scatter ----------------------------------------------------------
+struct OsSmemLayout {
+    // [items u64 x 4096][wcnt u16 x 8 x bins][tile_cnt u32 x bins][gbase u32 x bins]
+    static size_t bytes(int bins) { return (size_t)OS_TILE * 8 + (size_t)OS_WARPS * bins * 2 + (size_t)bins * 4 * 2 + 64; }
+};
+
+__global__ void __launch_bounds__(OS_THREADS) os_pass_kernel(const uint64_t* __restrict__ src, uint64_t* __restrict__ dst, uint64_t n,
+                                                             int vbits, int shift, int bits, const uint32_t* __restrict__ gbase,
+                                                             volatile uint32_t* status /* [tiles][bins] */, uint32_t* ticket) {
+    extern __shared__ __align__(16) unsigned char os_raw[];
+    const int bins = 1 << bits;
+    uint64_t* s_items = reinterpret_cast<uint64_t*>(os_raw);
+    uint16_t* s_wcnt = reinterpret_cast<uint16_t*>(os_raw + (size_t)OS_TILE * 8);          // [warp][bin]
+    uint32_t* s_cnt = reinterpret_cast<uint32_t*>(os_raw + (size_t)OS_TILE * 8 + (size_t)OS_WARPS * bins * 2);  // tile count, then local start
+    uint32_t* s_gbase = s_cnt + bins;
+    uint32_t* s_misc = s_gbase + bins;  // [0] tile id, [1..8] scan scratch
+
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) s_misc[0] = atomicAdd(ticket, 1u);  // tiles start in index order: a predecessor is always running or done
+    for (int i = tid; i < OS_WARPS * bins / 2; i += OS_THREADS) reinterpret_cast<uint32_t*>(s_wcnt)[i] = 0;
+    __syncthreads();
+    const uint32_t tile = s_misc[0];
+    const uint64_t tile_base = (uint64_t)tile * OS_TILE;
+    const uint64_t base = tile_base + (uint64_t)w * (32 * OS_ITEMS);
+
+    uint64_t item[OS_ITEMS];
+    uint16_t rank[OS_ITEMS];
+#pragma unroll
+    for (int i = 0; i < OS_ITEMS; ++i) {
+        const uint64_t idx = base + (uint64_t)i * 32 + lane;
+        item[i] = idx < n ? __ldcs(src + idx) : ~0ull;
+    }
+    uint16_t* my_wcnt = s_wcnt + (size_t)w * bins;
+#pragma unroll
+    for (int i = 0; i < OS_ITEMS; ++i) {
+        const uint64_t idx = base + (uint64_t)i * 32 + lane;
+        const bool ok = idx < n;
+        const uint32_t d = os_digit(item[i], vbits, shift, bits);
+        const uint32_t peers = os_match(d, bits) & __ballot_sync(0xffffffffu, ok);
+        uint32_t before = 0;
+        if (ok) before = my_wcnt[d];
+        __syncwarp();
+        if (ok && lane == (__ffs(peers) - 1)) my_wcnt[d] = (uint16_t)(before + __popc(peers));
+        __syncwarp();
+        rank[i] = (uint16_t)(before + __popc(peers & ((1u << lane) - 1u)));
+    }
+    __syncthreads();
+
+    // per bin: offsets of the warps inside the bin and the tile's count, published at once so that
+    // successor tiles can already look back through this tile
+    for (int d = tid; d < bins; d += OS_THREADS) {
+        uint32_t run = 0;
+#pragma unroll
+        for (int j = 0; j < OS_WARPS; ++j) {
+            const uint32_t c = s_wcnt[(size_t)j * bins + d];
+            s_wcnt[(size_t)j * bins + d] = (uint16_t)run;
+            run += c;
+        }
+        s_cnt[d] = run;
+        status[(size_t)tile * bins + d] = run | (tile == 0 ? OS_FLAG_PREFIX : OS_FLAG_AGG);
+    }
+    // decoupled look-back: add the predecessors' counts until one of them carries an inclusive prefix
+    for (int d = tid; d < bins; d += OS_THREADS) {
+        uint32_t excl = 0;
+        if (tile != 0) {
+            for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
+                volatile uint32_t* prev = status + (size_t)t * bins + d;
+                uint32_t s;
+                while ((s = *prev) == 0) { /* the predecessor holds a ticket, so it is resident and will publish */ }
+                excl += s & OS_COUNT_MASK;
+                if (s & OS_FLAG_PREFIX) break;
+            }
+            status[(size_t)tile * bins + d] = (excl + s_cnt[d]) | OS_FLAG_PREFIX;
+        }
+        s_gbase[d] = gbase[d] + excl;
+    }
+    __syncthreads();
+
+    // exclusive scan of the tile counts over the bins -> first local position of each bin
+    {
+        const int per = bins / OS_THREADS > 0 ? bins / OS_THREADS : 1;  // bins >= 256 is guaranteed by the planner
+        const int d0 = tid * per;
+        uint32_t local[8];
+        uint32_t sum = 0;
+        for (int j = 0; j < per; ++j) { local[j] = s_cnt[d0 + j]; sum += local[j]; }
+        uint32_t v = sum;
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += y;
+        }
+        if (lane == 31) s_misc[1 + w] = v;
+        __syncthreads();
+        uint32_t woff = 0;
+#pragma unroll
+        for (int j = 0; j < OS_WARPS; ++j)
+            if (j < w) woff += s_misc[1 + j];
+        uint32_t run = woff + v - sum;
+        for (int j = 0; j < per; ++j) { s_cnt[d0 + j] = run; run += local[j]; }
+    }
+    __syncthreads();
+
+#pragma unroll
+    for (int i = 0; i < OS_ITEMS; ++i) {
+        const uint64_t idx = base + (uint64_t)i * 32 + lane;
+        if (idx < n) {
+            const uint32_t d = os_digit(item[i], vbits, shift, bits);
+            s_items[s_cnt[d] + my_wcnt[d] + rank[i]] = item[i];
+        }
+    }
+    __syncthreads();
+    const uint32_t in_tile = tile_base >= n ? 0u : (uint32_t)((n - tile_base) < (uint64_t)OS_TILE ? (n - tile_base) : OS_TILE);
+    for (uint32_t j = tid; j < in_tile; j += OS_THREADS) {
+        const uint64_t x = s_items[j];
+        const uint32_t d = os_digit(x, vbits, shift, bits);
+        dst[(uint64_t)s_gbase[d] + (j - s_cnt[d])] = x;
+    }
+}
+
+}  // namespace
+
+size_t apm_onesweep_scratch_bytes(uint64_t max_n) {
+    const uint64_t tiles = (max_n + OS_TILE - 1) / OS_TILE;
+    // [tickets: 64 B][ghist: 6 x 2048 u32][status: 6 x tiles x 2048 u32]
+    return 64 + (size_t)OS_MAX_PASSES * 2048 * 4 + (size_t)OS_MAX_PASSES * tiles * 2048 * 4;
+}
+
+// Sorts n words between a and b on `st`; returns the buffer holding the result, or nullptr when
+// the scratch is too small for this n (the caller falls back to the three-kernel sort).
+uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t n, unsigned char* scratch, size_t scratch_bytes,
+                            int vbits, int kbits, uint64_t* launches, cudaError_t* err) {
+    *err = cudaSuccess;
+    int total = vbits + kbits;
+    if (total < 1) total = 1;
+    OsPlan plan;
+    plan.npass = (total + OS_MAX_BITS - 1) / OS_MAX_BITS;
+    if (plan.npass > OS_MAX_PASSES) return nullptr;
+    int per = (total + plan.npass - 1) / plan.npass;
+    if (per < 8) per = 8;  // at least 256 bins: one per thread in the per-bin phases
+    plan.vbits = vbits;
+    for (int p = 0; p < plan.npass; ++p) { plan.shift[p] = p * per; plan.bits[p] = per; }
+    const int bins = 1 << per;
+    const uint64_t tiles = (n + OS_TILE - 1) / OS_TILE;
+    const size_t status_bytes = (size_t)plan.npass * tiles * bins * 4;
+    const size_t head = 64 + (size_t)OS_MAX_PASSES * 2048 * 4;
+    if (head + status_bytes > scratch_bytes || n >= (1ull << 30)) return nullptr;
+    uint32_t* tickets = reinterpret_cast<uint32_t*>(scratch);
+    uint32_t* ghist = reinterpret_cast<uint32_t*>(scratch + 64);
+    uint32_t* status = reinterpret_cast<uint32_t*>(scratch + head);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(os_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout::bytes(2048));
+        cudaFuncSetAttribute(os_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_MAX_PASSES * 2048 * 4);
+        attr_set = true;
+    }
+    *err = cudaMemsetAsync(scratch, 0, head + status_bytes, st);
+    if (*err != cudaSuccess) return nullptr;
+    unsigned hg = (unsigned)((n + OS_THREADS * 16 - 1) / (OS_THREADS * 16));
+    if (hg > 148 * 4) hg = 148 * 4;
+    os_hist_kernel<<<hg, OS_THREADS, (size_t)plan.npass * 2048 * 4, st>>>(a, n, plan, ghist);
+    os_scan_kernel<<<plan.npass, 1024, 0, st>>>(ghist);
+    uint64_t* src = a;
+    uint64_t* dst = b;
+    for (int p = 0; p < plan.npass; ++p) {
+        os_pass_kernel<<<(unsigned)tiles, OS_THREADS, OsSmemLayout::bytes(bins), st>>>(
+            src, dst, n, plan.vbits, plan.shift[p], plan.bits[p], ghist + ((size_t)p << OS_MAX_BITS),
+            status + (size_t)p * tiles * bins, tickets + p);
+        uint64_t* t = src; src = dst; dst = t;
+    }
+    if (launches) *launches += 2 + plan.npass;
+    *err = cudaGetLastError();
+    return src;
+}

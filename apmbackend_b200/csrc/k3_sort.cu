@@ -321,8 +321,16 @@ apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value)
     if (n > 0xFFFFFFFFull) return apm_fail(c, APM_E_CAPACITY, "value log above 2^32 entries");
     if (apm_radix_sort_tiles(n) > c->sort_tiles_cap) return apm_fail(c, APM_E_CAPACITY, "sort scratch too small");
     const int vbits = bits_of(max_value), kbits = bits_of(c->K > 1 ? c->K - 1 : 0);
-    uint64_t* res = apm_radix_sort_words(c->s_main, c->log_buf[slot], c->log_buf[c->S], n, c->sort_hist, c->sort_base, vbits,
-                                         kbits, &c->launches);
+    uint64_t* res = nullptr;
+    if (!c->sort_legacy && c->sort_scratch) {
+        cudaError_t e = cudaSuccess;
+        res = apm_onesweep_sort(c->s_main, c->log_buf[slot], c->log_buf[c->S], n, c->sort_scratch, c->sort_scratch_bytes, vbits,
+                                kbits, &c->launches, &e);
+        CUDA_TRY(c, e);
+    }
+    if (!res)
+        res = apm_radix_sort_words(c->s_main, c->log_buf[slot], c->log_buf[c->S], n, c->sort_hist, c->sort_base, vbits, kbits,
+                                   &c->launches);
     CUDA_TRY(c, cudaGetLastError());
     if (res != c->log_buf[slot]) {  // result sits in the spare buffer: swap roles
         c->log_buf[c->S] = c->log_buf[slot];

@@ -177,9 +177,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "DONE:\n"
         "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int r0, uint64_t* bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(r0), "r"(smem_u32(bar)) : "memory");
+// The ring is read exactly once per tick and is far larger than L2: mark its lines evict-first so
+// the stream does not push the ingest / sort working set (a few tens of MB, re-read by the next
+// kernel of that chain) out of L2 while both streams run.
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int r0, uint64_t* bar, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, %3}], [%4], %5;"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(r0), "r"(smem_u32(bar)), "l"(policy) : "memory");
 }
 
 template <int K4T_STAGES>
@@ -203,6 +212,7 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
     double sum = 0.0, last = nan;
     uint32_t cnt = 0;
     if (__any_sync(0xffffffffu, full)) {
+        const uint64_t policy = l2_evict_first_policy();
         // oldest first: rows head .. L-1, then 0 .. head-1, in chunks of K4T_ROWS slots
         const uint32_t nA = (p.L - p.head + K4T_ROWS - 1) / K4T_ROWS, nB = (p.head + K4T_ROWS - 1) / K4T_ROWS;
         const uint32_t n = nA + nB;
@@ -221,7 +231,7 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
         if (lane == 0) {
             for (uint32_t c = 0; c < n && c < (uint32_t)K4T_STAGES; ++c) {
                 mbar_expect_tx(&sm.bar[c], K4T_STAGE_BYTES);  // rows past the end are zero-filled but still counted
-                tma_load_2d(&sm.buf[c][0][0], &tmap, (int)col0, (int)row0_of(c), &sm.bar[c]);
+                tma_load_2d(&sm.buf[c][0][0], &tmap, (int)col0, (int)row0_of(c), &sm.bar[c], policy);
             }
         }
         for (uint32_t c = 0; c < n; ++c) {
@@ -247,7 +257,7 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
             __syncwarp();  // every lane holds its values in registers: the stage may be overwritten
             if (lane == 0 && c + K4T_STAGES < n) {
                 mbar_expect_tx(&sm.bar[s], K4T_STAGE_BYTES);
-                tma_load_2d(&sm.buf[s][0][0], &tmap, (int)col0, (int)row0_of(c + K4T_STAGES), &sm.bar[s]);
+                tma_load_2d(&sm.buf[s][0][0], &tmap, (int)col0, (int)row0_of(c + K4T_STAGES), &sm.bar[s], policy);
             }
         }
     }

@@ -15,17 +15,24 @@ __global__ void __launch_bounds__(256) synth_kernel(const synth_params p, uint64
         syn_tx(p, p.first + j, svc + j, jvm + j, ts + j, el + j);
 }
 
-// ring pre-fill: value of (slot, series, key) = level(key, series) + small deterministic noise in tenths
+// ring pre-fill: a plausible history for every (series, key) column - the level follows the
+// service's duration scale (mean ~ 1.13 x base, p95 ~ 2.28 x, p99 ~ 3.2 x for lognormal(0, 0.5)),
+// plus a small deterministic noise, all in tenths like the values toFixed(1) produces
+__host__ __device__ __forceinline__ double ring_fill_value(uint64_t i, uint64_t ncol, uint64_t seed, const uint32_t* base,
+                                                           uint32_t num_services, uint32_t K) {
+    const uint64_t col = i % ncol;
+    const uint32_t series = (uint32_t)(col / K), key = (uint32_t)(col % K);
+    const uint32_t mult = series == 0 ? 113u : (series == 1 ? 228u : 320u);
+    const uint64_t hn = syn_mix(seed ^ (i * 0xD1B54A32D192ED03ull) ^ 0x5555);
+    const uint32_t tenths = base[key % num_services] * mult / 10u + (uint32_t)(hn % 41u);
+    return (double)tenths / 10.0;
+}
+
 __global__ void __launch_bounds__(256) ring_fill_kernel(double* out, uint64_t rows, uint64_t ncol, uint64_t seed,
-                                                        uint32_t level_lo, uint32_t level_span) {
+                                                        const uint32_t* base, uint32_t num_services, uint32_t K) {
     const uint64_t total = rows * ncol, stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-        const uint64_t col = i % ncol;
-        const uint64_t hl = syn_mix(seed ^ (col * 0x9E3779B97F4A7C15ull));
-        const uint64_t hn = syn_mix(seed ^ (i * 0xD1B54A32D192ED03ull) ^ 0x5555);
-        const uint32_t tenths = (level_lo + (uint32_t)(hl % level_span)) * 10u + (uint32_t)(hn % 41u);
-        out[i] = (double)tenths / 10.0;
-    }
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride)
+        out[i] = ring_fill_value(i, ncol, seed, base, num_services, K);
 }
 }  // namespace
 
@@ -60,24 +67,21 @@ void synth_generate_host(const synth_params* p, uint64_t count, apm_tx_columns* 
         syn_tx(*p, p->first + j, cols->service_id + j, cols->jvm_id + j, cols->end_ts_ms + j, cols->elapsed_ms + j);
 }
 
-int synth_ring_fill_device(double* out, uint64_t rows, uint64_t ncol, uint64_t seed, uint32_t level_lo, uint32_t level_span) {
-    ring_fill_kernel<<<148 * 8, 256>>>(out, rows, ncol, seed, level_lo, level_span);
+// base: device pointer to the stream's duration-scale table
+int synth_ring_fill_device(double* out, uint64_t rows, uint64_t ncol, uint64_t seed, const uint32_t* base, uint32_t num_services,
+                           uint32_t K) {
+    ring_fill_kernel<<<148 * 8, 256>>>(out, rows, ncol, seed, base, num_services, K);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
     return (int)cudaDeviceSynchronize();
 }
 
-void synth_ring_fill_host(double* out, uint64_t rows, uint64_t ncol, uint64_t seed, uint32_t level_lo, uint32_t level_span,
-                          const uint64_t* cols, uint64_t ncols_sel) {
-    // only the selected columns, packed [rows][ncols_sel]
+// the same values for a selection of columns, packed [rows][ncols_sel]; base: host pointer
+void synth_ring_fill_host(double* out, uint64_t rows, uint64_t ncol, uint64_t seed, const uint32_t* base, uint32_t num_services,
+                          uint32_t K, const uint64_t* cols, uint64_t ncols_sel) {
     for (uint64_t r = 0; r < rows; ++r)
-        for (uint64_t c = 0; c < ncols_sel; ++c) {
-            const uint64_t col = cols[c], i = r * ncol + col;
-            const uint64_t hl = syn_mix(seed ^ (col * 0x9E3779B97F4A7C15ull));
-            const uint64_t hn = syn_mix(seed ^ (i * 0xD1B54A32D192ED03ull) ^ 0x5555);
-            const uint32_t tenths = (level_lo + (uint32_t)(hl % level_span)) * 10u + (uint32_t)(hn % 41u);
-            out[r * ncols_sel + c] = (double)tenths / 10.0;
-        }
+        for (uint64_t c = 0; c < ncols_sel; ++c)
+            out[r * ncols_sel + c] = ring_fill_value(r * ncol + cols[c], ncol, seed, base, num_services, K);
 }
 
 // L2 flush helper for the bench: overwrite a buffer larger than L2

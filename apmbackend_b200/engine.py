@@ -74,11 +74,15 @@ class Engine:
         if st != _capi.OK:
             raise ApmError(st, (self._lib.apm_last_error(None) or b"").decode())
         self._h = h
+        self._pinned = {}
         self.K = cfg.num_services * cfg.num_jvms
 
     # ---- lifecycle
     def close(self):
         if getattr(self, "_h", None):
+            for p, _ in getattr(self, "_pinned", {}).values():
+                self._lib.apm_host_free(p)
+            self._pinned = {}
             self._lib.apm_ctx_destroy(self._h)
             self._h = None
 
@@ -144,23 +148,39 @@ class Engine:
     def ticks_buffered(self) -> int:
         return int(self._lib.apm_ticks_buffered(self._h))
 
-    def fetch_stats(self) -> np.ndarray:
+    def _out_buffer(self, kind: str, dtype, cap: int, pinned: bool) -> np.ndarray:
+        """Output array for a fetch.  pinned=True reuses one page-locked buffer per record kind
+        (apm_host_alloc): the returned view is then only valid until the next fetch of that kind."""
+        if not pinned:
+            return np.zeros(max(cap, 1), dtype=dtype)
+        have = self._pinned.get(kind)
+        if have is None or have[1].size < cap:
+            if have is not None:
+                self._lib.apm_host_free(have[0])
+            p = C.c_void_p()
+            nbytes = max(cap, 1) * np.dtype(dtype).itemsize
+            self._check(self._lib.apm_host_alloc(nbytes, C.byref(p)))
+            arr = np.frombuffer((C.c_char * nbytes).from_address(p.value), dtype=dtype, count=max(cap, 1))
+            self._pinned[kind] = have = (p, arr)
+        return have[1]
+
+    def fetch_stats(self, pinned: bool = False) -> np.ndarray:
         cap = self.ticks_buffered * self.K
-        out = np.zeros(max(cap, 1), dtype=_capi.STAT_DTYPE)
+        out = self._out_buffer("stats", _capi.STAT_DTYPE, cap, pinned)
         n = C.c_uint64(0)
         self._check(self._lib.apm_fetch_stats(self._h, out.ctypes.data, cap, C.byref(n)))
         return out[:n.value]
 
-    def fetch_fs(self) -> np.ndarray:
+    def fetch_fs(self, pinned: bool = False) -> np.ndarray:
         cap = self.ticks_buffered * self.K * len(self.cfg.lags)
-        out = np.zeros(max(cap, 1), dtype=_capi.FS_DTYPE)
+        out = self._out_buffer("fs", _capi.FS_DTYPE, cap, pinned)
         n = C.c_uint64(0)
         self._check(self._lib.apm_fetch_fs(self._h, out.ctypes.data, cap, C.byref(n)))
         return out[:n.value]
 
-    def fetch_alerts(self) -> np.ndarray:
+    def fetch_alerts(self, pinned: bool = False) -> np.ndarray:
         cap = self.ticks_buffered * self.cfg.max_alerts_per_tick
-        out = np.zeros(max(cap, 1), dtype=_capi.FS_DTYPE)
+        out = self._out_buffer("alerts", _capi.FS_DTYPE, cap, pinned)
         n = C.c_uint64(0)
         self._check(self._lib.apm_fetch_alerts(self._h, out.ctypes.data, cap, C.byref(n)))
         return out[:n.value]

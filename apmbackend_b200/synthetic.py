@@ -209,13 +209,19 @@ class SynthStream:
             b.free()
 
 
-def ring_fill_device(buf: DeviceBuffer, rows: int, ncol: int, seed: int, level_lo=20, level_span=400):
-    _chk(_capi.synth().synth_ring_fill_device(buf.ptr, rows, ncol, seed, level_lo, level_span), "ring_fill")
+def ring_fill_device(buf: DeviceBuffer, rows: int, stream: "SynthStream", seed: int):
+    """Fills buf as [rows][3][K] with a plausible baseline history for `stream`'s services."""
+    sp = stream.spec
+    K = sp.num_services * sp.num_jvms
+    _chk(_capi.synth().synth_ring_fill_device(buf.ptr, rows, 3 * K, seed, stream._dev[1].ptr, sp.num_services, K), "ring_fill")
 
 
-def ring_fill_host(rows: int, ncol: int, seed: int, cols, level_lo=20, level_span=400) -> np.ndarray:
-    """The same values for a selection of columns, as [rows][len(cols)]."""
+def ring_fill_host(rows: int, stream: "SynthStream", seed: int, cols) -> np.ndarray:
+    """The same values for a selection of columns (series * K + key), as [rows][len(cols)]."""
+    sp = stream.spec
+    K = sp.num_services * sp.num_jvms
     cols = np.ascontiguousarray(cols, dtype=np.uint64)
     out = np.empty((rows, cols.size), dtype=np.float64)
-    _capi.synth().synth_ring_fill_host(out.ctypes.data, rows, ncol, seed, level_lo, level_span, cols.ctypes.data, cols.size)
+    _capi.synth().synth_ring_fill_host(out.ctypes.data, rows, 3 * K, seed, stream.base.ctypes.data, sp.num_services, K,
+                                       cols.ctypes.data, cols.size)
     return out

@@ -113,7 +113,7 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------
 # the reference's algorithm on the host cores (oracle port; test/baseline infrastructure)
 # ---------------------------------------------------------------------------------------------
-def cpu_reference_run(wl, cols, ring_seed, threads, prefill=True):
+def cpu_reference_run(wl, cols, ring_seed, threads, stream, prefill=True):
     """Times the reference-structure CPU port (oracle fast=0: sorted insert per element, four
     list passes per statistic, shift() memmove) on the given columns.  Keys are independent,
     so the host threads each own key % threads of them while all of them walk the whole
@@ -137,7 +137,7 @@ def cpu_reference_run(wl, cols, ring_seed, threads, prefill=True):
             L = wl["lags"][0]
             mine = np.arange(t, K, threads)
             for s in range(3):
-                vals = syn.ring_fill_host(L, 3 * K, ring_seed, s * K + mine)
+                vals = syn.ring_fill_host(L, stream, ring_seed, s * K + mine)
                 for j, key in enumerate(mine):
                     p.ring_load(int(key), 0, s, vals[:, j])
         pipes.append(p)
@@ -219,18 +219,18 @@ def main():
         dist.broadcast(uid, 0)
         eng.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
 
-    ring_seed = 77 + rank
-    if wl["zscore"]:
-        L = wl["lags"][0]
-        buf = syn.DeviceBuffer(L * 3 * K * 8)
-        syn.ring_fill_device(buf, L, 3 * K, ring_seed)
-        eng.ring_load_all(0, length=L, device_ptr=buf.ptr)
-        buf.free()
-
     nsteps = args.warmup + args.steps
     spec = syn.StreamSpec(seed=wl["seed"] + 1000 * rank, n=wl["n"], num_services=wl["services"], num_jvms=wl["jvms"],
                           span_ms=span_ms, shift_mod=97)
     stream = syn.SynthStream(spec, device=True)
+    ring_seed = 77 + rank
+    if wl["zscore"]:
+        L = wl["lags"][0]
+        buf = syn.DeviceBuffer(L * 3 * K * 8)
+        syn.ring_fill_device(buf, L, stream, ring_seed)
+        eng.ring_load_all(0, length=L, device_ptr=buf.ptr)
+        buf.free()
+
     t0 = spec.t0_ms
 
     def step_t0(s):
@@ -306,13 +306,13 @@ def main():
             p = host_steps[s]
             eng.process_host(p[0].array, p[1].array, p[2].array, p[3].array)
             if wl["zscore"]:
-                fs = eng.fetch_fs()
-                al = eng.fetch_alerts()
+                fs = eng.fetch_fs(pinned=True)
+                al = eng.fetch_alerts(pinned=True)
                 out_bytes[0] = fs.nbytes + al.nbytes
                 if world > 1:
                     eng.gather_alerts(ecfg.max_alerts_per_tick * world)
             else:
-                st = eng.fetch_stats()
+                st = eng.fetch_stats(pinned=True)
                 out_bytes[0] = st.nbytes
             eng.release_ticks()
 
@@ -384,7 +384,7 @@ def main():
         hs = syn.SynthStream(spec, device=False)
         cols, n_s = sample_for_cpu(wl, hs, ticks=6)
         threads = 1
-        dt, tks = cpu_reference_run(wl, cols, ring_seed, threads)
+        dt, tks = cpu_reference_run(wl, cols, ring_seed, threads, hs)
         line["cpu_baseline"] = {"value": n_s / dt, "unit": "transactions/s", "cores": threads, "kind": "port",
                                 "sample": f"first {n_s} transactions of the same stream (6 of its buckets + the tick "
                                           f"that closes the last, all {K} keys, rings pre-filled): {tks} ticks in {dt:.1f} s, "
@@ -410,7 +410,7 @@ def run_reference(args, wl, rank, world, config, span_ms):
     times, ticks = [], 0
     for s in range(args.warmup + args.steps):
         # prefill only matters for the z stage's cost; it is rebuilt each step so every step does the same work
-        dt, tk = cpu_reference_run(wl, (svc, jvm, ts + s * span_ms, el), 77, threads)
+        dt, tk = cpu_reference_run(wl, (svc, jvm, ts + s * span_ms, el), 77, threads, hs)
         if s >= args.warmup:
             times.append(dt); ticks += tk
     total = float(np.sum(times))

@@ -195,6 +195,10 @@ apm_status apm_fetch_stats(apm_ctx* ctx, apm_stat_record* out, uint64_t cap, uin
 apm_status apm_fetch_fs(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
 apm_status apm_fetch_alerts(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
 apm_status apm_release_ticks(apm_ctx* ctx);
+/* Page-locked host memory for the `out` buffers above (the N-API addon wraps it as an external
+ * ArrayBuffer): a fetch into it is one DMA instead of a staged copy.  No reference counterpart. */
+apm_status apm_host_alloc(uint64_t bytes, void** out);
+void apm_host_free(void* p);
 uint32_t apm_ticks_buffered(const apm_ctx* ctx);
 /* wait for all queued device work (for timing) */
 apm_status apm_sync(apm_ctx* ctx);
