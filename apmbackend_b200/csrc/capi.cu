@@ -158,6 +158,8 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
             CUDA_TRY(c, cudaStreamWaitEvent(sb, c->ev_stats[ev], 0));
         }
         const uint32_t fslot = (c->cfg.flags & APM_F_KEEP_FS) ? tslot : 0;
+        st = apm_launch_realign(c, buf, sb);  // lists of keys that were silent re-enter the lock step
+        if (st) return st;
         for (int l = 0; l < c->cfg.num_lags; ++l) {  // Object.entries(lags): ascending (:217)
             st = apm_launch_baseline(c, l, tick_ts, fslot, buf, sb);
             if (st) return st;
@@ -255,7 +257,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
     free_columns_device(&c->dev[0]); free_columns_device(&c->dev[1]);
     cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
-    for (int l = 0; l < APM_MAX_LAGS; ++l) { cudaFree(c->ring[l]); cudaFree(c->ring_len[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
+    for (int l = 0; l < APM_MAX_LAGS; ++l) { cudaFree(c->ring[l]); cudaFree(c->ring_len[l]); cudaFree(c->ring_next[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
     cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->d_gather);
     for (int i = 0; i < 2; ++i) { if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); if (c->ev_consumed[i]) cudaEventDestroy(c->ev_consumed[i]); }
     for (int i = 0; i < 4; ++i) { if (c->ev_stats[i]) cudaEventDestroy(c->ev_stats[i]); if (c->ev_base[i]) cudaEventDestroy(c->ev_base[i]); }
@@ -372,6 +374,8 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
             TRY_CREATE(cudaMemsetAsync(c->ring[l], 0, L * c->ring_pitch * sizeof(double), c->s_main));
             TRY_CREATE(dalloc(&c->ring_len[l], 3 * K));
             TRY_CREATE(cudaMemsetAsync(c->ring_len[l], 0, sizeof(uint32_t) * 3 * K, c->s_main));
+            TRY_CREATE(dalloc(&c->ring_next[l], 3 * K));
+            TRY_CREATE(cudaMemsetAsync(c->ring_next[l], 0, sizeof(uint32_t) * 3 * K, c->s_main));
             TRY_CREATE(dalloc(&c->thr[l], K));
             TRY_CREATE(dalloc(&c->infl[l], K));
             std::vector<double> t(K, cfg->default_threshold[l]), f(K, cfg->default_influence[l]);
@@ -585,6 +589,7 @@ apm_status apm_ring_load(apm_ctx* c, uint32_t key, int32_t l, int32_t series, co
     if (n1) CUDA_TRY(c, cudaMemcpy2D(c->ring[l] + (size_t)first * ncol + col, ncol * sizeof(double), tmp.data(), sizeof(double), sizeof(double), n1, cudaMemcpyHostToDevice));
     if (len > n1) CUDA_TRY(c, cudaMemcpy2D(c->ring[l] + col, ncol * sizeof(double), tmp.data() + n1, sizeof(double), sizeof(double), len - n1, cudaMemcpyHostToDevice));
     CUDA_TRY(c, cudaMemcpy(c->ring_len[l] + col, &len, sizeof(uint32_t), cudaMemcpyHostToDevice));
+    CUDA_TRY(c, cudaMemcpy(c->ring_next[l] + col, &head, sizeof(uint32_t), cudaMemcpyHostToDevice));  // the list ends just before `head`
     return APM_OK;
 }
 
@@ -602,6 +607,8 @@ apm_status apm_ring_load_all(apm_ctx* c, int32_t l, const double* values, uint32
     if (len > n1) CUDA_TRY(c, cudaMemcpy2D(c->ring[l], pitch, values + (size_t)n1 * ncol, row, row, len - n1, kind));
     std::vector<uint32_t> lens(ncol, len);
     CUDA_TRY(c, cudaMemcpy(c->ring_len[l], lens.data(), ncol * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    std::vector<uint32_t> nexts(ncol, head);
+    CUDA_TRY(c, cudaMemcpy(c->ring_next[l], nexts.data(), ncol * sizeof(uint32_t), cudaMemcpyHostToDevice));
     return APM_OK;
 }
 
@@ -617,7 +624,8 @@ apm_status apm_ring_read(apm_ctx* c, uint32_t key, int32_t l, int32_t series, do
     *len_out = len;
     if (len == 0) return APM_OK;
     if (!values || cap < len) return apm_fail(c, APM_E_CAPACITY, "ring_read: buffer too small");
-    const uint32_t head = c->ring_head[l];
+    uint32_t head = 0;  // the slot this column's next push belongs in: a silent key's list does not follow the global head
+    CUDA_TRY(c, cudaMemcpy(&head, c->ring_next[l] + col, sizeof(uint32_t), cudaMemcpyDeviceToHost));
     const uint32_t first = (head + L - len) % L;
     const uint32_t n1 = std::min(len, L - first);
     CUDA_TRY(c, cudaMemcpy2D(values, sizeof(double), c->ring[l] + (size_t)first * ncol + col, ncol * sizeof(double), sizeof(double), n1, cudaMemcpyDeviceToHost));

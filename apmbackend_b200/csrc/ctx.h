@@ -74,6 +74,7 @@ struct apm_ctx {
     // --- rolling baseline
     double* ring[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};        // [L][ring_pitch], column = series*K + key
     uint32_t* ring_len[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};  // [3][K]
+    uint32_t* ring_next[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr}; // [3][K] slot the column's next push belongs in
     size_t ring_pitch = 0;  // doubles per ring row: 3K rounded up to 32 (TMA box width, 256-byte rows)
     CUtensorMap ring_tmap[APM_MAX_LAGS];  // 2-D view [L][ring_pitch] of each ring for the bulk-tensor loads
     bool ring_tmap_ok = false;
@@ -143,6 +144,7 @@ apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_
 // k4_baseline.cu
 apm_status apm_launch_baseline(apm_ctx* c, int lag_idx, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st);
 apm_status apm_baseline_make_tmaps(apm_ctx* c);
+apm_status apm_launch_realign(apm_ctx* c, int buf, cudaStream_t st);
 apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot, cudaStream_t st);
 // comm.cu
 void apm_comm_destroy_internal(apm_ctx* c);

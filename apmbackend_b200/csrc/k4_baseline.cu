@@ -22,6 +22,7 @@ constexpr int K4_UNROLL = 32;
 struct BaselineParams {
     double* ring;          // [L][3K]
     uint32_t* ring_len;    // [3K]
+    uint32_t* ring_next;   // [3K] slot each column's next push belongs in (== head for every lock-step list)
     const double* zin;     // [4][K]: tpm', val0..2
     const double* thr;     // [K]
     const double* infl;    // [K]
@@ -129,6 +130,7 @@ __global__ void __launch_bounds__(K4_THREADS) baseline_kernel(const BaselinePara
     }
     // shift() + push() (:285-306): the oldest slot is the one the push overwrites
     p.ring[(size_t)p.head * ncol + col] = infl_value;
+    p.ring_next[col] = p.head + 1 == p.L ? 0u : p.head + 1;
 
     if (rec) {
         if (series == 0) {
@@ -292,6 +294,7 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
         p.ring_len[col] = len + 1;
     }
     p.ring[(size_t)p.head * p.pitch + col] = infl_value;  // shift() + push() (:285-306)
+    p.ring_next[col] = p.head + 1 == p.L ? 0u : p.head + 1;
     if (rec) {
         if (series == 0) {
             rec->tick_ts = p.tick_ts;
@@ -306,6 +309,53 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
         rec->lb[series] = lb;
         rec->ub[series] = ub;
         rec->signal[series] = (int8_t)signal;
+    }
+}
+
+// Lists that were loaded for a key (resume) but did not advance while the key was silent are out of
+// step with the lag's global head.  Before such a key takes part in the lock-step pushes again its
+// column is rotated so that the list ends just before `head` (three strided reversals, one thread;
+// this happens at most once per silent period of a key).
+__device__ void rotate_column(double* col, size_t pitch, uint32_t L, uint32_t d) {
+    auto rev = [&](uint32_t lo, uint32_t hi) {  // reverse [lo, hi)
+        while (lo + 1 < hi) {
+            --hi;
+            const double a = col[(size_t)lo * pitch], b = col[(size_t)hi * pitch];
+            col[(size_t)lo * pitch] = b;
+            col[(size_t)hi * pitch] = a;
+            ++lo;
+        }
+    };
+    rev(0, L);
+    rev(0, d);
+    rev(d, L);  // new[(s + d) mod L] = old[s]
+}
+
+struct RingAlign {
+    int num_lags;
+    double* ring[APM_MAX_LAGS];
+    const uint32_t* len[APM_MAX_LAGS];
+    uint32_t* next[APM_MAX_LAGS];
+    uint32_t L[APM_MAX_LAGS], head[APM_MAX_LAGS];
+    size_t pitch;
+};
+
+
+// One thread per key, on the baseline stream right before the lag kernels of the same tick (so it
+// is ordered against the pushes of the previous tick).
+__global__ void __launch_bounds__(128) realign_kernel(const RingAlign ra, const uint8_t* __restrict__ emit, uint32_t K) {
+    const uint32_t key = blockIdx.x * blockDim.x + threadIdx.x;
+    if (key >= K || !emit[key]) return;
+    for (int l = 0; l < ra.num_lags; ++l) {
+#pragma unroll 1
+        for (int s = 0; s < APM_NUM_SERIES; ++s) {
+            const size_t col = (size_t)s * K + key;
+            if (ra.len[l][col] != 0 && ra.next[l][col] != ra.head[l]) {
+                const uint32_t d = (ra.head[l] + ra.L[l] - ra.next[l][col]) % ra.L[l];
+                rotate_column(ra.ring[l] + col, ra.pitch, ra.L[l], d);
+                ra.next[l][col] = ra.head[l];
+            }
+        }
     }
 }
 
@@ -357,7 +407,7 @@ apm_status apm_baseline_make_tmaps(apm_ctx* c) {
 apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st) {
     ProfScope prof_scope_(c, APM_PG_BASELINE, st);
     BaselineParams p;
-    p.ring = c->ring[l]; p.ring_len = c->ring_len[l]; p.zin = c->zin[buf]; p.thr = c->thr[l]; p.infl = c->infl[l];
+    p.ring = c->ring[l]; p.ring_len = c->ring_len[l]; p.ring_next = c->ring_next[l]; p.zin = c->zin[buf]; p.thr = c->thr[l]; p.infl = c->infl[l];
     p.seen = c->emit[buf];
     p.fs = c->d_fs ? c->d_fs + ((size_t)tick_slot * c->cfg.num_lags + l) * c->K : nullptr;
     p.K = c->K; p.L = (uint32_t)c->cfg.lags[l]; p.head = c->ring_head[l]; p.lag_value = (uint32_t)c->cfg.lags[l];
@@ -379,6 +429,21 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
     c->ring_head[l] = (c->ring_head[l] + 1) % p.L;
+    return APM_OK;
+}
+
+apm_status apm_launch_realign(apm_ctx* c, int buf, cudaStream_t st) {
+    ProfScope prof_scope_(c, APM_PG_BASELINE, st);
+    RingAlign ra;
+    ra.num_lags = c->cfg.num_lags;
+    ra.pitch = c->ring_pitch;
+    for (int l = 0; l < ra.num_lags; ++l) {
+        ra.ring[l] = c->ring[l]; ra.len[l] = c->ring_len[l]; ra.next[l] = c->ring_next[l];
+        ra.L[l] = (uint32_t)c->cfg.lags[l]; ra.head[l] = c->ring_head[l];
+    }
+    realign_kernel<<<(c->K + 127) / 128, 128, 0, st>>>(ra, c->emit[buf], c->K);
+    c->launches += 1;
+    CUDA_TRY(c, cudaGetLastError());
     return APM_OK;
 }
 

@@ -158,6 +158,36 @@ def test_ring_load_read_and_state_roundtrip(tmp_path):
     a.close(); b.close()
 
 
+def test_list_loaded_for_a_silent_key_realigns_when_the_key_appears():
+    """A resumed lag list of a key that stays silent for a while does not advance with the other
+    keys' lists; when the key shows up, its list must continue exactly where it stopped."""
+    from apmbackend_b200 import Engine
+    from oracle import capi as ocapi
+    from tests.gpu_util import engine_config, oracle_config
+    c = dict(CASES[0], lags=(8, 40), n=3000)
+    svc, jvm, ts, el = stream_for(c)
+    late_key = 5
+    quiet = (svc == late_key % c["S"]) & (jvm == late_key // c["S"]) & (np.arange(svc.size) < svc.size // 2)
+    svc, jvm, ts, el = svc[~quiet], jvm[~quiet], ts[~quiet], el[~quiet]  # key 5 is silent in the first half
+    eng = Engine(engine_config(c))
+    orc = ocapi.Pipeline(oracle_config(c), fast=True)
+    hist = np.round(np.linspace(20.0, 60.0, 40), 1)
+    hist[7] = np.nan
+    for s in range(3):
+        eng.ring_load(late_key, 1, s, hist + s)
+        orc.ring_load(late_key, 1, s, hist + s)
+        eng.ring_load(late_key, 0, s, hist[:5] + s)   # a partial list, too
+        orc.ring_load(late_key, 0, s, hist[:5] + s)
+    orc.consume(svc, jvm, ts, el)
+    eng.process_host(svc, jvm, ts, el)
+    assert_fs_equal(eng.fetch_fs(), orc.fs())
+    for li in (0, 1):
+        for s in range(3):
+            a, b = eng.ring_read(late_key, li, s), orc.ring_read(late_key, li, s)
+            assert a.tobytes() == b.tobytes()
+    eng.close()
+
+
 def test_alerts_are_the_signalled_fs_records():
     c = CASES[0]
     eng, orc, st, fs = run_both(c, stream_for(c))
