@@ -65,7 +65,7 @@ class KernelTimes(C.Structure):
 
 
 KERNEL_GROUPS = ("tick_finder", "keyed_reduce", "slot_clear", "radix_sort", "window_percentiles", "rolling_baseline",
-                 "alert_compaction")
+                 "alert_compaction", "list_realign")
 
 
 class ApmError(RuntimeError):

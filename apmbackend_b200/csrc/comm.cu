@@ -91,9 +91,10 @@ apm_status apm_comm_init(apm_ctx* c, int32_t rank, int32_t nranks, const void* u
     c->nccl_comm = comm;
     c->rank = rank;
     c->nranks = nranks;
-    // one block per rank: a header record (count in .key) followed by the alert records
-    const size_t block = 1 + (size_t)c->cfg.max_alerts_per_tick;
-    CUDA_TRY(c, cudaMalloc((void**)&c->d_gather, (size_t)(nranks + 1) * block * sizeof(apm_fs_record)));
+    // send area: header + this rank's alerts of all retained ticks; receive area: nranks headers, then nranks
+    // record blocks of the same capacity
+    const size_t G = (size_t)c->cfg.max_alerts_per_tick * c->cfg.out_ticks;
+    CUDA_TRY(c, cudaMalloc((void**)&c->d_gather, ((size_t)(nranks + 1) * (G + 1)) * sizeof(apm_fs_record)));
     return APM_OK;
 }
 
@@ -102,10 +103,12 @@ apm_status apm_gather_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint6
     *n = 0;
     if (!c->nccl_comm) return apm_fail(c, APM_E_STATE, "apm_comm_init has not been called");
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));  // the alert blocks are written on the baseline stream
-    const size_t G = c->cfg.max_alerts_per_tick, block = 1 + G;
-    apm_fs_record* send = c->d_gather;          // this rank's block
-    apm_fs_record* recv = c->d_gather + block;  // nranks blocks
-    // pack this rank's alerts of the retained ticks behind a header
+    const size_t A = c->cfg.max_alerts_per_tick, G = A * c->cfg.out_ticks;
+    apm_fs_record* send_hdr = c->d_gather;                       // [1]
+    apm_fs_record* send_rec = c->d_gather + 1;                   // [G]
+    apm_fs_record* recv_hdr = c->d_gather + 1 + G;               // [nranks]
+    apm_fs_record* recv_rec = recv_hdr + c->nranks;              // [nranks][<= G]
+    // pack this rank's alerts of the retained ticks
     std::vector<unsigned int> counts(c->ticks_buffered);
     if (c->ticks_buffered) {
         CUDA_TRY(c, cudaMemcpyAsync(counts.data(), c->d_alert_count, sizeof(unsigned int) * c->ticks_buffered, cudaMemcpyDeviceToHost, c->s_main));
@@ -113,10 +116,9 @@ apm_status apm_gather_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint6
     }
     size_t total = 0;
     for (uint32_t t = 0; t < c->ticks_buffered; ++t) {
-        if (counts[t] > G) return apm_fail(c, APM_E_CAPACITY, "more alerts in one tick than max_alerts_per_tick");
-        if (total + counts[t] > G) return apm_fail(c, APM_E_CAPACITY, "more alerts since the last gather than max_alerts_per_tick");
+        if (counts[t] > A) return apm_fail(c, APM_E_CAPACITY, "more alerts in one tick than max_alerts_per_tick");
         if (counts[t])
-            CUDA_TRY(c, cudaMemcpyAsync(send + 1 + total, c->d_alerts + (size_t)t * G, counts[t] * sizeof(apm_fs_record), cudaMemcpyDeviceToDevice, c->s_main));
+            CUDA_TRY(c, cudaMemcpyAsync(send_rec + total, c->d_alerts + (size_t)t * A, counts[t] * sizeof(apm_fs_record), cudaMemcpyDeviceToDevice, c->s_main));
         total += counts[t];
     }
     apm_fs_record hdr;
@@ -124,20 +126,29 @@ apm_status apm_gather_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint6
     hdr.key = (uint32_t)total;
     hdr.lag = (uint32_t)c->rank;
     hdr.tick_ts = (int64_t)c->counters.ticks;
-    CUDA_TRY(c, cudaMemcpyAsync(send, &hdr, sizeof hdr, cudaMemcpyHostToDevice, c->s_main));
-    nccl_result_t r = nccl().AllGather(send, recv, block * sizeof(apm_fs_record), NCCL_INT8, (nccl_comm_t)c->nccl_comm, c->s_main);
-    if (r) return nccl_fail(c, r, "ncclAllGather");
-    // headers first, then each rank's records
+    CUDA_TRY(c, cudaMemcpyAsync(send_hdr, &hdr, sizeof hdr, cudaMemcpyHostToDevice, c->s_main));
+    // 1) the counts, 2) the records, padded to the largest count of any rank
+    nccl_result_t r = nccl().AllGather(send_hdr, recv_hdr, sizeof(apm_fs_record), NCCL_INT8, (nccl_comm_t)c->nccl_comm, c->s_main);
+    if (r) return nccl_fail(c, r, "ncclAllGather (headers)");
     std::vector<apm_fs_record> hdrs(c->nranks);
-    CUDA_TRY(c, cudaMemcpy2DAsync(hdrs.data(), sizeof(apm_fs_record), recv, block * sizeof(apm_fs_record), sizeof(apm_fs_record), c->nranks, cudaMemcpyDeviceToHost, c->s_main));
+    CUDA_TRY(c, cudaMemcpyAsync(hdrs.data(), recv_hdr, sizeof(apm_fs_record) * c->nranks, cudaMemcpyDeviceToHost, c->s_main));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    size_t most = 0, sum = 0;
+    for (int rk = 0; rk < c->nranks; ++rk) {
+        if (hdrs[rk].key > G) return apm_fail(c, APM_E_COMM, "corrupt alert block header");
+        most = std::max<size_t>(most, hdrs[rk].key);
+        sum += hdrs[rk].key;
+    }
+    if (sum > cap) return apm_fail(c, APM_E_CAPACITY, "gather output buffer too small");
+    if (most) {
+        r = nccl().AllGather(send_rec, recv_rec, most * sizeof(apm_fs_record), NCCL_INT8, (nccl_comm_t)c->nccl_comm, c->s_main);
+        if (r) return nccl_fail(c, r, "ncclAllGather (records)");
+    }
     uint64_t w = 0;
     for (int rk = 0; rk < c->nranks; ++rk) {
         const uint32_t k = hdrs[rk].key;
-        if (k > G) return apm_fail(c, APM_E_COMM, "corrupt alert block header");
-        if (w + k > cap) return apm_fail(c, APM_E_CAPACITY, "gather output buffer too small");
         if (k && out)
-            CUDA_TRY(c, cudaMemcpyAsync(out + w, recv + (size_t)rk * block + 1, k * sizeof(apm_fs_record), cudaMemcpyDeviceToHost, c->s_main));
+            CUDA_TRY(c, cudaMemcpyAsync(out + w, recv_rec + (size_t)rk * most, k * sizeof(apm_fs_record), cudaMemcpyDeviceToHost, c->s_main));
         w += k;
     }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
@@ -152,6 +163,7 @@ apm_status apm_gather_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint6
         off += k;
     }
     c->counters.d2h_bytes += (w + c->nranks) * sizeof(apm_fs_record);
+    c->counters.alerts += w;
     *n = w;
     return APM_OK;
 }

@@ -106,7 +106,7 @@ struct apm_ctx {
     std::string err;
 };
 
-enum { APM_PG_TICKFIND = 0, APM_PG_REDUCE, APM_PG_CLEAR, APM_PG_SORT, APM_PG_TICKSTATS, APM_PG_BASELINE, APM_PG_ALERTS, APM_PG_COUNT };
+enum { APM_PG_TICKFIND = 0, APM_PG_REDUCE, APM_PG_CLEAR, APM_PG_SORT, APM_PG_TICKSTATS, APM_PG_BASELINE, APM_PG_ALERTS, APM_PG_REALIGN, APM_PG_COUNT };
 
 // Brackets the launches issued during its lifetime with an event pair when profiling is on.
 struct ProfScope {

@@ -433,7 +433,7 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
 }
 
 apm_status apm_launch_realign(apm_ctx* c, int buf, cudaStream_t st) {
-    ProfScope prof_scope_(c, APM_PG_BASELINE, st);
+    ProfScope prof_scope_(c, APM_PG_REALIGN, st);
     RingAlign ra;
     ra.num_lags = c->cfg.num_lags;
     ra.pitch = c->ring_pitch;

@@ -211,6 +211,7 @@ def main():
                         out_ticks=wl["span_buckets"] + 12, max_alerts_per_tick=max(K * max(len(wl["lags"]), 1), 1024),
                         device=local_rank)
     eng = Engine(ecfg)
+    gather_cap = 4 * K * world  # alert records a step may gather (fs records with a signal are a few % of all)
     if world > 1:
         import torch
         uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -246,7 +247,7 @@ def main():
     def run_step_device(s):
         eng.process_device(dev_steps[s].columns(), wl["n"])
         if world > 1 and wl["zscore"]:
-            eng.gather_alerts(ecfg.max_alerts_per_tick * world)
+            eng.gather_alerts(gather_cap)
         eng.release_ticks()
 
     def barrier():
@@ -310,7 +311,7 @@ def main():
                 al = eng.fetch_alerts(pinned=True)
                 out_bytes[0] = fs.nbytes + al.nbytes
                 if world > 1:
-                    eng.gather_alerts(ecfg.max_alerts_per_tick * world)
+                    eng.gather_alerts(gather_cap)
             else:
                 st = eng.fetch_stats(pinned=True)
                 out_bytes[0] = st.nbytes

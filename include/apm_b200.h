@@ -223,7 +223,7 @@ apm_status apm_state_load(apm_ctx* ctx, const char* path);
  * inserts, stream_insert_db.js:295-308).  When enabled, every launch group is bracketed by
  * CUDA events on the context's stream; read sums them per group and resets.
  * groups: 0 tick finder, 1 keyed reduce, 2 slot clear, 3 radix sort, 4 window/percentiles,
- *         5 rolling baseline, 6 alert compaction. */
+ *         5 rolling baseline, 6 alert compaction, 7 lag-list realignment. */
 #define APM_KT_GROUPS 8
 typedef struct apm_kernel_times {
     double ms[APM_KT_GROUPS];
@@ -279,7 +279,7 @@ apm_status apm_comm_unique_id(void* out128);                 /* ncclGetUniqueId 
 apm_status apm_comm_init(apm_ctx* ctx, int32_t rank, int32_t nranks, const void* unique_id128);
 /* Collective: every rank calls it at the same point of the stream.  Gathers the
  * alerts of this rank's retained ticks from all ranks (rank-major, then
- * tick, lag, key); at most max_alerts_per_tick records per rank per call. */
+ * tick, lag, key): first the counts, then the records padded to the largest count. */
 apm_status apm_gather_alerts(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
 
 #ifdef __cplusplus
