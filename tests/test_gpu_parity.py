@@ -188,6 +188,29 @@ def test_list_loaded_for_a_silent_key_realigns_when_the_key_appears():
     eng.close()
 
 
+@pytest.mark.parametrize("S,n,hi", [(50, 20000, 60000), (20000, 300000, 60000), (300, 50000, 5_000_000)],
+                         ids=["few-keys", "more-keys-than-table-entries", "durations-above-2^16"])
+def test_stats_only_mode_uses_the_shared_memory_tables(S, n, hi):
+    """Without percentiles the keyed reduction accumulates in per-CTA shared-memory hash tables
+    (misses and durations >= 2^16 ms go straight to the global planes): count, sum, min, max,
+    mean, tpm and the extension stddev must still equal the oracle's."""
+    from apmbackend_b200 import Engine, EngineConfig, _capi
+    from oracle import capi as ocapi
+    svc, jvm, ts, el = make_stream(77, n, S, 1, 60000, 12, elapsed_hi=hi, late_frac=0.02, late_ms=90000)
+    if hi > 65536:
+        el = el.copy()
+        el[::7] = np.minimum(el[::7].astype(np.int64) * 900, hi).astype(np.int32)
+    eng = Engine(EngineConfig(num_services=S, bucket_ms=60000, window=2, buffer=1, percentiles=(), lags=(), thresholds=(),
+                              influences=(), flags=_capi.F_KEEP_STATS, max_batch=1 << 16, out_ticks=64))
+    orc = ocapi.Pipeline(ocapi.make_config(S, 1, 60000, 2, 1, (), (0, 1), (), (), (), flags=ocapi.F_KEEP_STATS), fast=True)
+    orc.consume(svc, jvm, ts, el)
+    eng.process_host(svc, jvm, ts, el)
+    st = eng.fetch_stats()
+    assert st.size > 0 and int(st["count"].sum()) > n // 2
+    assert_stats_equal(st, orc.stats())
+    eng.close()
+
+
 def test_alerts_are_the_signalled_fs_records():
     c = CASES[0]
     eng, orc, st, fs = run_both(c, stream_for(c))
