@@ -1,0 +1,80 @@
+/*
+ * Hand-declared subset of Node-API (<= v6) used by apm_b200_addon.c.
+ *
+ * Neither Node.js nor its headers exist in this image, so the prototypes are restated here from
+ * the stable, documented Node-API ABI (node_api.h / js_native_api.h).  The addon is linked with
+ * these symbols left undefined: a real `node` process resolves them when it loads the .node file;
+ * tests/fake_napi.c provides test doubles so the marshalling can be exercised without Node.
+ */
+#ifndef NODE_API_MIN_H
+#define NODE_API_MIN_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct napi_env__* napi_env;
+typedef struct napi_value__* napi_value;
+typedef struct napi_ref__* napi_ref;
+typedef struct napi_callback_info__* napi_callback_info;
+
+typedef enum { napi_ok = 0, napi_invalid_arg, napi_object_expected, napi_string_expected, napi_name_expected,
+               napi_function_expected, napi_number_expected, napi_boolean_expected, napi_array_expected,
+               napi_generic_failure, napi_pending_exception } napi_status;
+typedef enum { napi_undefined, napi_null, napi_boolean, napi_number, napi_string, napi_symbol, napi_object,
+               napi_function, napi_external, napi_bigint } napi_valuetype;
+typedef enum { napi_int8_array, napi_uint8_array, napi_uint8_clamped_array, napi_int16_array, napi_uint16_array,
+               napi_int32_array, napi_uint32_array, napi_float32_array, napi_float64_array, napi_bigint64_array,
+               napi_biguint64_array } napi_typedarray_type;
+typedef enum { napi_default = 0 } napi_property_attributes;
+
+typedef napi_value (*napi_callback)(napi_env env, napi_callback_info info);
+typedef void (*napi_finalize)(napi_env env, void* finalize_data, void* finalize_hint);
+
+typedef struct {
+    const char* utf8name;
+    napi_value name;
+    napi_callback method;
+    napi_callback getter;
+    napi_callback setter;
+    napi_value value;
+    napi_property_attributes attributes;
+    void* data;
+} napi_property_descriptor;
+
+napi_status napi_define_class(napi_env env, const char* utf8name, size_t length, napi_callback constructor, void* data,
+                              size_t property_count, const napi_property_descriptor* properties, napi_value* result);
+napi_status napi_set_named_property(napi_env env, napi_value object, const char* utf8name, napi_value value);
+napi_status napi_get_named_property(napi_env env, napi_value object, const char* utf8name, napi_value* result);
+napi_status napi_has_named_property(napi_env env, napi_value object, const char* utf8name, bool* result);
+napi_status napi_get_cb_info(napi_env env, napi_callback_info cbinfo, size_t* argc, napi_value* argv, napi_value* this_arg,
+                             void** data);
+napi_status napi_wrap(napi_env env, napi_value js_object, void* native_object, napi_finalize finalize_cb, void* finalize_hint,
+                      napi_ref* result);
+napi_status napi_unwrap(napi_env env, napi_value js_object, void** result);
+napi_status napi_typeof(napi_env env, napi_value value, napi_valuetype* result);
+napi_status napi_get_value_double(napi_env env, napi_value value, double* result);
+napi_status napi_get_value_int64(napi_env env, napi_value value, int64_t* result);
+napi_status napi_get_value_uint32(napi_env env, napi_value value, uint32_t* result);
+napi_status napi_get_value_string_utf8(napi_env env, napi_value value, char* buf, size_t bufsize, size_t* result);
+napi_status napi_is_array(napi_env env, napi_value value, bool* result);
+napi_status napi_get_array_length(napi_env env, napi_value value, uint32_t* result);
+napi_status napi_get_element(napi_env env, napi_value object, uint32_t index, napi_value* result);
+napi_status napi_get_typedarray_info(napi_env env, napi_value typedarray, napi_typedarray_type* type, size_t* length,
+                                     void** data, napi_value* arraybuffer, size_t* byte_offset);
+napi_status napi_create_arraybuffer(napi_env env, size_t byte_length, void** data, napi_value* result);
+napi_status napi_create_object(napi_env env, napi_value* result);
+napi_status napi_create_double(napi_env env, double value, napi_value* result);
+napi_status napi_create_int64(napi_env env, int64_t value, napi_value* result);
+napi_status napi_create_string_utf8(napi_env env, const char* str, size_t length, napi_value* result);
+napi_status napi_get_undefined(napi_env env, napi_value* result);
+napi_status napi_throw_error(napi_env env, const char* code, const char* msg);
+
+#define NAPI_AUTO_LENGTH SIZE_MAX
+
+#ifdef __cplusplus
+}
+#endif
+#endif
