@@ -106,6 +106,7 @@ SYMBOLS = {
     "apm_state_load": (C.c_int32, [C.c_void_p, C.c_char_p]),
     "apm_profile_enable": (C.c_int32, [C.c_void_p, C.c_int32]),
     "apm_profile_read": (C.c_int32, [C.c_void_p, C.POINTER(KernelTimes)]),
+    "apm_set_overlap": (C.c_int32, [C.c_void_p, C.c_int32]),
     "apm_timer_start": (C.c_int32, [C.c_void_p]),
     "apm_timer_stop": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
     "apm_get_counters": (C.c_int32, [C.c_void_p, C.POINTER(Counters)]),

@@ -69,8 +69,11 @@ apm_status validate(const apm_config* cfg) {
 
 // waits for everything queued on the context (ingest/sort stream, baseline stream, copies)
 apm_status sync_all(apm_ctx* c) {
+    apm_status fl = apm_flush_pending(c);
+    if (fl) return fl;
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     return APM_OK;
 }
@@ -79,15 +82,36 @@ bool with_pct(const apm_ctx* c) { return (c->cfg.flags & APM_F_PERCENTILES) && c
 bool with_z(const apm_ctx* c) { return (c->cfg.flags & APM_F_ZSCORE) && c->cfg.num_lags > 0; }
 
 apm_status refresh_counters(apm_ctx* c) {
+    apm_status fl = apm_flush_pending(c);
+    if (fl) return fl;
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));  // first: the baseline stream also writes a counter (pending_lists)
     CUDA_TRY(c, cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->s_main));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     c->counters.tx_ingested = c->h_counters->ingested;
     c->counters.tx_dropped = c->h_counters->dropped;
     c->counters.tx_invalid = c->h_counters->invalid + c->h_counters->future;
     c->counters.kernel_launches = c->launches;
+    if (c->may_misalign && c->tick_seq > c->misalign_mark && c->h_counters->pending_lists == 0) c->may_misalign = false;
     if (c->h_counters->log_overflow)
         return apm_fail(c, APM_E_CAPACITY, "a bucket's value log overflowed max_tx_per_bucket; percentiles of that bucket are incomplete - recreate the context with a larger capacity");
+    return APM_OK;
+}
+
+// The z-score stage of one tick: realignment (when lists were loaded), one kernel per lag, alert compaction.
+apm_status launch_baseline_group(apm_ctx* c, const PendingBaseline& pb, cudaStream_t sb) {
+    apm_status st;
+    if (c->may_misalign) {
+        st = apm_launch_realign(c, pb.buf, sb);  // lists of keys that were silent re-enter the lock step
+        if (st) return st;
+    }
+    for (int l = 0; l < c->cfg.num_lags; ++l) {  // Object.entries(lags): ascending (:217)
+        st = apm_launch_baseline(c, l, pb.tick_ts, pb.fslot, pb.buf, sb);
+        if (st) return st;
+    }
+    if (c->cfg.flags & APM_F_ALERTS) {
+        st = apm_launch_compact_alerts(c, pb.fslot, pb.tslot, sb);
+        if (st) return st;
+    }
     return APM_OK;
 }
 
@@ -95,6 +119,8 @@ apm_status refresh_counters(apm_ctx* c) {
 // (stream_calc_stats.js:348-367) and, behind it, processData for each emitted StatEntry.
 apm_status do_tick(apm_ctx* c, int64_t new_latest) {
     if (new_latest <= c->latest) return apm_fail(c, APM_E_INVALID, "tick label must exceed latestBucket");
+    apm_status fl = apm_flush_pending(c);  // the previous tick's baseline goes in behind whatever was ingested since
+    if (fl) return fl;
     const bool keep_any = c->cfg.flags & (APM_F_KEEP_STATS | APM_F_KEEP_FS | APM_F_ALERTS);
     if (keep_any && c->ticks_buffered >= c->cfg.out_ticks) return apm_fail(c, APM_E_WOULDBLOCK, "output ring full: fetch results first");
     const int64_t old_latest = c->latest;
@@ -146,29 +172,21 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
     const uint32_t tslot = keep_any ? c->ticks_buffered : 0;
     const uint64_t seq = c->tick_seq++;
     const int buf = (int)(seq & 1), ev = (int)(seq & 3);
-    cudaStream_t sb = c->overlap ? c->s_base : c->s_main;
     // the window kernel overwrites zin/emit[buf], last read by the baseline of two ticks ago
     if (c->overlap && with_z(c) && seq >= 2) CUDA_TRY(c, cudaStreamWaitEvent(c->s_main, c->ev_base[(seq - 2) & 3], 0));
     st = apm_launch_tick_stats(c, w, tick_ts, (c->cfg.flags & APM_F_KEEP_STATS) ? tslot : 0, buf);
     if (st) return st;
     if (with_z(c)) {
-        // the baseline of this tick runs on its own stream, under the ingest / sort of the next tick
+        PendingBaseline pb = {true, tick_ts, (c->cfg.flags & APM_F_KEEP_FS) ? tslot : 0, tslot, buf, ev};
         if (c->overlap) {
+            // Launched later - behind the next segment's ingest kernel (see apm_flush_pending) - so that the
+            // bandwidth-hungry baseline does not start on top of the latency-bound head of the next tick's chain.
             CUDA_TRY(c, cudaEventRecord(c->ev_stats[ev], c->s_main));
-            CUDA_TRY(c, cudaStreamWaitEvent(sb, c->ev_stats[ev], 0));
-        }
-        const uint32_t fslot = (c->cfg.flags & APM_F_KEEP_FS) ? tslot : 0;
-        st = apm_launch_realign(c, buf, sb);  // lists of keys that were silent re-enter the lock step
-        if (st) return st;
-        for (int l = 0; l < c->cfg.num_lags; ++l) {  // Object.entries(lags): ascending (:217)
-            st = apm_launch_baseline(c, l, tick_ts, fslot, buf, sb);
+            c->pending = pb;
+        } else {
+            st = launch_baseline_group(c, pb, c->s_main);
             if (st) return st;
         }
-        if (c->cfg.flags & APM_F_ALERTS) {
-            st = apm_launch_compact_alerts(c, fslot, tslot, sb);
-            if (st) return st;
-        }
-        if (c->overlap) CUDA_TRY(c, cudaEventRecord(c->ev_base[ev], sb));
     }
     if (keep_any) c->ticks_buffered++;
     c->counters.ticks++;
@@ -206,6 +224,7 @@ static apm_status fetch_dense(apm_ctx* c, const R* d_src, size_t per_tick, R* ou
     if (total == 0) return APM_OK;
     if (cap < total) return apm_fail(c, APM_E_CAPACITY, "output buffer smaller than ticks_buffered * records per tick");
     CUDA_TRY(c, cudaMemcpyAsync(out, d_src, total * sizeof(R), cudaMemcpyDeviceToHost, c->s_main));
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     c->counters.d2h_bytes += total * sizeof(R);
@@ -235,6 +254,21 @@ static apm_status finish_result(apm_ctx* c, const apm_counters& before, apm_tick
 
 }  // namespace
 
+// Launches the deferred baseline of the last tick on the baseline stream, ordered after that tick's window
+// kernel and after everything queued on the ingest stream so far.
+apm_status apm_flush_pending(apm_ctx* c) {
+    if (!c->pending.valid) return APM_OK;
+    const PendingBaseline pb = c->pending;
+    c->pending.valid = false;
+    CUDA_TRY(c, cudaStreamWaitEvent(c->s_base, c->ev_stats[pb.ev], 0));
+    CUDA_TRY(c, cudaEventRecord(c->ev_mid, c->s_main));
+    CUDA_TRY(c, cudaStreamWaitEvent(c->s_base, c->ev_mid, 0));
+    apm_status st = launch_baseline_group(c, pb, c->s_base);
+    if (st) return st;
+    CUDA_TRY(c, cudaEventRecord(c->ev_base[pb.ev], c->s_base));
+    return APM_OK;
+}
+
 extern "C" {
 
 uint32_t apm_abi_version(void) { return APM_ABI_VERSION; }
@@ -247,6 +281,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     if (c->s_main) cudaStreamSynchronize(c->s_main);
+    c->pending.valid = false;
     if (c->s_base) cudaStreamSynchronize(c->s_base);
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
     cudaFree(c->acc_raw); cudaFree(c->seen); cudaFree(c->slot_meta);
@@ -261,6 +296,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->d_gather);
     for (int i = 0; i < 2; ++i) { if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); if (c->ev_consumed[i]) cudaEventDestroy(c->ev_consumed[i]); }
     for (int i = 0; i < 4; ++i) { if (c->ev_stats[i]) cudaEventDestroy(c->ev_stats[i]); if (c->ev_base[i]) cudaEventDestroy(c->ev_base[i]); }
+    if (c->ev_mid) cudaEventDestroy(c->ev_mid);
     if (c->s_base) cudaStreamDestroy(c->s_base);
     if (c->s_main) cudaStreamDestroy(c->s_main);
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
@@ -311,6 +347,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_stats[i], cudaEventDisableTiming));
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_base[i], cudaEventDisableTiming));
     }
+    TRY_CREATE(cudaEventCreateWithFlags(&c->ev_mid, cudaEventDisableTiming));
     if (const char* e = getenv("APM_NO_OVERLAP")) c->overlap = atoi(e) == 0;
     for (int i = 0; i < 2; ++i) {
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
@@ -500,6 +537,7 @@ apm_status apm_process_host(apm_ctx* c, const apm_tx_columns* h, uint64_t n, apm
 apm_status apm_set_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, int32_t l, const double* thr, const double* infl) {
     if (!c || !thr || !infl) return APM_E_INVALID;
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || (uint64_t)key_lo + n > c->K) return apm_fail(c, APM_E_INVALID, "set_key_params: range");
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     CUDA_TRY(c, cudaMemcpy(c->thr[l] + key_lo, thr, n * sizeof(double), cudaMemcpyHostToDevice));
@@ -510,6 +548,7 @@ apm_status apm_set_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, int32_t l
 apm_status apm_drop_lag(apm_ctx* c, int32_t l) {
     if (!c) return APM_E_INVALID;
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags) return apm_fail(c, APM_E_INVALID, "drop_lag: index");
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaMemsetAsync(c->ring_len[l], 0, sizeof(uint32_t) * 3 * c->K, c->s_main));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
@@ -539,6 +578,7 @@ apm_status apm_fetch_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64
     if (c->ticks_buffered == 0) return APM_OK;
     std::vector<unsigned int> counts(c->ticks_buffered);
     CUDA_TRY(c, cudaMemcpyAsync(counts.data(), c->d_alert_count, sizeof(unsigned int) * c->ticks_buffered, cudaMemcpyDeviceToHost, c->s_main));
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     uint64_t total = 0;
@@ -565,6 +605,7 @@ apm_status apm_fetch_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64
 apm_status apm_release_ticks(apm_ctx* c) {
     if (!c) return APM_E_INVALID;
     if (c->d_alert_count) {
+        { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
         CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
         CUDA_TRY(c, cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * c->cfg.out_ticks, c->s_main));
         CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
@@ -578,6 +619,7 @@ apm_status apm_ring_load(apm_ctx* c, uint32_t key, int32_t l, int32_t series, co
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || series < 0 || series >= APM_NUM_SERIES || key >= c->K) return apm_fail(c, APM_E_INVALID, "ring_load: index");
     const uint32_t L = (uint32_t)c->cfg.lags[l];
     if (len > L) return apm_fail(c, APM_E_INVALID, "ring_load: list longer than its lag");
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     const size_t ncol = c->ring_pitch, col = (size_t)series * c->K + key;
@@ -590,6 +632,8 @@ apm_status apm_ring_load(apm_ctx* c, uint32_t key, int32_t l, int32_t series, co
     if (len > n1) CUDA_TRY(c, cudaMemcpy2D(c->ring[l] + col, ncol * sizeof(double), tmp.data() + n1, sizeof(double), sizeof(double), len - n1, cudaMemcpyHostToDevice));
     CUDA_TRY(c, cudaMemcpy(c->ring_len[l] + col, &len, sizeof(uint32_t), cudaMemcpyHostToDevice));
     CUDA_TRY(c, cudaMemcpy(c->ring_next[l] + col, &head, sizeof(uint32_t), cudaMemcpyHostToDevice));  // the list ends just before `head`
+    c->may_misalign = true;
+    c->misalign_mark = c->tick_seq;
     return APM_OK;
 }
 
@@ -598,6 +642,7 @@ apm_status apm_ring_load_all(apm_ctx* c, int32_t l, const double* values, uint32
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags) return apm_fail(c, APM_E_INVALID, "ring_load_all: index");
     const uint32_t L = (uint32_t)c->cfg.lags[l];
     if (len > L) return apm_fail(c, APM_E_INVALID, "ring_load_all: lists longer than the lag");
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     const size_t ncol = 3 * (size_t)c->K, row = ncol * sizeof(double), pitch = c->ring_pitch * sizeof(double);
@@ -609,12 +654,15 @@ apm_status apm_ring_load_all(apm_ctx* c, int32_t l, const double* values, uint32
     CUDA_TRY(c, cudaMemcpy(c->ring_len[l], lens.data(), ncol * sizeof(uint32_t), cudaMemcpyHostToDevice));
     std::vector<uint32_t> nexts(ncol, head);
     CUDA_TRY(c, cudaMemcpy(c->ring_next[l], nexts.data(), ncol * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    c->may_misalign = true;
+    c->misalign_mark = c->tick_seq;
     return APM_OK;
 }
 
 apm_status apm_ring_read(apm_ctx* c, uint32_t key, int32_t l, int32_t series, double* values, uint32_t cap, uint32_t* len_out) {
     if (!c || !len_out) return APM_E_INVALID;
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || series < 0 || series >= APM_NUM_SERIES || key >= c->K) return apm_fail(c, APM_E_INVALID, "ring_read: index");
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     const uint32_t L = (uint32_t)c->cfg.lags[l];
@@ -670,6 +718,7 @@ extern "C" apm_status apm_timer_start(apm_ctx* c) {
     if (!c) return APM_E_INVALID;
     if (!c->timer[0]) { CUDA_TRY(c, cudaEventCreate(&c->timer[0])); CUDA_TRY(c, cudaEventCreate(&c->timer[1])); }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaEventRecord(c->timer[0], c->s_main));
     return APM_OK;
@@ -679,6 +728,7 @@ extern "C" apm_status apm_timer_stop(apm_ctx* c, double* ms) {
     if (!c || !ms) return APM_E_INVALID;
     if (!c->timer[0]) return apm_fail(c, APM_E_STATE, "timer_stop without timer_start");
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));  // the stop event on s_main then follows all work of both streams
     CUDA_TRY(c, cudaEventRecord(c->timer[1], c->s_main));
     CUDA_TRY(c, cudaEventSynchronize(c->timer[1]));
@@ -697,6 +747,7 @@ extern "C" apm_status apm_profile_enable(apm_ctx* c, int32_t on) {
 extern "C" apm_status apm_profile_read(apm_ctx* c, apm_kernel_times* out) {
     if (!c || !out) return APM_E_INVALID;
     memset(out, 0, sizeof *out);
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     for (auto& sp : c->prof_spans) {
@@ -709,6 +760,15 @@ extern "C" apm_status apm_profile_read(apm_ctx* c, apm_kernel_times* out) {
         c->prof_pool.push_back(sp.b);
     }
     c->prof_spans.clear();
+    return APM_OK;
+}
+
+// Run the rolling baseline on its own stream under the next tick's ingest/sort (default), or in line.
+extern "C" apm_status apm_set_overlap(apm_ctx* c, int32_t on) {
+    if (!c) return APM_E_INVALID;
+    apm_status st = sync_all(c);
+    if (st) return st;
+    c->overlap = on != 0;
     return APM_OK;
 }
 

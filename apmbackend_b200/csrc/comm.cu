@@ -102,6 +102,7 @@ apm_status apm_gather_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint6
     if (!c || !n) return APM_E_INVALID;
     *n = 0;
     if (!c->nccl_comm) return apm_fail(c, APM_E_STATE, "apm_comm_init has not been called");
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));  // the alert blocks are written on the baseline stream
     const size_t A = c->cfg.max_alerts_per_tick, G = A * c->cfg.out_ticks;
     apm_fs_record* send_hdr = c->d_gather;                       // [1]

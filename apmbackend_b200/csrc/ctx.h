@@ -12,6 +12,13 @@ struct TickMark {
     long long label;         // its bucket label (the new latestBucket)
 };
 
+struct PendingBaseline {
+    bool valid;
+    int64_t tick_ts;
+    uint32_t fslot, tslot;
+    int buf, ev;
+};
+
 struct apm_ctx {
     apm_config cfg;
     uint32_t K = 0;       // keys = num_services * num_jvms
@@ -25,6 +32,8 @@ struct apm_ctx {
     // which overlaps the ingest/sort of tick i+1 (linked by ev_stats / ev_base).  s_copy: H2D staging.
     cudaStream_t s_main = nullptr, s_copy = nullptr, s_base = nullptr;
     cudaEvent_t ev_stats[4] = {nullptr, nullptr, nullptr, nullptr}, ev_base[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_mid = nullptr;
+    PendingBaseline pending = {false, 0, 0, 0, 0, 0};  // baseline of the last tick, not launched yet
     uint64_t tick_seq = 0;        // ticks run so far (selects the zin / emit buffer and the events)
     bool overlap = true;          // APM_NO_OVERLAP=1 runs the baseline on s_main (A/B measurements)
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
@@ -78,6 +87,8 @@ struct apm_ctx {
     size_t ring_pitch = 0;  // doubles per ring row: 3K rounded up to 32 (TMA box width, 256-byte rows)
     CUtensorMap ring_tmap[APM_MAX_LAGS];  // 2-D view [L][ring_pitch] of each ring for the bulk-tensor loads
     bool ring_tmap_ok = false;
+    uint64_t misalign_mark = 0;  // tick_seq at the last list load: the pending count is only meaningful after a later tick
+    bool may_misalign = false;  // lists were loaded for keys that may be silent: run the realign kernel until none is left
     uint32_t ring_head[APM_MAX_LAGS] = {0, 0, 0, 0};                          // slot the next push writes
     double* thr[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};         // [K]
     double* infl[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};        // [K]
@@ -148,3 +159,5 @@ apm_status apm_launch_realign(apm_ctx* c, int buf, cudaStream_t st);
 apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot, cudaStream_t st);
 // comm.cu
 void apm_comm_destroy_internal(apm_ctx* c);
+// capi.cu
+apm_status apm_flush_pending(apm_ctx* c);

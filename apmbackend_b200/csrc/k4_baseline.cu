@@ -343,9 +343,17 @@ struct RingAlign {
 
 // One thread per key, on the baseline stream right before the lag kernels of the same tick (so it
 // is ordered against the pushes of the previous tick).
-__global__ void __launch_bounds__(128) realign_kernel(const RingAlign ra, const uint8_t* __restrict__ emit, uint32_t K) {
+__global__ void __launch_bounds__(128) realign_kernel(const RingAlign ra, const uint8_t* __restrict__ emit, uint32_t K,
+                                                      uint32_t* __restrict__ pending) {
     const uint32_t key = blockIdx.x * blockDim.x + threadIdx.x;
-    if (key >= K || !emit[key]) return;
+    if (key >= K) return;
+    if (!emit[key]) {  // still silent: remember that it holds a list, so the host keeps this kernel in the tick
+        bool holds = false;
+        for (int l = 0; l < ra.num_lags; ++l)
+            for (int s = 0; s < APM_NUM_SERIES; ++s) holds |= ra.len[l][(size_t)s * K + key] != 0;
+        if (holds) atomicAdd(pending, 1u);
+        return;
+    }
     for (int l = 0; l < ra.num_lags; ++l) {
 #pragma unroll 1
         for (int s = 0; s < APM_NUM_SERIES; ++s) {
@@ -441,7 +449,8 @@ apm_status apm_launch_realign(apm_ctx* c, int buf, cudaStream_t st) {
         ra.ring[l] = c->ring[l]; ra.len[l] = c->ring_len[l]; ra.next[l] = c->ring_next[l];
         ra.L[l] = (uint32_t)c->cfg.lags[l]; ra.head[l] = c->ring_head[l];
     }
-    realign_kernel<<<(c->K + 127) / 128, 128, 0, st>>>(ra, c->emit[buf], c->K);
+    CUDA_TRY(c, cudaMemsetAsync(&c->d_counters->pending_lists, 0, sizeof(uint32_t), st));
+    realign_kernel<<<(c->K + 127) / 128, 128, 0, st>>>(ra, c->emit[buf], c->K, &c->d_counters->pending_lists);
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;

@@ -55,6 +55,7 @@ apm_status apm_state_save(apm_ctx* c, const char* path) {
     if (!c || !path) return APM_E_INVALID;
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     File fl;
     fl.f = fopen(path, "wb");
@@ -95,6 +96,7 @@ apm_status apm_state_load(apm_ctx* c, const char* path) {
     if (!c || !path) return APM_E_INVALID;
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     File fl;
     fl.f = fopen(path, "rb");
@@ -129,6 +131,8 @@ apm_status apm_state_load(apm_ctx* c, const char* path) {
     for (int s = 0; s < c->S; ++s) c->slot_label[s] = h.slot_label[s];
     for (int l = 0; l < c->cfg.num_lags; ++l) c->ring_head[l] = h.ring_head[l];
     c->ticks_buffered = 0;
+    c->may_misalign = true;  // loaded lists of keys that are silent now re-enter the lock step when they emit
+    c->misalign_mark = c->tick_seq;
     return APM_OK;
 }
 

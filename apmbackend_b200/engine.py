@@ -228,6 +228,9 @@ class Engine:
         self._check(self._lib.apm_get_counters(self._h, C.byref(c)))
         return c
 
+    def set_overlap(self, on: bool):
+        self._check(self._lib.apm_set_overlap(self._h, 1 if on else 0))
+
     def timer_start(self):
         self._check(self._lib.apm_timer_start(self._h))
 

@@ -230,6 +230,9 @@ typedef struct apm_kernel_times {
     uint64_t spans[APM_KT_GROUPS]; /* event-bracketed launch groups (one per tick and kernel group) */
 } apm_kernel_times;
 apm_status apm_profile_enable(apm_ctx* ctx, int32_t on);
+/* The baseline of tick i normally runs on a second stream under the ingest / sort of tick i+1;
+ * 0 runs everything in line on one stream (isolated kernel timings).  Results are identical. */
+apm_status apm_set_overlap(apm_ctx* ctx, int32_t on);
 /* stopwatch: CUDA events on the context's stream; stop waits for the queued work and returns ms. */
 apm_status apm_timer_start(apm_ctx* ctx);
 apm_status apm_timer_stop(apm_ctx* ctx, double* ms);
