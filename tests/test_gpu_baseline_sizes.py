@@ -119,3 +119,43 @@ def test_cfg3_hundred_million_transactions_sampled_keys_and_invariants():
     assert_fs_equal(fs[m_fs], ofs)
     assert ofs.size > 50 * sample.size
     eng.close()
+
+
+def test_cfg5_heavy_skew_top10_services_carry_80_percent():
+    """BASELINE configs[4]'s distribution (top 10 services = 80 % of the traffic) on one GPU at a
+    reduced length (8 M transactions): the hot keys' 100 k-value runs go through the warp-combined
+    path of the accumulator rebuild and the long-run percentile selection; all of them plus a
+    sample of cold keys are compared with the oracle, and every tick's totals are checked."""
+    K, n, buckets = 10_000, 8_000_000, 12
+    spec = syn.StreamSpec(seed=4, n=n, num_services=K, span_ms=buckets * 60_000, hot=(10, 0.8), shift_mod=3)
+    stream = syn.SynthStream(spec, device=True)
+    cols = syn.DeviceColumns(n)
+    stream.generate_device(cols)
+    lags, thr, infl = (6,), (1.5,), (0.3,)
+    eng = Engine(EngineConfig(num_services=K, bucket_ms=60_000, window=1, buffer=0, percentiles=(50.0, 95.0, 99.0),
+                              z_series_pct=(1, 2), lags=lags, thresholds=thr, influences=infl,
+                              max_tx_per_bucket=int(n / buckets * 1.5), max_batch=1 << 22, out_ticks=32, max_alerts_per_tick=K))
+    res = eng.process_device(cols.columns(), n)
+    st, fs = eng.fetch_stats(), eng.fetch_fs()
+    svc, jvm, ts, el = cols.to_host()
+    cols.free()
+    assert res.tx_ingested + res.tx_dropped == n
+    hot_share = np.count_nonzero(svc < 10) / n
+    assert 0.78 < hot_share < 0.82
+    sample = np.unique(np.concatenate([np.arange(10), np.random.default_rng(3).choice(K, 60, replace=False)]))
+    keep = np.zeros(K, np.uint8)
+    keep[sample] = 1
+    orc = ocapi.Pipeline(ocapi.make_config(K, 1, 60_000, 1, 0, (50.0, 95.0, 99.0), (1, 2), lags, thr, infl), fast=True)
+    orc.set_filter(keep)
+    orc.consume(svc, jvm, ts, el)
+    assert_stats_equal(st[np.isin(st["key"], sample)], orc.stats())
+    assert_fs_equal(fs[np.isin(fs["key"], sample)], orc.fs())
+    assert int(st[st["key"] < 10]["count"].max()) > 40_000
+    labels = ts // 60_000
+    run = np.maximum.accumulate(labels)
+    tick_pos = np.flatnonzero(np.concatenate([[True], run[1:] > run[:-1]]))
+    for i in range(1, tick_pos.size):
+        closing = labels[tick_pos[i]] - 1
+        rows = st[st["tick_ts"] == closing * 60_000]
+        assert int(rows["count"].sum()) == int(np.count_nonzero(labels[:tick_pos[i]] == closing))
+    eng.close()
