@@ -60,6 +60,16 @@ class Counters(C.Structure):
         "h2d_bytes", "d2h_bytes", "kernel_launches", "keys_seen")]
 
 
+class AlertRules(C.Structure):
+    """apm_alert_rules; defaults are config/apm_config.json:189-204."""
+    _fields_ = [("struct_size", C.c_uint32), ("enabled", C.c_int32), ("window", C.c_int32), ("required", C.c_int32),
+                ("alert_on_both_only", C.c_int32), ("suppressed_lag_mask", C.c_uint32),
+                ("hard_max_ms", C.c_double), ("hard_min_ms", C.c_double), ("hard_min_tpm", C.c_double)]
+
+
+CAUSE_AVG_HARD_MAX, CAUSE_P75_HARD_MAX, CAUSE_AVG_UB, CAUSE_P75_UB, CAUSE_BOTH_UB = 1, 2, 4, 8, 16
+
+
 class KernelTimes(C.Structure):
     _fields_ = [("ms", C.c_double * 8), ("spans", C.c_uint64 * 8)]
 
@@ -90,6 +100,8 @@ SYMBOLS = {
     "apm_process_device": (C.c_int32, [C.c_void_p, C.POINTER(TxColumns), C.c_uint64, C.POINTER(TickResult)]),
     "apm_set_key_params": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int32, C.c_void_p, C.c_void_p]),
     "apm_drop_lag": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "apm_set_alert_rules": (C.c_int32, [C.c_void_p, C.POINTER(AlertRules)]),
+    "apm_set_alert_key_params": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]),
     "apm_fetch_stats": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "apm_fetch_fs": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "apm_fetch_alerts": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),

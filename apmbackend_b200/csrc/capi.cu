@@ -108,6 +108,8 @@ apm_status launch_baseline_group(apm_ctx* c, const PendingBaseline& pb, cudaStre
         st = apm_launch_baseline(c, l, pb.tick_ts, pb.fslot, pb.buf, sb);
         if (st) return st;
     }
+    st = apm_launch_alert_counter(c, pb.fslot, sb);  // processFSEntry's counter, when rules are set
+    if (st) return st;
     if (c->cfg.flags & APM_F_ALERTS) {
         st = apm_launch_compact_alerts(c, pb.fslot, pb.tslot, sb);
         if (st) return st;
@@ -294,6 +296,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
     for (int l = 0; l < APM_MAX_LAGS; ++l) { cudaFree(c->ring[l]); cudaFree(c->ring_len[l]); cudaFree(c->ring_next[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
     cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->d_gather);
+    cudaFree(c->alert_count); cudaFree(c->alert_hard_max); cudaFree(c->alert_suppressed);
     for (int i = 0; i < 2; ++i) { if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); if (c->ev_consumed[i]) cudaEventDestroy(c->ev_consumed[i]); }
     for (int i = 0; i < 4; ++i) { if (c->ev_stats[i]) cudaEventDestroy(c->ev_stats[i]); if (c->ev_base[i]) cudaEventDestroy(c->ev_base[i]); }
     if (c->ev_mid) cudaEventDestroy(c->ev_mid);
@@ -405,6 +408,12 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
             TRY_CREATE(cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * cfg->out_ticks, c->s_main));
         }
         c->ring_pitch = (3 * K + 31) & ~(size_t)31;
+        TRY_CREATE(dalloc(&c->alert_count, (size_t)cfg->num_lags * K));
+        TRY_CREATE(cudaMemsetAsync(c->alert_count, 0, sizeof(uint32_t) * cfg->num_lags * K, c->s_main));
+        TRY_CREATE(dalloc(&c->alert_hard_max, K));
+        TRY_CREATE(cudaMemsetAsync(c->alert_hard_max, 0, sizeof(double) * K, c->s_main));
+        TRY_CREATE(dalloc(&c->alert_suppressed, K));
+        TRY_CREATE(cudaMemsetAsync(c->alert_suppressed, 0, K, c->s_main));
         for (int l = 0; l < cfg->num_lags; ++l) {
             const size_t L = (size_t)cfg->lags[l];
             TRY_CREATE(dalloc(&c->ring[l], L * c->ring_pitch));
@@ -542,6 +551,27 @@ apm_status apm_set_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, int32_t l
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     CUDA_TRY(c, cudaMemcpy(c->thr[l] + key_lo, thr, n * sizeof(double), cudaMemcpyHostToDevice));
     CUDA_TRY(c, cudaMemcpy(c->infl[l] + key_lo, infl, n * sizeof(double), cudaMemcpyHostToDevice));
+    return APM_OK;
+}
+
+apm_status apm_set_alert_rules(apm_ctx* c, const apm_alert_rules* r) {
+    if (!c || !r) return APM_E_INVALID;
+    if (r->struct_size != sizeof(apm_alert_rules)) return apm_fail(c, APM_E_INVALID, "apm_alert_rules.struct_size mismatch");
+    if (!with_z(c)) return apm_fail(c, APM_E_STATE, "alert rules need APM_F_ZSCORE and at least one lag");
+    if (r->enabled && !(c->cfg.flags & (APM_F_KEEP_FS | APM_F_ALERTS))) return apm_fail(c, APM_E_STATE, "alert rules need APM_F_KEEP_FS or APM_F_ALERTS");
+    apm_status st = sync_all(c);
+    if (st) return st;
+    c->alert_rules = *r;
+    return APM_OK;
+}
+
+apm_status apm_set_alert_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, const double* hard_max_ms, const uint8_t* suppressed) {
+    if (!c || !hard_max_ms || !suppressed) return APM_E_INVALID;
+    if (!with_z(c) || (uint64_t)key_lo + n > c->K) return apm_fail(c, APM_E_INVALID, "set_alert_key_params: range");
+    apm_status st = sync_all(c);
+    if (st) return st;
+    CUDA_TRY(c, cudaMemcpy(c->alert_hard_max + key_lo, hard_max_ms, n * sizeof(double), cudaMemcpyHostToDevice));
+    CUDA_TRY(c, cudaMemcpy(c->alert_suppressed + key_lo, suppressed, n, cudaMemcpyHostToDevice));
     return APM_OK;
 }
 

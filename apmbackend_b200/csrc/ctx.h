@@ -92,6 +92,11 @@ struct apm_ctx {
     uint32_t ring_head[APM_MAX_LAGS] = {0, 0, 0, 0};                          // slot the next push writes
     double* thr[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};         // [K]
     double* infl[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};        // [K]
+    // alert counter core (stream_process_alerts.js:348-434)
+    apm_alert_rules alert_rules = {};
+    uint32_t* alert_count = nullptr;   // [num_lags][K] recentAlertCounts
+    double* alert_hard_max = nullptr;  // [K] per-key hardMaxMsAlertThreshold, <= 0: default
+    uint8_t* alert_suppressed = nullptr;  // [K]
 
     DevCounters* d_counters = nullptr;
     DevCounters* h_counters = nullptr;  // pinned mirror
@@ -156,6 +161,7 @@ apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_
 apm_status apm_launch_baseline(apm_ctx* c, int lag_idx, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st);
 apm_status apm_baseline_make_tmaps(apm_ctx* c);
 apm_status apm_launch_realign(apm_ctx* c, int buf, cudaStream_t st);
+apm_status apm_launch_alert_counter(apm_ctx* c, uint32_t fs_slot, cudaStream_t st);
 apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot, cudaStream_t st);
 // comm.cu
 void apm_comm_destroy_internal(apm_ctx* c);

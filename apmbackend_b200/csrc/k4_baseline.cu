@@ -367,15 +367,69 @@ __global__ void __launch_bounds__(128) realign_kernel(const RingAlign ra, const 
     }
 }
 
+// ---- alert counter core --------------------------------------------------------------------------
+// processFSEntry (stream_process_alerts.js:348-434) for one (lag, key) per thread.  Its inputs are
+// the fields an `fs` line carries after the toFixed hop, which the record already holds quantised.
+struct AlertParams {
+    apm_fs_record* fs;      // [num_lags][K] records of this tick
+    uint32_t* count;        // [num_lags][K]
+    const double* hard_max; // [K]
+    const uint8_t* suppressed;  // [K]
+    uint32_t K, num_lags;
+    apm_alert_rules r;
+};
+
+__global__ void __launch_bounds__(256) alert_counter_kernel(const AlertParams p) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.K * p.num_lags) return;
+    apm_fs_record* en = p.fs + i;
+    if (!(en->flags & 1)) return;
+    const uint32_t lag_idx = i / p.K, key = i - lag_idx * p.K;
+    uint32_t cnt = p.count[i];
+    bool incremented = false, trigger = false;
+    uint32_t causes = 0;
+    auto alert = [&](uint32_t cause) {
+        if (!incremented) {  // only once per entry, and only while the rolling total is <= the window (:372-377)
+            if (cnt <= (uint32_t)p.r.window) cnt++;
+            incremented = true;
+        }
+        if (p.r.window > 1 && p.r.required > 1) {
+            if (cnt >= (uint32_t)p.r.required) { trigger = true; causes |= cause; }
+        } else {
+            trigger = true;
+            causes |= cause;
+        }
+    };
+    if (!((p.r.suppressed_lag_mask >> lag_idx) & 1u) && !p.suppressed[key]) {
+        const double hm = p.hard_max[key] > 0.0 ? p.hard_max[key] : p.r.hard_max_ms;
+        const double avg = en->val[0], p75 = en->val[1], tpm = en->tpm;
+        if (avg > hm) alert(APM_CAUSE_AVG_HARD_MAX);
+        if (p75 > hm) alert(APM_CAUSE_P75_HARD_MAX);
+        int both = 0;
+        if (en->signal[0] > 0 && avg > p.r.hard_min_ms && tpm > p.r.hard_min_tpm) {
+            if (!p.r.alert_on_both_only) alert(APM_CAUSE_AVG_UB); else both++;
+        }
+        if (en->signal[1] > 0 && p75 > p.r.hard_min_ms && tpm > p.r.hard_min_tpm) {
+            if (!p.r.alert_on_both_only) alert(APM_CAUSE_P75_UB); else both++;
+        }
+        if (p.r.alert_on_both_only && both >= 2) alert(APM_CAUSE_BOTH_UB);
+    }
+    if (!incremented && cnt > 0) cnt--;  // (:427-429)
+    p.count[i] = cnt;
+    en->flags = (uint8_t)(1u | (trigger ? 2u : 0u));
+    en->pad_[0] = (uint8_t)causes;
+    en->pad_[1] = (uint8_t)(cnt > 255u ? 255u : cnt);
+}
+
 // Copies the fs records that carry a signal into the tick's compact alert block.
 __global__ void __launch_bounds__(256) compact_alerts_kernel(const apm_fs_record* __restrict__ fs, uint32_t n,
                                                              apm_fs_record* __restrict__ alerts,
-                                                             unsigned int* __restrict__ count, uint32_t cap) {
+                                                             unsigned int* __restrict__ count, uint32_t cap, int by_trigger) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const apm_fs_record* r = fs + i;
     if (!(r->flags & 1)) return;
-    if (r->signal[0] | r->signal[1] | r->signal[2]) {
+    if (by_trigger ? (r->flags & 2) != 0 : (r->signal[0] | r->signal[1] | r->signal[2]) != 0) {
         const unsigned int k = atomicAdd(count, 1u);
         if (k < cap) {
             const uint4* s = reinterpret_cast<const uint4*>(r);
@@ -456,6 +510,20 @@ apm_status apm_launch_realign(apm_ctx* c, int buf, cudaStream_t st) {
     return APM_OK;
 }
 
+apm_status apm_launch_alert_counter(apm_ctx* c, uint32_t fs_slot, cudaStream_t st) {
+    if (!c->alert_rules.enabled || !c->d_fs) return APM_OK;
+    ProfScope prof_scope_(c, APM_PG_ALERTS, st);
+    AlertParams p;
+    p.fs = c->d_fs + (size_t)fs_slot * c->cfg.num_lags * c->K;
+    p.count = c->alert_count; p.hard_max = c->alert_hard_max; p.suppressed = c->alert_suppressed;
+    p.K = c->K; p.num_lags = (uint32_t)c->cfg.num_lags; p.r = c->alert_rules;
+    const uint32_t n = c->K * (uint32_t)c->cfg.num_lags;
+    alert_counter_kernel<<<(n + 255) / 256, 256, 0, st>>>(p);
+    c->launches += 1;
+    CUDA_TRY(c, cudaGetLastError());
+    return APM_OK;
+}
+
 apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot, cudaStream_t st) {
     ProfScope prof_scope_(c, APM_PG_ALERTS, st);
     if (!c->d_alerts || !c->d_fs) return APM_OK;
@@ -463,7 +531,7 @@ apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t aler
     compact_alerts_kernel<<<(n + 255) / 256, 256, 0, st>>>(
         c->d_fs + (size_t)fs_slot * c->cfg.num_lags * c->K, n,
         c->d_alerts + (size_t)alert_slot * c->cfg.max_alerts_per_tick, c->d_alert_count + alert_slot,
-        c->cfg.max_alerts_per_tick);
+        c->cfg.max_alerts_per_tick, c->alert_rules.enabled);
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;

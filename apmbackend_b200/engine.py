@@ -194,6 +194,23 @@ class Engine:
         f = np.ascontiguousarray(infl, dtype=np.float64)
         self._check(self._lib.apm_set_key_params(self._h, key_lo, t.size, lag_idx, t.ctypes.data, f.ctypes.data))
 
+    def set_alert_rules(self, window=60, required=45, alert_on_both_only=True, suppressed_lags=(), hard_max_ms=10000.0,
+                        hard_min_ms=200.0, hard_min_tpm=1.0, enabled=True):
+        """The counter core of processFSEntry (stream_process_alerts.js:348-434) behind every tick;
+        defaults are the reference's (config/apm_config.json:189-204)."""
+        r = _capi.AlertRules()
+        r.struct_size = C.sizeof(_capi.AlertRules)
+        r.enabled, r.window, r.required, r.alert_on_both_only = int(enabled), window, required, int(alert_on_both_only)
+        r.suppressed_lag_mask = sum(1 << list(self.cfg.lags).index(l) for l in suppressed_lags if l in self.cfg.lags)
+        r.hard_max_ms, r.hard_min_ms, r.hard_min_tpm = hard_max_ms, hard_min_ms, hard_min_tpm
+        self._check(self._lib.apm_set_alert_rules(self._h, C.byref(r)))
+
+    def set_alert_key_params(self, key_lo: int, hard_max_ms, suppressed):
+        h = np.ascontiguousarray(hard_max_ms, dtype=np.float64)
+        s = np.ascontiguousarray(suppressed, dtype=np.uint8)
+        assert h.size == s.size
+        self._check(self._lib.apm_set_alert_key_params(self._h, key_lo, h.size, h.ctypes.data, s.ctypes.data))
+
     def drop_lag(self, lag_idx: int):
         self._check(self._lib.apm_drop_lag(self._h, lag_idx))
 

@@ -123,9 +123,32 @@ typedef struct apm_fs_record {
     double lb[APM_NUM_SERIES];
     double ub[APM_NUM_SERIES];
     int8_t signal[APM_NUM_SERIES];
-    uint8_t flags;               /* bit0: record valid                                    */
-    uint8_t pad_[4];
+    uint8_t flags;               /* bit0: record valid; bit1: triggerAlert (alert rules on) */
+    uint8_t pad_[4];             /* with alert rules on: [0] causes (APM_CAUSE_*), [1] bad-interval count (<= 255) */
 } apm_fs_record;
+
+/* causes of an alert, in the order processFSEntry tests them (stream_process_alerts.js:398-423) */
+#define APM_CAUSE_AVG_HARD_MAX 1u  /* 'average exceeded hard ms threshold' */
+#define APM_CAUSE_P75_HARD_MAX 2u  /* 'per75 exceeded hard ms threshold'   */
+#define APM_CAUSE_AVG_UB 4u        /* 'average UB exceeded'                */
+#define APM_CAUSE_P75_UB 8u        /* 'per75 UB exceeded'                  */
+#define APM_CAUSE_BOTH_UB 16u      /* 'average and per75 UB exceeded'      */
+
+/* The deterministic core of the alert stage: replaces the counter logic of
+ * processFSEntry (stream_process_alerts.js:348-434) for every (key, lag) of a tick, fused behind
+ * the baseline kernels.  The wall-clock cooldown, batching and e-mail (:436-468) stay on the host.
+ * Values mirror config/apm_config.json:189-204. */
+typedef struct apm_alert_rules {
+    uint32_t struct_size;
+    int32_t enabled;
+    int32_t window;              /* rollingAlertWindowSizeInIntervals (60)                     */
+    int32_t required;            /* requiredNumberBadIntervalsInAlertWindowToTrigger (45)      */
+    int32_t alert_on_both_only;  /* alertOnBothOnly                                            */
+    uint32_t suppressed_lag_mask; /* bit i: lag index i is in suppressedLags                   */
+    double hard_max_ms;          /* hardMaxMsAlertThreshold (per-key overrides: apm_set_alert_key_params) */
+    double hard_min_ms;          /* hardMinMsAlertThreshold                                    */
+    double hard_min_tpm;         /* hardMinTpmAlertThreshold                                   */
+} apm_alert_rules;
 
 typedef struct apm_tick_result {
     uint64_t ticks;        /* ticks run by this call                        */
@@ -179,6 +202,13 @@ apm_status apm_process_device(apm_ctx* ctx, const apm_tx_columns* dev_cols, uint
  * [key_lo, key_lo+n) of lag index lag_idx. */
 apm_status apm_set_key_params(apm_ctx* ctx, uint32_t key_lo, uint32_t n, int32_t lag_idx,
                               const double* thr, const double* infl);
+/* With rules enabled every fs record carries triggerAlert / causes / the bad-interval count, and the
+ * compact alert block (apm_fetch_alerts, apm_gather_alerts) holds the records with triggerAlert set
+ * instead of every record with a signal.  hard_max_ms[i] <= 0 keeps the default for key key_lo + i
+ * (the reference's `!= 0` test, :396); suppressed[i] != 0 puts the key's service in suppressedServices. */
+apm_status apm_set_alert_rules(apm_ctx* ctx, const apm_alert_rules* rules);
+apm_status apm_set_alert_key_params(apm_ctx* ctx, uint32_t key_lo, uint32_t n, const double* hard_max_ms,
+                                    const uint8_t* suppressed);
 /* replaces removeStaleLagData (:170-193) for one lag: forget its lists. */
 apm_status apm_drop_lag(apm_ctx* ctx, int32_t lag_idx);
 

@@ -226,12 +226,56 @@ static int js_process_zscore(long lag, double threshold, double influence, doubl
     return signal;
 }
 
+/* processFSEntry(), stream_process_alerts.js:348-434: the deterministic counter core (the
+ * wall-clock cooldown and e-mail that follow, :436-468, are host business).  `en` holds what
+ * the fs line carries after the toFixed hop; *count is recentAlertCounts[server][service][lag].
+ * Returns triggerAlert, causes as APM_CAUSE_* bits. */
+static bool js_process_fs_entry(const apm_alert_rules& R, bool lag_suppressed, bool service_suppressed, double hard_max_override,
+                                const apm_fs_record& en, uint32_t* count, uint32_t* causes_out) {
+    bool trigger = false, incremented = false;
+    uint32_t causes = 0;
+    const long window = R.window, required = R.required;
+    auto alert = [&](uint32_t cause) {
+        if (!incremented) {
+            if ((long)*count <= window) (*count)++;
+            incremented = true;
+        }
+        if (window && window > 1 && required && required > 1) {
+            if ((long)*count >= required) { trigger = true; causes |= cause; }
+        } else {
+            trigger = true;
+            causes |= cause;
+        }
+    };
+    if (!lag_suppressed) {
+        if (!service_suppressed) {
+            /* (serviceOverrides.hardMaxMsAlertThreshold && != 0) ? override : default, :396 */
+            const double hard_max = (hard_max_override > 0) ? hard_max_override : R.hard_max_ms;
+            const double average = en.val[0], per75 = en.val[1], tpm = en.tpm;
+            if (average > hard_max) alert(APM_CAUSE_AVG_HARD_MAX);
+            if (per75 > hard_max) alert(APM_CAUSE_P75_HARD_MAX);
+            int both = 0;
+            if (en.signal[0] > 0 && average > R.hard_min_ms && tpm > R.hard_min_tpm) {
+                if (!R.alert_on_both_only) alert(APM_CAUSE_AVG_UB); else both++;
+            }
+            if (en.signal[1] > 0 && per75 > R.hard_min_ms && tpm > R.hard_min_tpm) {
+                if (!R.alert_on_both_only) alert(APM_CAUSE_P75_UB); else both++;
+            }
+            if (R.alert_on_both_only && both >= 2) alert(APM_CAUSE_BOTH_UB);
+        }
+    }
+    if (!incremented && *count > 0) (*count)--;
+    *causes_out = causes;
+    return trigger;
+}
+
 /* ------------------------------------------------------------------ */
 /* The two stages                                                      */
 /* ------------------------------------------------------------------ */
 
 struct LagState { /* one entry of lags{} in stream_calc_z_score.js:205-229 */
     double thr, infl;
+    uint32_t alert_count = 0; /* recentAlertCounts[server][service][lag], stream_process_alerts.js:362 */
     std::vector<double> list[APM_NUM_SERIES]; /* faithful: front = oldest          */
     size_t head[APM_NUM_SERIES] = {0, 0, 0};  /* fast: ring start once len == lag  */
 };
@@ -254,6 +298,8 @@ struct Pipeline {
     std::unordered_map<uint32_t, KeyState> keys;
     std::vector<double> thr_override, infl_override; /* [lag][key], NaN = default */
     std::unordered_map<uint64_t, std::vector<double>> preload; /* (key,lag,series) -> list */
+    apm_alert_rules rules = {};
+    std::unordered_map<uint32_t, std::pair<double, bool>> alert_key; /* key -> (hardMax override, suppressed) */
     std::vector<apm_stat_record> stats;
     std::vector<apm_fs_record> fs;
     uint64_t ticks = 0, ingested = 0, invalid = 0;
@@ -334,6 +380,15 @@ void Pipeline::z_process(const apm_stat_record& st, KeyState& ks) {
             } else {
                 lst.push_back(infl_v[s]);
             }
+        }
+        if (rules.enabled) { /* the alert stage reads the fs line next (stream_process_alerts.js:625) */
+            auto ak = alert_key.find(ks.key);
+            uint32_t causes = 0;
+            const bool trig = js_process_fs_entry(rules, (rules.suppressed_lag_mask >> l) & 1u, ak != alert_key.end() && ak->second.second,
+                                                  ak != alert_key.end() ? ak->second.first : 0.0, r, &L.alert_count, &causes);
+            r.flags = (uint8_t)(1u | (trig ? 2u : 0u));
+            r.pad_[0] = (uint8_t)causes;
+            r.pad_[1] = (uint8_t)(L.alert_count > 255u ? 255u : L.alert_count);
         }
         if (keep_outputs) fs.push_back(r);
     }
@@ -477,6 +532,14 @@ void orc_set_key_params(void* h, uint32_t key, int lag_idx, double thr, double i
 void orc_ring_load(void* h, uint32_t key, int lag_idx, int series, const double* v, uint32_t len) {
     Pipeline* p = (Pipeline*)h;
     p->preload[((uint64_t)key << 8) | (uint64_t)(lag_idx * 4 + series)] = std::vector<double>(v, v + len);
+}
+void orc_set_alert_rules(void* h, const apm_alert_rules* r) { ((Pipeline*)h)->rules = *r; }
+void orc_set_alert_key_params(void* h, uint32_t key, double hard_max, int suppressed) {
+    ((Pipeline*)h)->alert_key[key] = std::make_pair(hard_max, suppressed != 0);
+}
+int orc_process_fs_entry(const apm_alert_rules* r, int lag_suppressed, int service_suppressed, double hard_max_override,
+                         const apm_fs_record* en, uint32_t* count, uint32_t* causes) {
+    return js_process_fs_entry(*r, lag_suppressed != 0, service_suppressed != 0, hard_max_override, *en, count, causes) ? 1 : 0;
 }
 void orc_consume(void* h, const uint32_t* svc, const uint32_t* jvm, const int64_t* ts, const int32_t* el, uint64_t n) {
     Pipeline* p = (Pipeline*)h;

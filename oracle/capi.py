@@ -45,6 +45,23 @@ class ApmConfig(C.Structure):
     ]
 
 
+class AlertRules(C.Structure):
+    """Mirror of apm_alert_rules (include/apm_b200.h); defaults = config/apm_config.json:189-204."""
+    _fields_ = [("struct_size", C.c_uint32), ("enabled", C.c_int32), ("window", C.c_int32), ("required", C.c_int32),
+                ("alert_on_both_only", C.c_int32), ("suppressed_lag_mask", C.c_uint32),
+                ("hard_max_ms", C.c_double), ("hard_min_ms", C.c_double), ("hard_min_tpm", C.c_double)]
+
+
+def make_alert_rules(window=60, required=45, alert_on_both_only=True, suppressed_lag_mask=0, hard_max_ms=10000.0,
+                     hard_min_ms=200.0, hard_min_tpm=1.0, enabled=True) -> AlertRules:
+    r = AlertRules()
+    r.struct_size = C.sizeof(AlertRules)
+    r.enabled, r.window, r.required = int(enabled), window, required
+    r.alert_on_both_only, r.suppressed_lag_mask = int(alert_on_both_only), suppressed_lag_mask
+    r.hard_max_ms, r.hard_min_ms, r.hard_min_tpm = hard_max_ms, hard_min_ms, hard_min_tpm
+    return r
+
+
 F_PERCENTILES, F_ZSCORE, F_KEEP_STATS, F_KEEP_FS, F_ALERTS = 1, 2, 4, 8, 16
 
 
@@ -108,6 +125,10 @@ def lib():
         L.orc_ring_load.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_uint32]
         L.orc_ring_read.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_uint32]
         L.orc_ring_read.restype = C.c_uint32
+        L.orc_set_alert_rules.argtypes = [C.c_void_p, C.POINTER(AlertRules)]
+        L.orc_set_alert_key_params.argtypes = [C.c_void_p, C.c_uint32, C.c_double, C.c_int]
+        L.orc_process_fs_entry.argtypes = [C.POINTER(AlertRules), C.c_int, C.c_int, C.c_double, C.c_void_p,
+                                           C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         L.orc_consume.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
         for name in ("orc_num_stats", "orc_num_fs", "orc_ticks", "orc_ingested"):
             getattr(L, name).argtypes = [C.c_void_p]
@@ -191,6 +212,12 @@ class Pipeline:
         n = lib().orc_ring_read(self._h, key, lag_idx, series, out.ctypes.data, cap)
         return out[:n].copy()
 
+    def set_alert_rules(self, rules: AlertRules):
+        lib().orc_set_alert_rules(self._h, C.byref(rules))
+
+    def set_alert_key_params(self, key, hard_max_ms=0.0, suppressed=False):
+        lib().orc_set_alert_key_params(self._h, key, hard_max_ms, int(suppressed))
+
     def consume(self, service_id, jvm_id, end_ts_ms, elapsed_ms):
         s = np.ascontiguousarray(service_id, dtype=np.uint32)
         j = np.ascontiguousarray(jvm_id, dtype=np.uint32)
@@ -241,3 +268,12 @@ def format_fs(rec, server: str, service: str) -> str:
     buf = C.create_string_buffer(1024)
     lib().orc_format_fs(r.ctypes.data, server.encode(), service.encode(), buf, 1024)
     return buf.value.decode()
+
+
+def process_fs_entry(rules: AlertRules, rec, count: int, lag_suppressed=False, service_suppressed=False, hard_max_override=0.0):
+    """One call of processFSEntry's counter core: returns (triggerAlert, causes bits, new count)."""
+    r = np.ascontiguousarray(rec).reshape(1)
+    c, causes = C.c_uint32(count), C.c_uint32(0)
+    t = lib().orc_process_fs_entry(C.byref(rules), int(lag_suppressed), int(service_suppressed), hard_max_override,
+                                   r.ctypes.data, C.byref(c), C.byref(causes))
+    return bool(t), causes.value, c.value

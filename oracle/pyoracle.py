@@ -426,3 +426,75 @@ def run_pipeline(txs, bucket_ms=10000, window=30, buffer=6, percentiles=(75, 95)
         for e in zp.processData(StatEntry.from_csv(line)):
             fs.append(e.to_csv())
     return sp.out, fs, sp, zp
+
+
+# --------------------------------------------------------------------------
+# stream_process_alerts.js: processFSEntry (348-434), the deterministic counter core
+# --------------------------------------------------------------------------
+CAUSES = ("average exceeded hard ms threshold", "per75 exceeded hard ms threshold", "average UB exceeded",
+          "per75 UB exceeded", "average and per75 UB exceeded")
+
+
+class AlertsCounter:
+    """ALERTSCONFIG is the dict of config/apm_config.json:176-214 the function reads."""
+
+    def __init__(self, config=None):
+        self.cfg = {"hardMinMsAlertThreshold": 200, "hardMaxMsAlertThreshold": 10000, "hardMinTpmAlertThreshold": 1.0,
+                    "alertOnBothOnly": True, "overrides": {"services": {}}, "suppressedLags": [],
+                    "rollingAlertWindowSizeInIntervals": 60, "requiredNumberBadIntervalsInAlertWindowToTrigger": 45,
+                    "suppressedServices": ["S:getSalesServiceOffers"]}
+        if config:
+            self.cfg.update(config)
+        self.recentAlertCounts = {}
+
+    def processFSEntry(self, en: FullStatEntry):
+        """Returns (triggerAlert, causes list); the cooldown / AlertEntry part (:436-468) is left out."""
+        cfg = self.cfg
+        trigger, incremented, causes = False, False, []
+        ov = cfg["overrides"]["services"].get(en.service)
+        counts = self.recentAlertCounts.setdefault(en.server, {}).setdefault(en.service, {})
+        if not counts.get(en.lag):
+            counts[en.lag] = 0
+        window = int(cfg["rollingAlertWindowSizeInIntervals"])
+        required = int(cfg["requiredNumberBadIntervalsInAlertWindowToTrigger"])
+
+        def alert(s):
+            nonlocal trigger, incremented
+            if not incremented:
+                if counts[en.lag] <= window:
+                    counts[en.lag] += 1
+                incremented = True
+            if window and window > 1 and required and required > 1:
+                if counts[en.lag] >= required:
+                    trigger = True
+                    causes.append(s)
+            else:
+                trigger = True
+                causes.append(s)
+
+        if int(en.lag) not in cfg["suppressedLags"]:
+            if en.service not in cfg["suppressedServices"]:
+                hard_max = ov["hardMaxMsAlertThreshold"] if (ov and ov.get("hardMaxMsAlertThreshold")) \
+                    else cfg["hardMaxMsAlertThreshold"]
+                if en.average > hard_max:
+                    alert(CAUSES[0])
+                if en.per75 > hard_max:
+                    alert(CAUSES[1])
+                both = 0
+                if en.averageSignal > 0 and en.average > cfg["hardMinMsAlertThreshold"] and en.tpm > cfg["hardMinTpmAlertThreshold"]:
+                    if not cfg["alertOnBothOnly"]:
+                        alert(CAUSES[2])
+                    else:
+                        both += 1
+                if en.per75Signal > 0 and en.per75 > cfg["hardMinMsAlertThreshold"] and en.tpm > cfg["hardMinTpmAlertThreshold"]:
+                    if not cfg["alertOnBothOnly"]:
+                        alert(CAUSES[3])
+                    else:
+                        both += 1
+                if cfg["alertOnBothOnly"] and both >= 2:
+                    alert(CAUSES[4])
+        if not incremented and counts[en.lag] > 0:
+            counts[en.lag] -= 1
+        if counts[en.lag] < 0:
+            counts[en.lag] = 0
+        return trigger, causes
