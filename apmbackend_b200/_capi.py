@@ -121,6 +121,10 @@ SYMBOLS = {
     "apm_set_overlap": (C.c_int32, [C.c_void_p, C.c_int32]),
     "apm_timer_start": (C.c_int32, [C.c_void_p]),
     "apm_timer_stop": (C.c_int32, [C.c_void_p, C.POINTER(C.c_double)]),
+    "apm_set_latest": (C.c_int32, [C.c_void_p, C.c_int64]),
+    "apm_mark_seen": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_uint32]),
+    "apm_log_read": (C.c_int32, [C.c_void_p, C.c_int64, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "apm_latest": (C.c_int64, [C.c_void_p]),
     "apm_get_counters": (C.c_int32, [C.c_void_p, C.POINTER(Counters)]),
     "apm_reset_counters": (C.c_int32, [C.c_void_p]),
     "apm_quantize": (C.c_double, [C.c_double, C.c_int32]),

@@ -711,6 +711,55 @@ apm_status apm_ring_read(apm_ctx* c, uint32_t key, int32_t l, int32_t series, do
     return APM_OK;
 }
 
+int64_t apm_latest(const apm_ctx* c) { return c ? c->latest : 0; }
+
+apm_status apm_set_latest(apm_ctx* c, int64_t latest) {
+    if (!c) return APM_E_INVALID;
+    if (latest <= 0) return apm_fail(c, APM_E_INVALID, "set_latest: label must be positive");
+    apm_status st = sync_all(c);
+    if (st) return st;
+    c->latest = latest;
+    uint64_t mask = 0;
+    for (int s = 0; s < c->S; ++s) c->slot_label[s] = -1;
+    for (int64_t lab = std::max<int64_t>(0, latest - c->keep); lab <= latest; ++lab) {
+        const int slot = (int)(lab % c->S);
+        c->slot_label[slot] = lab;
+        mask |= 1ull << slot;
+    }
+    st = apm_launch_clear_slots(c, mask);
+    if (st) return st;
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    return APM_OK;
+}
+
+apm_status apm_mark_seen(apm_ctx* c, uint32_t key_lo, uint32_t n) {
+    if (!c) return APM_E_INVALID;
+    if ((uint64_t)key_lo + n > c->K) return apm_fail(c, APM_E_INVALID, "mark_seen: range");
+    apm_status st = sync_all(c);
+    if (st) return st;
+    if (n) CUDA_TRY(c, cudaMemset(c->seen + key_lo, 1, n));
+    return APM_OK;
+}
+
+apm_status apm_log_read(apm_ctx* c, int64_t label, uint64_t* out, uint64_t cap, uint64_t* n) {
+    if (!c || !n) return APM_E_INVALID;
+    *n = 0;
+    if (!c->log_cap) return apm_fail(c, APM_E_STATE, "value logs are only kept with APM_F_PERCENTILES");
+    apm_status st = sync_all(c);
+    if (st) return st;
+    if (label < 0) return APM_OK;
+    const int slot = (int)(label % c->S);
+    if (c->slot_label[slot] != label) return APM_OK;  // not retained
+    SlotMeta m;
+    CUDA_TRY(c, cudaMemcpy(&m, c->slot_meta + slot, sizeof m, cudaMemcpyDeviceToHost));
+    const uint64_t cnt = std::min<uint64_t>(m.count, c->log_cap);
+    *n = cnt;
+    if (cnt == 0 || !out) return APM_OK;  // out == NULL: size query
+    if (cap < cnt) return apm_fail(c, APM_E_CAPACITY, "log_read: buffer too small");
+    CUDA_TRY(c, cudaMemcpy(out, c->log_buf[slot], cnt * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    return APM_OK;
+}
+
 apm_status apm_get_counters(apm_ctx* c, apm_counters* out) {
     if (!c || !out) return APM_E_INVALID;
     apm_status st = refresh_counters(c);

@@ -233,6 +233,26 @@ class Engine:
         self._check(self._lib.apm_ring_read(self._h, key, lag_idx, series, out.ctypes.data, cap, C.byref(n)))
         return out[:n.value].copy()
 
+    # ---- interop with the reference's JSON resume files
+    @property
+    def latest(self) -> int:
+        return int(self._lib.apm_latest(self._h))
+
+    def set_latest(self, latest_bucket: int):
+        self._check(self._lib.apm_set_latest(self._h, int(latest_bucket)))
+
+    def mark_seen(self, key_lo: int, n: int = 1):
+        self._check(self._lib.apm_mark_seen(self._h, key_lo, n))
+
+    def log_read(self, label: int) -> np.ndarray:
+        """(key << 32 | elapsed) words of one retained bucket (arrival order until the bucket is sorted)."""
+        n = C.c_uint64(0)
+        self._check(self._lib.apm_log_read(self._h, int(label), None, 0, C.byref(n)))
+        out = np.empty(max(n.value, 1), dtype=np.uint64)
+        if n.value:
+            self._check(self._lib.apm_log_read(self._h, int(label), out.ctypes.data, out.size, C.byref(n)))
+        return out[:n.value]
+
     # ---- checkpoint
     def state_save(self, path: str):
         self._check(self._lib.apm_state_save(self._h, path.encode()))

@@ -268,6 +268,17 @@ apm_status apm_timer_start(apm_ctx* ctx);
 apm_status apm_timer_stop(apm_ctx* ctx, double* ms);
 apm_status apm_profile_read(apm_ctx* ctx, apm_kernel_times* out);
 
+/* ---- interop with the reference's JSON resume files (the host converts the schemas of
+ * stream_calc_stats.js:54-87 and stream_calc_z_score.js:37-64, apmbackend_b200/resume_interop.py) ----
+ * apm_set_latest: latestBucket of a resumed StatParser without running a tick (retained bucket slots are
+ *   assigned to the labels latest-keep .. latest and emptied).
+ * apm_mark_seen: keys that exist in `servers{}` even if none of their buckets is retained.
+ * apm_log_read: the raw (key << 32 | elapsed) words of one retained bucket, i.e. buckets[label] of every key. */
+apm_status apm_set_latest(apm_ctx* ctx, int64_t latest_bucket);
+apm_status apm_mark_seen(apm_ctx* ctx, uint32_t key_lo, uint32_t n);
+apm_status apm_log_read(apm_ctx* ctx, int64_t label, uint64_t* out, uint64_t cap, uint64_t* n);
+int64_t apm_latest(const apm_ctx* ctx);
+
 apm_status apm_get_counters(apm_ctx* ctx, apm_counters* out);
 apm_status apm_reset_counters(apm_ctx* ctx);
 
