@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libapm_b200.so")
 SYNTH_PATH = os.path.join(_HERE, "libapm_synth.so")
 
 OK, E_INVALID, E_DEVICE, E_CAPACITY, E_WOULDBLOCK, E_STATE, E_IO, E_COMM = range(8)
-F_PERCENTILES, F_ZSCORE, F_KEEP_STATS, F_KEEP_FS, F_ALERTS = 1, 2, 4, 8, 16
+F_PERCENTILES, F_ZSCORE, F_KEEP_STATS, F_KEEP_FS, F_ALERTS, F_INCREMENTAL = 1, 2, 4, 8, 16, 32
 MAX_PCT, MAX_LAGS, NUM_SERIES = 4, 4, 3
 
 STAT_DTYPE = np.dtype([
@@ -57,7 +57,7 @@ class TickResult(C.Structure):
 class Counters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "tx_ingested", "tx_dropped", "tx_invalid", "ticks", "stat_records", "fs_records", "alerts",
-        "h2d_bytes", "d2h_bytes", "kernel_launches", "keys_seen")]
+        "h2d_bytes", "d2h_bytes", "kernel_launches", "keys_seen", "inc_fallbacks")]
 
 
 class AlertRules(C.Structure):

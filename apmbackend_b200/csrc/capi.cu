@@ -91,6 +91,7 @@ apm_status refresh_counters(apm_ctx* c) {
     c->counters.tx_dropped = c->h_counters->dropped;
     c->counters.tx_invalid = c->h_counters->invalid + c->h_counters->future;
     c->counters.kernel_launches = c->launches;
+    c->counters.inc_fallbacks = c->h_counters->inc_fallbacks;
     if (c->may_misalign && c->tick_seq > c->misalign_mark && c->h_counters->pending_lists == 0) c->may_misalign = false;
     if (c->h_counters->log_overflow)
         return apm_fail(c, APM_E_CAPACITY, "a bucket's value log overflowed max_tx_per_bucket; percentiles of that bucket are incomplete - recreate the context with a larger capacity");
@@ -294,7 +295,8 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
     free_columns_device(&c->dev[0]); free_columns_device(&c->dev[1]);
     cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
-    for (int l = 0; l < APM_MAX_LAGS; ++l) { cudaFree(c->ring[l]); cudaFree(c->ring_len[l]); cudaFree(c->ring_next[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
+    for (int l = 0; l < APM_MAX_LAGS; ++l) { cudaFree(c->ring[l]); cudaFree(c->ring_len[l]); cudaFree(c->ring_next[l]);
+        cudaFree(c->inc_sum[l]); cudaFree(c->inc_comp[l]); cudaFree(c->inc_cnt[l]); cudaFree(c->inc_nz[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
     cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->d_gather);
     cudaFree(c->alert_count); cudaFree(c->alert_hard_max); cudaFree(c->alert_suppressed);
     for (int i = 0; i < 2; ++i) { if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); if (c->ev_consumed[i]) cudaEventDestroy(c->ev_consumed[i]); }
@@ -420,6 +422,12 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
             TRY_CREATE(cudaMemsetAsync(c->ring[l], 0, L * c->ring_pitch * sizeof(double), c->s_main));
             TRY_CREATE(dalloc(&c->ring_len[l], 3 * K));
             TRY_CREATE(cudaMemsetAsync(c->ring_len[l], 0, sizeof(uint32_t) * 3 * K, c->s_main));
+            if (cfg->flags & APM_F_INCREMENTAL) {
+                TRY_CREATE(dalloc(&c->inc_sum[l], 3 * K)); TRY_CREATE(cudaMemsetAsync(c->inc_sum[l], 0, sizeof(double) * 3 * K, c->s_main));
+                TRY_CREATE(dalloc(&c->inc_comp[l], 3 * K)); TRY_CREATE(cudaMemsetAsync(c->inc_comp[l], 0, sizeof(double) * 3 * K, c->s_main));
+                TRY_CREATE(dalloc(&c->inc_cnt[l], 3 * K)); TRY_CREATE(cudaMemsetAsync(c->inc_cnt[l], 0, sizeof(uint32_t) * 3 * K, c->s_main));
+                TRY_CREATE(dalloc(&c->inc_nz[l], 3 * K)); TRY_CREATE(cudaMemsetAsync(c->inc_nz[l], 0, sizeof(uint32_t) * 3 * K, c->s_main));
+            }
             TRY_CREATE(dalloc(&c->ring_next[l], 3 * K));
             TRY_CREATE(cudaMemsetAsync(c->ring_next[l], 0, sizeof(uint32_t) * 3 * K, c->s_main));
             TRY_CREATE(dalloc(&c->thr[l], K));
@@ -582,6 +590,7 @@ apm_status apm_drop_lag(apm_ctx* c, int32_t l) {
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaMemsetAsync(c->ring_len[l], 0, sizeof(uint32_t) * 3 * c->K, c->s_main));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    c->inc_dirty[l] = true;
     return APM_OK;
 }
 
@@ -664,6 +673,7 @@ apm_status apm_ring_load(apm_ctx* c, uint32_t key, int32_t l, int32_t series, co
     CUDA_TRY(c, cudaMemcpy(c->ring_next[l] + col, &head, sizeof(uint32_t), cudaMemcpyHostToDevice));  // the list ends just before `head`
     c->may_misalign = true;
     c->misalign_mark = c->tick_seq;
+    c->inc_dirty[l] = true;
     return APM_OK;
 }
 
@@ -686,6 +696,7 @@ apm_status apm_ring_load_all(apm_ctx* c, int32_t l, const double* values, uint32
     CUDA_TRY(c, cudaMemcpy(c->ring_next[l], nexts.data(), ncol * sizeof(uint32_t), cudaMemcpyHostToDevice));
     c->may_misalign = true;
     c->misalign_mark = c->tick_seq;
+    c->inc_dirty[l] = true;
     return APM_OK;
 }
 

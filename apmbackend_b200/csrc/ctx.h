@@ -92,6 +92,12 @@ struct apm_ctx {
     uint32_t ring_head[APM_MAX_LAGS] = {0, 0, 0, 0};                          // slot the next push writes
     double* thr[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};         // [K]
     double* infl[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};        // [K]
+    // guarded incremental baseline (APM_F_INCREMENTAL): running statistics per column
+    double* inc_sum[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};
+    double* inc_comp[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t* inc_cnt[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t* inc_nz[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};
+    bool inc_dirty[APM_MAX_LAGS] = {false, false, false, false};  // lists were loaded: rebuild before the next tick
     // alert counter core (stream_process_alerts.js:348-434)
     apm_alert_rules alert_rules = {};
     uint32_t* alert_count = nullptr;   // [num_lags][K] recentAlertCounts

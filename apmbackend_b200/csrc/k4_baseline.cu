@@ -312,6 +312,173 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
     }
 }
 
+// ---- guarded incremental baseline (APM_F_INCREMENTAL) ------------------------------------------
+// The exact-order rescan above costs K x L x 24 B per tick.  This variant keeps, per column, a
+// compensated running sum of the list (Neumaier), the number of valid entries and the number of
+// non-zero entries, updated with the evicted and the pushed value: O(K) per tick.  Its mean
+// differs from the reference's left-to-right sum by rounding only (both are within ~L x 2^-53
+// relative of the true mean), so the record's mean / bounds agree to ~1e-12 relative (the spec
+// allows 1e-9) - but a signal must be bit-identical.  Therefore the strict test
+// |new - mean| > threshold * sqrt(mean) is decided from the running mean only when its margin is
+// 1e-9 relative or more; inside that guard band the thread re-sums its column in the reference's
+// order and decides exactly as the exact kernel does.  Pushed values depend on the signal and on
+// ring contents only, so the lists stay bit-identical to the reference's.
+// Assumes non-negative series (durations); a non-positive running mean over non-zero entries also
+// takes the exact path.
+struct IncState {
+    double* sum;      // [3K]
+    double* comp;     // [3K] Neumaier compensation
+    uint32_t* cnt;    // [3K] valid (non-NaN) entries
+    uint32_t* nz;     // [3K] valid entries != 0
+};
+
+__device__ __forceinline__ void neumaier_add(double& s, double& c, double x) {
+    const double t = __dadd_rn(s, x);
+    if (fabs(s) >= fabs(x)) c = __dadd_rn(c, __dadd_rn(__dsub_rn(s, t), x));
+    else c = __dadd_rn(c, __dadd_rn(__dsub_rn(x, t), s));
+    s = t;
+}
+
+// left-to-right sum of a full list in the reference's order (slots head, head+1, ...)
+__device__ void exact_column_sum(const double* base, uint32_t head, uint32_t L, size_t pitch, double& sum, uint32_t& cnt) {
+    sum = 0.0;
+    cnt = 0;
+    uint32_t i = 0;
+    for (; i + 8 <= L; i += 8) {
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            uint32_t sl = head + i + u;
+            sl = sl >= L ? sl - L : sl;
+            v[u] = base[(size_t)sl * pitch];
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) accumulate(v[u], sum, cnt);
+    }
+    for (; i < L; ++i) {
+        uint32_t sl = head + i;
+        sl = sl >= L ? sl - L : sl;
+        accumulate(base[(size_t)sl * pitch], sum, cnt);
+    }
+}
+
+__global__ void __launch_bounds__(K4_THREADS) baseline_inc_kernel(const BaselineParams p, const IncState st,
+                                                                  unsigned long long* __restrict__ fallbacks) {
+    const uint32_t col = blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= 3u * p.K) return;
+    const uint32_t series = col / p.K, key = col - series * p.K;
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    apm_fs_record* rec = p.fs ? p.fs + key : nullptr;
+    if (!p.seen[key]) {
+        if (rec && series == 0) rec->flags = 0;
+        return;
+    }
+    const uint32_t len = p.ring_len[col];
+    const double new_value = p.zin[(size_t)(1 + series) * p.K + key];
+    const double threshold = p.thr[key], influence = p.infl[key];
+    double infl_value = new_value, avg = nan, lb = nan, ub = nan;
+    int signal = 0;
+    double S = st.sum[col], C = st.comp[col];
+    uint32_t cnt = st.cnt[col], nz = st.nz[col];
+    double* base = p.ring + col;
+    const bool full = len >= p.L;
+    double evicted = nan;
+    if (full) {
+        evicted = base[(size_t)p.head * p.pitch];
+        const double last = base[(size_t)(p.head == 0 ? p.L - 1 : p.head - 1) * p.pitch];
+        if (cnt > 0) {
+            bool exact = false;
+            double m = __ddiv_rn(__dadd_rn(S, C), (double)cnt);
+            if (nz == 0) m = 0.0;                    // all valid entries are zero: the reference's mean is exactly 0
+            else if (!(m > 0.0)) exact = true;       // negative entries in play: no shortcut
+            double sd = nan, band = 0.0;
+            if (!exact && m != 0.0) {
+                sd = __dsqrt_rn(m);
+                band = __dmul_rn(threshold, sd);
+                if (new_value == new_value) {
+                    const double d = fabs(__dsub_rn(new_value, m)) - band;
+                    if (fabs(d) <= 1e-9 * (fabs(new_value) + m + fabs(band))) exact = true;  // inside the guard band
+                }
+            }
+            if (exact) {
+                double es;
+                uint32_t ec;
+                exact_column_sum(base, p.head, p.L, p.pitch, es, ec);
+                m = __ddiv_rn(es, (double)ec);
+                sd = nan;
+                if (m != 0.0) sd = __dsqrt_rn(m);
+                band = __dmul_rn(threshold, sd);
+                atomicAdd(fallbacks, 1ull);
+            }
+            avg = m;
+            if (sd == sd) {
+                lb = __dsub_rn(avg, band);
+                ub = __dadd_rn(avg, band);
+                if (new_value == new_value && fabs(__dsub_rn(new_value, avg)) > band) {
+                    signal = new_value > avg ? 1 : -1;
+                    if (last == last)
+                        infl_value = __dadd_rn(__dmul_rn(influence, new_value), __dmul_rn(__dsub_rn(1.0, influence), last));
+                }
+            }
+        }
+    } else {
+        p.ring_len[col] = len + 1;
+    }
+    // running statistics follow the shift() + push()
+    if (evicted == evicted) {
+        neumaier_add(S, C, -evicted);
+        cnt -= 1;
+        if (evicted != 0.0) nz -= 1;
+    }
+    if (infl_value == infl_value) {
+        neumaier_add(S, C, infl_value);
+        cnt += 1;
+        if (infl_value != 0.0) nz += 1;
+    }
+    if (cnt == 0) { S = 0.0; C = 0.0; }
+    st.sum[col] = S; st.comp[col] = C; st.cnt[col] = cnt; st.nz[col] = nz;
+    base[(size_t)p.head * p.pitch] = infl_value;
+    p.ring_next[col] = p.head + 1 == p.L ? 0u : p.head + 1;
+    if (rec) {
+        if (series == 0) {
+            rec->tick_ts = p.tick_ts;
+            rec->key = key;
+            rec->lag = p.lag_value;
+            rec->tpm = p.zin[key];
+            rec->flags = 1;
+            rec->pad_[0] = rec->pad_[1] = rec->pad_[2] = rec->pad_[3] = 0;
+        }
+        rec->val[series] = new_value;
+        rec->avg[series] = avg;
+        rec->lb[series] = lb;
+        rec->ub[series] = ub;
+        rec->signal[series] = (int8_t)signal;
+    }
+}
+
+// (Re)builds the running statistics of every column from its list (after lists were loaded).
+__global__ void __launch_bounds__(K4_THREADS) inc_init_kernel(const double* __restrict__ ring, const uint32_t* __restrict__ ring_len,
+                                                              const uint32_t* __restrict__ ring_next, const IncState st, uint32_t K,
+                                                              uint32_t L, size_t pitch) {
+    const uint32_t col = blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= 3u * K) return;
+    const uint32_t len = ring_len[col] < L ? ring_len[col] : L;
+    const uint32_t first = (ring_next[col] + L - len) % L;
+    double S = 0.0, C = 0.0;
+    uint32_t cnt = 0, nz = 0;
+    for (uint32_t i = 0; i < len; ++i) {
+        uint32_t sl = first + i;
+        sl = sl >= L ? sl - L : sl;
+        const double v = __ldcs(ring + (size_t)sl * pitch + col);
+        if (v == v) {
+            neumaier_add(S, C, v);
+            cnt += 1;
+            if (v != 0.0) nz += 1;
+        }
+    }
+    st.sum[col] = S; st.comp[col] = C; st.cnt[col] = cnt; st.nz[col] = nz;
+}
+
 // Lists that were loaded for a key (resume) but did not advance while the key was silent are out of
 // step with the lag's global head.  Before such a key takes part in the lock-step pushes again its
 // column is rotated so that the list ends just before `head` (three strided reversals, one thread;
@@ -477,7 +644,16 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
     p.tick_ts = tick_ts;
     p.sd_mode = c->cfg.sd_mode;
     const uint32_t ncol = 3u * c->K;
-    if (c->ring_tmap_ok && c->cfg.sd_mode == APM_SD_REFERENCE && !c->k4_force_ldg) {
+    if ((c->cfg.flags & APM_F_INCREMENTAL) && c->cfg.sd_mode == APM_SD_REFERENCE) {
+        IncState is = {c->inc_sum[l], c->inc_comp[l], c->inc_cnt[l], c->inc_nz[l]};
+        if (c->inc_dirty[l]) {  // lists were loaded since the last tick: rebuild the running statistics first
+            inc_init_kernel<<<(ncol + K4_THREADS - 1) / K4_THREADS, K4_THREADS, 0, st>>>(c->ring[l], c->ring_len[l], c->ring_next[l], is,
+                                                                                   c->K, p.L, c->ring_pitch);
+            c->inc_dirty[l] = false;
+            c->launches += 1;
+        }
+        baseline_inc_kernel<<<(ncol + K4_THREADS - 1) / K4_THREADS, K4_THREADS, 0, st>>>(p, is, &c->d_counters->inc_fallbacks);
+    } else if (c->ring_tmap_ok && c->cfg.sd_mode == APM_SD_REFERENCE && !c->k4_force_ldg) {
         const unsigned g = (ncol + K4T_COLS - 1) / K4T_COLS;
         switch (c->k4_stages) {
             case 2: baseline_tma_kernel<2><<<g, 32, 0, st>>>(c->ring_tmap[l], p); break;

@@ -133,6 +133,7 @@ apm_status apm_state_load(apm_ctx* c, const char* path) {
     for (int s = 0; s < c->S; ++s) c->slot_label[s] = h.slot_label[s];
     for (int l = 0; l < c->cfg.num_lags; ++l) c->ring_head[l] = h.ring_head[l];
     c->ticks_buffered = 0;
+    for (int l = 0; l < APM_MAX_LAGS; ++l) c->inc_dirty[l] = true;
     c->may_misalign = true;  // loaded lists of keys that are silent now re-enter the lock step when they emit
     c->misalign_mark = c->tick_seq;
     return APM_OK;

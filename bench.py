@@ -38,6 +38,12 @@ WORKLOADS = {
                  influences=(0.0,), zscore=True, pct=True, seed=2,
                  desc="100M transactions, 10k service keys, 1-min buckets, p50/p95/p99 + z-score vs 7-day "
                       "rolling baseline (10080 buckets/key, pre-filled), exact-order baseline"),
+    # one rank's share of BASELINE.json configs[3] at 8 GPUs: 1 B transactions / 8, 1 M keys / 8
+    "cfg4_shard": dict(n=125_000_000, services=125_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
+                       percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
+                       influences=(0.0,), zscore=True, pct=True, seed=3,
+                       desc="one of 8 key-hash shards of 1B transactions / 1M keys: 125M transactions, 125k keys, "
+                            "p50/p95/p99 + z-score vs 10080-bucket baseline (30 GB of rings)"),
     # BASELINE.json configs[1]
     "cfg2": dict(n=100_000_000, services=10_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
                  percentiles=(), z_series_pct=(0, 1), lags=(), thresholds=(), influences=(), zscore=False, pct=False,
@@ -53,6 +59,9 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
     ap.add_argument("--scale", type=float, default=1.0, help="shrink n (debug only; the line says so)")
+    ap.add_argument("--baseline", default="exact", choices=["exact", "incremental"],
+                    help="exact: left-to-right re-sum of every lag list per tick (bit-identical means, the parity default); "
+                         "incremental: guarded running sums (APM_F_INCREMENTAL: signals and lists bit-identical, means to 1e-9)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -204,6 +213,10 @@ def main():
         flags |= _capi.F_ZSCORE
     if wl["pct"]:
         flags |= _capi.F_PERCENTILES
+    if args.baseline == "incremental" and wl["zscore"]:
+        flags |= _capi.F_INCREMENTAL
+        config["workload"] = config["workload"].replace("exact-order baseline", "guarded incremental baseline")
+        config["baseline_mode"] = "incremental (APM_F_INCREMENTAL): signals and lag lists bit-identical, rolling mean to 1e-9"
     ecfg = EngineConfig(num_services=wl["services"], num_jvms=wl["jvms"], bucket_ms=wl["bucket_ms"], window=wl["window"],
                         buffer=wl["buffer"], percentiles=wl["percentiles"], z_series_pct=wl["z_series_pct"],
                         lags=wl["lags"], thresholds=wl["thresholds"], influences=wl["influences"], flags=flags,

@@ -48,6 +48,9 @@ enum {
 #define APM_F_KEEP_STATS 4u  /* retain apm_stat_record per tick for apm_fetch_stats */
 #define APM_F_KEEP_FS 8u     /* retain apm_fs_record per tick for apm_fetch_fs      */
 #define APM_F_ALERTS 16u     /* compact signalled fs records for apm_fetch_alerts / all-gather */
+#define APM_F_INCREMENTAL 32u /* guarded incremental baseline: running sums instead of the exact-order rescan of every
+                                 list; signals and lists stay bit-identical (exact re-sum inside a 1e-9 guard band),
+                                 rolling mean / bounds agree to ~1e-12 relative instead of bit for bit */
 
 /* apm_config.sd_mode */
 #define APM_SD_REFERENCE 0 /* "stddev" = sqrt(mean), as util_methods.js:26-50 computes it */
@@ -164,6 +167,7 @@ typedef struct apm_counters {
     uint64_t h2d_bytes, d2h_bytes;
     uint64_t kernel_launches;
     uint64_t keys_seen;
+    uint64_t inc_fallbacks; /* APM_F_INCREMENTAL: columns re-summed exactly because the signal test was inside the guard band */
 } apm_counters;
 
 typedef struct apm_ctx apm_ctx;

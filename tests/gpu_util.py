@@ -56,15 +56,16 @@ def assert_fs_equal(got, want, exact=True):
         assert np.array_equal(np.isnan(a), np.isnan(b)), f
         if exact:  # exact-order summation: identical bits
             assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), f
-        else:
+        else:  # 1e-9 relative to the size of the rolling mean (a bound close to zero is compared on that scale, too)
             m = ~np.isnan(a)
-            assert np.all(np.abs(a[m] - b[m]) <= 1e-9 * np.abs(b[m])), f
+            scale = np.maximum(np.abs(want["avg"]), np.abs(b))
+            assert np.all(np.abs(a[m] - b[m]) <= 1e-9 * scale[m]), f
 
 
-def run_both(c, cols, chunks=None, via="host"):
+def run_both(c, cols, chunks=None, via="host", **engine_kw):
     """Feeds the same columns to the engine (optionally cut in chunks) and the oracle."""
     svc, jvm, ts, el = cols
-    eng = Engine(engine_config(c))
+    eng = Engine(engine_config(c, **engine_kw))
     orc = ocapi.Pipeline(oracle_config(c), fast=True)
     orc.consume(svc, jvm, ts, el)
     n = svc.size

@@ -33,7 +33,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_the_header():
     assert C.sizeof(_capi.ApmConfig) == 200 == C.sizeof(ocapi.ApmConfig)
     assert _capi.STAT_DTYPE == ocapi.STAT_DTYPE and _capi.FS_DTYPE == ocapi.FS_DTYPE
-    assert C.sizeof(_capi.Counters) == 88 and C.sizeof(_capi.TickResult) == 40
+    assert C.sizeof(_capi.Counters) == 96 and C.sizeof(_capi.TickResult) == 40
 
 
 def test_quantize_matches_oracle_to_fixed():
