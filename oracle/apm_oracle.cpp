@@ -196,14 +196,32 @@ static double js_calc_percentile(const int32_t* a, size_t n, double percentile) 
 
 /* processZScoreStats(), stream_calc_z_score.js:66-104.
  * out = {inflNewValue, avg, lb, ub}; NaN == undefined. */
+/* EXTENSION (APM_SD_TRUE, not in the reference): what standardDeviation() was evidently meant to
+ * compute - the population standard deviation of the valid entries, summed left to right. */
+static double true_standard_deviation(const double* a, size_t n, bool* undefined_out) {
+    const double avg = js_average(a, n);
+    *undefined_out = std::isnan(avg);
+    if (*undefined_out) return kNaN;
+    size_t cnt = 0;
+    double ss = 0;
+    for (size_t i = 0; i < n; ++i)
+        if (!std::isnan(a[i])) {
+            const double d = a[i] - avg;
+            ss = ss + d * d;
+            cnt++;
+        }
+    return std::sqrt(ss / (double)cnt);
+}
+
 static int js_process_zscore(long lag, double threshold, double influence, double new_value,
-                             const double* list, size_t len, bool faithful, double out[4]) {
+                             const double* list, size_t len, bool faithful, double out[4], int sd_mode = APM_SD_REFERENCE) {
     double infl = new_value, avg = kNaN, sd = kNaN, lb = kNaN, ub = kNaN;
     int signal = 0;
     if ((long)len >= lag) {
         avg = js_average(list, len);
         bool sd_undef;
-        sd = js_standard_deviation(list, len, faithful, &sd_undef);
+        sd = sd_mode == APM_SD_TRUE ? true_standard_deviation(list, len, &sd_undef)
+                                    : js_standard_deviation(list, len, faithful, &sd_undef);
         bool avg_ok = !std::isnan(avg);           /* (avg || avg == 0)       */
         bool sd_ok = !sd_undef && !std::isnan(sd); /* (stdDev || stdDev == 0) */
         if (avg_ok && sd_ok) {
@@ -353,7 +371,7 @@ void Pipeline::z_process(const apm_stat_record& st, KeyState& ks) {
             double o[4];
             int sig;
             if (!fast || lst.size() < (size_t)lag) {
-                sig = js_process_zscore(lag, L.thr, L.infl, val[s], lst.data(), lst.size(), !fast, o);
+                sig = js_process_zscore(lag, L.thr, L.infl, val[s], lst.data(), lst.size(), !fast, o, cfg.sd_mode);
             } else {
                 /* ring: rotate view so that index 0 is the oldest; summation order is unchanged */
                 size_t h = L.head[s];
@@ -361,7 +379,7 @@ void Pipeline::z_process(const apm_stat_record& st, KeyState& ks) {
                 tmp.resize(lst.size());
                 std::copy(lst.begin() + h, lst.end(), tmp.begin());
                 std::copy(lst.begin(), lst.begin() + h, tmp.begin() + (lst.size() - h));
-                sig = js_process_zscore(lag, L.thr, L.infl, val[s], tmp.data(), tmp.size(), false, o);
+                sig = js_process_zscore(lag, L.thr, L.infl, val[s], tmp.data(), tmp.size(), false, o, cfg.sd_mode);
             }
             infl_v[s] = o[0];
             r.val[s] = val[s]; r.avg[s] = o[1]; r.lb[s] = o[2]; r.ub[s] = o[3];

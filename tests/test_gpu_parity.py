@@ -211,6 +211,26 @@ def test_stats_only_mode_uses_the_shared_memory_tables(S, n, hi):
     eng.close()
 
 
+def test_true_stddev_mode_extension():
+    """APM_SD_TRUE (extension, not in the reference): population stddev of the list instead of the
+    reference's sqrt(mean); same operation order on both sides, so still bit for bit."""
+    from apmbackend_b200 import Engine
+    from oracle import capi as ocapi
+    from tests.gpu_util import engine_config, oracle_config
+    c = dict(CASES[0], thr=(2.5, 2.0))
+    cols = stream_for(c)
+    eng = Engine(engine_config(c, sd_mode=1))
+    ocfg = oracle_config(c)
+    ocfg.sd_mode = 1
+    orc = ocapi.Pipeline(ocfg, fast=True)
+    orc.consume(*cols)
+    eng.process_host(*cols)
+    fs = eng.fetch_fs()
+    assert_fs_equal(fs, orc.fs())
+    assert int(np.abs(fs["signal"]).sum()) > 0
+    eng.close()
+
+
 def test_alerts_are_the_signalled_fs_records():
     c = CASES[0]
     eng, orc, st, fs = run_both(c, stream_for(c))
