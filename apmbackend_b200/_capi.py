@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libapm_b200.so")
 SYNTH_PATH = os.path.join(_HERE, "libapm_synth.so")
 
 OK, E_INVALID, E_DEVICE, E_CAPACITY, E_WOULDBLOCK, E_STATE, E_IO, E_COMM = range(8)
-F_PERCENTILES, F_ZSCORE, F_KEEP_STATS, F_KEEP_FS, F_ALERTS, F_INCREMENTAL = 1, 2, 4, 8, 16, 32
+F_PERCENTILES, F_ZSCORE, F_KEEP_STATS, F_KEEP_FS, F_ALERTS, F_INCREMENTAL, F_PASSTHROUGH = 1, 2, 4, 8, 16, 32, 64
 MAX_PCT, MAX_LAGS, NUM_SERIES = 4, 4, 3
 
 STAT_DTYPE = np.dtype([
@@ -71,11 +71,11 @@ CAUSE_AVG_HARD_MAX, CAUSE_P75_HARD_MAX, CAUSE_AVG_UB, CAUSE_P75_UB, CAUSE_BOTH_U
 
 
 class KernelTimes(C.Structure):
-    _fields_ = [("ms", C.c_double * 8), ("spans", C.c_uint64 * 8)]
+    _fields_ = [("ms", C.c_double * 12), ("spans", C.c_uint64 * 12)]
 
 
 KERNEL_GROUPS = ("tick_finder", "keyed_reduce", "slot_clear", "radix_sort", "window_percentiles", "rolling_baseline",
-                 "alert_compaction", "list_realign")
+                 "alert_compaction", "list_realign", "passthrough")
 
 
 class ApmError(RuntimeError):
@@ -106,6 +106,8 @@ SYMBOLS = {
     "apm_fetch_fs": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "apm_fetch_alerts": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "apm_release_ticks": (C.c_int32, [C.c_void_p]),
+    "apm_fetch_passthrough": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.c_void_p,
+                                          C.c_uint32, C.POINTER(C.c_uint32)]),
     "apm_ticks_buffered": (C.c_uint32, [C.c_void_p]),
     "apm_host_alloc": (C.c_int32, [C.c_uint64, C.POINTER(C.c_void_p)]),
     "apm_host_free": (None, [C.c_void_p]),

@@ -94,7 +94,7 @@ apm_status refresh_counters(apm_ctx* c) {
     c->counters.inc_fallbacks = c->h_counters->inc_fallbacks;
     if (c->may_misalign && c->tick_seq > c->misalign_mark && c->h_counters->pending_lists == 0) c->may_misalign = false;
     if (c->h_counters->log_overflow)
-        return apm_fail(c, APM_E_CAPACITY, "a bucket's value log overflowed max_tx_per_bucket; percentiles of that bucket are incomplete - recreate the context with a larger capacity");
+        return apm_fail(c, APM_E_CAPACITY, "a device buffer sized by max_tx_per_bucket overflowed (a bucket's value log or the passthrough reorder buffer); results that depend on it are incomplete - recreate the context with a larger capacity");
     return APM_OK;
 }
 
@@ -139,6 +139,11 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
     }
     apm_status st = apm_launch_clear_slots(c, mask);
     if (st) return st;
+    if (c->pt_cap) {  // writeHeapToQueue(edgeTs) comes before generateAllStatsToQueue (:364-366)
+        if (c->pt_base_ms == INT64_MIN) c->pt_base_ms = new_latest * c->cfg.bucket_ms - (1ll << 39);
+        st = apm_pt_tick(c, (new_latest - c->cfg.buffer_buckets - 1) * c->cfg.bucket_ms, keep_any ? c->ticks_buffered : 0);
+        if (st) return st;
+    }
 
     // window = labels in [latest - keep, latest - buffer] (:172)
     WindowSlots w;
@@ -209,12 +214,18 @@ apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n,
         const TickMark tm = c->h_ticks[i];
         st = apm_launch_reduce(c, d, pos, tm.pos);  // everything that arrived before the trigger
         if (st) return st;
+        st = apm_pt_append(c, d, pos, tm.pos);
+        if (st) return st;
+        c->pt_seq += tm.pos - pos;
         st = do_tick(c, tm.label);  // tick BEFORE the triggering transaction is added (:348-370)
         if (st) return st;
         pos = tm.pos;
     }
     st = apm_launch_reduce(c, d, pos, n);
     if (st) return st;
+    st = apm_pt_append(c, d, pos, n);
+    if (st) return st;
+    c->pt_seq += n - pos;
     if (res) res->ticks += nt;
     return APM_OK;
 }
@@ -299,6 +310,7 @@ void apm_ctx_destroy(apm_ctx* c) {
         cudaFree(c->inc_sum[l]); cudaFree(c->inc_comp[l]); cudaFree(c->inc_cnt[l]); cudaFree(c->inc_nz[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
     cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->d_gather);
     cudaFree(c->alert_count); cudaFree(c->alert_hard_max); cudaFree(c->alert_suppressed);
+    cudaFree(c->pt_pend[0]); cudaFree(c->pt_pend[1]); cudaFree(c->pt_emit); cudaFree(c->pt_tmp); cudaFree(c->pt_out); cudaFree(c->pt_cursors);
     for (int i = 0; i < 2; ++i) { if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); if (c->ev_consumed[i]) cudaEventDestroy(c->ev_consumed[i]); }
     for (int i = 0; i < 4; ++i) { if (c->ev_stats[i]) cudaEventDestroy(c->ev_stats[i]); if (c->ev_base[i]) cudaEventDestroy(c->ev_base[i]); }
     if (c->ev_mid) cudaEventDestroy(c->ev_mid);
@@ -375,12 +387,28 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     TRY_CREATE(dalloc(&c->slot_meta, (size_t)c->S));
     TRY_CREATE(cudaMemsetAsync(c->slot_meta, 0, sizeof(SlotMeta) * c->S, c->s_main));
     TRY_CREATE(dalloc(&c->d_log_ptrs, (size_t)APM_MAX_SLOTS));
+    if (cfg->flags & APM_F_PASSTHROUGH) {
+        if (cfg->max_tx_per_bucket == 0) { c->err = "max_tx_per_bucket must be > 0 with APM_F_PASSTHROUGH"; return fail(APM_E_INVALID); }
+        c->pt_cap = cfg->max_tx_per_bucket * (uint64_t)(cfg->buffer_buckets + 3);  // due at buffer+1 buckets of age, plus late arrivals
+        c->pt_out_cap = 2 * c->pt_cap;
+        TRY_CREATE(dalloc(&c->pt_pend[0], (size_t)c->pt_cap));
+        TRY_CREATE(dalloc(&c->pt_pend[1], (size_t)c->pt_cap));
+        TRY_CREATE(dalloc(&c->pt_emit, (size_t)c->pt_cap));
+        TRY_CREATE(dalloc(&c->pt_tmp, (size_t)c->pt_cap));
+        TRY_CREATE(dalloc(&c->pt_out, (size_t)c->pt_out_cap));
+        TRY_CREATE(dalloc(&c->pt_cursors, (size_t)3));
+        TRY_CREATE(cudaMemsetAsync(c->pt_cursors, 0, 3 * sizeof(unsigned long long), c->s_main));
+        c->pt_tick_counts.assign(cfg->out_ticks, 0);
+    }
+    if (with_pct(c) || c->pt_cap) {
+        const uint64_t sort_cap = std::max<uint64_t>(with_pct(c) ? cfg->max_tx_per_bucket : 0, c->pt_cap);
+        c->sort_tiles_cap = (sort_cap + 4095) / 4096;
+        TRY_CREATE(dalloc(&c->sort_hist, (size_t)256 * c->sort_tiles_cap));
+        TRY_CREATE(dalloc(&c->sort_base, (size_t)256));
+    }
     if (with_pct(c)) {
         c->log_cap = cfg->max_tx_per_bucket;
         for (int i = 0; i <= c->S; ++i) TRY_CREATE(dalloc(&c->log_buf[i], (size_t)c->log_cap));
-        c->sort_tiles_cap = (c->log_cap + 4095) / 4096;
-        TRY_CREATE(dalloc(&c->sort_hist, (size_t)256 * c->sort_tiles_cap));
-        TRY_CREATE(dalloc(&c->sort_base, (size_t)256));
         c->sort_scratch_bytes = apm_onesweep_scratch_bytes(c->log_cap);
         if (c->sort_scratch_bytes <= ((size_t)1 << 30)) TRY_CREATE(cudaMalloc((void**)&c->sort_scratch, c->sort_scratch_bytes));
         else c->sort_scratch_bytes = 0;  // very large logs keep the three-kernel sort
@@ -487,6 +515,9 @@ apm_status apm_ingest_commit(apm_ctx* c, uint64_t n) {
     c->counters.h2d_bytes += n * 20;
     apm_status st = apm_launch_reduce(c, d, 0, n);
     if (st) return st;
+    st = apm_pt_append(c, d, 0, n);
+    if (st) return st;
+    c->pt_seq += n;
     CUDA_TRY(c, cudaEventRecord(c->ev_consumed[0], c->s_main));
     return APM_OK;
 }
@@ -650,6 +681,7 @@ apm_status apm_release_ticks(apm_ctx* c) {
         CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     }
     c->ticks_buffered = 0;
+    c->pt_out_used = 0;
     return APM_OK;
 }
 

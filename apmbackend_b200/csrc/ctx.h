@@ -1,5 +1,7 @@
 // Context layout and the host-side launchers of each kernel group.
 #pragma once
+#include <climits>
+#include <cstdint>
 #include <string>
 #include <vector>
 
@@ -92,6 +94,16 @@ struct apm_ctx {
     uint32_t ring_head[APM_MAX_LAGS] = {0, 0, 0, 0};                          // slot the next push writes
     double* thr[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};         // [K]
     double* infl[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};        // [K]
+    // transaction passthrough (APM_F_PASSTHROUGH): pending words, due words, sort spare, per-tick output
+    uint64_t* pt_pend[2] = {nullptr, nullptr};
+    uint64_t* pt_emit = nullptr;
+    uint64_t* pt_tmp = nullptr;
+    uint64_t* pt_out = nullptr;
+    unsigned long long* pt_cursors = nullptr;  // [0] pending, [1] due, [2] kept
+    uint64_t pt_cap = 0, pt_out_cap = 0, pt_out_used = 0, pt_seq = 0;
+    int pt_cur = 0;
+    int64_t pt_base_ms = INT64_MIN;
+    std::vector<uint32_t> pt_tick_counts;
     // guarded incremental baseline (APM_F_INCREMENTAL): running statistics per column
     double* inc_sum[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};
     double* inc_comp[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr};
@@ -128,7 +140,7 @@ struct apm_ctx {
     std::string err;
 };
 
-enum { APM_PG_TICKFIND = 0, APM_PG_REDUCE, APM_PG_CLEAR, APM_PG_SORT, APM_PG_TICKSTATS, APM_PG_BASELINE, APM_PG_ALERTS, APM_PG_REALIGN, APM_PG_COUNT };
+enum { APM_PG_TICKFIND = 0, APM_PG_REDUCE, APM_PG_CLEAR, APM_PG_SORT, APM_PG_TICKSTATS, APM_PG_BASELINE, APM_PG_ALERTS, APM_PG_REALIGN, APM_PG_PASSTHROUGH, APM_PG_COUNT };
 
 // Brackets the launches issued during its lifetime with an event pair when profiling is on.
 struct ProfScope {
@@ -169,6 +181,9 @@ apm_status apm_baseline_make_tmaps(apm_ctx* c);
 apm_status apm_launch_realign(apm_ctx* c, int buf, cudaStream_t st);
 apm_status apm_launch_alert_counter(apm_ctx* c, uint32_t fs_slot, cudaStream_t st);
 apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t alert_slot, cudaStream_t st);
+// k5_passthrough.cu
+apm_status apm_pt_append(apm_ctx* c, const apm_tx_columns& d, uint64_t begin, uint64_t end);
+apm_status apm_pt_tick(apm_ctx* c, int64_t edge_ts, uint32_t tick_slot);
 // comm.cu
 void apm_comm_destroy_internal(apm_ctx* c);
 // capi.cu

@@ -185,6 +185,16 @@ class Engine:
         self._check(self._lib.apm_fetch_alerts(self._h, out.ctypes.data, cap, C.byref(n)))
         return out[:n.value]
 
+    def fetch_passthrough(self, cap: int = 1 << 22):
+        """(end_ts, seq, per-tick counts) of the transactions the retained ticks released, oldest first."""
+        ts = np.empty(cap, np.int64)
+        seq = np.empty(cap, np.uint32)
+        counts = np.zeros(max(self.cfg.out_ticks, 1), np.uint32)
+        n, nt = C.c_uint64(0), C.c_uint32(0)
+        self._check(self._lib.apm_fetch_passthrough(self._h, ts.ctypes.data, seq.ctypes.data, cap, C.byref(n), counts.ctypes.data,
+                                                    counts.size, C.byref(nt)))
+        return ts[:n.value], seq[:n.value], counts[:nt.value]
+
     def release_ticks(self):
         self._check(self._lib.apm_release_ticks(self._h))
 

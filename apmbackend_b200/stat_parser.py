@@ -44,6 +44,12 @@ class StatParser:
         self._jvm_names = []
         self._pending = ([], [], [], [])  # service_id, jvm_id, endTs, elapsed
         self.lastFsRecords = None  # fs records of the most recent tick (read by ZScoreParser)
+        # With APM_F_PASSTHROUGH the device keeps the reorder buffer: the host only remembers each
+        # transaction by its arrival sequence number until the device releases it.
+        self._device_heap = bool(engine.cfg.flags & 64)
+        self._tx_by_seq = {}
+        self._seq = 0
+        self._released = []
 
     # ---- :40-52
     def setProperties(self, servers, latestBucket, minHeap):
@@ -94,7 +100,11 @@ class StatParser:
         sid, jid = self._ids(txEntry.server, txEntry.service)
         p = self._pending
         p[0].append(sid); p[1].append(jid); p[2].append(int(txEntry.endTs)); p[3].append(int(txEntry.elapsed))
-        self.minHeap.push(txEntry)
+        if self._device_heap:
+            self._tx_by_seq[self._seq & 0xFFFFFF] = txEntry
+            self._seq += 1
+        else:
+            self.minHeap.push(txEntry)
 
     def _flush(self):
         p = self._pending
@@ -105,6 +115,10 @@ class StatParser:
 
     # ---- :136-155
     def writeHeapToQueue(self, ts, outQueue):
+        if self._device_heap:
+            # the device releases them during the tick that follows (same edgeTs): remember where they go
+            self._released_queue = outQueue
+            return
         for el in self.minHeap.popAllLessOrEqualToScore(self.minHeap.scoreFunction(_Score(ts))):
             outQueue.writeLineToQueue(el.toCSVString(), False)
 
@@ -115,6 +129,13 @@ class StatParser:
             raise ValueError("interval/window/buffer differ from the engine's configuration")
         self._flush()
         self.engine.tick(int(self.latestBucket))
+        if self._device_heap:
+            _, seqs, _ = self.engine.fetch_passthrough()
+            q = getattr(self, "_released_queue", None)
+            for sq in seqs.tolist():
+                tx = self._tx_by_seq.pop(sq)
+                if q is not None:
+                    q.writeLineToQueue(tx.toCSVString(), False)
         stats = self.engine.fetch_stats()
         self.lastFsRecords = self.engine.fetch_fs().copy() if cfg.lags else None
         self.engine.release_ticks()

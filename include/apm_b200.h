@@ -48,6 +48,8 @@ enum {
 #define APM_F_KEEP_STATS 4u  /* retain apm_stat_record per tick for apm_fetch_stats */
 #define APM_F_KEEP_FS 8u     /* retain apm_fs_record per tick for apm_fetch_fs      */
 #define APM_F_ALERTS 16u     /* compact signalled fs records for apm_fetch_alerts / all-gather */
+#define APM_F_PASSTHROUGH 64u /* keep a device-side reorder buffer and emit the time-ordered transaction passthrough at
+                                 every tick (replaces the stats stage's min-heap) */
 #define APM_F_INCREMENTAL 32u /* guarded incremental baseline: running sums instead of the exact-order rescan of every
                                  list; signals and lists stay bit-identical (exact re-sum inside a 1e-9 guard band),
                                  rolling mean / bounds agree to ~1e-12 relative instead of bit for bit */
@@ -229,6 +231,13 @@ apm_status apm_fetch_stats(apm_ctx* ctx, apm_stat_record* out, uint64_t cap, uin
 apm_status apm_fetch_fs(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
 apm_status apm_fetch_alerts(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
 apm_status apm_release_ticks(apm_ctx* ctx);
+/* With APM_F_PASSTHROUGH: replaces writeHeapToQueue (stream_calc_stats.js:136-155).  Every valid
+ * transaction that was ingested gets the next arrival sequence number (counted over all submitted
+ * transactions, modulo 2^24); at each tick those with endTs <= edgeTs leave the device's reorder
+ * buffer in non-decreasing endTs order (ties in arrival order).  Returns the retained ticks' output
+ * concatenated (end_ts and/or seq may be NULL) and how many entries each tick released. */
+apm_status apm_fetch_passthrough(apm_ctx* ctx, int64_t* end_ts, uint32_t* seq, uint64_t cap, uint64_t* n,
+                                 uint32_t* tick_counts, uint32_t tick_cap, uint32_t* nticks);
 /* Page-locked host memory for the `out` buffers above (the N-API addon wraps it as an external
  * ArrayBuffer): a fetch into it is one DMA instead of a staged copy.  No reference counterpart. */
 apm_status apm_host_alloc(uint64_t bytes, void** out);
@@ -257,8 +266,8 @@ apm_status apm_state_load(apm_ctx* ctx, const char* path);
  * inserts, stream_insert_db.js:295-308).  When enabled, every launch group is bracketed by
  * CUDA events on the context's stream; read sums them per group and resets.
  * groups: 0 tick finder, 1 keyed reduce, 2 slot clear, 3 radix sort, 4 window/percentiles,
- *         5 rolling baseline, 6 alert compaction, 7 lag-list realignment. */
-#define APM_KT_GROUPS 8
+ *         5 rolling baseline, 6 alert compaction, 7 lag-list realignment, 8 transaction passthrough. */
+#define APM_KT_GROUPS 12
 typedef struct apm_kernel_times {
     double ms[APM_KT_GROUPS];
     uint64_t spans[APM_KT_GROUPS]; /* event-bracketed launch groups (one per tick and kernel group) */

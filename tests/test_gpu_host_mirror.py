@@ -51,6 +51,23 @@ def test_consume_msg_protocol_emits_the_reference_lines():
     eng.close()
 
 
+def test_device_reorder_buffer_forwards_the_same_transactions():
+    """With APM_F_PASSTHROUGH the mirror keeps no heap: the db_insert lines must be the reference heap's."""
+    txs = _stream(seed=25, n=2000)
+    lags, thr, infl = (8,), (2.0,), (0.1,)
+    host = StatParser(Engine(EngineConfig(num_services=8, num_jvms=2, lags=lags, thresholds=thr, influences=infl, out_ticks=8)))
+    dev = StatParser(Engine(EngineConfig(num_services=8, num_jvms=2, lags=lags, thresholds=thr, influences=infl, out_ticks=8,
+                                         flags=1 | 2 | 4 | 8 | 16 | 64, max_tx_per_bucket=1 << 14)))
+    out_h, db_h, out_d, db_d = ListQueue(), ListQueue(), ListQueue(), ListQueue()
+    for tx in txs:
+        host.consumeMsg(tx.toCSVString(), out_h, db_h)
+        dev.consumeMsg(tx.toCSVString(), out_d, db_d)
+    assert out_d.lines == out_h.lines
+    ts_d = [int(l.split("|")[6]) for l in db_d.lines]
+    assert ts_d == sorted(ts_d) and sorted(db_d.lines) == sorted(db_h.lines) and len(db_d.lines) > 1000
+    assert dev.minHeap.size() == 0 and len(dev._tx_by_seq) == host.minHeap.size()
+
+
 def test_batch_fast_path_emits_the_same_lines():
     txs = _stream(seed=22)
     lags, thr, infl = (8, 30), (2.0, 1.5), (0.1, 0.0)
