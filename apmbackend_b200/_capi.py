@@ -111,6 +111,7 @@ SYMBOLS = {
     "apm_ticks_buffered": (C.c_uint32, [C.c_void_p]),
     "apm_host_alloc": (C.c_int32, [C.c_uint64, C.POINTER(C.c_void_p)]),
     "apm_host_free": (None, [C.c_void_p]),
+    "apm_bind_fs_output": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64]),
     "apm_sync": (C.c_int32, [C.c_void_p]),
     "apm_ring_load": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint32]),
     "apm_ring_read": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint32,

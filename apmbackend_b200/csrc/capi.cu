@@ -115,6 +115,17 @@ apm_status launch_baseline_group(apm_ctx* c, const PendingBaseline& pb, cudaStre
         st = apm_launch_compact_alerts(c, pb.fslot, pb.tslot, sb);
         if (st) return st;
     }
+    if (c->h_fs_bound && (c->cfg.flags & APM_F_KEEP_FS)) {
+        // this tick's records go to the bound pinned buffer on their own stream, under the following ticks
+        const size_t per_tick = (size_t)c->K * c->cfg.num_lags;
+        if (((size_t)pb.tslot + 1) * per_tick <= c->h_fs_bound_cap) {
+            CUDA_TRY(c, cudaEventRecord(c->ev_d2h, sb));
+            CUDA_TRY(c, cudaStreamWaitEvent(c->s_d2h, c->ev_d2h, 0));
+            CUDA_TRY(c, cudaMemcpyAsync(c->h_fs_bound + (size_t)pb.tslot * per_tick, c->d_fs + (size_t)pb.fslot * per_tick,
+                                        per_tick * sizeof(apm_fs_record), cudaMemcpyDeviceToHost, c->s_d2h));
+            c->counters.d2h_bytes += per_tick * sizeof(apm_fs_record);
+        }
+    }
     return APM_OK;
 }
 
@@ -237,9 +248,10 @@ static apm_status fetch_dense(apm_ctx* c, const R* d_src, size_t per_tick, R* ou
     const size_t total = (size_t)c->ticks_buffered * per_tick;
     if (total == 0) return APM_OK;
     if (cap < total) return apm_fail(c, APM_E_CAPACITY, "output buffer smaller than ticks_buffered * records per tick");
-    CUDA_TRY(c, cudaMemcpyAsync(out, d_src, total * sizeof(R), cudaMemcpyDeviceToHost, c->s_main));
+    // the records of the last tick are written on the baseline stream: finish that first, then copy
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
+    CUDA_TRY(c, cudaMemcpyAsync(out, d_src, total * sizeof(R), cudaMemcpyDeviceToHost, c->s_main));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     c->counters.d2h_bytes += total * sizeof(R);
     size_t w = 0;
@@ -314,6 +326,8 @@ void apm_ctx_destroy(apm_ctx* c) {
     for (int i = 0; i < 2; ++i) { if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); if (c->ev_consumed[i]) cudaEventDestroy(c->ev_consumed[i]); }
     for (int i = 0; i < 4; ++i) { if (c->ev_stats[i]) cudaEventDestroy(c->ev_stats[i]); if (c->ev_base[i]) cudaEventDestroy(c->ev_base[i]); }
     if (c->ev_mid) cudaEventDestroy(c->ev_mid);
+    if (c->ev_d2h) cudaEventDestroy(c->ev_d2h);
+    if (c->s_d2h) { cudaStreamSynchronize(c->s_d2h); cudaStreamDestroy(c->s_d2h); }
     if (c->s_base) cudaStreamDestroy(c->s_base);
     if (c->s_main) cudaStreamDestroy(c->s_main);
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
@@ -365,6 +379,8 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_base[i], cudaEventDisableTiming));
     }
     TRY_CREATE(cudaEventCreateWithFlags(&c->ev_mid, cudaEventDisableTiming));
+    TRY_CREATE(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
+    TRY_CREATE(cudaEventCreateWithFlags(&c->ev_d2h, cudaEventDisableTiming));
     if (const char* e = getenv("APM_NO_OVERLAP")) c->overlap = atoi(e) == 0;
     for (int i = 0; i < 2; ++i) {
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
@@ -553,11 +569,26 @@ apm_status apm_process_host(apm_ctx* c, const apm_tx_columns* h, uint64_t n, apm
     if (!c || !h) return APM_E_INVALID;
     if (res) memset(res, 0, sizeof *res);
     const apm_counters before = c->counters;
+    // chunk plan: the first chunks are small so that compute starts while most of the
+    // input is still crossing PCIe; after that every chunk's copy hides behind the previous chunk's kernels
     const uint64_t B = c->cfg.max_batch;
-    const uint64_t nchunks = (n + B - 1) / B;
+    std::vector<std::pair<uint64_t, uint64_t>> chunks;  // (offset, length)
+    {
+        // when the call spans several batches the host path is copy-bound: quarter-size chunks keep the
+        // un-overlapped head (first copy) and tail (last chunk's kernels) short
+        const uint64_t top = n > B ? std::max<uint64_t>(B / 4, 1) : B;
+        uint64_t off = 0, len = n > B ? std::max<uint64_t>(B / 16, 1) : B;
+        while (off < n) {
+            const uint64_t m = std::min<uint64_t>(n - off, len);
+            chunks.emplace_back(off, m);
+            off += m;
+            len = std::min<uint64_t>(len * 2, top);
+        }
+    }
+    const uint64_t nchunks = chunks.size();
     auto enqueue_copy = [&](uint64_t ci) -> apm_status {
         const int b = (int)(ci & 1);
-        const uint64_t off = ci * B, m = std::min<uint64_t>(n - off, B);
+        const uint64_t off = chunks[ci].first, m = chunks[ci].second;
         apm_tx_columns& d = c->dev[b];
         CUDA_TRY(c, cudaStreamWaitEvent(c->s_copy, c->ev_consumed[b], 0));
         CUDA_TRY(c, cudaMemcpyAsync(d.service_id, h->service_id + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
@@ -571,11 +602,10 @@ apm_status apm_process_host(apm_ctx* c, const apm_tx_columns* h, uint64_t n, apm
     if (nchunks) { apm_status st = enqueue_copy(0); if (st) return st; }
     for (uint64_t ci = 0; ci < nchunks; ++ci) {
         const int b = (int)(ci & 1);
-        const uint64_t off = ci * B, m = std::min<uint64_t>(n - off, B);
         // the next chunk's copy overlaps this chunk's kernels
         if (ci + 1 < nchunks) { apm_status st = enqueue_copy(ci + 1); if (st) return st; }
         CUDA_TRY(c, cudaStreamWaitEvent(c->s_main, c->ev_copied[b], 0));
-        apm_status st = process_chunk_device(c, c->dev[b], m, res);
+        apm_status st = process_chunk_device(c, c->dev[b], chunks[ci].second, res);
         if (st) return st;
         CUDA_TRY(c, cudaEventRecord(c->ev_consumed[b], c->s_main));
     }
@@ -636,9 +666,48 @@ apm_status apm_fetch_stats(apm_ctx* c, apm_stat_record* out, uint64_t cap, uint6
 apm_status apm_fetch_fs(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64_t* n) {
     if (!c || !n) return APM_E_INVALID;
     if (!(c->cfg.flags & APM_F_KEEP_FS) || !with_z(c)) return apm_fail(c, APM_E_STATE, "fs records are not retained (APM_F_KEEP_FS | APM_F_ZSCORE)");
-    apm_status st = fetch_dense(c, c->d_fs, (size_t)c->K * c->cfg.num_lags, out, cap, n);
+    const size_t per_tick = (size_t)c->K * c->cfg.num_lags, total = (size_t)c->ticks_buffered * per_tick;
+    if (out && out == c->h_fs_bound && total <= c->h_fs_bound_cap) {
+        // the records were streamed here tick by tick: wait for the last copy and drop invalid ones in place
+        *n = 0;
+        apm_status st = sync_all(c);
+        if (st) return st;
+        if (cap < total) return apm_fail(c, APM_E_CAPACITY, "output buffer smaller than ticks_buffered * records per tick");
+        uint32_t unseen = 1;
+        CUDA_TRY(c, cudaMemcpy(&unseen, &c->d_counters->unseen_records, sizeof unseen, cudaMemcpyDeviceToHost));
+        size_t w = total;
+        if (unseen) {  // some keys have not been seen yet: their slots hold invalid records
+            w = 0;
+            for (size_t i = 0; i < total; ++i)
+                if (out[i].flags & 1) {
+                    if (w != i) out[w] = out[i];
+                    ++w;
+                }
+        }
+        *n = w;
+        c->counters.fs_records += w;
+        return APM_OK;
+    }
+    apm_status st = fetch_dense(c, c->d_fs, per_tick, out, cap, n);
     if (!st) c->counters.fs_records += *n;
     return st;
+}
+
+apm_status apm_bind_fs_output(apm_ctx* c, apm_fs_record* pinned, uint64_t cap_records) {
+    if (!c) return APM_E_INVALID;
+    apm_status st = sync_all(c);
+    if (st) return st;
+    if (pinned) {
+        if (!(c->cfg.flags & APM_F_KEEP_FS) || !with_z(c)) return apm_fail(c, APM_E_STATE, "bind_fs_output needs APM_F_KEEP_FS | APM_F_ZSCORE");
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, pinned) != cudaSuccess || at.type != cudaMemoryTypeHost) {
+            cudaGetLastError();
+            return apm_fail(c, APM_E_INVALID, "bind_fs_output: the buffer must be page-locked host memory (apm_host_alloc)");
+        }
+    }
+    c->h_fs_bound = pinned;
+    c->h_fs_bound_cap = pinned ? cap_records : 0;
+    return APM_OK;
 }
 
 apm_status apm_fetch_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64_t* n) {
@@ -647,9 +716,9 @@ apm_status apm_fetch_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64
     if (!c->d_alerts) return apm_fail(c, APM_E_STATE, "alerts are not compacted (APM_F_ALERTS | APM_F_ZSCORE)");
     if (c->ticks_buffered == 0) return APM_OK;
     std::vector<unsigned int> counts(c->ticks_buffered);
-    CUDA_TRY(c, cudaMemcpyAsync(counts.data(), c->d_alert_count, sizeof(unsigned int) * c->ticks_buffered, cudaMemcpyDeviceToHost, c->s_main));
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
-    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_base));  // the alert blocks are written on the baseline stream
+    CUDA_TRY(c, cudaMemcpyAsync(counts.data(), c->d_alert_count, sizeof(unsigned int) * c->ticks_buffered, cudaMemcpyDeviceToHost, c->s_main));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     uint64_t total = 0;
     for (unsigned int k : counts) {
@@ -680,6 +749,7 @@ apm_status apm_release_ticks(apm_ctx* c) {
         CUDA_TRY(c, cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * c->cfg.out_ticks, c->s_main));
         CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     }
+    CUDA_TRY(c, cudaMemsetAsync(&c->d_counters->unseen_records, 0, sizeof(uint32_t), c->s_main));
     c->ticks_buffered = 0;
     c->pt_out_used = 0;
     return APM_OK;

@@ -41,6 +41,8 @@ struct DevCounters {
     unsigned long long ingested, dropped, invalid, future, log_overflow;
     unsigned long long inc_fallbacks;  // guarded incremental baseline: columns that had to be re-summed exactly
     uint32_t max_value;      // largest elapsed ever ingested (bounds the radix passes)
+    uint32_t unseen_records; // record slots of keys not seen yet, over the retained ticks (0: every retained record is valid)
+    uint32_t pad_;
     uint32_t pending_lists;  // keys that hold a loaded lag list but have not emitted yet (may still need realigning)
 };
 

@@ -79,6 +79,11 @@ struct apm_ctx {
     unsigned int* d_alert_count = nullptr;  // [out_ticks]
     double* zin[2] = {nullptr, nullptr};     // double-buffered [4][K]: tpm', val0, val1, val2 (quantised)
     uint8_t* emit[2] = {nullptr, nullptr};   // [K] key emitted a StatEntry this tick (snapshot of `seen`)
+    // optional: fs records stream to a caller-owned pinned buffer as each tick's baseline finishes
+    apm_fs_record* h_fs_bound = nullptr;
+    uint64_t h_fs_bound_cap = 0;
+    cudaStream_t s_d2h = nullptr;
+    cudaEvent_t ev_d2h = nullptr;
     uint32_t ticks_buffered = 0;
     uint32_t alerts_gather_from = 0;     // first buffered tick not yet all-gathered
 

@@ -91,6 +91,7 @@ struct TickParams {
     apm_stat_record* stats;  // nullptr when stat records are not retained
     double* zin;             // [4][K]
     uint8_t* emit;           // [K]
+    uint32_t* unseen_records;
     int with_pct;
     uint64_t log_cap;
 };
@@ -102,6 +103,7 @@ __global__ void __launch_bounds__(128) tick_stats_kernel(const TickParams p) {
     if (!p.seen[key]) {
         if (p.stats) p.stats[key].flags = 0;
         p.emit[key] = 0;
+        atomicAdd(p.unseen_records, 1u);
         return;
     }
     p.emit[key] = 1;
@@ -232,6 +234,7 @@ apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_
     p.stats = (c->cfg.flags & APM_F_KEEP_STATS) ? c->d_stats + (size_t)tick_slot * c->K : nullptr;
     p.zin = c->zin[buf];
     p.emit = c->emit[buf];
+    p.unseen_records = &c->d_counters->unseen_records;
     p.with_pct = (c->cfg.flags & APM_F_PERCENTILES) && c->cfg.num_percentiles > 0;
     p.log_cap = c->log_cap;
     tick_stats_kernel<<<(c->K + 127) / 128, 128, 0, c->s_main>>>(p);

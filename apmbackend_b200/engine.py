@@ -164,6 +164,12 @@ class Engine:
             self._pinned[kind] = have = (p, arr)
         return have[1]
 
+    def bind_fs_output(self):
+        """fs records stream into one pinned buffer tick by tick; fetch_fs(pinned=True) then returns a view of it."""
+        cap = self.cfg.out_ticks * self.K * len(self.cfg.lags)
+        out = self._out_buffer("fs", _capi.FS_DTYPE, cap, True)
+        self._check(self._lib.apm_bind_fs_output(self._h, out.ctypes.data, out.size))
+
     def fetch_stats(self, pinned: bool = False) -> np.ndarray:
         cap = self.ticks_buffered * self.K
         out = self._out_buffer("stats", _capi.STAT_DTYPE, cap, pinned)
@@ -175,7 +181,7 @@ class Engine:
         cap = self.ticks_buffered * self.K * len(self.cfg.lags)
         out = self._out_buffer("fs", _capi.FS_DTYPE, cap, pinned)
         n = C.c_uint64(0)
-        self._check(self._lib.apm_fetch_fs(self._h, out.ctypes.data, cap, C.byref(n)))
+        self._check(self._lib.apm_fetch_fs(self._h, out.ctypes.data, max(cap, 0), C.byref(n)))
         return out[:n.value]
 
     def fetch_alerts(self, pinned: bool = False) -> np.ndarray:

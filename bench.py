@@ -328,6 +328,8 @@ def main():
             host_steps.append(pins)
         tmp.free()
         out_bytes = [0]
+        if wl["zscore"]:
+            eng.bind_fs_output()  # fs records stream to the pinned result buffer tick by tick
 
         def run_step_host(s):
             p = host_steps[s]

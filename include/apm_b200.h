@@ -241,6 +241,10 @@ apm_status apm_fetch_passthrough(apm_ctx* ctx, int64_t* end_ts, uint32_t* seq, u
 /* Page-locked host memory for the `out` buffers above (the N-API addon wraps it as an external
  * ArrayBuffer): a fetch into it is one DMA instead of a staged copy.  No reference counterpart. */
 apm_status apm_host_alloc(uint64_t bytes, void** out);
+/* Streams the fs records of every tick into `pinned` (apm_host_alloc memory, cap_records >= out_ticks *
+ * keys * lags) as soon as that tick's baseline has finished, under the following ticks' work; a later
+ * apm_fetch_fs(ctx, pinned, ...) then only waits for the last copy.  NULL unbinds. */
+apm_status apm_bind_fs_output(apm_ctx* ctx, apm_fs_record* pinned, uint64_t cap_records);
 void apm_host_free(void* p);
 uint32_t apm_ticks_buffered(const apm_ctx* ctx);
 /* wait for all queued device work (for timing) */

@@ -231,6 +231,27 @@ def test_true_stddev_mode_extension():
     eng.close()
 
 
+def test_bound_pinned_output_streams_the_same_fs_records():
+    from apmbackend_b200 import Engine
+    from tests.gpu_util import engine_config
+    c = CASES[0]
+    cols = stream_for(c)
+    a = Engine(engine_config(c))
+    a.process_host(*cols)
+    want = a.fetch_fs().copy()
+    a.close()
+    b = Engine(engine_config(c))
+    b.bind_fs_output()
+    n = cols[0].size
+    parts = []
+    for lo in range(0, n, n // 3 + 1):
+        b.process_host(*[x[lo:lo + n // 3 + 1] for x in cols])
+        parts.append(b.fetch_fs(pinned=True).copy())
+        b.release_ticks()
+    assert np.concatenate(parts).tobytes() == want.tobytes()
+    b.close()
+
+
 def test_alerts_are_the_signalled_fs_records():
     c = CASES[0]
     eng, orc, st, fs = run_both(c, stream_for(c))
