@@ -397,6 +397,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
         c->acc.cnt = (uint32_t*)(c->acc.sq_hi + n);
         c->acc.vmin = c->acc.cnt + n;
         c->acc.vmax = c->acc.vmin + n;
+        c->acc.run_start = c->acc.vmax + n;
     }
     TRY_CREATE(dalloc(&c->seen, K));
     TRY_CREATE(cudaMemsetAsync(c->seen, 0, K, c->s_main));

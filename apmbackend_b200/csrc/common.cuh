@@ -25,8 +25,9 @@ struct AccSoA {
     uint32_t* cnt;
     uint32_t* vmin;  // 0xFFFFFFFF when empty
     uint32_t* vmax;
+    uint32_t* run_start;  // first word of the key's run in the slot's sorted log (percentile mode)
 };
-#define APM_ACC_BYTES_PER_ENTRY 36
+#define APM_ACC_BYTES_PER_ENTRY 40
 
 // Per bucket-slot bookkeeping of the value log (device resident).
 struct SlotMeta {

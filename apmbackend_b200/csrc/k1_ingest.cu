@@ -3,6 +3,8 @@
 // Replaces, for a whole batch at once, what consumeMsg does per message
 // (stream_calc_stats.js:331-371): generateBucketLabel (:89-91), the
 // `bucketLabel > latestBucket` test (:348) and addData (:115-134).
+#include <cstddef>
+
 #include "ctx.h"
 
 namespace {
@@ -178,13 +180,16 @@ constexpr uint32_t K1_EMPTY = 0xFFFFFFFFu;
 constexpr int K1_SLOT_SHIFT = 26;         // tag = slot << 26 | key  (K <= 2^26)
 
 struct K1Smem {
-    uint32_t tag[K1_TABLE], sum[K1_TABLE], sq_lo[K1_TABLE], cnt_hi[K1_TABLE], mn[K1_TABLE], mx[K1_TABLE];
-    uint32_t warp_scan[K1_THREADS / 32];
+    // used by both variants
     unsigned long long base;  // reserved log position of the current (tile, slot) group
+    unsigned long long c[5];
+    uint32_t warp_scan[K1_THREADS / 32];
     uint32_t pick;            // (first pending index << 8 | slot) of the current log group
     uint32_t vmax;
-    unsigned long long c[5];
+    // the hash table: only the stats-only variant allocates it
+    uint32_t tag[K1_TABLE], sum[K1_TABLE], sq_lo[K1_TABLE], cnt_hi[K1_TABLE], mn[K1_TABLE], mx[K1_TABLE];
 };
+constexpr size_t K1_SMEM_APPEND_ONLY = offsetof(K1Smem, tag);
 
 __device__ __forceinline__ uint32_t k1_hash(uint32_t x) {
     x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
@@ -463,9 +468,10 @@ apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin
         attr_set = true;
     }
     if (p.with_log) {
-        // append-only: no per-CTA table to flush, so spread the tiles over every SM
-        uint64_t b2 = tiles < max_blocks ? tiles : max_blocks;
-        reduce_kernel_v3<false><<<(unsigned)b2, K1_THREADS, sizeof(K1Smem), c->s_main>>>(p);
+        // append-only: no table in shared memory and none to flush, so the tiles spread over every SM (2 CTAs each: 64 registers per thread)
+        const uint64_t cap4 = (uint64_t)APM_NUM_SMS * 2;
+        uint64_t b2 = tiles < cap4 ? tiles : cap4;
+        reduce_kernel_v3<false><<<(unsigned)b2, K1_THREADS, K1_SMEM_APPEND_ONLY, c->s_main>>>(p);
     } else {
         reduce_kernel_v3<true><<<(unsigned)blocks, K1_THREADS, sizeof(K1Smem), c->s_main>>>(p);
     }

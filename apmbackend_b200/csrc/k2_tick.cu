@@ -14,7 +14,7 @@ __global__ void __launch_bounds__(256) clear_slots_kernel(const AccSoA acc, Slot
     const size_t base = (size_t)slot * K;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)K; i += (size_t)gridDim.x * blockDim.x) {
         acc.sum[base + i] = 0; acc.sq_lo[base + i] = 0; acc.sq_hi[base + i] = 0;
-        acc.cnt[base + i] = 0; acc.vmin[base + i] = 0xFFFFFFFFu; acc.vmax[base + i] = 0;
+        acc.cnt[base + i] = 0; acc.vmin[base + i] = 0xFFFFFFFFu; acc.vmax[base + i] = 0; acc.run_start[base + i] = 0;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         meta[slot].count = 0;
@@ -27,16 +27,6 @@ struct Run {
     const uint64_t* p;  // first word of this key's ascending run inside a sorted bucket log
     uint32_t n;
 };
-
-// first index in [0, n) whose word is >= x
-__device__ __forceinline__ uint64_t lower_bound_u64(const uint64_t* a, uint64_t n, uint64_t x) {
-    uint64_t lo = 0, hi = n;
-    while (lo < hi) {
-        const uint64_t mid = (lo + hi) >> 1;
-        if (__ldg(a + mid) < x) lo = mid + 1; else hi = mid;
-    }
-    return lo;
-}
 
 // number of values <= v in an ascending run (values are the low 32 bits)
 __device__ __forceinline__ uint32_t count_le(const Run& r, uint32_t v) {
@@ -130,11 +120,8 @@ __global__ void __launch_bounds__(128) tick_stats_kernel(const TickParams p) {
         sq_hi += add_hi + (t < sq_lo ? 1u : 0u);
         sq_lo = t;
         if (p.with_pct) {
-            const uint64_t* lg = p.logs[slot];
-            uint64_t ln = p.slot_meta[slot].count;
-            ln = ln < p.log_cap ? ln : p.log_cap;
-            const uint64_t s = lower_bound_u64(lg, ln, (uint64_t)key << 32);
-            runs[nruns].p = lg + s;
+            // the rebuild of the planes from the sorted log recorded where this key's run starts
+            runs[nruns].p = p.logs[slot] + p.acc.run_start[ai];
             runs[nruns].n = c;
             ++nruns;
         }

@@ -229,7 +229,10 @@ __global__ void __launch_bounds__(AS_THREADS) acc_from_sorted_kernel(const uint6
             if ((uint32_t)j < cnt_here) {
                 const uint32_t k = (uint32_t)(x[j] >> 32), v = (uint32_t)x[j];
                 const uint32_t nk = ((uint32_t)(j + 1) < cnt_here) ? (uint32_t)(x[(j + 1) % AS_ITEMS] >> 32) : next_key;
-                if (k != pk || (i0 + j) == 0) acc.vmin[base + k] = v;
+                if (k != pk || (i0 + j) == 0) {
+                    acc.vmin[base + k] = v;
+                    acc.run_start[base + k] = (uint32_t)(i0 + j);
+                }
                 if (k != nk) acc.vmax[base + k] = v;
                 pk = k;
             }
@@ -276,7 +279,7 @@ __global__ void __launch_bounds__(256) clear_planes_kernel(const AccSoA acc, uin
     const size_t base = (size_t)slot * K;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)K; i += (size_t)gridDim.x * blockDim.x) {
         acc.sum[base + i] = 0; acc.sq_lo[base + i] = 0; acc.sq_hi[base + i] = 0;
-        acc.cnt[base + i] = 0; acc.vmin[base + i] = 0xFFFFFFFFu; acc.vmax[base + i] = 0;
+        acc.cnt[base + i] = 0; acc.vmin[base + i] = 0xFFFFFFFFu; acc.vmax[base + i] = 0; acc.run_start[base + i] = 0;
     }
 }
 

@@ -63,7 +63,7 @@ apm_status apm_state_save(apm_ctx* c, const char* path) {
     StateHeader h;
     memset(&h, 0, sizeof h);
     memcpy(h.magic, "APMB200", 8);
-    h.version = 3; h.K = c->K; h.S = c->S; h.num_lags = c->log_cap ? c->cfg.num_lags : c->cfg.num_lags;
+    h.version = 4; h.K = c->K; h.S = c->S; h.num_lags = c->log_cap ? c->cfg.num_lags : c->cfg.num_lags;
     h.bucket_ms = c->cfg.bucket_ms; h.window = c->cfg.window_buckets; h.buffer = c->cfg.buffer_buckets;
     h.latest = c->latest;
     const bool rings = (c->cfg.flags & APM_F_ZSCORE) && c->cfg.num_lags > 0;
@@ -103,7 +103,7 @@ apm_status apm_state_load(apm_ctx* c, const char* path) {
     fl.f = fopen(path, "rb");
     if (!fl.f) return apm_fail(c, APM_E_IO, std::string("cannot open for reading: ") + path);
     StateHeader h;
-    if (fread(&h, sizeof h, 1, fl.f) != 1 || memcmp(h.magic, "APMB200", 8) != 0 || h.version != 3)
+    if (fread(&h, sizeof h, 1, fl.f) != 1 || memcmp(h.magic, "APMB200", 8) != 0 || h.version != 4)
         return apm_fail(c, APM_E_IO, "not an apm_b200 state file");
     const bool rings = (c->cfg.flags & APM_F_ZSCORE) && c->cfg.num_lags > 0;
     bool same = h.K == c->K && h.S == c->S && h.bucket_ms == c->cfg.bucket_ms && h.window == c->cfg.window_buckets &&
