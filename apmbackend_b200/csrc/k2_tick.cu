@@ -86,6 +86,79 @@ struct TickParams {
     uint64_t log_cap;
 };
 
+// calcPercentile's index rule (util_methods.js:112-142), double index arithmetic without contraction:
+// the percentile is element i0 of the sorted window, or the mean of elements i0 and i0 + 1 when `pair`
+__device__ __forceinline__ void pct_index(double pfrac, uint64_t cnt, uint64_t* i0_out, bool* pair_out) {
+    const double n = (double)cnt;
+    const double index = __dsub_rn(__dmul_rn(pfrac, n), 1.0);
+    uint64_t i0;
+    bool pair = false;
+    if (pfrac == 0.0) {
+        i0 = 0;
+    } else if (pfrac == 1.0) {
+        i0 = cnt - 1;
+    } else if (cnt == 1 || index == trunc(index)) {
+        i0 = index < 0 ? 0 : (uint64_t)index;
+    } else {
+        const double ci = ceil(index);
+        i0 = ci < 0 ? 0 : (uint64_t)ci;
+        pair = i0 != cnt - 1;
+    }
+    *i0_out = i0;
+    *pair_out = pair;
+}
+
+// mean and (extension) population stddev of a window from its exact integer moments
+__device__ __forceinline__ void key_moments(uint64_t cnt, uint64_t sum, uint64_t sq_lo, uint64_t sq_hi, double* avg, double* sd) {
+    *avg = __ddiv_rn((double)sum, (double)cnt);  // :181, one correctly rounded divide of exact integers
+    // var = (cnt*sumsq - sum^2) / cnt^2 in 128-bit integers (domain: result < 2^128)
+    const uint64_t a_lo = cnt * sq_lo, a_hi = __umul64hi(cnt, sq_lo) + cnt * sq_hi;
+    const uint64_t b_lo = sum * sum, b_hi = __umul64hi(sum, sum);
+    const uint64_t d_lo = a_lo - b_lo, d_hi = a_hi - b_hi - (a_lo < b_lo ? 1u : 0u);
+    const double num = __dadd_rn(__dmul_rn((double)d_hi, 18446744073709551616.0), (double)d_lo);
+    *sd = __ddiv_rn(__dsqrt_rn(num), (double)cnt);
+}
+
+// the stat record and what the z-score stage parses out of the `st` line
+__device__ __forceinline__ void key_epilogue(const TickParams& p, uint32_t key, uint64_t cnt, uint64_t sum, uint32_t vmin, uint32_t vmax,
+                                             double avg, double sd, const double* pct) {
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    const double tpm = __ddiv_rn((double)cnt, p.tpm_div);  // :186
+    if (p.stats) {
+        apm_stat_record r;
+        r.tick_ts = p.tick_ts;
+        r.key = key;
+        r.flags = 1u | (cnt ? 2u : 0u);
+        r.count = cnt;
+        r.sum = sum;
+        r.tpm = tpm;
+        r.avg = avg;
+#pragma unroll
+        for (int q = 0; q < APM_MAX_PCT; ++q) r.pct[q] = pct[q];
+        r.min = cnt ? (int32_t)vmin : 0;
+        r.max = (int32_t)vmax;
+        r.stddev = sd;
+        p.stats[key] = r;
+    }
+    // ---- what the z-score stage parses out of the `st` line (entries.js:71-73 -> 58-61)
+    p.zin[key] = apm_quantize_fixed(tpm, 2);
+    p.zin[(size_t)p.K + key] = apm_quantize_fixed(avg, 1);
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+        const int q = p.zpct[s];
+        p.zin[(size_t)(2 + s) * p.K + key] = (q >= 0 && q < p.npct) ? apm_quantize_fixed(pct[q], 1) : nan;
+    }
+}
+
+// 128-bit accumulate of one slot's sum of squares (stored as sq_hi * 2^32 + sq_lo)
+__device__ __forceinline__ void add_sq(uint64_t& sq_lo, uint64_t& sq_hi, uint64_t lo_part, uint64_t hi_part) {
+    const uint64_t add_lo = lo_part + (hi_part << 32);
+    const uint64_t add_hi = (hi_part >> 32) + (add_lo < lo_part ? 1u : 0u);
+    const uint64_t t = sq_lo + add_lo;
+    sq_hi += add_hi + (t < sq_lo ? 1u : 0u);
+    sq_lo = t;
+}
+
 __global__ void __launch_bounds__(128) tick_stats_kernel(const TickParams p) {
     const uint32_t key = blockIdx.x * blockDim.x + threadIdx.x;
     if (key >= p.K) return;
@@ -113,12 +186,7 @@ __global__ void __launch_bounds__(128) tick_stats_kernel(const TickParams p) {
         vmax = mx > vmax ? mx : vmax;
         sum += p.acc.sum[ai];
         // sum of squares = sq_hi * 2^32 + sq_lo, accumulated as a 128-bit (hi:lo) pair
-        const uint64_t lo_part = p.acc.sq_lo[ai], hi_part = p.acc.sq_hi[ai];
-        const uint64_t add_lo = lo_part + (hi_part << 32);
-        const uint64_t add_hi = (hi_part >> 32) + (add_lo < lo_part ? 1u : 0u);
-        const uint64_t t = sq_lo + add_lo;
-        sq_hi += add_hi + (t < sq_lo ? 1u : 0u);
-        sq_lo = t;
+        add_sq(sq_lo, sq_hi, p.acc.sq_lo[ai], p.acc.sq_hi[ai]);
         if (p.with_pct) {
             // the rebuild of the planes from the sorted log recorded where this key's run starts
             runs[nruns].p = p.logs[slot] + p.acc.run_start[ai];
@@ -128,33 +196,11 @@ __global__ void __launch_bounds__(128) tick_stats_kernel(const TickParams p) {
     }
     double avg = nan, sd = nan, pct[APM_MAX_PCT] = {nan, nan, nan, nan};
     if (cnt != 0) {
-        avg = __ddiv_rn((double)sum, (double)cnt);  // :181, one correctly rounded divide of exact integers
-        // extension: population stddev from exact moments, var = (cnt*sumsq - sum^2) / cnt^2
-        {
-            // 128-bit: cnt * (sq_hi:sq_lo) - sum * sum   (domain: result < 2^128)
-            const uint64_t a_lo = cnt * sq_lo, a_hi = __umul64hi(cnt, sq_lo) + cnt * sq_hi;
-            const uint64_t b_lo = sum * sum, b_hi = __umul64hi(sum, sum);
-            const uint64_t d_lo = a_lo - b_lo, d_hi = a_hi - b_hi - (a_lo < b_lo ? 1u : 0u);
-            const double num = __dadd_rn(__dmul_rn((double)d_hi, 18446744073709551616.0), (double)d_lo);
-            sd = __ddiv_rn(__dsqrt_rn(num), (double)cnt);
-        }
+        key_moments(cnt, sum, sq_lo, sq_hi, &avg, &sd);
         for (int q = 0; q < (p.with_pct ? p.npct : 0); ++q) {
-            // calcPercentile (util_methods.js:112-142), double index arithmetic without contraction
-            const double n = (double)cnt;
-            double index = __dsub_rn(__dmul_rn(p.pfrac[q], n), 1.0);
             uint64_t i0;
-            bool pair = false;
-            if (p.pfrac[q] == 0.0) {
-                i0 = 0;
-            } else if (p.pfrac[q] == 1.0) {
-                i0 = cnt - 1;
-            } else if (cnt == 1 || index == trunc(index)) {
-                i0 = index < 0 ? 0 : (uint64_t)index;
-            } else {
-                const double ci = ceil(index);
-                i0 = ci < 0 ? 0 : (uint64_t)ci;
-                pair = i0 != cnt - 1;
-            }
+            bool pair;
+            pct_index(p.pfrac[q], cnt, &i0, &pair);
             uint32_t v0, v1;
             if (nruns == 1) {
                 v0 = (uint32_t)__ldg(runs[0].p + i0);
@@ -168,30 +214,114 @@ __global__ void __launch_bounds__(128) tick_stats_kernel(const TickParams p) {
             pct[q] = pair ? __dmul_rn(__dadd_rn((double)v0, (double)v1), 0.5) : (double)v0;
         }
     }
-    const double tpm = __ddiv_rn((double)cnt, p.tpm_div);  // :186
-    if (p.stats) {
-        apm_stat_record r;
-        r.tick_ts = p.tick_ts;
-        r.key = key;
-        r.flags = 1u | (cnt ? 2u : 0u);
-        r.count = cnt;
-        r.sum = sum;
-        r.tpm = tpm;
-        r.avg = avg;
+    key_epilogue(p, key, cnt, sum, vmin, vmax, avg, sd, pct);
+}
+
+// ---- sliding windows (more than one bucket per window): one warp per key, one lane per bucket.
+// The thread-per-key kernel above walks the window's runs one after another inside every step of
+// the value bisection - 31 dependent binary searches per step with the reference's settings, and
+// with a few hundred keys only a handful of SMs are busy at all.  Here lane w owns the runs of
+// window buckets w and w + 32: a bisection step is one binary search per lane and a warp sum.
+__device__ __forceinline__ uint64_t warp_sum_u64(uint64_t v) {
 #pragma unroll
-        for (int q = 0; q < APM_MAX_PCT; ++q) r.pct[q] = pct[q];
-        r.min = cnt ? (int32_t)vmin : 0;
-        r.max = (int32_t)vmax;
-        r.stddev = sd;
-        p.stats[key] = r;
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(128) tick_stats_warp_kernel(const TickParams p) {
+    const uint32_t key = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (key >= p.K) return;
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    if (!p.seen[key]) {
+        if (lane == 0) {
+            if (p.stats) p.stats[key].flags = 0;
+            p.emit[key] = 0;
+            atomicAdd(p.unseen_records, 1u);
+        }
+        return;
     }
-    // ---- what the z-score stage parses out of the `st` line (entries.js:71-73 -> 58-61)
-    p.zin[key] = apm_quantize_fixed(tpm, 2);
-    p.zin[(size_t)p.K + key] = apm_quantize_fixed(avg, 1);
+    uint64_t cnt = 0, sum = 0, sq_lo = 0, sq_hi = 0;
+    uint32_t vmin = 0xFFFFFFFFu, vmax = 0;
+    Run runs[2];
 #pragma unroll
-    for (int s = 0; s < 2; ++s) {
-        const int q = p.zpct[s];
-        p.zin[(size_t)(2 + s) * p.K + key] = (q >= 0 && q < p.npct) ? apm_quantize_fixed(pct[q], 1) : nan;
+    for (int h = 0; h < 2; ++h) {
+        const int w = lane + 32 * h;
+        runs[h].p = nullptr;
+        runs[h].n = 0;
+        if (w < p.win.n) {
+            const int slot = p.win.slot[w];
+            const size_t ai = (size_t)slot * p.K + key;
+            const uint32_t c = p.acc.cnt[ai];
+            if (c != 0) {
+                cnt += c;
+                const uint32_t mn = p.acc.vmin[ai], mx = p.acc.vmax[ai];
+                vmin = mn < vmin ? mn : vmin;
+                vmax = mx > vmax ? mx : vmax;
+                sum += p.acc.sum[ai];
+                add_sq(sq_lo, sq_hi, p.acc.sq_lo[ai], p.acc.sq_hi[ai]);
+                runs[h].p = p.logs[slot] + p.acc.run_start[ai];
+                runs[h].n = c;
+            }
+        }
+    }
+    // exact integer moments of the whole window: every lane ends with the same totals
+    cnt = warp_sum_u64(cnt);
+    sum = warp_sum_u64(sum);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const uint64_t olo = __shfl_xor_sync(0xffffffffu, sq_lo, o), ohi = __shfl_xor_sync(0xffffffffu, sq_hi, o);
+        const uint64_t t = sq_lo + olo;
+        sq_hi += ohi + (t < sq_lo ? 1u : 0u);
+        sq_lo = t;
+    }
+    vmin = __reduce_min_sync(0xffffffffu, vmin);
+    vmax = __reduce_max_sync(0xffffffffu, vmax);
+    const int nruns = __popc(__ballot_sync(0xffffffffu, runs[0].n != 0)) + __popc(__ballot_sync(0xffffffffu, runs[1].n != 0));
+
+    double avg = nan, sd = nan, pct[APM_MAX_PCT] = {nan, nan, nan, nan};
+    if (cnt != 0) {
+        key_moments(cnt, sum, sq_lo, sq_hi, &avg, &sd);
+        for (int q = 0; q < (p.with_pct ? p.npct : 0); ++q) {
+            uint64_t i0;
+            bool pair;
+            pct_index(p.pfrac[q], cnt, &i0, &pair);
+            if (nruns == 1) {  // a single populated bucket: the window is that run, index it directly
+                uint32_t a = 0, b = 0;
+                if (runs[0].n | runs[1].n) {
+                    const Run& r = runs[0].n ? runs[0] : runs[1];
+                    a = (uint32_t)__ldg(r.p + i0);
+                    b = pair ? (uint32_t)__ldg(r.p + i0 + 1) : a;
+                }
+                const uint32_t v0 = __reduce_max_sync(0xffffffffu, a), v1 = __reduce_max_sync(0xffffffffu, b);
+                pct[q] = pair ? __dmul_rn(__dadd_rn((double)v0, (double)v1), 0.5) : (double)v0;
+                continue;
+            }
+            // value bisection: the i0-th smallest is the least v with #(values <= v) >= i0 + 1
+            uint32_t lo = vmin, hi = vmax;
+            while (lo < hi) {
+                const uint32_t mid = lo + ((hi - lo) >> 1);
+                const uint64_t c = warp_sum_u64((uint64_t)count_le(runs[0], mid) + count_le(runs[1], mid));
+                if (c >= i0 + 1) hi = mid; else lo = mid + 1;
+            }
+            const uint32_t v0 = lo;
+            uint32_t v1 = v0;
+            if (pair) {
+                const uint32_t c0 = count_le(runs[0], v0), c1 = count_le(runs[1], v0);
+                const uint64_t n_le = warp_sum_u64((uint64_t)c0 + c1);
+                if (n_le < i0 + 2) {  // element i0 + 1 is the smallest value above v0
+                    uint32_t best = 0xFFFFFFFFu;
+                    if (c0 < runs[0].n) best = (uint32_t)__ldg(runs[0].p + c0);
+                    if (c1 < runs[1].n) { const uint32_t x = (uint32_t)__ldg(runs[1].p + c1); best = x < best ? x : best; }
+                    v1 = __reduce_min_sync(0xffffffffu, best);
+                }
+            }
+            pct[q] = pair ? __dmul_rn(__dadd_rn((double)v0, (double)v1), 0.5) : (double)v0;
+        }
+    }
+    if (lane == 0) {
+        p.emit[key] = 1;
+        key_epilogue(p, key, cnt, sum, vmin, vmax, avg, sd, pct);
     }
 }
 
@@ -224,7 +354,10 @@ apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_
     p.unseen_records = &c->d_counters->unseen_records;
     p.with_pct = (c->cfg.flags & APM_F_PERCENTILES) && c->cfg.num_percentiles > 0;
     p.log_cap = c->log_cap;
-    tick_stats_kernel<<<(c->K + 127) / 128, 128, 0, c->s_main>>>(p);
+    if (p.with_pct && w.n >= 4)  // below that a warp per key is mostly idle lanes
+        tick_stats_warp_kernel<<<(c->K + 3) / 4, 128, 0, c->s_main>>>(p);
+    else
+        tick_stats_kernel<<<(c->K + 127) / 128, 128, 0, c->s_main>>>(p);
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;

@@ -317,12 +317,48 @@ uint64_t apm_radix_sort_tiles(uint64_t n) { return (n + RS_TILE - 1) / RS_TILE; 
 
 int apm_bits_of(uint64_t v) { return bits_of(v); }
 
+namespace {
+// ---- one-CTA sort for small buckets -----------------------------------------------------------
+// A bucket of a few hundred or thousand transactions (the reference's own deployment: ~10^2 tx
+// per 10-s bucket) is not worth five launches of the tiled radix sort: one CTA loads the words,
+// runs a bitonic network over them in shared memory and stores them back in place.  The words
+// are distinct-or-identical 64-bit integers, so any comparison sort gives the same array.
+constexpr int SS_CAP = 4096, SS_THREADS = 1024;
+
+__global__ void __launch_bounds__(SS_THREADS) small_sort_kernel(uint64_t* __restrict__ data, uint32_t n) {
+    __shared__ uint64_t s[SS_CAP];
+    uint32_t m = 2;
+    while (m < n) m <<= 1;
+    for (uint32_t i = threadIdx.x; i < m; i += SS_THREADS) s[i] = i < n ? data[i] : ~0ull;
+    __syncthreads();
+    for (uint32_t k = 2; k <= m; k <<= 1) {
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t t = threadIdx.x; t < (m >> 1); t += SS_THREADS) {
+                const uint32_t i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), l = i | j;
+                const uint64_t a = s[i], b = s[l];
+                const bool up = (i & k) == 0;
+                if ((a > b) == up) { s[i] = b; s[l] = a; }
+            }
+            __syncthreads();
+        }
+    }
+    for (uint32_t i = threadIdx.x; i < n; i += SS_THREADS) data[i] = s[i];
+}
+}  // namespace
+
+
 // Sorts log slot `slot` (entries were appended since its last sort).
 apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value) {
     ProfScope prof_scope_(c, APM_PG_SORT);
     if (n < 2) return APM_OK;
     if (n > 0xFFFFFFFFull) return apm_fail(c, APM_E_CAPACITY, "value log above 2^32 entries");
     if (apm_radix_sort_tiles(n) > c->sort_tiles_cap) return apm_fail(c, APM_E_CAPACITY, "sort scratch too small");
+    if (n <= (uint64_t)SS_CAP && !c->sort_legacy) {
+        small_sort_kernel<<<1, SS_THREADS, 0, c->s_main>>>(c->log_buf[slot], (uint32_t)n);
+        c->launches += 1;
+        CUDA_TRY(c, cudaGetLastError());
+        return APM_OK;
+    }
     const int vbits = bits_of(max_value), kbits = bits_of(c->K > 1 ? c->K - 1 : 0);
     uint64_t* res = nullptr;
     if (!c->sort_legacy && c->sort_scratch) {

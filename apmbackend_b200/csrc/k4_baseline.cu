@@ -35,11 +35,14 @@ struct BaselineParams {
 };
 
 __device__ __forceinline__ void accumulate(double v, double& sum, uint32_t& cnt) {
-    // average(): `value != null && !isNaN(parseFloat(value))` then `sum + parseFloat(value)`
-    if (v == v) {
-        sum = __dadd_rn(sum, v);
-        cnt += 1;
-    }
+    // average(): `value != null && !isNaN(parseFloat(value))` then `sum + parseFloat(value)`.
+    // A skipped entry is added as +0.0 instead of branching around the add: the running sum starts
+    // at +0.0 and can therefore never be -0.0 (x + y is -0.0 only when both are), so s + 0.0 == s
+    // bit for bit, and the select sits on the loaded value - off the dependent chain of adds, which
+    // is what bounds this kernel when only a few hundred lists are walked.
+    const bool ok = v == v;
+    sum = __dadd_rn(sum, ok ? v : 0.0);
+    cnt += ok ? 1u : 0u;
 }
 
 __global__ void __launch_bounds__(K4_THREADS) baseline_kernel(const BaselineParams p) {
@@ -159,6 +162,7 @@ __global__ void __launch_bounds__(K4_THREADS) baseline_kernel(const BaselinePara
 constexpr int K4T_COLS = 32;
 constexpr int K4T_ROWS = 16;
 constexpr uint32_t K4T_STAGE_BYTES = K4T_COLS * K4T_ROWS * sizeof(double);
+constexpr int K4T_DEEP_STAGES = 24;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -201,7 +205,10 @@ struct __align__(128) K4TSmem {
 
 template <int K4T_STAGES>
 __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant__ CUtensorMap tmap, const BaselineParams p) {
-    __shared__ K4TSmem<K4T_STAGES> sm;
+    // dynamic shared memory: the deep-pipeline instance (few columns, long lists) needs more than 48 KB
+    // (no static shared memory in this kernel, so the dynamic window starts at offset 0 and is 128-byte aligned)
+    extern __shared__ __align__(128) unsigned char k4t_smem_raw[];
+    K4TSmem<K4T_STAGES>& sm = *reinterpret_cast<K4TSmem<K4T_STAGES>*>(k4t_smem_raw);
     const int lane = threadIdx.x;
     const uint32_t col0 = blockIdx.x * K4T_COLS, col = col0 + lane;
     const bool in_range = col < 3u * p.K;
@@ -236,31 +243,54 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
                 tma_load_2d(&sm.buf[c][0][0], &tmap, (int)col0, (int)row0_of(c), &sm.bar[c], policy);
             }
         }
+        // Software pipeline over the chunks: the values of chunk c + 1 are pulled from shared memory
+        // into registers before the dependent adds of chunk c run, so with one warp per SM (few
+        // lists) the walk is paced by the add chain, not by barrier and shared-memory latency.
+        double v[K4T_ROWS], vn[K4T_ROWS];
+        mbar_wait(&sm.bar[0], 0);
+#pragma unroll
+        for (int r = 0; r < K4T_ROWS; ++r) v[r] = sm.buf[0][r][lane];
         for (uint32_t c = 0; c < n; ++c) {
-            const uint32_t s = c % K4T_STAGES, parity = (c / K4T_STAGES) & 1u;
-            mbar_wait(&sm.bar[s], parity);
+            const uint32_t s = c % K4T_STAGES;
+            if (c + 1 < n) {
+                const uint32_t s1 = (c + 1) % K4T_STAGES, parity1 = ((c + 1) / K4T_STAGES) & 1u;
+                mbar_wait(&sm.bar[s1], parity1);
+#pragma unroll
+                for (int r = 0; r < K4T_ROWS; ++r) vn[r] = sm.buf[s1][r][lane];
+            }
             const uint32_t rows = rows_of(c);
             if (rows == (uint32_t)K4T_ROWS) {
-                double v[K4T_ROWS];
-#pragma unroll
-                for (int r = 0; r < K4T_ROWS; ++r) v[r] = sm.buf[s][r][lane];
                 if (full) {
+                    // Sixteen bare adds, validity checked once on the result: a NaN entry (a tick
+                    // the key had no data for) poisons t, and only then is the chunk redone entry
+                    // by entry from the saved sum.  Without a NaN the adds are the same sequence.
+                    double t = sum;
 #pragma unroll
-                    for (int r = 0; r < K4T_ROWS; ++r) accumulate(v[r], sum, cnt);
+                    for (int r = 0; r < K4T_ROWS; ++r) t = __dadd_rn(t, v[r]);
+                    if (t == t) {
+                        sum = t;
+                        cnt += K4T_ROWS;
+                    } else {
+#pragma unroll
+                        for (int r = 0; r < K4T_ROWS; ++r) accumulate(v[r], sum, cnt);
+                    }
                 }
                 last = v[K4T_ROWS - 1];
             } else {
-                for (uint32_t r = 0; r < rows; ++r) {
-                    const double v = sm.buf[s][r][lane];
-                    if (full) accumulate(v, sum, cnt);
-                    last = v;
-                }
+#pragma unroll
+                for (int r = 0; r < K4T_ROWS; ++r)
+                    if ((uint32_t)r < rows) {
+                        if (full) accumulate(v[r], sum, cnt);
+                        last = v[r];
+                    }
             }
-            __syncwarp();  // every lane holds its values in registers: the stage may be overwritten
+            __syncwarp();  // every lane has consumed chunk c from registers: its stage may be overwritten
             if (lane == 0 && c + K4T_STAGES < n) {
                 mbar_expect_tx(&sm.bar[s], K4T_STAGE_BYTES);
                 tma_load_2d(&sm.buf[s][0][0], &tmap, (int)col0, (int)row0_of(c + K4T_STAGES), &sm.bar[s], policy);
             }
+#pragma unroll
+            for (int r = 0; r < K4T_ROWS; ++r) v[r] = vn[r];
         }
     }
     if (!in_range) return;
@@ -629,6 +659,8 @@ apm_status apm_baseline_make_tmaps(apm_ctx* c) {
                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return apm_fail(c, APM_E_DEVICE, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
     }
+    CUDA_TRY(c, cudaFuncSetAttribute(baseline_tma_kernel<K4T_DEEP_STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sizeof(K4TSmem<K4T_DEEP_STAGES>) + 128));
     c->ring_tmap_ok = true;
     return APM_OK;
 }
@@ -655,12 +687,20 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
         baseline_inc_kernel<<<(ncol + K4_THREADS - 1) / K4_THREADS, K4_THREADS, 0, st>>>(p, is, &c->d_counters->inc_fallbacks);
     } else if (c->ring_tmap_ok && c->cfg.sd_mode == APM_SD_REFERENCE && !c->k4_force_ldg) {
         const unsigned g = (ncol + K4T_COLS - 1) / K4T_COLS;
-        switch (c->k4_stages) {
-            case 2: baseline_tma_kernel<2><<<g, 32, 0, st>>>(c->ring_tmap[l], p); break;
-            case 3: baseline_tma_kernel<3><<<g, 32, 0, st>>>(c->ring_tmap[l], p); break;
-            case 6: baseline_tma_kernel<6><<<g, 32, 0, st>>>(c->ring_tmap[l], p); break;
-            default: baseline_tma_kernel<4><<<g, 32, 0, st>>>(c->ring_tmap[l], p); break;
+        // With few column groups (a few hundred keys) one warp per SM cannot keep enough bytes in
+        // flight with 4 x 4 KB stages: the list walk is then bound by load latency, not by HBM.
+        // Below two CTAs per SM the deep instance (24 stages, 96 KB in flight per CTA) is used.
+        int stages = c->k4_stages;
+        if (stages == 0) stages = g <= 2 * APM_NUM_SMS ? K4T_DEEP_STAGES : 4;
+#define APM_K4T_LAUNCH(NS) baseline_tma_kernel<NS><<<g, 32, sizeof(K4TSmem<NS>) + 128, st>>>(c->ring_tmap[l], p)
+        switch (stages) {
+            case 2: APM_K4T_LAUNCH(2); break;
+            case 3: APM_K4T_LAUNCH(3); break;
+            case 6: APM_K4T_LAUNCH(6); break;
+            case K4T_DEEP_STAGES: APM_K4T_LAUNCH(K4T_DEEP_STAGES); break;
+            default: APM_K4T_LAUNCH(4); break;
         }
+#undef APM_K4T_LAUNCH
     } else {
         baseline_kernel<<<(ncol + K4_THREADS - 1) / K4_THREADS, K4_THREADS, 0, st>>>(p);
     }

@@ -38,6 +38,12 @@ WORKLOADS = {
                  influences=(0.0,), zscore=True, pct=True, seed=2,
                  desc="100M transactions, 10k service keys, 1-min buckets, p50/p95/p99 + z-score vs 7-day "
                       "rolling baseline (10080 buckets/key, pre-filled), exact-order baseline"),
+    # BASELINE.json configs[0]: the reference's own settings (10 s buckets, window 30, buffer 6, p75/p95, lags 360 + 8640)
+    "cfg1": dict(n=1_000_000, services=200, jvms=2, bucket_ms=10_000, window=30, buffer=6, span_buckets=2160,
+                 percentiles=(75.0, 95.0), z_series_pct=(0, 1), lags=(360, 8640), thresholds=(20.0, 15.0),
+                 influences=(0.1, 0.0), zscore=True, pct=True, seed=0xA9B200, prefill=False,
+                 desc="1M transactions, 200 services x 2 JVMs, reference settings (10-s buckets, 31-bucket sliding window, "
+                      "p75/p95, lags 360 and 8640), 2160 ticks per step"),
     # one rank's share of BASELINE.json configs[3] at 8 GPUs: 1 B transactions / 8, 1 M keys / 8
     "cfg4_shard": dict(n=125_000_000, services=125_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
                        percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
@@ -142,7 +148,7 @@ def cpu_reference_run(wl, cols, ring_seed, threads, stream, prefill=True):
         keep[t::threads] = 1
         p.set_filter(keep)
         p.keep_outputs(False)
-        if prefill and wl["zscore"]:
+        if prefill and wl["zscore"] and wl.get("prefill", True):
             L = wl["lags"][0]
             mine = np.arange(t, K, threads)
             for s in range(3):
@@ -167,6 +173,8 @@ def sample_for_cpu(wl, stream, ticks=2):
     """A bounded sample of the same workload: the first `ticks` buckets' worth of the stream
     (all 10 k keys, same rates), plus one transaction of the next bucket to close the last tick."""
     per_bucket = wl["n"] // wl["span_buckets"]
+    if wl["n"] <= 2_000_000:
+        return stream.generate_host(first=0, count=wl["n"]), wl["n"]  # small enough to run whole
     n = int(per_bucket * ticks + per_bucket // 50)
     return stream.generate_host(first=0, count=n), n
 
@@ -220,7 +228,8 @@ def main():
     ecfg = EngineConfig(num_services=wl["services"], num_jvms=wl["jvms"], bucket_ms=wl["bucket_ms"], window=wl["window"],
                         buffer=wl["buffer"], percentiles=wl["percentiles"], z_series_pct=wl["z_series_pct"],
                         lags=wl["lags"], thresholds=wl["thresholds"], influences=wl["influences"], flags=flags,
-                        max_tx_per_bucket=int(per_bucket * 1.5) + 4096, max_batch=min(wl["n"], 1 << 24),
+                        max_tx_per_bucket=int(per_bucket * 1.5) + 4096 if per_bucket > 4096 else 1 << 16,
+                        max_batch=min(wl["n"], 1 << 24),
                         out_ticks=wl["span_buckets"] + 12, max_alerts_per_tick=max(K * max(len(wl["lags"]), 1), 1024),
                         device=local_rank)
     eng = Engine(ecfg)
@@ -238,7 +247,7 @@ def main():
                           span_ms=span_ms, shift_mod=97)
     stream = syn.SynthStream(spec, device=True)
     ring_seed = 77 + rank
-    if wl["zscore"]:
+    if wl["zscore"] and wl.get("prefill", True):
         L = wl["lags"][0]
         buf = syn.DeviceBuffer(L * 3 * K * 8)
         syn.ring_fill_device(buf, L, stream, ring_seed)
