@@ -147,6 +147,7 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
         const int slot = (int)(lab % c->S);
         mask |= 1ull << slot;
         c->slot_label[slot] = lab;
+        c->host_count[slot] = c->host_sorted[slot] = 0;
     }
     apm_status st = apm_launch_clear_slots(c, mask);
     if (st) return st;
@@ -166,24 +167,18 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
         w.slot[w.n++] = slot;
     }
     if (with_pct(c)) {
-        // sort the window's value logs that grew since their last sort
-        std::vector<SlotMeta> meta(c->S);
-        CUDA_TRY(c, cudaMemcpyAsync(meta.data(), c->slot_meta, sizeof(SlotMeta) * c->S, cudaMemcpyDeviceToHost, c->s_main));
-        CUDA_TRY(c, cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->s_main));
-        CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-        c->counters.d2h_bytes += sizeof(SlotMeta) * c->S + sizeof(DevCounters);
-        const uint32_t max_value = c->h_counters->max_value;
+        // sort the window's value logs that grew since their last sort; their lengths come from the chunk's
+        // segment table (apm_launch_seg_hist), not from the device, so nothing here waits for the GPU
         for (int i = 0; i < w.n; ++i) {
             const int slot = w.slot[i];
-            SlotMeta& m = meta[slot];
-            if (m.count > c->log_cap) return apm_fail(c, APM_E_CAPACITY, "a bucket's value log overflowed max_tx_per_bucket");
-            if (m.count != m.sorted) {
-                st = apm_sort_slot_n(c, slot, m.count, max_value);
+            const uint64_t count = c->host_count[slot];
+            if (count > c->log_cap) return apm_fail(c, APM_E_CAPACITY, "a bucket's value log overflowed max_tx_per_bucket");
+            if (count != c->host_sorted[slot]) {
+                st = apm_sort_slot_n(c, slot, count, c->known_max_value);
                 if (st) return st;
-                st = apm_acc_from_sorted(c, slot, m.count);  // count / sum / sum of squares / min / max from the runs
+                st = apm_acc_from_sorted(c, slot, count);  // count / sum / sum of squares / min / max from the runs
                 if (st) return st;
-                m.sorted = m.count;
-                CUDA_TRY(c, cudaMemcpyAsync(&c->slot_meta[slot].sorted, &m.sorted, sizeof(m.sorted), cudaMemcpyHostToDevice, c->s_main));
+                c->host_sorted[slot] = count;
             }
         }
     }
@@ -212,6 +207,14 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
     return APM_OK;
 }
 
+// What segment i of the current chunk appends to the value logs, by bucket age under the latestBucket in
+// force (c->latest): keeps host_count equal to the device's SlotMeta.count.
+void apply_seg_counts(apm_ctx* c, unsigned int i) {
+    const uint32_t* row = c->h_seg_counts + (size_t)i * (c->keep + 1);
+    for (int age = 0; age <= c->keep; ++age)
+        if (row[age]) c->host_count[(c->latest - age) % c->S] += row[age];
+}
+
 apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n, apm_tick_result* res) {
     unsigned int nt = 0;
     apm_status st = apm_launch_find_ticks(c, d.end_ts_ms, n, &nt);
@@ -220,9 +223,17 @@ apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n,
     if (keep_any && c->ticks_buffered + nt > c->cfg.out_ticks)
         return apm_fail(c, APM_E_WOULDBLOCK, "chunk holds more ticks than the output ring has room for: fetch results or raise out_ticks");
     std::sort(c->h_ticks, c->h_ticks + nt, [](const TickMark& a, const TickMark& b) { return a.pos < b.pos; });
+    const bool logs = with_pct(c);
+    if (logs) {
+        st = apm_launch_seg_hist(c, d, n, nt);
+        if (st) return st;
+        if (c->seg_max > c->known_max_value) c->known_max_value = c->seg_max;
+    }
+    auto account = [&](unsigned int i) { if (logs) apply_seg_counts(c, i); };
     uint64_t pos = 0;
     for (unsigned int i = 0; i < nt; ++i) {
         const TickMark tm = c->h_ticks[i];
+        account(i);
         st = apm_launch_reduce(c, d, pos, tm.pos);  // everything that arrived before the trigger
         if (st) return st;
         st = apm_pt_append(c, d, pos, tm.pos);
@@ -232,6 +243,7 @@ apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n,
         if (st) return st;
         pos = tm.pos;
     }
+    account(nt);
     st = apm_launch_reduce(c, d, pos, n);
     if (st) return st;
     st = apm_pt_append(c, d, pos, n);
@@ -315,6 +327,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFree(c->d_log_ptrs); cudaFree(c->sort_hist); cudaFree(c->sort_base); cudaFree(c->sort_scratch);
     cudaFree(c->tf_tile_max); cudaFree(c->tf_tile_prefix); cudaFree(c->d_ticks); cudaFree(c->d_nticks);
     cudaFreeHost(c->h_ticks); cudaFreeHost(c->h_nticks);
+    cudaFree(c->d_seg_counts); cudaFreeHost(c->h_seg_counts);
     cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
     free_columns_device(&c->dev[0]); free_columns_device(&c->dev[1]);
     cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
@@ -439,6 +452,12 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     TRY_CREATE(dalloc(&c->d_nticks, (size_t)1));
     TRY_CREATE(cudaMallocHost((void**)&c->h_ticks, sizeof(TickMark) * c->max_ticks_per_chunk));
     TRY_CREATE(cudaMallocHost((void**)&c->h_nticks, sizeof(unsigned int)));
+    {
+        const size_t cells = (size_t)(c->max_ticks_per_chunk + 1) * (c->keep + 1) + 1;
+        TRY_CREATE(dalloc(&c->d_seg_counts, cells));
+        TRY_CREATE(cudaMallocHost((void**)&c->h_seg_counts, sizeof(uint32_t) * cells));
+        for (int s = 0; s < APM_MAX_SLOTS; ++s) c->host_count[s] = c->host_sorted[s] = 0;
+    }
     for (int i = 0; i < 2; ++i) {
         TRY_CREATE(dalloc(&c->zin[i], 4 * K));
         TRY_CREATE(dalloc(&c->emit[i], K));
@@ -530,7 +549,14 @@ apm_status apm_ingest_commit(apm_ctx* c, uint64_t n) {
     CUDA_TRY(c, cudaEventRecord(c->ev_copied[0], c->s_copy));
     CUDA_TRY(c, cudaStreamWaitEvent(c->s_main, c->ev_copied[0], 0));
     c->counters.h2d_bytes += n * 20;
-    apm_status st = apm_launch_reduce(c, d, 0, n);
+    apm_status st;
+    if (with_pct(c)) {  // one segment under the current latestBucket
+        st = apm_launch_seg_hist(c, d, n, 0);
+        if (st) return st;
+        if (c->seg_max > c->known_max_value) c->known_max_value = c->seg_max;
+        apply_seg_counts(c, 0);
+    }
+    st = apm_launch_reduce(c, d, 0, n);
     if (st) return st;
     st = apm_pt_append(c, d, 0, n);
     if (st) return st;
@@ -839,6 +865,7 @@ apm_status apm_set_latest(apm_ctx* c, int64_t latest) {
         const int slot = (int)(lab % c->S);
         c->slot_label[slot] = lab;
         mask |= 1ull << slot;
+        c->host_count[slot] = c->host_sorted[slot] = 0;
     }
     st = apm_launch_clear_slots(c, mask);
     if (st) return st;

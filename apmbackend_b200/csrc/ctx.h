@@ -66,6 +66,14 @@ struct apm_ctx {
     TickMark* h_ticks = nullptr;       // pinned
     unsigned int* h_nticks = nullptr;  // pinned
     uint32_t max_ticks_per_chunk = 4096;
+    // per-chunk table of log entries per (segment, bucket age) and what the host derives from it: the
+    // exact length of every bucket's value log, so the tick loop never waits for the device
+    uint32_t* d_seg_counts = nullptr;  // [(max_ticks_per_chunk + 1)][keep + 1] + 1 (largest duration of the chunk)
+    uint32_t* h_seg_counts = nullptr;  // pinned
+    uint32_t seg_max = 0;
+    uint64_t host_count[APM_MAX_SLOTS];   // log entries per slot (== SlotMeta.count)
+    uint64_t host_sorted[APM_MAX_SLOTS];  // entries that were in place at the slot's last sort
+    uint32_t known_max_value = 0;         // largest duration appended to any log so far
 
     // --- staging of host batches: pinned SoA ring (acquire/commit) + two device buffers
     apm_tx_columns pin = {nullptr, nullptr, nullptr, nullptr};
@@ -169,6 +177,7 @@ apm_status apm_launch_find_ticks(apm_ctx* c, const int64_t* d_ts, uint64_t n, un
 apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin, uint64_t end);
 // k3_sort.cu
 apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value);
+apm_status apm_launch_seg_hist(apm_ctx* c, const apm_tx_columns& d, uint64_t n, unsigned int nt);
 uint64_t* apm_radix_sort_words(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t n, uint32_t* hist, uint32_t* totals,
                                int vbits, int kbits, uint64_t* launches);
 uint64_t apm_radix_sort_tiles(uint64_t n);

@@ -4,6 +4,7 @@
 // (stream_calc_stats.js:331-371): generateBucketLabel (:89-91), the
 // `bucketLabel > latestBucket` test (:348) and addData (:115-134).
 #include <cstddef>
+#include <cstring>
 
 #include "ctx.h"
 
@@ -135,6 +136,123 @@ __global__ void __launch_bounds__(TF_THREADS) tf_emit_kernel(const int64_t* __re
             }
         }
     }
+}
+
+// ---- K0d: how many log entries each segment adds to each bucket ---------------------------------
+// With the tick positions known, a transaction's segment - and with it the latestBucket in force
+// when consumeMsg would have handled it - is known too, so the outcome of addData's tests is a
+// pure function of the transaction: this kernel applies exactly the tests of the ingest kernel
+// below and counts, per segment s and bucket age d = latest - label, the transactions that will be
+// appended to a value log, plus the largest duration among them.  The host reads the table once
+// per chunk and from then on knows every bucket's log length (grid sizes, number of radix passes,
+// which buckets need a sort) without asking the device at each tick.
+struct SegHistParams {
+    const uint32_t* svc;
+    const uint32_t* jvm;
+    const int64_t* ts;
+    const int32_t* el;
+    uint64_t n;
+    int64_t bucket_ms;
+    double inv_bucket;
+    int64_t latest0;           // latestBucket before the chunk
+    int keep;
+    uint32_t num_services, num_jvms;
+    const TickMark* ticks;     // sorted by position
+    uint32_t nt;
+    uint32_t* counts;          // [(nt + 1)][keep + 1]
+    uint32_t* max_value;
+};
+
+constexpr int SH_THREADS = 256;
+constexpr int SH_ITEMS = 16;
+constexpr int SH_TILE = SH_THREADS * SH_ITEMS;
+constexpr int SH_SPAN = 32;  // segments of one tile counted in shared memory
+constexpr uint32_t SH_NONE = 0xFFFFFFFFu;
+
+// number of tick marks with pos <= i among ticks[lo, hi)
+__device__ __forceinline__ uint32_t sh_ticks_le(const TickMark* ticks, uint32_t lo, uint32_t hi, uint64_t i) {
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (ticks[mid].pos <= i) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(SH_THREADS) seg_hist_kernel(const SegHistParams p) {
+    __shared__ uint32_t s_cnt[SH_SPAN * APM_MAX_SLOTS];
+    __shared__ unsigned long long s_pos[SH_SPAN];
+    __shared__ long long s_lab[SH_SPAN];
+    __shared__ uint32_t s_seg_lo, s_nseg, s_max;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint64_t tile_begin = (uint64_t)blockIdx.x * SH_TILE;
+    const uint64_t tile_end = tile_begin + SH_TILE < p.n ? tile_begin + SH_TILE : p.n;
+    if (tid == 0) {
+        const uint32_t lo = sh_ticks_le(p.ticks, 0, p.nt, tile_begin);
+        const uint32_t hi = sh_ticks_le(p.ticks, lo, p.nt, tile_end - 1);
+        s_seg_lo = lo;          // segment of the tile's first transaction
+        s_nseg = hi - lo + 1;   // segments the tile touches
+        s_max = 0;
+    }
+    __syncthreads();
+    const uint32_t seg_lo = s_seg_lo, nseg = s_nseg;
+    const bool local = nseg <= (uint32_t)SH_SPAN;
+    const int width = p.keep + 1;
+    if (local) {
+        for (uint32_t j = tid; j < nseg; j += SH_THREADS) {
+            const uint32_t seg = seg_lo + j;
+            s_lab[j] = seg == 0 ? p.latest0 : p.ticks[seg - 1].label;
+            s_pos[j] = j + 1 < nseg ? p.ticks[seg].pos : ~0ull;  // where the next segment starts
+        }
+        for (uint32_t j = tid; j < nseg * APM_MAX_SLOTS; j += SH_THREADS) s_cnt[j] = 0;
+    }
+    __syncthreads();
+    uint32_t my_max = 0;
+#pragma unroll 4
+    for (int it = 0; it < SH_ITEMS; ++it) {
+        const uint64_t i = tile_begin + (uint64_t)it * SH_THREADS + tid;
+        uint32_t slot = SH_NONE;  // (segment, age) of the log entry this transaction becomes
+        if (i < tile_end) {
+            const uint32_t sv = __ldg(p.svc + i), jv = __ldg(p.jvm + i);
+            const int32_t e = __ldg(p.el + i);
+            const int64_t t = __ldg(p.ts + i);
+            if (sv < p.num_services && jv < p.num_jvms && e >= 0 && t >= 0) {
+                uint32_t sl = 0;
+                long long latest;
+                if (local) {
+                    while (s_pos[sl] <= i) ++sl;
+                    latest = s_lab[sl];
+                } else {
+                    sl = sh_ticks_le(p.ticks, seg_lo, seg_lo + nseg - 1, i) - seg_lo;
+                    latest = seg_lo + sl == 0 ? p.latest0 : p.ticks[seg_lo + sl - 1].label;
+                }
+                const long long lab = apm_label(t, p.bucket_ms, p.inv_bucket);
+                if (lab <= latest && lab >= latest - p.keep) {
+                    slot = sl * APM_MAX_SLOTS + (uint32_t)(latest - lab);
+                    my_max = (uint32_t)e > my_max ? (uint32_t)e : my_max;
+                }
+            }
+        }
+        // in-order streams put a whole warp on one counter: add once per warp then
+        const uint32_t first = __shfl_sync(0xffffffffu, slot, 0);
+        if (__all_sync(0xffffffffu, slot == first)) {
+            if (lane == 0 && first != SH_NONE) {
+                if (local) atomicAdd(&s_cnt[first], 32u);
+                else atomicAdd(&p.counts[(size_t)(seg_lo + first / APM_MAX_SLOTS) * width + first % APM_MAX_SLOTS], 32u);
+            }
+        } else if (slot != SH_NONE) {
+            if (local) atomicAdd(&s_cnt[slot], 1u);
+            else atomicAdd(&p.counts[(size_t)(seg_lo + slot / APM_MAX_SLOTS) * width + slot % APM_MAX_SLOTS], 1u);
+        }
+    }
+    my_max = __reduce_max_sync(0xffffffffu, my_max);
+    if (lane == 0 && my_max) atomicMax(&s_max, my_max);
+    __syncthreads();
+    if (local)
+        for (uint32_t j = tid; j < nseg * APM_MAX_SLOTS; j += SH_THREADS) {
+            const uint32_t v = s_cnt[j], d = j % APM_MAX_SLOTS;
+            if (v) atomicAdd(&p.counts[(size_t)(seg_lo + j / APM_MAX_SLOTS) * width + d], v);
+        }
+    if (tid == 0 && s_max) atomicMax(p.max_value, s_max);
 }
 
 // ---- K1: keyed segmented reduction ------------------------------------------------------------
@@ -435,6 +553,33 @@ apm_status apm_launch_find_ticks(apm_ctx* c, const int64_t* d_ts, uint64_t n, un
     }
     c->counters.d2h_bytes += sizeof(unsigned int);
     *n_ticks_out = nt;
+    return APM_OK;
+}
+
+// Uploads the chunk's tick marks (sorted by position, in c->h_ticks), counts the log entries of every
+// (segment, bucket age) pair and brings the table back: c->h_seg_counts[(nt + 1)][keep + 1], c->seg_max.
+apm_status apm_launch_seg_hist(apm_ctx* c, const apm_tx_columns& d, uint64_t n, unsigned int nt) {
+    ProfScope prof_scope_(c, APM_PG_TICKFIND);
+    const size_t cells = (size_t)(nt + 1) * (c->keep + 1);
+    memset(c->h_seg_counts, 0, cells * sizeof(uint32_t));
+    c->seg_max = 0;
+    if (n == 0) return APM_OK;
+    if (nt) CUDA_TRY(c, cudaMemcpyAsync(c->d_ticks, c->h_ticks, nt * sizeof(TickMark), cudaMemcpyHostToDevice, c->s_main));
+    CUDA_TRY(c, cudaMemsetAsync(c->d_seg_counts, 0, (cells + 1) * sizeof(uint32_t), c->s_main));
+    SegHistParams p;
+    p.svc = d.service_id; p.jvm = d.jvm_id; p.ts = d.end_ts_ms; p.el = d.elapsed_ms; p.n = n;
+    p.bucket_ms = c->cfg.bucket_ms; p.inv_bucket = c->inv_bucket; p.latest0 = c->latest; p.keep = c->keep;
+    p.num_services = c->cfg.num_services; p.num_jvms = c->cfg.num_jvms;
+    p.ticks = c->d_ticks; p.nt = nt;
+    p.counts = c->d_seg_counts; p.max_value = c->d_seg_counts + cells;  // the chunk maximum rides behind the table
+    seg_hist_kernel<<<(unsigned)((n + SH_TILE - 1) / SH_TILE), SH_THREADS, 0, c->s_main>>>(p);
+    c->launches += 1;
+    CUDA_TRY(c, cudaGetLastError());
+    CUDA_TRY(c, cudaMemcpyAsync(c->h_seg_counts, c->d_seg_counts, (cells + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->s_main));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    c->seg_max = c->h_seg_counts[cells];
+    c->counters.d2h_bytes += (cells + 1) * sizeof(uint32_t);
+    c->counters.h2d_bytes += nt * sizeof(TickMark);
     return APM_OK;
 }
 

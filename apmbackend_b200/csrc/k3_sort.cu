@@ -275,7 +275,9 @@ __global__ void __launch_bounds__(AS_THREADS) acc_from_sorted_kernel(const uint6
     as_emit(acc, base, cur, run);
 }
 
-__global__ void __launch_bounds__(256) clear_planes_kernel(const AccSoA acc, uint32_t K, int slot) {
+__global__ void __launch_bounds__(256) clear_planes_kernel(const AccSoA acc, uint32_t K, int slot, SlotMeta* __restrict__ meta,
+                                                           uint64_t n_sorted) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) meta[slot].sorted = n_sorted;  // the device copy of the host's bookkeeping (checkpoints)
     const size_t base = (size_t)slot * K;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)K; i += (size_t)gridDim.x * blockDim.x) {
         acc.sum[base + i] = 0; acc.sq_lo[base + i] = 0; acc.sq_hi[base + i] = 0;
@@ -384,7 +386,7 @@ apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value)
 apm_status apm_acc_from_sorted(apm_ctx* c, int slot, uint64_t n) {
     ProfScope prof_scope_(c, APM_PG_REDUCE);
     unsigned g = (c->K + 255) / 256;
-    clear_planes_kernel<<<g < 592 ? g : 592, 256, 0, c->s_main>>>(c->acc, c->K, slot);
+    clear_planes_kernel<<<g < 592 ? g : 592, 256, 0, c->s_main>>>(c->acc, c->K, slot, c->slot_meta, n);
     c->launches += 1;
     if (n) {
         const uint64_t per_block = (uint64_t)AS_THREADS * AS_ITEMS;

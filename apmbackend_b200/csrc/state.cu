@@ -26,6 +26,7 @@ struct StateHeader {
     int64_t slot_label[APM_MAX_SLOTS];
     uint64_t log_count[APM_MAX_SLOTS];
     uint32_t has_logs, has_rings;
+    uint32_t max_value, pad_;  // largest duration in any value log (bounds the radix passes after a resume)
 };
 
 struct File {
@@ -63,12 +64,13 @@ apm_status apm_state_save(apm_ctx* c, const char* path) {
     StateHeader h;
     memset(&h, 0, sizeof h);
     memcpy(h.magic, "APMB200", 8);
-    h.version = 4; h.K = c->K; h.S = c->S; h.num_lags = c->log_cap ? c->cfg.num_lags : c->cfg.num_lags;
+    h.version = 5; h.K = c->K; h.S = c->S; h.num_lags = c->log_cap ? c->cfg.num_lags : c->cfg.num_lags;
     h.bucket_ms = c->cfg.bucket_ms; h.window = c->cfg.window_buckets; h.buffer = c->cfg.buffer_buckets;
     h.latest = c->latest;
     const bool rings = (c->cfg.flags & APM_F_ZSCORE) && c->cfg.num_lags > 0;
     h.has_logs = c->log_cap ? 1 : 0;
     h.has_rings = rings ? 1 : 0;
+    h.max_value = c->known_max_value;
     for (int l = 0; l < c->cfg.num_lags; ++l) { h.lags[l] = c->cfg.lags[l]; h.ring_head[l] = c->ring_head[l]; }
     std::vector<SlotMeta> meta(c->S);
     CUDA_TRY(c, cudaMemcpy(meta.data(), c->slot_meta, sizeof(SlotMeta) * c->S, cudaMemcpyDeviceToHost));
@@ -103,7 +105,7 @@ apm_status apm_state_load(apm_ctx* c, const char* path) {
     fl.f = fopen(path, "rb");
     if (!fl.f) return apm_fail(c, APM_E_IO, std::string("cannot open for reading: ") + path);
     StateHeader h;
-    if (fread(&h, sizeof h, 1, fl.f) != 1 || memcmp(h.magic, "APMB200", 8) != 0 || h.version != 4)
+    if (fread(&h, sizeof h, 1, fl.f) != 1 || memcmp(h.magic, "APMB200", 8) != 0 || h.version != 5)
         return apm_fail(c, APM_E_IO, "not an apm_b200 state file");
     const bool rings = (c->cfg.flags & APM_F_ZSCORE) && c->cfg.num_lags > 0;
     bool same = h.K == c->K && h.S == c->S && h.bucket_ms == c->cfg.bucket_ms && h.window == c->cfg.window_buckets &&
@@ -131,6 +133,12 @@ apm_status apm_state_load(apm_ctx* c, const char* path) {
     if (!ok) return apm_fail(c, APM_E_IO, std::string("short read: ") + path);
     c->latest = h.latest;
     for (int s = 0; s < c->S; ++s) c->slot_label[s] = h.slot_label[s];
+    {   // the host's view of the value logs
+        std::vector<SlotMeta> meta(c->S);
+        CUDA_TRY(c, cudaMemcpy(meta.data(), c->slot_meta, sizeof(SlotMeta) * c->S, cudaMemcpyDeviceToHost));
+        for (int s = 0; s < c->S; ++s) { c->host_count[s] = meta[s].count; c->host_sorted[s] = meta[s].sorted; }
+        c->known_max_value = h.max_value;
+    }
     for (int l = 0; l < c->cfg.num_lags; ++l) c->ring_head[l] = h.ring_head[l];
     c->ticks_buffered = 0;
     for (int l = 0; l < APM_MAX_LAGS; ++l) c->inc_dirty[l] = true;

@@ -70,6 +70,9 @@ def parse_args():
                          "incremental: guarded running sums (APM_F_INCREMENTAL: signals and lists bit-identical, means to 1e-9)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-profile", action="store_true",
+                    help="no per-kernel CUDA-event spans inside the timed region (they cost host time when ticks are "
+                         "tiny, e.g. cfg1); the roofline then comes from the isolated pass only")
     return ap.parse_args()
 
 
@@ -280,7 +283,7 @@ def main():
     for s in range(args.warmup):
         run_step_device(s)
     eng.profile_read()
-    eng.profile_enable(True)
+    eng.profile_enable(not args.no_profile)
     c0 = eng.counters()
     launches0 = c0.kernel_launches
     clocks = ClockSampler(local_rank)
@@ -385,6 +388,8 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+    if args.no_profile and prof_iso:
+        prof = prof_iso  # nothing was recorded in the timed region: fall back to the isolated pass
     dom = max(prof, key=lambda g: prof[g]["ms"])
     if dom == "rolling_baseline":
         L = wl["lags"][0]
