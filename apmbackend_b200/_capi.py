@@ -25,7 +25,15 @@ FS_DTYPE = np.dtype([
     ("val", "<f8", (3,)), ("avg", "<f8", (3,)), ("lb", "<f8", (3,)), ("ub", "<f8", (3,)),
     ("signal", "i1", (3,)), ("flags", "u1"), ("pad", "u1", (4,)),
 ])
-assert STAT_DTYPE.itemsize == 96 and FS_DTYPE.itemsize == 128
+LOG_DTYPE = np.dtype([
+    ("line_offset", "<u8"), ("line_length", "<u4"), ("kind", "u1"), ("flags", "u1"), ("service_length", "<u2"),
+    ("service_offset", "<u4"), ("service_id", "<u4"), ("elapsed_ms", "<i4"), ("logid_length", "<u4"),
+    ("ts_ms", "<i8"), ("start_ms", "<i8"), ("logid_hash", "<u8"), ("name_hash", "<u8"),
+])
+assert STAT_DTYPE.itemsize == 96 and FS_DTYPE.itemsize == 128 and LOG_DTYPE.itemsize == 64
+LK_CT_START, LK_CT_STOP, LK_EJB_ENTRY, LK_EJB_EXIT = 1, 2, 3, 4
+LR_LOGID_EMPTY, LR_BAD_TIME, LR_BAD_ELAPSED, LR_PAIRED, LR_OPEN_START, LR_BAF_INFO, LR_TOP_LEVEL, LR_FED = 1, 2, 4, 8, 16, 32, 64, 128
+NO_SERVICE = 0xFFFFFFFF
 
 
 class ApmConfig(C.Structure):
@@ -88,6 +96,11 @@ _lib = None
 _synth = None
 
 # every symbol include/apm_b200.h declares (tests check the library exports them all)
+class ParseResult(C.Structure):
+    _fields_ = [("lines", C.c_uint64), ("records", C.c_uint64), ("exits", C.c_uint64), ("fed", C.c_uint64),
+                ("unknown_service", C.c_uint64), ("malformed", C.c_uint64)]
+
+
 SYMBOLS = {
     "apm_abi_version": (C.c_uint32, []),
     "apm_ctx_create": (C.c_int32, [C.POINTER(ApmConfig), C.POINTER(C.c_void_p)]),
@@ -139,6 +152,11 @@ SYMBOLS = {
     "apm_comm_unique_id": (C.c_int32, [C.c_void_p]),
     "apm_comm_init": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "apm_gather_alerts": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "apm_name_hash": (C.c_uint64, [C.c_char_p, C.c_uint64]),
+    "apm_dict_set": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
+    "apm_parse_log_host": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
+                                       C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(ParseResult)]),
+    "apm_feed_parsed": (C.c_int32, [C.c_void_p, C.POINTER(TickResult)]),
 }
 
 

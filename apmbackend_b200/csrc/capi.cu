@@ -328,6 +328,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFree(c->tf_tile_max); cudaFree(c->tf_tile_prefix); cudaFree(c->d_ticks); cudaFree(c->d_nticks);
     cudaFreeHost(c->h_ticks); cudaFreeHost(c->h_nticks);
     cudaFree(c->d_seg_counts); cudaFreeHost(c->h_seg_counts);
+    apm_lp_destroy(c);
     cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
     free_columns_device(&c->dev[0]); free_columns_device(&c->dev[1]);
     cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);

@@ -137,6 +137,8 @@ struct apm_ctx {
     int k4_stages = 0;              // APM_K4_STAGES: bulk-tensor loads in flight per CTA (2, 3, 4, 6 or 24); 0 = by grid size
     bool k4_force_ldg = false;      // APM_K4_LDG=1: register-pipelined loads instead of TMA (A/B measurements)
 
+    // log feeder (k6_logparse.cu), created by the first apm_dict_set / apm_parse_log_host
+    void* lp = nullptr;
     // multi-GPU
     void* nccl_comm = nullptr;
     int rank = 0, nranks = 1;
@@ -198,6 +200,8 @@ apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t aler
 // k5_passthrough.cu
 apm_status apm_pt_append(apm_ctx* c, const apm_tx_columns& d, uint64_t begin, uint64_t end);
 apm_status apm_pt_tick(apm_ctx* c, int64_t edge_ts, uint32_t tick_slot);
+// k6_logparse.cu
+void apm_lp_destroy(apm_ctx* c);
 // comm.cu
 void apm_comm_destroy_internal(apm_ctx* c);
 // capi.cu

@@ -120,6 +120,36 @@ class Engine:
         self._check(self._lib.apm_process_device(self._h, C.byref(cols), n, C.byref(res)))
         return res
 
+    # ---- log feeder
+    @staticmethod
+    def name_hash(name) -> int:
+        b = name.encode() if isinstance(name, str) else bytes(name)
+        return int(_capi.lib().apm_name_hash(b, len(b)))
+
+    def dict_set(self, names_to_ids: dict):
+        """Service dictionary of the device parser: rewritten service name -> service id."""
+        h = np.array([self.name_hash(k) for k in names_to_ids], np.uint64)
+        v = np.array(list(names_to_ids.values()), np.uint32)
+        self._check(self._lib.apm_dict_set(self._h, h.ctypes.data, v.ctypes.data, h.size))
+
+    def parse_log(self, text: bytes, file_type: int, jvm_id: int, tz_rules=((-(1 << 62), 0),), want_records=True):
+        """apm_parse_log_host: (records in line order, ParseResult); the fed exits stay on the device."""
+        tz = np.array(tz_rules, np.int64).reshape(-1, 2)
+        buf = np.frombuffer(text, np.uint8)
+        res = _capi.ParseResult()
+        n = C.c_uint64(0)
+        cap = max(1, text.count(b"\n") + 1) if want_records else 0
+        out = np.zeros(cap, _capi.LOG_DTYPE) if want_records else None
+        self._check(self._lib.apm_parse_log_host(self._h, buf.ctypes.data if buf.size else None, buf.size, file_type, jvm_id,
+                                                 tz.ctypes.data, tz.shape[0], out.ctypes.data if want_records else None, cap,
+                                                 C.byref(n), C.byref(res)))
+        return (out[:n.value] if want_records else None), res
+
+    def feed_parsed(self) -> TickResult:
+        res = TickResult()
+        self._check(self._lib.apm_feed_parsed(self._h, C.byref(res)))
+        return res
+
     def add_batch(self, service_id, jvm_id, end_ts_ms, elapsed_ms):
         """addData (:115-134) for a batch that contains no tick (the caller ticks first, as consumeMsg does)."""
         s, j, t, e = _cols(service_id, jvm_id, end_ts_ms, elapsed_ms)

@@ -50,7 +50,7 @@ def parse_int(v) -> float:
         return NaN if math.isnan(v) or math.isinf(v) else int(v)
     s = str(v).strip()
     i, sign = 0, 1
-    if s[:1] in "+-":
+    if s[:1] and s[:1] in "+-":
         sign = -1 if s[0] == "-" else 1
         s = s[1:]
     while i < len(s) and s[i].isdigit():

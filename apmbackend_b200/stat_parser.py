@@ -79,13 +79,17 @@ class StatParser:
             raise ValueError("numKeepIntervals differs from the engine's window + buffer")
 
     # ---- :115-134
-    def _ids(self, server, service):
+    def _server(self, server):
         srv = self.servers.get(server)
         if srv is None:
             if len(self._jvm_names) >= self.engine.cfg.num_jvms:
                 raise OverflowError("more servers than EngineConfig.num_jvms")
             srv = self.servers[server] = {"id": len(self._jvm_names), "services": {}}
             self._jvm_names.append(server)
+        return srv
+
+    def _ids(self, server, service):
+        srv = self._server(server)
         sid = self._svc_ids.get(service)
         if sid is None:
             if len(self._svc_names) >= self.engine.cfg.num_services:

@@ -343,6 +343,88 @@ apm_status apm_comm_init(apm_ctx* ctx, int32_t rank, int32_t nranks, const void*
  * tick, lag, key): first the counts, then the records padded to the largest count. */
 apm_status apm_gather_alerts(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
 
+/* ------------------------------------------------------------------------------------------------
+ * Log feeder: CommonTiming lines of a WildFly log parsed on the device.
+ *
+ * Replaces, for a buffer of raw log text of ONE file (one server), what stream_parse_transactions.js
+ * does line by line: readLine's dispatch on the four CommonTiming patterns (:733-777),
+ * parseEjbCommonTimingEntry / Exit (:378-446), parseCommonTimingEntry / Exit (:451-565: token
+ * positions, the INFO-based split), convertStringDateToMs (:242-256, the standard-log form) and
+ * outputRecord's `Provider[x]` -> `Provider:x` rewrite, start = end - elapsed fallback and `^S:`
+ * top-level test (:264-293).  Start and Stop lines of the same (logId, service) are paired inside the
+ * buffer (the reference's recordCache, :393-400 / :471-480, without its 120-s wall-clock TTL).
+ *
+ * Stays with the host (it reads the records below): SOAP logs and parseAppLine (account numbers),
+ * the need-number cache and its TTL, Start lines whose Stop is in a later buffer (flag
+ * APM_LR_OPEN_START), service names not in the dictionary yet (service_id == APM_NO_SERVICE).
+ * Only ASCII white space separates tokens (JavaScript's \s also matches Unicode spaces).
+ * ---------------------------------------------------------------------------------------------- */
+#define APM_NO_SERVICE 0xFFFFFFFFu
+
+enum {
+    APM_LK_CT_START = 1,   /* INFO *CommonTiming::Start           -> parseCommonTimingEntry     */
+    APM_LK_CT_STOP = 2,    /* INFO *CommonTiming::Stop            -> parseCommonTimingExit      */
+    APM_LK_EJB_ENTRY = 3,  /* INFO *[CommonTiming] The EJB        -> parseEjbCommonTimingEntry  */
+    APM_LK_EJB_EXIT = 4    /* INFO *[CommonTiming] Total time     -> parseEjbCommonTimingExit   */
+};
+enum {
+    APM_LR_LOGID_EMPTY = 1,   /* `[]`: entries are discarded, exits become incomplete records (:386, :411, :526) */
+    APM_LR_BAD_TIME = 2,      /* the date / time tokens are not seven decimal fields: ts_ms is unset           */
+    APM_LR_BAD_ELAPSED = 4,   /* parseInt(elapsed) is NaN                                                      */
+    APM_LR_PAIRED = 8,        /* exit: its Start was found in this buffer, start_ms is that line's time        */
+    APM_LR_OPEN_START = 16,   /* entry: no Stop consumed it inside this buffer                                 */
+    APM_LR_BAF_INFO = 32,     /* the line matches /\[[^ ]+] +INFO / (attemptReadAccountNumberFromBAFInfo)      */
+    APM_LR_TOP_LEVEL = 64,    /* the rewritten service starts with "S:"                                        */
+    APM_LR_FED = 128          /* exit: well formed and known, part of the columns apm_feed_parsed ingests      */
+};
+
+typedef struct apm_log_record {
+    uint64_t line_offset;     /* of the line in the text buffer */
+    uint32_t line_length;     /* without the newline */
+    uint8_t kind;             /* APM_LK_* */
+    uint8_t flags;            /* APM_LR_* */
+    uint16_t service_length;  /* of the raw service token (without the "S:" the EJB forms prepend) */
+    uint32_t service_offset;  /* of the raw service token inside the line */
+    uint32_t service_id;      /* dictionary id of the rewritten name, or APM_NO_SERVICE */
+    int32_t elapsed_ms;       /* exits: parseInt(elapsed) */
+    uint32_t logid_length;    /* of arr[0], brackets included */
+    int64_t ts_ms;            /* entries: startTs, exits: endTs (epoch ms) */
+    int64_t start_ms;         /* exits: paired Start's time, else end - elapsed (:279-281) */
+    uint64_t logid_hash;      /* apm_name_hash of the logId with its brackets removed */
+    uint64_t name_hash;       /* apm_name_hash of the rewritten service name (what the dictionary is keyed by) */
+} apm_log_record;             /* 64 bytes */
+
+/* offset_ms (local - UTC) applies to local wall-clock times >= local_from_ms (local time counted as if it
+ * were UTC); rules ascending, the first one covers everything before the second.  What `new Date(y, m, d,
+ * H, M, S, ms)` resolves through the host's zone database is passed in by the host. */
+typedef struct apm_tz_rule {
+    int64_t local_from_ms;
+    int64_t offset_ms;
+} apm_tz_rule;
+#define APM_MAX_TZ_RULES 8
+
+typedef struct apm_parse_result {
+    uint64_t lines;            /* newline-separated lines seen */
+    uint64_t records;          /* lines recognised as one of the four forms */
+    uint64_t exits;            /* Stop / Total-time lines among them */
+    uint64_t fed;              /* exits that went into the transaction columns */
+    uint64_t unknown_service;  /* exits held back because their name is not in the dictionary */
+    uint64_t malformed;        /* exits held back for APM_LR_BAD_TIME / APM_LR_BAD_ELAPSED */
+} apm_parse_result;
+
+/* FNV-1a 64 of a byte string: the hash the device computes for service names and log ids. */
+uint64_t apm_name_hash(const char* s, uint64_t len);
+/* Replaces the device dictionary: rewritten service name hash -> service id (< num_services). */
+apm_status apm_dict_set(apm_ctx* ctx, const uint64_t* name_hashes, const uint32_t* service_ids, uint32_t n);
+/* Parses `nbytes` of log text (host memory).  file_type: 0 = application log (CommonTiming::Start / Stop
+ * only), 1 = server.log (the EJB forms take precedence, :764-776).  Records come back in line order; the
+ * transaction columns of the fed exits stay on the device for apm_feed_parsed.  `out` may be NULL. */
+apm_status apm_parse_log_host(apm_ctx* ctx, const char* text, uint64_t nbytes, uint32_t file_type, uint32_t jvm_id,
+                              const apm_tz_rule* tz, uint32_t num_tz, apm_log_record* out, uint64_t cap, uint64_t* n,
+                              apm_parse_result* result);
+/* Runs the hot path (as apm_process_device) over the columns the last apm_parse_log_host left on the device. */
+apm_status apm_feed_parsed(apm_ctx* ctx, apm_tick_result* result);
+
 #ifdef __cplusplus
 }
 #endif
