@@ -135,15 +135,19 @@ class Engine:
     def parse_log(self, text: bytes, file_type: int, jvm_id: int, tz_rules=((-(1 << 62), 0),), want_records=True):
         """apm_parse_log_host: (records in line order, ParseResult); the fed exits stay on the device."""
         tz = np.array(tz_rules, np.int64).reshape(-1, 2)
-        buf = np.frombuffer(text, np.uint8)
+        buf = text if isinstance(text, np.ndarray) else np.frombuffer(text, np.uint8)  # an ndarray may be pinned memory
         res = _capi.ParseResult()
         n = C.c_uint64(0)
-        cap = max(1, text.count(b"\n") + 1) if want_records else 0
+        cap = max(1, int(np.count_nonzero(buf == 10)) + 1) if want_records else 0
         out = np.zeros(cap, _capi.LOG_DTYPE) if want_records else None
         self._check(self._lib.apm_parse_log_host(self._h, buf.ctypes.data if buf.size else None, buf.size, file_type, jvm_id,
                                                  tz.ctypes.data, tz.shape[0], out.ctypes.data if want_records else None, cap,
                                                  C.byref(n), C.byref(res)))
         return (out[:n.value] if want_records else None), res
+
+    def pinned_bytes(self, nbytes: int) -> np.ndarray:
+        """A page-locked uint8 array (apm_host_alloc), e.g. for log text that is to be parsed at PCIe speed."""
+        return self._out_buffer("text", np.uint8, nbytes, True)[:nbytes]
 
     def feed_parsed(self) -> TickResult:
         res = TickResult()

@@ -266,3 +266,26 @@ def test_alerts_are_the_signalled_fs_records():
     assert al.size == want.size > 0
     assert sort_records(al, True).tobytes() == sort_records(want, True).tobytes()
     e.close()
+
+
+def test_window_wider_than_a_warp():
+    """51 buckets per window: the warp-per-key window kernel gives every lane two buckets."""
+    c = dict(seed=21, n=20000, S=7, J=2, bucket_ms=10000, window=45, buffer=5, span=140, lags=(10, 30), thr=(2.0, 1.5),
+             infl=(0.1, 0.0), pcts=(50.0, 75.0, 99.0), zpct=(1, 2), gap=(60, 66))
+    _, orc, st, fs = run_both(c, stream_for(c))
+    assert orc.ticks > 100
+    assert_stats_equal(st, orc.stats())
+    assert_fs_equal(fs, orc.fs())
+
+
+def test_buckets_around_the_one_cta_sort_limit():
+    """~4100 transactions per bucket: some buckets take the one-CTA bitonic sort (<= 4096 words), some the tiled
+    radix sort, and the sliding window mixes runs produced by both."""
+    c = dict(seed=22, n=82000, S=11, J=2, bucket_ms=10000, window=3, buffer=1, span=20, lags=(6,), thr=(1.5,),
+             infl=(0.2,), pcts=(75.0, 95.0), gap=None, log_cap=1 << 14, max_batch=1 << 17)
+    eng, orc, st, fs = run_both(c, stream_for(c, late_frac=0.02, late_ms=15000))
+    assert_stats_equal(st, orc.stats())
+    assert_fs_equal(fs, orc.fs())
+    per_bucket = np.unique(stream_for(c, late_frac=0.02, late_ms=15000)[2] // 10000, return_counts=True)[1]
+    assert ((per_bucket > 3000) & (per_bucket <= 4096)).any() and (per_bucket > 4096).any()
+    eng.close()
