@@ -8,7 +8,9 @@
 // look-back over the predecessor tiles' published counts instead.
 //
 // Only the significant bits are sorted: the logical word is the low `vbits` of the value
-// field with the key field packed directly above it, cut into equal digits of <= 11 bits.
+// field with the key field packed directly above it, cut into equal digits of 8 bits (up to 11 on request).
+#include <cstdlib>
+
 #include "ctx.h"
 
 namespace {
@@ -224,7 +226,17 @@ uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t 
     int total = vbits + kbits;
     if (total < 1) total = 1;
     OsPlan plan;
-    plan.npass = (total + OS_MAX_BITS - 1) / OS_MAX_BITS;
+    // Widest digit the planner uses (APM_SORT_BITS, 8..11).  A 4096-word tile has two words per 11-bit bin, so
+    // the per-bin work of a pass (warp offsets, publish, look-back, scan, 8 KB of status per tile) is as large as
+    // its per-word work: four 8-bit passes sort a 31-bit word faster than three 11-bit ones (measured 139 vs
+    // 150 us for 1.67 M words; 37-bit words: 5 x 8 bits 97 us, 4 x 10 bits 135 us).
+    static int digit_bits = 0;
+    if (!digit_bits) {
+        const char* e = getenv("APM_SORT_BITS");
+        digit_bits = e ? atoi(e) : 8;
+        if (digit_bits < 8 || digit_bits > OS_MAX_BITS) digit_bits = 8;
+    }
+    plan.npass = (total + digit_bits - 1) / digit_bits;
     if (plan.npass > OS_MAX_PASSES) return nullptr;
     int per = (total + plan.npass - 1) / plan.npass;
     if (per < 8) per = 8;  // at least 256 bins: one per thread in the per-bin phases
