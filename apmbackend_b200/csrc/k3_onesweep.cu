@@ -98,7 +98,7 @@ struct OsSmemLayout {
     static size_t bytes(int bins) { return (size_t)OS_TILE * 8 + (size_t)OS_WARPS * bins * 2 + (size_t)bins * 4 * 2 + 64; }
 };
 
-__global__ void __launch_bounds__(OS_THREADS) os_pass_kernel(const uint64_t* __restrict__ src, uint64_t* __restrict__ dst, uint64_t n,
+__global__ void __launch_bounds__(OS_THREADS, 3) os_pass_kernel(const uint64_t* __restrict__ src, uint64_t* __restrict__ dst, uint64_t n,
                                                              int vbits, int shift, int bits, const uint32_t* __restrict__ gbase,
                                                              volatile uint32_t* status /* [tiles][bins] */, uint32_t* ticket) {
     extern __shared__ __align__(16) unsigned char os_raw[];
