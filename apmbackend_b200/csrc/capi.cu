@@ -757,12 +757,11 @@ apm_status apm_fetch_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64
     uint64_t w = 0;
     for (uint32_t t = 0; t < c->ticks_buffered; ++t) {
         if (!counts[t]) continue;
+        // each tick's block is already (lag, key)-ascending (ordered compaction)
         CUDA_TRY(c, cudaMemcpyAsync(out + w, c->d_alerts + (size_t)t * c->cfg.max_alerts_per_tick, counts[t] * sizeof(apm_fs_record), cudaMemcpyDeviceToHost, c->s_main));
-        // atomics append in arbitrary order: present each tick's alerts (lag, key)-ascending
-        CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-        std::sort(out + w, out + w + counts[t], [](const apm_fs_record& a, const apm_fs_record& b) { return a.lag != b.lag ? a.lag < b.lag : a.key < b.key; });
         w += counts[t];
     }
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     c->counters.d2h_bytes += total * sizeof(apm_fs_record) + counts.size() * 4;
     c->counters.alerts += total;
     *n = total;

@@ -618,23 +618,47 @@ __global__ void __launch_bounds__(256) alert_counter_kernel(const AlertParams p)
     en->pad_[1] = (uint8_t)(cnt > 255u ? 255u : cnt);
 }
 
-// Copies the fs records that carry a signal into the tick's compact alert block.
-__global__ void __launch_bounds__(256) compact_alerts_kernel(const apm_fs_record* __restrict__ fs, uint32_t n,
-                                                             apm_fs_record* __restrict__ alerts,
-                                                             unsigned int* __restrict__ count, uint32_t cap, int by_trigger) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const apm_fs_record* r = fs + i;
-    if (!(r->flags & 1)) return;
-    if (by_trigger ? (r->flags & 2) != 0 : (r->signal[0] | r->signal[1] | r->signal[2]) != 0) {
-        const unsigned int k = atomicAdd(count, 1u);
-        if (k < cap) {
-            const uint4* s = reinterpret_cast<const uint4*>(r);
-            uint4* d = reinterpret_cast<uint4*>(alerts + k);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) d[j] = s[j];
+// Copies the fs records that carry a signal into the tick's compact alert block, in the order of the fs
+// block itself ((lag, key)-ascending): one CTA walks the tick's records 1024 at a time and ranks the hits with
+// a block scan, so the block needs no sorting afterwards and no counter has to be zeroed beforehand.
+constexpr int CA_THREADS = 1024;
+__global__ void __launch_bounds__(CA_THREADS) compact_alerts_kernel(const apm_fs_record* __restrict__ fs, uint32_t n,
+                                                                    apm_fs_record* __restrict__ alerts,
+                                                                    unsigned int* __restrict__ count, uint32_t cap, int by_trigger) {
+    __shared__ uint32_t s_warp[CA_THREADS / 32];
+    __shared__ uint32_t s_base;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (uint32_t i0 = 0; i0 < n; i0 += CA_THREADS) {
+        const uint32_t i = i0 + tid;
+        bool hit = false;
+        if (i < n) {
+            const apm_fs_record* r = fs + i;
+            if (r->flags & 1) hit = by_trigger ? (r->flags & 2) != 0 : (r->signal[0] | r->signal[1] | r->signal[2]) != 0;
         }
+        const uint32_t bal = __ballot_sync(0xffffffffu, hit);
+        if (lane == 0) s_warp[w] = __popc(bal);
+        __syncthreads();
+        uint32_t before = 0, total = 0;
+#pragma unroll
+        for (int j = 0; j < CA_THREADS / 32; ++j) {
+            const uint32_t c = s_warp[j];
+            if (j < w) before += c;
+            total += c;
+        }
+        const uint32_t k = s_base + before + __popc(bal & ((1u << lane) - 1u));
+        if (hit && k < cap) {
+            const uint4* src = reinterpret_cast<const uint4*>(fs + i);
+            uint4* dst = reinterpret_cast<uint4*>(alerts + k);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dst[j] = src[j];
+        }
+        __syncthreads();
+        if (tid == 0) s_base += total;
+        __syncthreads();
     }
+    if (tid == 0) *count = s_base;
 }
 
 }  // namespace
@@ -744,7 +768,7 @@ apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t aler
     ProfScope prof_scope_(c, APM_PG_ALERTS, st);
     if (!c->d_alerts || !c->d_fs) return APM_OK;
     const uint32_t n = c->K * (uint32_t)c->cfg.num_lags;
-    compact_alerts_kernel<<<(n + 255) / 256, 256, 0, st>>>(
+    compact_alerts_kernel<<<1, CA_THREADS, 0, st>>>(
         c->d_fs + (size_t)fs_slot * c->cfg.num_lags * c->K, n,
         c->d_alerts + (size_t)alert_slot * c->cfg.max_alerts_per_tick, c->d_alert_count + alert_slot,
         c->cfg.max_alerts_per_tick, c->alert_rules.enabled);

@@ -349,8 +349,8 @@ class Engine:
     def comm_init(self, rank: int, nranks: int, unique_id: bytes):
         self._check(self._lib.apm_comm_init(self._h, rank, nranks, unique_id))
 
-    def gather_alerts(self, cap: int) -> np.ndarray:
-        out = np.zeros(max(cap, 1), dtype=_capi.FS_DTYPE)
+    def gather_alerts(self, cap: int, pinned: bool = False) -> np.ndarray:
+        out = self._out_buffer("gather", _capi.FS_DTYPE, cap, pinned)
         n = C.c_uint64(0)
         self._check(self._lib.apm_gather_alerts(self._h, out.ctypes.data, cap, C.byref(n)))
         return out[:n.value]

@@ -183,8 +183,26 @@ def sample_for_cpu(wl, stream, ticks=2):
 
 
 # ---------------------------------------------------------------------------------------------
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """The one JSON line goes to the process's real stdout; everything else libraries print while the bench
+    runs (NCCL's version banner, for one) was sent to stderr."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)  # stdout of everything below (C libraries included) joins stderr
     wl = dict(WORKLOADS[args.workload])
     if args.scale != 1.0:
         wl["n"] = int(wl["n"] * args.scale)
@@ -269,10 +287,15 @@ def main():
         stream.generate_device(dc, t0_ms=step_t0(s), seed=spec.seed + s)
         dev_steps.append(dc)
 
+    gather_wall = [0.0, 0]
+
     def run_step_device(s):
         eng.process_device(dev_steps[s].columns(), wl["n"])
         if world > 1 and wl["zscore"]:
-            eng.gather_alerts(gather_cap)
+            g0 = time.perf_counter()
+            got = eng.gather_alerts(gather_cap, pinned=True)
+            gather_wall[0] += time.perf_counter() - g0
+            gather_wall[1] = len(got)
         eng.release_ticks()
 
     def barrier():
@@ -299,6 +322,9 @@ def main():
     clk = clocks.stop()
     prof = eng.profile_read()
     eng.profile_enable(False)
+    if world > 1:
+        print(f"[rank {rank}] alert gather: {gather_wall[0] * 1e3 / max(nsteps, 1):.2f} ms wall per step, "
+              f"{gather_wall[1]} records in the last one", file=sys.stderr)
     c1 = eng.counters()
     launches = c1.kernel_launches - launches0
     ticks = c1.ticks - c0.ticks
@@ -310,7 +336,7 @@ def main():
         eng.profile_enable(True)
         eng.process_device(dev_steps[0].columns(), wl["n"])
         if world > 1:
-            eng.gather_alerts(gather_cap)
+            eng.gather_alerts(gather_cap, pinned=True)
         eng.release_ticks()
         prof_iso = eng.profile_read()
         eng.profile_enable(False)
@@ -351,7 +377,7 @@ def main():
                 al = eng.fetch_alerts(pinned=True)
                 out_bytes[0] = fs.nbytes + al.nbytes
                 if world > 1:
-                    eng.gather_alerts(gather_cap)
+                    eng.gather_alerts(gather_cap, pinned=True)
             else:
                 st = eng.fetch_stats(pinned=True)
                 out_bytes[0] = st.nbytes
@@ -442,7 +468,7 @@ def main():
                                           "single-threaded Node process; Node itself is absent on this box)"}
     eng.close()
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -476,7 +502,7 @@ def run_reference(args, wl, rank, world, config, span_ms):
             "e2e": {"value": v, "unit": "transactions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "Node.js is absent on this box (node --version: not found), so the reference's own JS cannot be "
                     "timed; this is its CPU restatement"}
-    print(json.dumps(line))
+    emit(line)
 
 
 if __name__ == "__main__":
