@@ -294,6 +294,111 @@ static napi_value state_io(napi_env env, napi_callback_info info, int save) {
 static napi_value SaveState(napi_env env, napi_callback_info info) { return state_io(env, info, 1); }
 static napi_value LoadState(napi_env env, napi_callback_info info) { return state_io(env, info, 0); }
 
+/* ---- log feeder: stream_parse_transactions.js:733-791 readLine over a whole buffer ---- */
+
+/* dictSet(namesArray, idsUint32Array): rewritten service names -> service ids of the device parser */
+static napi_value DictSet(napi_env env, napi_callback_info info) {
+    size_t argc = 2;
+    napi_value argv[2];
+    addon_obj* o = self_of(env, info, &argc, argv);
+    if (!o) return NULL;
+    bool is_arr = false;
+    uint32_t n = 0;
+    napi_typedarray_type t;
+    size_t len = 0;
+    void* ids = NULL;
+    if (argc < 2 || napi_is_array(env, argv[0], &is_arr) != napi_ok || !is_arr || napi_get_array_length(env, argv[0], &n) != napi_ok ||
+        napi_get_typedarray_info(env, argv[1], &t, &len, &ids, NULL, NULL) != napi_ok || t != napi_uint32_array || len != n) {
+        napi_throw_error(env, "APM_B200", "dictSet(names: string[], ids: Uint32Array) of equal length");
+        return NULL;
+    }
+    uint64_t* hashes = (uint64_t*)malloc((n ? n : 1) * sizeof *hashes);
+    char name[1024];
+    for (uint32_t i = 0; i < n; ++i) {
+        napi_value e;
+        size_t got = 0;
+        if (napi_get_element(env, argv[0], i, &e) != napi_ok || napi_get_value_string_utf8(env, e, name, sizeof name, &got) != napi_ok) {
+            free(hashes);
+            napi_throw_error(env, "APM_B200", "dictSet: names must be strings shorter than 1024 bytes");
+            return NULL;
+        }
+        hashes[i] = apm_name_hash(name, got);
+    }
+    apm_status st = apm_dict_set(o->ctx, hashes, (const uint32_t*)ids, n);
+    free(hashes);
+    if (st) return fail(env, o->ctx, st, "apm_dict_set");
+    return undefined(env);
+}
+
+/* parseLog(text: Uint8Array, fileType, jvmId[, tz: number[] = [localFromMs, offsetMs, ...]]) ->
+ * { records: ArrayBuffer of 64-byte apm_log_record, lines, exits, fed, unknownService, malformed } */
+static napi_value ParseLog(napi_env env, napi_callback_info info) {
+    size_t argc = 4;
+    napi_value argv[4];
+    addon_obj* o = self_of(env, info, &argc, argv);
+    if (!o) return NULL;
+    napi_typedarray_type t;
+    size_t len = 0;
+    void* text = NULL;
+    uint32_t file_type = 0, jvm = 0;
+    if (argc < 3 || napi_get_typedarray_info(env, argv[0], &t, &len, &text, NULL, NULL) != napi_ok || t != napi_uint8_array ||
+        napi_get_value_uint32(env, argv[1], &file_type) != napi_ok || napi_get_value_uint32(env, argv[2], &jvm) != napi_ok) {
+        napi_throw_error(env, "APM_B200", "parseLog(text: Uint8Array, fileType: 0|1, jvmId[, tzRules: number[]])");
+        return NULL;
+    }
+    apm_tz_rule tz[APM_MAX_TZ_RULES];
+    uint32_t ntz = 0;
+    bool is_arr = false;
+    if (argc >= 4 && napi_is_array(env, argv[3], &is_arr) == napi_ok && is_arr) {
+        uint32_t m = 0;
+        napi_get_array_length(env, argv[3], &m);
+        if (m % 2 || m / 2 > APM_MAX_TZ_RULES) {
+            napi_throw_error(env, "APM_B200", "parseLog: tzRules is a flat array of (localFromMs, offsetMs) pairs, at most 8");
+            return NULL;
+        }
+        for (uint32_t i = 0; i < m; ++i) {
+            napi_value e;
+            double d = 0;
+            napi_get_element(env, argv[3], i, &e);
+            if (napi_get_value_double(env, e, &d) != napi_ok) { napi_throw_error(env, "APM_B200", "parseLog: tzRules must be numbers"); return NULL; }
+            if (i % 2) tz[i / 2].offset_ms = (int64_t)d; else tz[i / 2].local_from_ms = d < -9e18 ? INT64_MIN : (int64_t)d;
+        }
+        ntz = m / 2;
+    }
+    uint64_t cap = 1;
+    for (size_t i = 0; i < len; ++i) cap += ((const unsigned char*)text)[i] == '\n';
+    apm_log_record* tmp = (apm_log_record*)malloc(cap * sizeof *tmp);
+    uint64_t n = 0;
+    apm_parse_result pr;
+    apm_status st = apm_parse_log_host(o->ctx, (const char*)text, len, file_type, jvm, ntz ? tz : NULL, ntz, tmp, cap, &n, &pr);
+    if (st) { free(tmp); return fail(env, o->ctx, st, "apm_parse_log_host"); }
+    napi_value out, v;
+    void* p;
+    napi_create_object(env, &out);
+    napi_create_arraybuffer(env, n * sizeof *tmp, &p, &v);
+    memcpy(p, tmp, n * sizeof *tmp);
+    free(tmp);
+    napi_set_named_property(env, out, "records", v);
+    const struct { const char* name; uint64_t val; } f[] = {{"lines", pr.lines}, {"exits", pr.exits}, {"fed", pr.fed},
+                                                            {"unknownService", pr.unknown_service}, {"malformed", pr.malformed}};
+    for (size_t i = 0; i < sizeof f / sizeof f[0]; ++i) {
+        napi_create_double(env, (double)f[i].val, &v);
+        napi_set_named_property(env, out, f[i].name, v);
+    }
+    return out;
+}
+
+/* feedParsed(): the exits of the last parseLog go through stats + z-score on the device */
+static napi_value FeedParsed(napi_env env, napi_callback_info info) {
+    size_t argc = 0;
+    addon_obj* o = self_of(env, info, &argc, NULL);
+    if (!o) return NULL;
+    apm_tick_result res;
+    apm_status st = apm_feed_parsed(o->ctx, &res);
+    if (st) return fail(env, o->ctx, st, "apm_feed_parsed");
+    return collect(env, o, &res);
+}
+
 static napi_value Close(napi_env env, napi_callback_info info) {
     size_t argc = 0;
     napi_value self;
@@ -314,6 +419,9 @@ napi_value napi_register_module_v1(napi_env env, napi_value exports) {
         {"setKeyParams", NULL, SetKeyParams, NULL, NULL, NULL, napi_default, NULL},
         {"saveState", NULL, SaveState, NULL, NULL, NULL, napi_default, NULL},
         {"loadState", NULL, LoadState, NULL, NULL, NULL, napi_default, NULL},
+        {"dictSet", NULL, DictSet, NULL, NULL, NULL, napi_default, NULL},
+        {"parseLog", NULL, ParseLog, NULL, NULL, NULL, napi_default, NULL},
+        {"feedParsed", NULL, FeedParsed, NULL, NULL, NULL, napi_default, NULL},
         {"close", NULL, Close, NULL, NULL, NULL, napi_default, NULL},
     };
     napi_value cls, v;

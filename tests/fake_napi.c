@@ -59,6 +59,13 @@ void* fk_array(const double* vals, uint32_t n) {
     for (uint32_t i = 0; i < n; ++i) a->elems[i] = V(fk_number(vals[i]));
     return a;
 }
+void* fk_array_of(void** vals, uint32_t n) {
+    fk_value* a = mk(FK_ARRAY);
+    a->elems = (fk_value**)calloc(n ? n : 1, sizeof(fk_value*));
+    a->nelems = n;
+    for (uint32_t i = 0; i < n; ++i) a->elems[i] = V(vals[i]);
+    return a;
+}
 void* fk_typedarray(int type, void* data, size_t n) {
     fk_value* t = mk(FK_TYPED); t->ttype = (napi_typedarray_type)type; t->data = data; t->len = n; return t;
 }

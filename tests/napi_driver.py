@@ -6,7 +6,7 @@ import subprocess
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-U32, I32, BIGI64 = 6, 5, 9  # napi_typedarray_type
+U8, U32, I32, BIGI64 = 1, 6, 5, 9  # napi_typedarray_type
 
 
 def load():
@@ -24,6 +24,8 @@ def load():
     L.fk_string.argtypes = [C.c_char_p]
     L.fk_array.restype = C.c_void_p
     L.fk_array.argtypes = [C.c_void_p, C.c_uint32]
+    L.fk_array_of.restype = C.c_void_p
+    L.fk_array_of.argtypes = [C.c_void_p, C.c_uint32]
     L.fk_typedarray.restype = C.c_void_p
     L.fk_typedarray.argtypes = [C.c_int, C.c_void_p, C.c_size_t]
     L.fk_set.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
@@ -64,7 +66,7 @@ class FakeNode:
         return o
 
     def typed(self, arr: np.ndarray):
-        kind = {np.dtype(np.uint32): U32, np.dtype(np.int32): I32, np.dtype(np.int64): BIGI64}[arr.dtype]
+        kind = {np.dtype(np.uint8): U8, np.dtype(np.uint32): U32, np.dtype(np.int32): I32, np.dtype(np.int64): BIGI64}[arr.dtype]
         a = np.ascontiguousarray(arr)
         self._keep.append(a)
         return self.L.fk_typedarray(kind, a.ctypes.data, a.size)
@@ -92,6 +94,15 @@ class FakeNode:
 
     def string(self, s):
         return self.L.fk_string(s.encode())
+
+    def strings(self, items):
+        vals = self._args([self.string(x) for x in items])
+        return self.L.fk_array_of(vals, len(items))
+
+    def numbers(self, items):
+        a = np.ascontiguousarray(items, dtype=np.float64)
+        self._keep.append(a)
+        return self.L.fk_array(a.ctypes.data, a.size)
 
     def prop(self, o, name):
         return self.L.fk_get(o, name.encode())

@@ -15,7 +15,8 @@ def test_module_registers_the_class_and_its_methods():
     node = FakeNode()
     assert node.L.fk_number_value(node.prop(node.exports, "abiVersion")) == 1.0
     cls = node.prop(node.exports, "ApmB200")
-    for m in ("addBatch", "tick", "processColumns", "setKeyParams", "saveState", "loadState", "close"):
+    for m in ("addBatch", "tick", "processColumns", "setKeyParams", "saveState", "loadState", "dictSet", "parseLog",
+              "feedParsed", "close"):
         assert node.prop(cls, m), m
 
 
@@ -75,3 +76,40 @@ def test_records_through_the_shim_equal_the_ctypes_path(tmp_path):
     node.call(gpu2, "close")
     with pytest.raises(JsError, match="closed"):
         node.call(gpu2, "tick", node.number(latest + 1))
+
+
+@pytest.mark.gpu
+def test_log_feeder_through_the_shim_equals_the_ctypes_path():
+    from apmbackend_b200 import Engine, EngineConfig
+    from apmbackend_b200.transaction_parser import rewrite_service
+    from tests.logs import SERVICES, make_log
+    text = make_log(seed=31, n=1500, span_ms=400_000, unique_ids=True)
+    names = {}
+    for sv in SERVICES + ["Svc", "undefined", "Login"]:
+        for nm in (rewrite_service(sv), rewrite_service("S:" + sv)):
+            names.setdefault(nm, len(names))
+    cfg = dict(num_services=64, num_jvms=2, lags=(8, 40), thresholds=(2.0, 1.5), influences=(0.1, 0.0), out_ticks=256,
+               max_batch=1 << 16, max_tx_per_bucket=1 << 16)
+    eng = Engine(EngineConfig(**cfg))
+    eng.dict_set(names)
+    want_rec, want_res = eng.parse_log(text, 1, 1)
+    eng.feed_parsed()
+    want_st, want_fs = eng.fetch_stats().copy(), eng.fetch_fs().copy()
+    eng.close()
+
+    node = FakeNode()
+    gpu = node.new("ApmB200", node.obj(dict(OPTS, numServices=64)))
+    node.call(gpu, "dictSet", node.strings(list(names)), node.typed(np.array(list(names.values()), np.uint32)))
+    r = node.call(gpu, "parseLog", node.typed(np.frombuffer(text, np.uint8)), node.number(1), node.number(1),
+                  node.numbers([-9.3e18, 0]))
+    assert node.buffer(node.prop(r, "records"), _capi.LOG_DTYPE).tobytes() == want_rec.tobytes() and len(want_rec) > 1000
+    assert node.L.fk_number_value(node.prop(r, "fed")) == want_res.fed > 500
+    assert node.L.fk_number_value(node.prop(r, "unknownService")) == 0
+    out = node.call(gpu, "feedParsed")
+    assert node.buffer(node.prop(out, "stats"), _capi.STAT_DTYPE).tobytes() == want_st.tobytes()
+    assert node.buffer(node.prop(out, "fs"), _capi.FS_DTYPE).tobytes() == want_fs.tobytes()
+    with pytest.raises(JsError, match="equal length"):
+        node.call(gpu, "dictSet", node.strings(["a", "b"]), node.typed(np.array([1], np.uint32)))
+    with pytest.raises(JsError, match="Uint8Array"):
+        node.call(gpu, "parseLog", node.typed(np.zeros(4, np.uint32)), node.number(0), node.number(0))
+    node.call(gpu, "close")
