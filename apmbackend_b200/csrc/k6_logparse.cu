@@ -52,17 +52,6 @@ struct LogParseState {
     uint32_t dict_mask = 0;
 };
 
-template <typename T>
-cudaError_t grow(T** p, uint64_t* cap, uint64_t need) {
-    if (need <= *cap && *p) return cudaSuccess;
-    if (*p) cudaFree(*p);
-    *p = nullptr;
-    const uint64_t n = need + need / 4 + 1024;
-    cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
-    *cap = e == cudaSuccess ? n : 0;
-    return e;
-}
-
 __host__ __device__ __forceinline__ uint64_t fnv_step(uint64_t h, unsigned char c) { return (h ^ c) * FNV_PRIME; }
 
 __device__ __forceinline__ bool lp_is_ws(unsigned char c) { return c == ' ' || (c >= 9 && c <= 13); }
@@ -692,8 +681,10 @@ apm_status apm_parse_log_host(apm_ctx* c, const char* text, uint64_t nbytes, uin
     if (nbytes + 16 > s->text_cap) {
         cudaFree(s->d_text);
         s->d_text = nullptr;
-        s->text_cap = nbytes + nbytes / 4 + 4096;
-        LP_CUDA(cudaMalloc((void**)&s->d_text, s->text_cap));
+        s->text_cap = 0;
+        const uint64_t want = nbytes + nbytes / 4 + 4096;
+        LP_CUDA(cudaMalloc((void**)&s->d_text, want));
+        s->text_cap = want;
     }
     LP_CUDA(cudaMemcpyAsync(s->d_text, text, nbytes, cudaMemcpyHostToDevice, st));
     c->counters.h2d_bytes += nbytes;
@@ -702,8 +693,11 @@ apm_status apm_parse_log_host(apm_ctx* c, const char* text, uint64_t nbytes, uin
         if (tiles <= s->tiles_cap) return cudaSuccess;
         cudaFree(s->tile_counts);
         s->tile_counts = nullptr;
-        s->tiles_cap = tiles + tiles / 4 + 64;
-        return cudaMalloc((void**)&s->tile_counts, s->tiles_cap * sizeof(uint32_t));
+        s->tiles_cap = 0;
+        const uint64_t want = tiles + tiles / 4 + 64;
+        const cudaError_t e = cudaMalloc((void**)&s->tile_counts, want * sizeof(uint32_t));
+        if (e == cudaSuccess) s->tiles_cap = want;
+        return e;
     };
     LP_CUDA(ensure_tiles(btiles));
     LP_CUDA(cudaMemsetAsync(s->d_total, 0, 16 * sizeof(unsigned long long), st));
@@ -719,10 +713,12 @@ apm_status apm_parse_log_host(apm_ctx* c, const char* text, uint64_t nbytes, uin
     if (nlines > s->lines_cap) {
         cudaFree(s->nlpos); cudaFree(s->rec_sparse); cudaFree(s->rawh_sparse);
         s->nlpos = nullptr; s->rec_sparse = nullptr; s->rawh_sparse = nullptr;
-        s->lines_cap = nlines + nlines / 4 + 1024;
-        LP_CUDA(cudaMalloc((void**)&s->nlpos, s->lines_cap * sizeof(uint64_t)));
-        LP_CUDA(cudaMalloc((void**)&s->rec_sparse, s->lines_cap * sizeof(apm_log_record)));
-        LP_CUDA(cudaMalloc((void**)&s->rawh_sparse, s->lines_cap * sizeof(uint64_t)));
+        s->lines_cap = 0;  // stays 0 if an allocation below fails: the next call starts over
+        const uint64_t want = nlines + nlines / 4 + 1024;
+        LP_CUDA(cudaMalloc((void**)&s->nlpos, want * sizeof(uint64_t)));
+        LP_CUDA(cudaMalloc((void**)&s->rec_sparse, want * sizeof(apm_log_record)));
+        LP_CUDA(cudaMalloc((void**)&s->rawh_sparse, want * sizeof(uint64_t)));
+        s->lines_cap = want;
     }
     if (nl) {
         lp_write_newlines_kernel<<<(unsigned)btiles, LP_THREADS, 0, st>>>(s->d_text, nbytes, s->tile_counts, s->nlpos);
@@ -757,18 +753,20 @@ apm_status apm_parse_log_host(apm_ctx* c, const char* text, uint64_t nbytes, uin
         cudaFree(s->cols.service_id); cudaFree(s->cols.jvm_id); cudaFree(s->cols.end_ts_ms); cudaFree(s->cols.elapsed_ms);
         s->rec = nullptr; s->rawh = nullptr; s->words[0] = s->words[1] = nullptr; s->sort_hist = s->sort_base = nullptr;
         s->cols = {nullptr, nullptr, nullptr, nullptr};
-        s->rec_cap = nrec + nrec / 4 + 1024;
-        s->sort_tiles_cap = apm_radix_sort_tiles(s->rec_cap);
-        LP_CUDA(cudaMalloc((void**)&s->rec, s->rec_cap * sizeof(apm_log_record)));
-        LP_CUDA(cudaMalloc((void**)&s->rawh, s->rec_cap * sizeof(uint64_t)));
-        LP_CUDA(cudaMalloc((void**)&s->words[0], s->rec_cap * sizeof(uint64_t)));
-        LP_CUDA(cudaMalloc((void**)&s->words[1], s->rec_cap * sizeof(uint64_t)));
+        s->rec_cap = 0;  // stays 0 if an allocation below fails: the next call starts over
+        const uint64_t want = nrec + nrec / 4 + 1024;
+        s->sort_tiles_cap = apm_radix_sort_tiles(want);
+        LP_CUDA(cudaMalloc((void**)&s->rec, want * sizeof(apm_log_record)));
+        LP_CUDA(cudaMalloc((void**)&s->rawh, want * sizeof(uint64_t)));
+        LP_CUDA(cudaMalloc((void**)&s->words[0], want * sizeof(uint64_t)));
+        LP_CUDA(cudaMalloc((void**)&s->words[1], want * sizeof(uint64_t)));
         LP_CUDA(cudaMalloc((void**)&s->sort_hist, 256 * s->sort_tiles_cap * sizeof(uint32_t)));
         LP_CUDA(cudaMalloc((void**)&s->sort_base, 256 * sizeof(uint32_t)));
-        LP_CUDA(cudaMalloc((void**)&s->cols.service_id, s->rec_cap * sizeof(uint32_t)));
-        LP_CUDA(cudaMalloc((void**)&s->cols.jvm_id, s->rec_cap * sizeof(uint32_t)));
-        LP_CUDA(cudaMalloc((void**)&s->cols.end_ts_ms, s->rec_cap * sizeof(int64_t)));
-        LP_CUDA(cudaMalloc((void**)&s->cols.elapsed_ms, s->rec_cap * sizeof(int32_t)));
+        LP_CUDA(cudaMalloc((void**)&s->cols.service_id, want * sizeof(uint32_t)));
+        LP_CUDA(cudaMalloc((void**)&s->cols.jvm_id, want * sizeof(uint32_t)));
+        LP_CUDA(cudaMalloc((void**)&s->cols.end_ts_ms, want * sizeof(int64_t)));
+        LP_CUDA(cudaMalloc((void**)&s->cols.elapsed_ms, want * sizeof(int32_t)));
+        s->rec_cap = want;
     }
     lp_gather_records_kernel<<<(unsigned)ltiles, LP_THREADS, 0, st>>>(s->rec_sparse, s->rawh_sparse, nlines, s->tile_counts, s->rec,
                                                                       s->rawh, s->words[0]);
