@@ -291,7 +291,7 @@ def main():
                         buffer=wl["buffer"], percentiles=wl["percentiles"], z_series_pct=wl["z_series_pct"],
                         lags=wl["lags"], thresholds=wl["thresholds"], influences=wl["influences"], flags=flags,
                         max_tx_per_bucket=int(per_bucket * 1.5) + 4096 if per_bucket > 4096 else 1 << 16,
-                        max_batch=min(wl["n"], 1 << 24),
+                        max_batch=min(wl["n"], int(os.environ.get("APM_BENCH_MAX_BATCH", 1 << 24))),
                         out_ticks=wl["span_buckets"] + 12, max_alerts_per_tick=max(K * max(len(wl["lags"]), 1), 1024),
                         device=local_rank)
     eng = Engine(ecfg)
