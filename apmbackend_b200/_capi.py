@@ -96,6 +96,10 @@ _lib = None
 _synth = None
 
 # every symbol include/apm_b200.h declares (tests check the library exports them all)
+class TxPacked(C.Structure):
+    _fields_ = [("key", C.c_void_p), ("end_ts_delta_ms", C.c_void_p), ("elapsed_ms", C.c_void_p)]
+
+
 class ParseResult(C.Structure):
     _fields_ = [("lines", C.c_uint64), ("records", C.c_uint64), ("exits", C.c_uint64), ("fed", C.c_uint64),
                 ("unknown_service", C.c_uint64), ("malformed", C.c_uint64)]
@@ -152,6 +156,7 @@ SYMBOLS = {
     "apm_comm_unique_id": (C.c_int32, [C.c_void_p]),
     "apm_comm_init": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "apm_gather_alerts": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "apm_process_host_packed": (C.c_int32, [C.c_void_p, C.POINTER(TxPacked), C.c_int64, C.c_uint64, C.POINTER(TickResult)]),
     "apm_name_hash": (C.c_uint64, [C.c_char_p, C.c_uint64]),
     "apm_dict_set": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
     "apm_parse_log_host": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,

@@ -31,6 +31,18 @@ cudaError_t dalloc(T** p, size_t n) {
     return cudaMalloc((void**)p, n * sizeof(T));
 }
 
+// 12-byte transactions (apm_tx_packed) -> the 20-byte columns every kernel reads
+__global__ void __launch_bounds__(256) widen_tx_kernel(const uint32_t* __restrict__ key, const uint32_t* __restrict__ dt,
+                                                       const uint32_t* __restrict__ el, int64_t base, uint64_t n, apm_tx_columns d) {
+    const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t k = __ldcs(key + i);
+    d.service_id[i] = k & 0xFFFFu;
+    d.jvm_id[i] = k >> 16;
+    d.end_ts_ms[i] = base + (int64_t)__ldcs(dt + i);
+    d.elapsed_ms[i] = (int32_t)__ldcs(el + i);
+}
+
 apm_status alloc_columns_device(apm_ctx* c, apm_tx_columns* d, uint64_t n) {
     CUDA_TRY(c, dalloc(&d->service_id, n));
     CUDA_TRY(c, dalloc(&d->jvm_id, n));
@@ -290,6 +302,49 @@ static apm_status finish_result(apm_ctx* c, const apm_counters& before, apm_tick
     return st;
 }
 
+// A host buffer goes through in chunks: the first ones are small so that compute starts while most of the input
+// is still crossing PCIe; after that every chunk's copy hides behind the previous chunk's kernels.
+// enqueue_copy(offset, count, b) puts transactions [offset, offset + count) into c->dev[b] on the copy stream.
+template <typename Copy>
+apm_status process_host_chunks(apm_ctx* c, uint64_t n, apm_tick_result* res, Copy enqueue_copy) {
+    if (res) memset(res, 0, sizeof *res);
+    const apm_counters before = c->counters;
+    const uint64_t B = c->cfg.max_batch;
+    std::vector<std::pair<uint64_t, uint64_t>> chunks;  // (offset, length)
+    {
+        // when the call spans several batches the host path is copy-bound: quarter-size chunks keep the
+        // un-overlapped head (first copy) and tail (last chunk's kernels) short
+        const uint64_t top = n > B ? std::max<uint64_t>(B / 4, 1) : B;
+        uint64_t off = 0, len = n > B ? std::max<uint64_t>(B / 16, 1) : B;
+        while (off < n) {
+            const uint64_t m = std::min<uint64_t>(n - off, len);
+            chunks.emplace_back(off, m);
+            off += m;
+            len = std::min<uint64_t>(len * 2, top);
+        }
+    }
+    const uint64_t nchunks = chunks.size();
+    auto copy = [&](uint64_t ci) -> apm_status {
+        const int b = (int)(ci & 1);
+        CUDA_TRY(c, cudaStreamWaitEvent(c->s_copy, c->ev_consumed[b], 0));
+        apm_status st = enqueue_copy(chunks[ci].first, chunks[ci].second, b);
+        if (st) return st;
+        CUDA_TRY(c, cudaEventRecord(c->ev_copied[b], c->s_copy));
+        return APM_OK;
+    };
+    if (nchunks) { apm_status st = copy(0); if (st) return st; }
+    for (uint64_t ci = 0; ci < nchunks; ++ci) {
+        const int b = (int)(ci & 1);
+        // the next chunk's copy overlaps this chunk's kernels
+        if (ci + 1 < nchunks) { apm_status st = copy(ci + 1); if (st) return st; }
+        CUDA_TRY(c, cudaStreamWaitEvent(c->s_main, c->ev_copied[b], 0));
+        apm_status st = process_chunk_device(c, c->dev[b], chunks[ci].second, res);
+        if (st) return st;
+        CUDA_TRY(c, cudaEventRecord(c->ev_consumed[b], c->s_main));
+    }
+    return finish_result(c, before, res);
+}
+
 }  // namespace
 
 // Launches the deferred baseline of the last tick on the baseline stream, ordered after that tick's window
@@ -329,6 +384,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFreeHost(c->h_ticks); cudaFreeHost(c->h_nticks);
     cudaFree(c->d_seg_counts); cudaFreeHost(c->h_seg_counts);
     apm_lp_destroy(c);
+    cudaFree(c->pk[0]); cudaFree(c->pk[1]);
     cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
     free_columns_device(&c->dev[0]); free_columns_device(&c->dev[1]);
     cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
@@ -595,49 +651,35 @@ apm_status apm_process_device(apm_ctx* c, const apm_tx_columns* cols, uint64_t n
 
 apm_status apm_process_host(apm_ctx* c, const apm_tx_columns* h, uint64_t n, apm_tick_result* res) {
     if (!c || !h) return APM_E_INVALID;
-    if (res) memset(res, 0, sizeof *res);
-    const apm_counters before = c->counters;
-    // chunk plan: the first chunks are small so that compute starts while most of the
-    // input is still crossing PCIe; after that every chunk's copy hides behind the previous chunk's kernels
-    const uint64_t B = c->cfg.max_batch;
-    std::vector<std::pair<uint64_t, uint64_t>> chunks;  // (offset, length)
-    {
-        // when the call spans several batches the host path is copy-bound: quarter-size chunks keep the
-        // un-overlapped head (first copy) and tail (last chunk's kernels) short
-        const uint64_t top = n > B ? std::max<uint64_t>(B / 4, 1) : B;
-        uint64_t off = 0, len = n > B ? std::max<uint64_t>(B / 16, 1) : B;
-        while (off < n) {
-            const uint64_t m = std::min<uint64_t>(n - off, len);
-            chunks.emplace_back(off, m);
-            off += m;
-            len = std::min<uint64_t>(len * 2, top);
-        }
-    }
-    const uint64_t nchunks = chunks.size();
-    auto enqueue_copy = [&](uint64_t ci) -> apm_status {
-        const int b = (int)(ci & 1);
-        const uint64_t off = chunks[ci].first, m = chunks[ci].second;
+    return process_host_chunks(c, n, res, [&](uint64_t off, uint64_t m, int b) -> apm_status {
         apm_tx_columns& d = c->dev[b];
-        CUDA_TRY(c, cudaStreamWaitEvent(c->s_copy, c->ev_consumed[b], 0));
         CUDA_TRY(c, cudaMemcpyAsync(d.service_id, h->service_id + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
         CUDA_TRY(c, cudaMemcpyAsync(d.jvm_id, h->jvm_id + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
         CUDA_TRY(c, cudaMemcpyAsync(d.end_ts_ms, h->end_ts_ms + off, m * 8, cudaMemcpyHostToDevice, c->s_copy));
         CUDA_TRY(c, cudaMemcpyAsync(d.elapsed_ms, h->elapsed_ms + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
-        CUDA_TRY(c, cudaEventRecord(c->ev_copied[b], c->s_copy));
         c->counters.h2d_bytes += m * 20;
         return APM_OK;
-    };
-    if (nchunks) { apm_status st = enqueue_copy(0); if (st) return st; }
-    for (uint64_t ci = 0; ci < nchunks; ++ci) {
-        const int b = (int)(ci & 1);
-        // the next chunk's copy overlaps this chunk's kernels
-        if (ci + 1 < nchunks) { apm_status st = enqueue_copy(ci + 1); if (st) return st; }
-        CUDA_TRY(c, cudaStreamWaitEvent(c->s_main, c->ev_copied[b], 0));
-        apm_status st = process_chunk_device(c, c->dev[b], chunks[ci].second, res);
-        if (st) return st;
-        CUDA_TRY(c, cudaEventRecord(c->ev_consumed[b], c->s_main));
+    });
+}
+
+apm_status apm_process_host_packed(apm_ctx* c, const apm_tx_packed* h, int64_t base_ts_ms, uint64_t n, apm_tick_result* res) {
+    if (!c || !h) return APM_E_INVALID;
+    if (base_ts_ms < 0) return apm_fail(c, APM_E_INVALID, "process_host_packed: base_ts_ms must not be negative");
+    if (!c->pk[0]) {  // 12-byte staging, one third of the wide staging, created at the first packed call
+        for (int i = 0; i < 2; ++i) CUDA_TRY(c, cudaMalloc((void**)&c->pk[i], c->cfg.max_batch * 3 * sizeof(uint32_t)));
     }
-    return finish_result(c, before, res);
+    return process_host_chunks(c, n, res, [&](uint64_t off, uint64_t m, int b) -> apm_status {
+        uint32_t* p = c->pk[b];
+        const uint64_t B = c->cfg.max_batch;
+        CUDA_TRY(c, cudaMemcpyAsync(p, h->key + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
+        CUDA_TRY(c, cudaMemcpyAsync(p + B, h->end_ts_delta_ms + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
+        CUDA_TRY(c, cudaMemcpyAsync(p + 2 * B, h->elapsed_ms + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
+        widen_tx_kernel<<<(unsigned)((m + 255) / 256), 256, 0, c->s_copy>>>(p, p + B, p + 2 * B, base_ts_ms, m, c->dev[b]);
+        c->launches += 1;
+        CUDA_TRY(c, cudaGetLastError());
+        c->counters.h2d_bytes += m * 12;
+        return APM_OK;
+    });
 }
 
 apm_status apm_set_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, int32_t l, const double* thr, const double* infl) {

@@ -79,6 +79,7 @@ struct apm_ctx {
     apm_tx_columns pin = {nullptr, nullptr, nullptr, nullptr};
     apm_tx_columns dev[2] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
     uint64_t acquired = 0;
+    uint32_t* pk[2] = {nullptr, nullptr};  // staging of 12-byte transactions: [3][max_batch] each (apm_process_host_packed)
 
     // --- tick outputs
     apm_stat_record* d_stats = nullptr;  // [out_ticks][K]

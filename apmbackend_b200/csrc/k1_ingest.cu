@@ -542,16 +542,19 @@ apm_status apm_launch_find_ticks(apm_ctx* c, const int64_t* d_ts, uint64_t n, un
                                                                   c->d_nticks, c->max_ticks_per_chunk);
     c->launches += 3;
     CUDA_TRY(c, cudaGetLastError());
+    // the count and a first slice of the marks come back in one round trip; only a chunk with more ticks than
+    // the slice holds pays a second one
+    const unsigned int first = c->max_ticks_per_chunk < 256u ? c->max_ticks_per_chunk : 256u;
     CUDA_TRY(c, cudaMemcpyAsync(c->h_nticks, c->d_nticks, sizeof(unsigned int), cudaMemcpyDeviceToHost, c->s_main));
+    CUDA_TRY(c, cudaMemcpyAsync(c->h_ticks, c->d_ticks, first * sizeof(TickMark), cudaMemcpyDeviceToHost, c->s_main));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     unsigned int nt = *c->h_nticks;
     if (nt > c->max_ticks_per_chunk) return apm_fail(c, APM_E_CAPACITY, "too many ticks in one chunk");
-    if (nt) {
-        CUDA_TRY(c, cudaMemcpyAsync(c->h_ticks, c->d_ticks, nt * sizeof(TickMark), cudaMemcpyDeviceToHost, c->s_main));
+    if (nt > first) {
+        CUDA_TRY(c, cudaMemcpyAsync(c->h_ticks + first, c->d_ticks + first, (nt - first) * sizeof(TickMark), cudaMemcpyDeviceToHost, c->s_main));
         CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-        c->counters.d2h_bytes += nt * sizeof(TickMark);
     }
-    c->counters.d2h_bytes += sizeof(unsigned int);
+    c->counters.d2h_bytes += sizeof(unsigned int) + (nt > first ? nt : first) * sizeof(TickMark);
     *n_ticks_out = nt;
     return APM_OK;
 }

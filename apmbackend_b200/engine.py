@@ -115,6 +115,18 @@ class Engine:
         self._check(self._lib.apm_process_host(self._h, C.byref(cols), s.size, C.byref(res)))
         return res
 
+    def process_host_packed(self, key, end_ts_delta_ms, elapsed_ms, base_ts_ms: int) -> TickResult:
+        """apm_process_host_packed: 12-byte transactions (key = jvm << 16 | service, endTs - base, elapsed), all uint32."""
+        k = np.ascontiguousarray(key, dtype=np.uint32)
+        t = np.ascontiguousarray(end_ts_delta_ms, dtype=np.uint32)
+        e = np.ascontiguousarray(elapsed_ms, dtype=np.uint32)
+        if not (k.size == t.size == e.size):
+            raise ValueError("columns differ in length")
+        cols = _capi.TxPacked(k.ctypes.data, t.ctypes.data, e.ctypes.data)
+        res = TickResult()
+        self._check(self._lib.apm_process_host_packed(self._h, C.byref(cols), int(base_ts_ms), k.size, C.byref(res)))
+        return res
+
     def process_device(self, cols: TxColumns, n: int) -> TickResult:
         res = TickResult()
         self._check(self._lib.apm_process_device(self._h, C.byref(cols), n, C.byref(res)))

@@ -291,7 +291,7 @@ def main():
                         buffer=wl["buffer"], percentiles=wl["percentiles"], z_series_pct=wl["z_series_pct"],
                         lags=wl["lags"], thresholds=wl["thresholds"], influences=wl["influences"], flags=flags,
                         max_tx_per_bucket=int(per_bucket * 1.5) + 4096 if per_bucket > 4096 else 1 << 16,
-                        max_batch=min(wl["n"], int(os.environ.get("APM_BENCH_MAX_BATCH", 1 << 24))),
+                        max_batch=min(wl["n"], int(os.environ.get("APM_BENCH_MAX_BATCH", 1 << 25))),
                         out_ticks=wl["span_buckets"] + 12, max_alerts_per_tick=max(K * max(len(wl["lags"]), 1), 1024),
                         device=local_rank)
     eng = Engine(ecfg)
@@ -392,60 +392,85 @@ def main():
     total_tx = wl["n"] * args.steps * world
     value = total_tx / (ms / 1e3)
 
-    # ---- e2e: host buffers, H2D inside the timed region, fs + alert records read back
+    # ---- e2e: host buffers, H2D inside the timed region, fs + alert records read back.  Measured through both
+    # host entry points: apm_process_host_packed (12 B per transaction; the headline, PCIe is the bound) and
+    # apm_process_host (20 B per transaction, `e2e_columns20`).
     e2e = None
+    e2e_wide = None
     if not args.no_e2e:
-        host_steps = []
-        tmp = syn.DeviceColumns(wl["n"])
-        for s in range(nsteps):
-            # time keeps moving forward after the device-resident steps
-            stream.generate_device(tmp, t0_ms=step_t0(nsteps + 1 + s), seed=spec.seed + 100 + s)
-            pins = [syn.PinnedArray(np.uint32, wl["n"]), syn.PinnedArray(np.uint32, wl["n"]),
-                    syn.PinnedArray(np.int64, wl["n"]), syn.PinnedArray(np.int32, wl["n"])]
-            for pa, b, dt in zip(pins, tmp.bufs, (np.uint32, np.uint32, np.int64, np.int32)):
-                _capi.synth().synth_d2h(pa.ptr, b.ptr, wl["n"] * np.dtype(dt).itemsize)
-            host_steps.append(pins)
-        tmp.free()
-        out_bytes = [0]
         if wl["zscore"]:
             eng.bind_fs_output()  # fs records stream to the pinned result buffer tick by tick
 
-        def run_step_host(s):
-            p = host_steps[s]
-            eng.process_host(p[0].array, p[1].array, p[2].array, p[3].array)
-            if wl["zscore"]:
-                fs = eng.fetch_fs(pinned=True)
-                al = eng.fetch_alerts(pinned=True)
-                out_bytes[0] = fs.nbytes + al.nbytes
-                if world > 1:
-                    eng.gather_alerts(gather_cap, pinned=True)
-            else:
-                st = eng.fetch_stats(pinned=True)
-                out_bytes[0] = st.nbytes
-            eng.release_ticks()
+        def measure_e2e(packed, epoch):
+            host_steps = []
+            tmp = syn.DeviceColumns(wl["n"])
+            for s in range(nsteps):
+                # time keeps moving forward after the device-resident steps (and after the other e2e pass)
+                stream.generate_device(tmp, t0_ms=step_t0((epoch + 1) * (nsteps + 1) + s), seed=spec.seed + 100 * (epoch + 1) + s)
+                pins = [syn.PinnedArray(np.uint32, wl["n"]), syn.PinnedArray(np.uint32, wl["n"]),
+                        syn.PinnedArray(np.int64, wl["n"]), syn.PinnedArray(np.int32, wl["n"])]
+                for pa, b, dt in zip(pins, tmp.bufs, (np.uint32, np.uint32, np.int64, np.int32)):
+                    _capi.synth().synth_d2h(pa.ptr, b.ptr, wl["n"] * np.dtype(dt).itemsize)
+                if packed:  # the same transactions as three pinned uint32 columns (built outside the timed region)
+                    base = int(pins[2].array.min())
+                    pk = [syn.PinnedArray(np.uint32, wl["n"]) for _ in range(3)]
+                    np.left_shift(pins[1].array, 16, out=pk[0].array)
+                    np.bitwise_or(pk[0].array, pins[0].array, out=pk[0].array)
+                    pk[1].array[:] = pins[2].array - base
+                    pk[2].array[:] = pins[3].array.view(np.uint32)
+                    for pa in pins:
+                        pa.free()
+                    host_steps.append((pk, base))
+                else:
+                    host_steps.append((pins, 0))
+            tmp.free()
+            out_bytes = [0]
 
-        for s in range(args.warmup):
-            run_step_host(s)
-        ce0 = eng.counters()
-        barrier()
-        eng.timer_start()
-        for s in range(args.warmup, nsteps):
-            run_step_host(s)
-        ems = eng.timer_stop()
-        barrier()
-        ce1 = eng.counters()
-        if dist is not None:
-            import torch
-            t = torch.tensor([ems], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ems = float(t.item())
-        e2e = {"value": total_tx / (ems / 1e3), "unit": "transactions/s",
-               "h2d_bytes_per_step": int((ce1.h2d_bytes - ce0.h2d_bytes) // args.steps),
-               "d2h_bytes_per_step": int((ce1.d2h_bytes - ce0.d2h_bytes) // args.steps),
-               "ms_per_step": ems / args.steps, "records_bytes_per_step": int(out_bytes[0])}
-        for pins in host_steps:
-            for pa in pins:
-                pa.free()
+            def run_step_host(s):
+                p, base = host_steps[s]
+                if packed:
+                    eng.process_host_packed(p[0].array, p[1].array, p[2].array, base)
+                else:
+                    eng.process_host(p[0].array, p[1].array, p[2].array, p[3].array)
+                if wl["zscore"]:
+                    fs = eng.fetch_fs(pinned=True)
+                    al = eng.fetch_alerts(pinned=True)
+                    out_bytes[0] = fs.nbytes + al.nbytes
+                    if world > 1:
+                        eng.gather_alerts(gather_cap, pinned=True)
+                else:
+                    st = eng.fetch_stats(pinned=True)
+                    out_bytes[0] = st.nbytes
+                eng.release_ticks()
+
+            for s in range(args.warmup):
+                run_step_host(s)
+            ce0 = eng.counters()
+            barrier()
+            eng.timer_start()
+            for s in range(args.warmup, nsteps):
+                run_step_host(s)
+            ems = eng.timer_stop()
+            barrier()
+            ce1 = eng.counters()
+            if dist is not None:
+                import torch
+                t = torch.tensor([ems], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ems = float(t.item())
+            for pins, _ in host_steps:
+                for pa in pins:
+                    pa.free()
+            return {"value": total_tx / (ems / 1e3), "unit": "transactions/s",
+                    "h2d_bytes_per_step": int((ce1.h2d_bytes - ce0.h2d_bytes) // args.steps),
+                    "d2h_bytes_per_step": int((ce1.d2h_bytes - ce0.d2h_bytes) // args.steps),
+                    "ms_per_step": ems / args.steps, "records_bytes_per_step": int(out_bytes[0]),
+                    "api": "apm_process_host_packed (12 B per transaction: key u32, endTs - base u32, elapsed u32)" if packed
+                           else "apm_process_host (20 B per transaction: service u32, jvm u32, endTs i64, elapsed i32)"}
+
+        e2e_wide = measure_e2e(False, 0)
+        can_pack = wl["services"] < 65536 and wl["jvms"] < 65536 and wl["span_buckets"] * wl["bucket_ms"] < (1 << 32)
+        e2e = measure_e2e(True, 1) if can_pack else e2e_wide
 
     # ---- roofline of the dominant kernel (live CUDA-event spans recorded inside the timed region)
     peaks = {}
@@ -495,6 +520,8 @@ def main():
             "ticks": int(ticks), "wall_ms_per_step": wall_ms / args.steps, "roofline": roofline}
     if e2e:
         line["e2e"] = e2e
+        if e2e_wide is not e2e:
+            line["e2e_columns20"] = e2e_wide
 
     # ---- CPU baseline: the reference-structure port on a bounded sample, rank 0 at N = 1 only
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -203,6 +203,19 @@ apm_status apm_tick(apm_ctx* ctx, int64_t latest_bucket, apm_tick_result* res);
 apm_status apm_process_host(apm_ctx* ctx, const apm_tx_columns* host_cols, uint64_t n, apm_tick_result* res);
 apm_status apm_process_device(apm_ctx* ctx, const apm_tx_columns* dev_cols, uint64_t n, apm_tick_result* res);
 
+/* The same run of consumeMsg calls from 12-byte instead of 20-byte transactions, for hosts whose ingest is
+ * bound by the PCIe link: key = jvm_id << 16 | service_id (both below 65536), end_ts_delta_ms = endTs -
+ * base_ts_ms (the chunk spans less than 2^32 ms = 49 days), elapsed_ms as unsigned (a value above INT32_MAX is
+ * the invalid transaction a negative elapsed is in the wide form).  Widened on the device, then identical to
+ * apm_process_host: same ticks, same records. */
+typedef struct apm_tx_packed {
+    const uint32_t* key;
+    const uint32_t* end_ts_delta_ms;
+    const uint32_t* elapsed_ms;
+} apm_tx_packed;
+apm_status apm_process_host_packed(apm_ctx* ctx, const apm_tx_packed* host_cols, int64_t base_ts_ms, uint64_t n,
+                                   apm_tick_result* res);
+
 /* ---- per-key z-score settings: replaces updateServiceSettings
  * (stream_calc_z_score.js:134-150); thr/infl hold n values for keys
  * [key_lo, key_lo+n) of lag index lag_idx. */

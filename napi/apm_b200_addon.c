@@ -261,6 +261,30 @@ static napi_value ProcessColumns(napi_env env, napi_callback_info info) {
 }
 
 /* setKeyParams(key, lagIndex, threshold, influence) */
+/* processPacked(key, endTsDelta, elapsed: Uint32Array x3, baseTsMs): 12-byte transactions, see apm_process_host_packed */
+static napi_value ProcessPacked(napi_env env, napi_callback_info info) {
+    size_t argc = 4;
+    napi_value argv[4];
+    addon_obj* o = self_of(env, info, &argc, argv);
+    if (!o) return NULL;
+    napi_typedarray_type t[3];
+    size_t len[3] = {0, 0, 0};
+    void* p[3] = {NULL, NULL, NULL};
+    int64_t base = 0;
+    bool ok = argc >= 4 && napi_get_value_int64(env, argv[3], &base) == napi_ok;
+    for (int i = 0; ok && i < 3; ++i)
+        ok = napi_get_typedarray_info(env, argv[i], &t[i], &len[i], &p[i], NULL, NULL) == napi_ok && t[i] == napi_uint32_array;
+    if (!ok || len[0] != len[1] || len[0] != len[2]) {
+        napi_throw_error(env, "APM_B200", "processPacked(Uint32Array, Uint32Array, Uint32Array, baseTsMs) of equal length");
+        return NULL;
+    }
+    const apm_tx_packed src = {(const uint32_t*)p[0], (const uint32_t*)p[1], (const uint32_t*)p[2]};
+    apm_tick_result res;
+    apm_status st = apm_process_host_packed(o->ctx, &src, base, len[0], &res);
+    if (st) return fail(env, o->ctx, st, "apm_process_host_packed");
+    return collect(env, o, &res);
+}
+
 static napi_value SetKeyParams(napi_env env, napi_callback_info info) {
     size_t argc = 4;
     napi_value argv[4];
@@ -416,6 +440,7 @@ napi_value napi_register_module_v1(napi_env env, napi_value exports) {
         {"addBatch", NULL, AddBatch, NULL, NULL, NULL, napi_default, NULL},
         {"tick", NULL, Tick, NULL, NULL, NULL, napi_default, NULL},
         {"processColumns", NULL, ProcessColumns, NULL, NULL, NULL, napi_default, NULL},
+        {"processPacked", NULL, ProcessPacked, NULL, NULL, NULL, napi_default, NULL},
         {"setKeyParams", NULL, SetKeyParams, NULL, NULL, NULL, napi_default, NULL},
         {"saveState", NULL, SaveState, NULL, NULL, NULL, napi_default, NULL},
         {"loadState", NULL, LoadState, NULL, NULL, NULL, napi_default, NULL},

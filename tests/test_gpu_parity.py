@@ -289,3 +289,24 @@ def test_buckets_around_the_one_cta_sort_limit():
     per_bucket = np.unique(stream_for(c, late_frac=0.02, late_ms=15000)[2] // 10000, return_counts=True)[1]
     assert ((per_bucket > 3000) & (per_bucket <= 4096)).any() and (per_bucket > 4096).any()
     eng.close()
+
+
+def test_packed_transactions_give_the_same_records():
+    """apm_process_host_packed (12 B per transaction) == apm_process_host (20 B), invalid rows included."""
+    from apmbackend_b200 import Engine
+    from tests.gpu_util import engine_config
+    c = dict(CASES[0], n=6000, max_batch=1 << 10)   # several chunks per call
+    svc, jvm, ts, el = stream_for(c, late_frac=0.05)
+    svc, el = svc.copy(), el.copy()
+    svc[17] = c["S"] + 3                           # unknown service: invalid in both forms
+    el[29] = -5                                    # negative elapsed: invalid in both forms
+    a = Engine(engine_config(c))
+    ra = a.process_host(svc, jvm, ts, el)
+    base = int(ts.min())
+    b = Engine(engine_config(c))
+    rb = b.process_host_packed((jvm.astype(np.uint32) << 16) | svc, (ts - base).astype(np.uint32), el.astype(np.int32).view(np.uint32), base)
+    assert (ra.ticks, ra.tx_ingested, ra.tx_dropped, ra.tx_invalid, ra.latest_bucket) == \
+           (rb.ticks, rb.tx_ingested, rb.tx_dropped, rb.tx_invalid, rb.latest_bucket) and ra.tx_invalid == 2
+    assert a.fetch_stats().tobytes() == b.fetch_stats().tobytes() and a.fetch_fs().tobytes() == b.fetch_fs().tobytes()
+    a.close()
+    b.close()

@@ -15,7 +15,7 @@ def test_module_registers_the_class_and_its_methods():
     node = FakeNode()
     assert node.L.fk_number_value(node.prop(node.exports, "abiVersion")) == 1.0
     cls = node.prop(node.exports, "ApmB200")
-    for m in ("addBatch", "tick", "processColumns", "setKeyParams", "saveState", "loadState", "dictSet", "parseLog",
+    for m in ("addBatch", "tick", "processColumns", "processPacked", "setKeyParams", "saveState", "loadState", "dictSet", "parseLog",
               "feedParsed", "close"):
         assert node.prop(cls, m), m
 
@@ -49,6 +49,15 @@ def test_records_through_the_shim_equal_the_ctypes_path(tmp_path):
     assert node.buffer(node.prop(res, "stats"), _capi.STAT_DTYPE).tobytes() == want_st.tobytes()
     assert node.buffer(node.prop(res, "fs"), _capi.FS_DTYPE).tobytes() == want_fs.tobytes()
     assert node.buffer(node.prop(res, "alerts"), _capi.FS_DTYPE).tobytes() == want_al.tobytes()
+
+    # the 12-byte form of the same transactions
+    gpu3 = node.new("ApmB200", node.obj(OPTS))
+    base = int(ts.min())
+    res3 = node.call(gpu3, "processPacked", node.typed((jvm.astype(np.uint32) << 16) | svc), node.typed((ts - base).astype(np.uint32)),
+                     node.typed(el.view(np.uint32)), node.number(base))
+    assert node.buffer(node.prop(res3, "stats"), _capi.STAT_DTYPE).tobytes() == want_st.tobytes()
+    assert node.buffer(node.prop(res3, "fs"), _capi.FS_DTYPE).tobytes() == want_fs.tobytes()
+    node.call(gpu3, "close")
 
     # the per-message protocol: addBatch up to the tick, tick(label), as consumeMsg does (stream_calc_stats.js:348-370)
     gpu2 = node.new("ApmB200", node.obj(OPTS))
