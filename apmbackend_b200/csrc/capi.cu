@@ -229,6 +229,10 @@ void apply_seg_counts(apm_ctx* c, unsigned int i) {
 
 apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n, apm_tick_result* res) {
     unsigned int nt = 0;
+    // The baseline of the last tick is normally launched behind the next segment's ingest kernel.  At a chunk
+    // boundary the host is about to block on the tick marks and the segment table: launch it now (it sits behind
+    // the previous chunk's tail segment), or the baseline stream idles for those round trips.
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     apm_status st = apm_launch_find_ticks(c, d.end_ts_ms, n, &nt);
     if (st) return st;
     const bool keep_any = c->cfg.flags & (APM_F_KEEP_STATS | APM_F_KEEP_FS | APM_F_ALERTS);
@@ -314,7 +318,9 @@ apm_status process_host_chunks(apm_ctx* c, uint64_t n, apm_tick_result* res, Cop
     {
         // when the call spans several batches the host path is copy-bound: quarter-size chunks keep the
         // un-overlapped head (first copy) and tail (last chunk's kernels) short
-        const uint64_t top = n > B ? std::max<uint64_t>(B / 4, 1) : B;
+        static int top_div = 0;
+        if (!top_div) { const char* e = getenv("APM_CHUNK_TOP_DIV"); top_div = e ? atoi(e) : 4; if (top_div < 1) top_div = 1; }
+        const uint64_t top = n > B ? std::max<uint64_t>(B / top_div, 1) : B;
         uint64_t off = 0, len = n > B ? std::max<uint64_t>(B / 16, 1) : B;
         while (off < n) {
             const uint64_t m = std::min<uint64_t>(n - off, len);

@@ -11,7 +11,7 @@ per_bucket = n // wl["span_buckets"]
 flags = _capi.F_KEEP_FS | _capi.F_ALERTS | _capi.F_ZSCORE | _capi.F_PERCENTILES
 ecfg = EngineConfig(num_services=K, bucket_ms=wl["bucket_ms"], window=1, buffer=0, percentiles=wl["percentiles"],
                     z_series_pct=wl["z_series_pct"], lags=wl["lags"], thresholds=wl["thresholds"], influences=wl["influences"],
-                    flags=flags, max_tx_per_bucket=int(per_bucket * 1.5) + 4096, max_batch=int(os.environ.get("BATCH", 1 << 24)),
+                    flags=flags, max_tx_per_bucket=int(per_bucket * 1.5) + 4096, max_batch=int(os.environ.get("BATCH", 1 << 25)),
                     out_ticks=72, max_alerts_per_tick=K)
 eng = Engine(ecfg)
 L = wl["lags"][0]
@@ -37,3 +37,21 @@ for s in range(3):
     al = eng.fetch_alerts(pinned=True); t3 = time.perf_counter()
     eng.release_ticks(); t4 = time.perf_counter()
     print(f"step {s}: process_host {1e3*(t1-t0):.1f} ms, fetch_fs {1e3*(t2-t1):.1f} ms ({fs.nbytes/1e6:.0f} MB), fetch_alerts {1e3*(t3-t2):.1f} ms ({al.size}), release {1e3*(t4-t3):.2f} ms")
+
+# the 12-byte form, fs records streamed to the bound pinned buffer
+eng.bind_fs_output()
+for s in range(3):
+    p = steps[s]
+    ts = p[2].array + 3 * span_ms            # keep time moving forward
+    base = int(ts.min())
+    key = (p[1].array << 16) | p[0].array
+    dtv = (ts - base).astype(np.uint32)
+    el = p[3].array.view(np.uint32)
+    pk = [syn.PinnedArray(np.uint32, n) for _ in range(3)]
+    pk[0].array[:] = key; pk[1].array[:] = dtv; pk[2].array[:] = el
+    t0 = time.perf_counter(); eng.process_host_packed(pk[0].array, pk[1].array, pk[2].array, base); t1 = time.perf_counter()
+    fs = eng.fetch_fs(pinned=True); t2 = time.perf_counter()
+    al = eng.fetch_alerts(pinned=True); t3 = time.perf_counter()
+    eng.release_ticks(); t4 = time.perf_counter()
+    print(f"packed step {s}: process {1e3*(t1-t0):.1f} ms, fetch_fs {1e3*(t2-t1):.2f} ms, fetch_alerts {1e3*(t3-t2):.2f} ms ({al.size}), release {1e3*(t4-t3):.2f} ms")
+    for a in pk: a.free()
