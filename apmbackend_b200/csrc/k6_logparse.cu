@@ -13,6 +13,8 @@
 // tokenise, convert, hash, dictionary lookup) -> ordered compaction of the recognised lines ->
 // radix sort of (pair hash, record index) -> pairing against the neighbour in sorted order ->
 // ordered compaction of the fed exits into service / jvm / endTs / elapsed columns.
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -25,6 +27,7 @@ constexpr int LP_TILE_BYTES = 4096;                       // 16 bytes per thread
 constexpr int LP_TILE_ITEMS = 1024;                       // flags per tile in the ordered compactions (4 per thread)
 constexpr uint64_t FNV_OFFSET = 0xcbf29ce484222325ull, FNV_PRIME = 0x100000001b3ull;
 constexpr uint32_t LP_MAX_RECORDS = 1u << 24;             // record index field of the pairing sort word
+constexpr uint64_t LP_SUB_BYTES = 32ull << 20;            // sub-buffer of a parse call: copy / parse overlap granularity
 
 struct LogParseState {
     unsigned char* d_text = nullptr;
@@ -50,6 +53,7 @@ struct LogParseState {
     uint64_t* dict_keys = nullptr;
     uint32_t* dict_vals = nullptr;
     uint32_t dict_mask = 0;
+    std::vector<cudaEvent_t> ev_sub;   // one per sub-buffer: its copy has landed
 };
 
 __host__ __device__ __forceinline__ uint64_t fnv_step(uint64_t h, unsigned char c) { return (h ^ c) * FNV_PRIME; }
@@ -112,22 +116,24 @@ __device__ __forceinline__ uint32_t lp_block_scan(uint32_t v, uint32_t* s_warp) 
 }
 
 // ---- line table ---------------------------------------------------------------------------------
-__global__ void __launch_bounds__(LP_THREADS) lp_count_newlines_kernel(const unsigned char* __restrict__ text, uint64_t n,
+// Both kernels work on the byte range [lo, hi) of the text buffer; tiles are anchored at lo rounded down to the
+// tile size, so the 16-byte loads stay aligned whatever the range.
+__global__ void __launch_bounds__(LP_THREADS) lp_count_newlines_kernel(const unsigned char* __restrict__ text, uint64_t lo, uint64_t hi,
                                                                        uint32_t* __restrict__ tile_counts) {
     __shared__ uint32_t s_warp[LP_THREADS / 32];
-    const uint64_t base = (uint64_t)blockIdx.x * LP_TILE_BYTES + (uint64_t)threadIdx.x * 16;
+    const uint64_t base = (lo & ~(uint64_t)(LP_TILE_BYTES - 1)) + (uint64_t)blockIdx.x * LP_TILE_BYTES + (uint64_t)threadIdx.x * 16;
     uint32_t cnt = 0;
-    if (base + 16 <= n) {
+    if (base >= lo && base + 16 <= hi) {
         const uint4 v = __ldg(reinterpret_cast<const uint4*>(text + base));  // the buffer is 256-byte aligned
         const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const uint32_t x = w[k] ^ 0x0A0A0A0Au;  // a zero byte where the text has '\n'
+            const uint32_t x = w[k] ^ 0x0A0A0A0Au;  // a zero byte where the text has a newline
 #pragma unroll
             for (int b = 0; b < 4; ++b) cnt += ((x >> (8 * b)) & 0xFFu) == 0u;
         }
     } else {
-        for (uint64_t i = base; i < n && i < base + 16; ++i) cnt += text[i] == '\n';
+        for (uint64_t i = base > lo ? base : lo; i < hi && i < base + 16; ++i) cnt += text[i] == 10;
     }
     cnt = __reduce_add_sync(0xffffffffu, cnt);
     if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = cnt;
@@ -140,28 +146,28 @@ __global__ void __launch_bounds__(LP_THREADS) lp_count_newlines_kernel(const uns
     }
 }
 
-__global__ void __launch_bounds__(LP_THREADS) lp_write_newlines_kernel(const unsigned char* __restrict__ text, uint64_t n,
+__global__ void __launch_bounds__(LP_THREADS) lp_write_newlines_kernel(const unsigned char* __restrict__ text, uint64_t lo, uint64_t hi,
                                                                        const uint32_t* __restrict__ tile_base,
                                                                        uint64_t* __restrict__ nlpos) {
     __shared__ uint32_t s_warp[LP_THREADS / 32];
-    const uint64_t base = (uint64_t)blockIdx.x * LP_TILE_BYTES + (uint64_t)threadIdx.x * 16;
+    const uint64_t base = (lo & ~(uint64_t)(LP_TILE_BYTES - 1)) + (uint64_t)blockIdx.x * LP_TILE_BYTES + (uint64_t)threadIdx.x * 16;
     unsigned char b[16];
     uint32_t cnt = 0;
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
-        b[k] = base + k < n ? __ldg(text + base + k) : 0;
-        cnt += b[k] == '\n';
+        b[k] = (base + k >= lo && base + k < hi) ? __ldg(text + base + k) : 0;
+        cnt += b[k] == 10;
     }
     uint32_t pos = tile_base[blockIdx.x] + lp_block_scan(cnt, s_warp);
 #pragma unroll
     for (int k = 0; k < 16; ++k)
-        if (b[k] == '\n') nlpos[pos++] = base + k;
+        if (b[k] == 10) nlpos[pos++] = base + k;  // absolute position in the buffer
 }
 
 // ---- one line -------------------------------------------------------------------------------------
 struct ParseParams {
     const unsigned char* text;
-    uint64_t nbytes;
+    uint64_t lo, hi;           // byte range of this sub-buffer; its lines are numbered from 0
     const uint64_t* nlpos;
     uint64_t nl, nlines;
     uint32_t file_type, jvm_id, num_services;
@@ -301,8 +307,8 @@ __device__ void lp_service_hashes(const unsigned char* t, Tok k, bool ejb, uint6
 __global__ void __launch_bounds__(LP_THREADS) lp_parse_kernel(const ParseParams p) {
     const uint64_t line = (uint64_t)blockIdx.x * LP_THREADS + threadIdx.x;
     if (line >= p.nlines) return;
-    const uint64_t ls = line == 0 ? 0 : p.nlpos[line - 1] + 1;
-    const uint64_t le = line < p.nl ? p.nlpos[line] : p.nbytes;
+    const uint64_t ls = line == 0 ? p.lo : p.nlpos[line - 1] + 1;
+    const uint64_t le = line < p.nl ? p.nlpos[line] : p.hi;
     apm_log_record r;
     memset(&r, 0, sizeof r);
     r.line_offset = ls;
@@ -464,7 +470,7 @@ __global__ void __launch_bounds__(LP_THREADS) lp_count_records_kernel(const apm_
 
 __global__ void __launch_bounds__(LP_THREADS) lp_gather_records_kernel(const apm_log_record* __restrict__ sparse,
                                                                        const uint64_t* __restrict__ rawh_sparse, uint64_t n,
-                                                                       const uint32_t* __restrict__ tile_base,
+                                                                       const uint32_t* __restrict__ tile_base, uint32_t rec_offset,
                                                                        apm_log_record* __restrict__ rec, uint64_t* __restrict__ rawh,
                                                                        uint64_t* __restrict__ words) {
     __shared__ uint32_t s_warp[LP_THREADS / 32];
@@ -476,7 +482,7 @@ __global__ void __launch_bounds__(LP_THREADS) lp_gather_records_kernel(const apm
         take[k] = base + k < n && sparse[base + k].kind != 0;
         cnt += take[k];
     }
-    uint32_t pos = tile_base[blockIdx.x] + lp_block_scan(cnt, s_warp);
+    uint32_t pos = rec_offset + tile_base[blockIdx.x] + lp_block_scan(cnt, s_warp);
 #pragma unroll
     for (int k = 0; k < 4; ++k)
         if (take[k]) {
@@ -613,6 +619,7 @@ void apm_lp_destroy(apm_ctx* c) {
     cudaFree(s->words[0]); cudaFree(s->words[1]); cudaFree(s->sort_hist); cudaFree(s->sort_base);
     cudaFree(s->cols.service_id); cudaFree(s->cols.jvm_id); cudaFree(s->cols.end_ts_ms); cudaFree(s->cols.elapsed_ms);
     cudaFree(s->dict_keys); cudaFree(s->dict_vals);
+    for (cudaEvent_t ev : s->ev_sub) cudaEventDestroy(ev);
     delete s;
     c->lp = nullptr;
 }
@@ -677,7 +684,8 @@ apm_status apm_parse_log_host(apm_ctx* c, const char* text, uint64_t nbytes, uin
         LP_CUDA(cudaMalloc((void**)&s->d_total, 16 * sizeof(unsigned long long)));
         LP_CUDA(cudaMallocHost((void**)&s->h_total, 16 * sizeof(unsigned long long)));
     }
-    // -- text to the device
+    // -- text to the device, in sub-buffers that end after a newline: the copy of the later ones (copy stream)
+    //    hides behind the line table / parse / compaction of the earlier ones
     if (nbytes + 16 > s->text_cap) {
         cudaFree(s->d_text);
         s->d_text = nullptr;
@@ -686,9 +694,34 @@ apm_status apm_parse_log_host(apm_ctx* c, const char* text, uint64_t nbytes, uin
         LP_CUDA(cudaMalloc((void**)&s->d_text, want));
         s->text_cap = want;
     }
-    LP_CUDA(cudaMemcpyAsync(s->d_text, text, nbytes, cudaMemcpyHostToDevice, st));
+    static uint64_t sub_bytes = 0;  // APM_LP_SUB_BYTES overrides the 32 MB default (tests cut small logs into many pieces)
+    if (!sub_bytes) { const char* e = getenv("APM_LP_SUB_BYTES"); sub_bytes = e && atoll(e) > 0 ? (uint64_t)atoll(e) : LP_SUB_BYTES; }
+    std::vector<uint64_t> cut(1, 0);
+    while (cut.back() < nbytes) {
+        const uint64_t lo = cut.back();
+        uint64_t e = std::min<uint64_t>(lo + sub_bytes, nbytes);
+        if (e < nbytes) {
+            const void* q = memrchr(text + lo, '\n', e - lo);
+            if (q) e = (uint64_t)((const char*)q - text) + 1;
+            else {  // one line longer than a sub-buffer: extend to its end
+                const void* f = memchr(text + e, '\n', nbytes - e);
+                e = f ? (uint64_t)((const char*)f - text) + 1 : nbytes;
+            }
+        }
+        cut.push_back(e);
+    }
+    const size_t nsub = cut.size() - 1;
+    while (s->ev_sub.size() < nsub) {
+        cudaEvent_t ev;
+        LP_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        s->ev_sub.push_back(ev);
+    }
+    LP_CUDA(cudaStreamSynchronize(c->s_copy));
+    for (size_t i = 0; i < nsub; ++i) {
+        LP_CUDA(cudaMemcpyAsync(s->d_text + cut[i], text + cut[i], cut[i + 1] - cut[i], cudaMemcpyHostToDevice, c->s_copy));
+        LP_CUDA(cudaEventRecord(s->ev_sub[i], c->s_copy));
+    }
     c->counters.h2d_bytes += nbytes;
-    const uint64_t btiles = (nbytes + LP_TILE_BYTES - 1) / LP_TILE_BYTES;
     auto ensure_tiles = [&](uint64_t tiles) -> cudaError_t {
         if (tiles <= s->tiles_cap) return cudaSuccess;
         cudaFree(s->tile_counts);
@@ -699,66 +732,28 @@ apm_status apm_parse_log_host(apm_ctx* c, const char* text, uint64_t nbytes, uin
         if (e == cudaSuccess) s->tiles_cap = want;
         return e;
     };
-    LP_CUDA(ensure_tiles(btiles));
-    LP_CUDA(cudaMemsetAsync(s->d_total, 0, 16 * sizeof(unsigned long long), st));
-    // -- line table
-    lp_count_newlines_kernel<<<(unsigned)btiles, LP_THREADS, 0, st>>>(s->d_text, nbytes, s->tile_counts);
-    lp_scan_kernel<<<1, 1024, 0, st>>>(s->tile_counts, btiles, s->d_total + 0);
-    c->launches += 2;
-    LP_CUDA(cudaMemcpyAsync(s->h_total, s->d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-    LP_CUDA(cudaStreamSynchronize(st));
-    const uint64_t nl = s->h_total[0];
-    const bool open_tail = text[nbytes - 1] != '\n';
-    const uint64_t nlines = nl + (open_tail ? 1 : 0);
-    if (nlines > s->lines_cap) {
-        cudaFree(s->nlpos); cudaFree(s->rec_sparse); cudaFree(s->rawh_sparse);
-        s->nlpos = nullptr; s->rec_sparse = nullptr; s->rawh_sparse = nullptr;
-        s->lines_cap = 0;  // stays 0 if an allocation below fails: the next call starts over
-        const uint64_t want = nlines + nlines / 4 + 1024;
-        LP_CUDA(cudaMalloc((void**)&s->nlpos, want * sizeof(uint64_t)));
-        LP_CUDA(cudaMalloc((void**)&s->rec_sparse, want * sizeof(apm_log_record)));
-        LP_CUDA(cudaMalloc((void**)&s->rawh_sparse, want * sizeof(uint64_t)));
-        s->lines_cap = want;
-    }
-    if (nl) {
-        lp_write_newlines_kernel<<<(unsigned)btiles, LP_THREADS, 0, st>>>(s->d_text, nbytes, s->tile_counts, s->nlpos);
-        c->launches += 1;
-    }
-    // -- one thread per line
-    ParseParams p;
-    memset(&p, 0, sizeof p);
-    p.text = s->d_text; p.nbytes = nbytes; p.nlpos = s->nlpos; p.nl = nl; p.nlines = nlines;
-    p.file_type = file_type; p.jvm_id = jvm_id; p.num_services = c->cfg.num_services;
-    for (uint32_t i = 0; i < num_tz; ++i) p.tz[i] = tz[i];
-    p.num_tz = num_tz;
-    p.dict_keys = s->dict_keys; p.dict_vals = s->dict_vals; p.dict_mask = s->dict_mask;
-    p.rec_sparse = s->rec_sparse; p.rawh_sparse = s->rawh_sparse;
-    lp_parse_kernel<<<(unsigned)((nlines + LP_THREADS - 1) / LP_THREADS), LP_THREADS, 0, st>>>(p);
-    c->launches += 1;
-    // -- recognised lines, in line order
-    const uint64_t ltiles = (nlines + LP_TILE_ITEMS - 1) / LP_TILE_ITEMS;
-    LP_CUDA(ensure_tiles(ltiles > btiles ? ltiles : btiles));
-    lp_count_records_kernel<<<(unsigned)ltiles, LP_THREADS, 0, st>>>(s->rec_sparse, nlines, s->tile_counts);
-    lp_scan_kernel<<<1, 1024, 0, st>>>(s->tile_counts, ltiles, s->d_total + 1);
-    c->launches += 2;
-    LP_CUDA(cudaMemcpyAsync(s->h_total + 1, s->d_total + 1, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-    LP_CUDA(cudaStreamSynchronize(st));
-    const uint64_t nrec = s->h_total[1];
-    if (result) { result->lines = nlines; result->records = nrec; }
-    if (nrec == 0) return APM_OK;
-    if (nrec > LP_MAX_RECORDS) return apm_fail(c, APM_E_CAPACITY, "parse_log: more than 2^24 CommonTiming lines in one buffer: split it");
-    if (out && cap < nrec) return apm_fail(c, APM_E_CAPACITY, "parse_log: record buffer too small");
-    if (nrec > s->rec_cap) {
+    // record arrays grow with what has been gathered so far (the first guess is one record per 96 bytes of text)
+    auto ensure_records = [&](uint64_t need, uint64_t have) -> apm_status {
+        if (need <= s->rec_cap) return APM_OK;
+        const uint64_t want = need + need / 2 + 1024;
+        apm_log_record* rec = nullptr;
+        uint64_t *rawh = nullptr, *w0 = nullptr;
+        LP_CUDA(cudaMalloc((void**)&rec, want * sizeof(apm_log_record)));
+        LP_CUDA(cudaMalloc((void**)&rawh, want * sizeof(uint64_t)));
+        LP_CUDA(cudaMalloc((void**)&w0, want * sizeof(uint64_t)));
+        if (have) {
+            LP_CUDA(cudaMemcpyAsync(rec, s->rec, have * sizeof(apm_log_record), cudaMemcpyDeviceToDevice, st));
+            LP_CUDA(cudaMemcpyAsync(rawh, s->rawh, have * sizeof(uint64_t), cudaMemcpyDeviceToDevice, st));
+            LP_CUDA(cudaMemcpyAsync(w0, s->words[0], have * sizeof(uint64_t), cudaMemcpyDeviceToDevice, st));
+            LP_CUDA(cudaStreamSynchronize(st));
+        }
         cudaFree(s->rec); cudaFree(s->rawh); cudaFree(s->words[0]); cudaFree(s->words[1]); cudaFree(s->sort_hist); cudaFree(s->sort_base);
         cudaFree(s->cols.service_id); cudaFree(s->cols.jvm_id); cudaFree(s->cols.end_ts_ms); cudaFree(s->cols.elapsed_ms);
-        s->rec = nullptr; s->rawh = nullptr; s->words[0] = s->words[1] = nullptr; s->sort_hist = s->sort_base = nullptr;
+        s->rec = rec; s->rawh = rawh; s->words[0] = w0;
+        s->words[1] = nullptr; s->sort_hist = s->sort_base = nullptr;
         s->cols = {nullptr, nullptr, nullptr, nullptr};
         s->rec_cap = 0;  // stays 0 if an allocation below fails: the next call starts over
-        const uint64_t want = nrec + nrec / 4 + 1024;
         s->sort_tiles_cap = apm_radix_sort_tiles(want);
-        LP_CUDA(cudaMalloc((void**)&s->rec, want * sizeof(apm_log_record)));
-        LP_CUDA(cudaMalloc((void**)&s->rawh, want * sizeof(uint64_t)));
-        LP_CUDA(cudaMalloc((void**)&s->words[0], want * sizeof(uint64_t)));
         LP_CUDA(cudaMalloc((void**)&s->words[1], want * sizeof(uint64_t)));
         LP_CUDA(cudaMalloc((void**)&s->sort_hist, 256 * s->sort_tiles_cap * sizeof(uint32_t)));
         LP_CUDA(cudaMalloc((void**)&s->sort_base, 256 * sizeof(uint32_t)));
@@ -767,10 +762,75 @@ apm_status apm_parse_log_host(apm_ctx* c, const char* text, uint64_t nbytes, uin
         LP_CUDA(cudaMalloc((void**)&s->cols.end_ts_ms, want * sizeof(int64_t)));
         LP_CUDA(cudaMalloc((void**)&s->cols.elapsed_ms, want * sizeof(int32_t)));
         s->rec_cap = want;
+        return APM_OK;
+    };
+    LP_CUDA(cudaMemsetAsync(s->d_total, 0, 16 * sizeof(unsigned long long), st));
+    { apm_status est = ensure_records(nbytes / 96 + 1024, 0); if (est) return est; }
+    ParseParams p;
+    memset(&p, 0, sizeof p);
+    p.text = s->d_text;
+    p.file_type = file_type; p.jvm_id = jvm_id; p.num_services = c->cfg.num_services;
+    for (uint32_t i = 0; i < num_tz; ++i) p.tz[i] = tz[i];
+    p.num_tz = num_tz;
+    p.dict_keys = s->dict_keys; p.dict_vals = s->dict_vals; p.dict_mask = s->dict_mask;
+    uint64_t nrec = 0, total_lines = 0;
+    for (size_t i = 0; i < nsub; ++i) {
+        const uint64_t lo = cut[i], hi = cut[i + 1];
+        if (hi == lo) continue;
+        LP_CUDA(cudaStreamWaitEvent(st, s->ev_sub[i], 0));
+        // -- line table of this sub-buffer
+        const uint64_t t0 = lo & ~(uint64_t)(LP_TILE_BYTES - 1);
+        const uint64_t btiles = (hi - t0 + LP_TILE_BYTES - 1) / LP_TILE_BYTES;
+        LP_CUDA(ensure_tiles(btiles));
+        lp_count_newlines_kernel<<<(unsigned)btiles, LP_THREADS, 0, st>>>(s->d_text, lo, hi, s->tile_counts);
+        lp_scan_kernel<<<1, 1024, 0, st>>>(s->tile_counts, btiles, s->d_total + 0);
+        c->launches += 2;
+        LP_CUDA(cudaMemcpyAsync(s->h_total, s->d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        LP_CUDA(cudaStreamSynchronize(st));
+        const uint64_t nl = s->h_total[0];
+        const uint64_t nlines = nl + (text[hi - 1] != '\n' ? 1 : 0);  // only the last sub-buffer can end without a newline
+        total_lines += nlines;
+        if (nlines > s->lines_cap) {
+            cudaFree(s->nlpos); cudaFree(s->rec_sparse); cudaFree(s->rawh_sparse);
+            s->nlpos = nullptr; s->rec_sparse = nullptr; s->rawh_sparse = nullptr;
+            s->lines_cap = 0;  // stays 0 if an allocation below fails: the next call starts over
+            const uint64_t want = nlines + nlines / 4 + 1024;
+            LP_CUDA(cudaMalloc((void**)&s->nlpos, want * sizeof(uint64_t)));
+            LP_CUDA(cudaMalloc((void**)&s->rec_sparse, want * sizeof(apm_log_record)));
+            LP_CUDA(cudaMalloc((void**)&s->rawh_sparse, want * sizeof(uint64_t)));
+            s->lines_cap = want;
+        }
+        if (nl) {
+            lp_write_newlines_kernel<<<(unsigned)btiles, LP_THREADS, 0, st>>>(s->d_text, lo, hi, s->tile_counts, s->nlpos);
+            c->launches += 1;
+        }
+        // -- one thread per line
+        p.lo = lo; p.hi = hi; p.nlpos = s->nlpos; p.nl = nl; p.nlines = nlines;
+        p.rec_sparse = s->rec_sparse; p.rawh_sparse = s->rawh_sparse;
+        lp_parse_kernel<<<(unsigned)((nlines + LP_THREADS - 1) / LP_THREADS), LP_THREADS, 0, st>>>(p);
+        c->launches += 1;
+        // -- its recognised lines, appended in line order
+        const uint64_t ltiles = (nlines + LP_TILE_ITEMS - 1) / LP_TILE_ITEMS;
+        LP_CUDA(ensure_tiles(ltiles));
+        lp_count_records_kernel<<<(unsigned)ltiles, LP_THREADS, 0, st>>>(s->rec_sparse, nlines, s->tile_counts);
+        lp_scan_kernel<<<1, 1024, 0, st>>>(s->tile_counts, ltiles, s->d_total + 1);
+        c->launches += 2;
+        LP_CUDA(cudaMemcpyAsync(s->h_total + 1, s->d_total + 1, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        LP_CUDA(cudaStreamSynchronize(st));
+        const uint64_t got = s->h_total[1];
+        if (got == 0) continue;
+        if (nrec + got > LP_MAX_RECORDS) return apm_fail(c, APM_E_CAPACITY, "parse_log: more than 2^24 CommonTiming lines in one buffer: split it");
+        { apm_status est = ensure_records(nrec + got, nrec); if (est) return est; }
+        lp_gather_records_kernel<<<(unsigned)ltiles, LP_THREADS, 0, st>>>(s->rec_sparse, s->rawh_sparse, nlines, s->tile_counts,
+                                                                          (uint32_t)nrec, s->rec, s->rawh, s->words[0]);
+        c->launches += 1;
+        nrec += got;
     }
-    lp_gather_records_kernel<<<(unsigned)ltiles, LP_THREADS, 0, st>>>(s->rec_sparse, s->rawh_sparse, nlines, s->tile_counts, s->rec,
-                                                                      s->rawh, s->words[0]);
-    c->launches += 1;
+    if (result) { result->lines = total_lines; result->records = nrec; }
+    if (nrec == 0) { LP_CUDA(cudaStreamSynchronize(st)); return APM_OK; }
+    if (out && cap < nrec) return apm_fail(c, APM_E_CAPACITY, "parse_log: record buffer too small");
+    const uint64_t ltiles_all = (nrec + LP_TILE_ITEMS - 1) / LP_TILE_ITEMS;
+    LP_CUDA(ensure_tiles(ltiles_all));
     // -- Start / Stop pairing: sort by (identity, line), look at the neighbour
     uint64_t* sorted = s->words[0];
     if (nrec > 1) sorted = apm_radix_sort_words(st, s->words[0], s->words[1], nrec, s->sort_hist, s->sort_base, 32, 32, &c->launches);

@@ -40,16 +40,19 @@ def main():
         eng.timer_start()
         t0 = time.perf_counter()
         _, res = eng.parse_log(pin, 1, 0, want_records=a.records)
+        t1 = time.perf_counter()
         tick = eng.feed_parsed()
         ms = eng.timer_stop()
         wall = (time.perf_counter() - t0) * 1e3
+        parse_wall = (t1 - t0) * 1e3
         eng.release_ticks()
         eng.set_latest(1)  # the same text again: start the clock over
         if r and (best is None or ms < best[0]):
-            best = (ms, wall, res, tick)
-    ms, wall, res, tick = best
+            best = (ms, wall, res, tick, parse_wall)
+    ms, wall, res, tick, parse_wall = best
     print(json.dumps({"text_mb": len(text) / 2 ** 20, "lines": int(res.lines), "records": int(res.records), "fed": int(res.fed),
-                      "ms": ms, "wall_ms": wall, "text_gb_per_s": len(text) / ms / 1e6, "lines_per_s": res.lines / ms * 1e3,
+                      "ms": ms, "wall_ms": wall, "parse_ms": parse_wall, "feed_ms": wall - parse_wall,
+                      "parse_only_text_gb_per_s": len(text) / parse_wall / 1e6, "text_gb_per_s": len(text) / ms / 1e6, "lines_per_s": res.lines / ms * 1e3,
                       "fed_tx_per_s": res.fed / ms * 1e3, "ticks": int(tick.ticks)}))
     eng.close()
 
