@@ -111,3 +111,34 @@ def test_empty_and_unterminated_buffers():
     out, _ = tp.readLines(APP, b"[k] 2020-01-07 10:00:02,000 INFO  CommonTiming::Stop Svc elapsed time = 5 ms", feed=False)
     assert out == ["tx|jvm02|Svc||NaN|1578391201995|1578391202000|5|N"]
     sp.engine.close()
+
+
+def test_error_behaviour_of_the_feeder_entry_points():
+    from apmbackend_b200 import _capi
+    from apmbackend_b200._capi import ApmError
+    sp, tp = _mirror()
+    eng = sp.engine
+    with pytest.raises(ApmError, match="file_type"):
+        eng.parse_log(b"x\n", 2, 0)
+    with pytest.raises(ApmError, match="jvm_id"):
+        eng.parse_log(b"x\n", 0, 7)
+    with pytest.raises(ApmError, match="zone rules"):
+        eng.parse_log(b"x\n", 0, 0, tz_rules=[(i, 0) for i in range(9)])
+    with pytest.raises(ApmError, match="outside num_services"):
+        eng.dict_set({"Svc": 64})
+    # a buffer without a CommonTiming line: nothing recognised, nothing to feed
+    recs, res = eng.parse_log(b"plain line\nanother INFO line\n", 0, 0)
+    assert len(recs) == 0 and (res.lines, res.records, res.fed) == (2, 0, 0)
+    assert eng.feed_parsed().ticks == 0
+    # an exit whose service is not in the dictionary is held back and reported
+    recs, res = eng.parse_log(b"[k] 2020-01-07 10:00:02,000 INFO  CommonTiming::Stop Nobody elapsed time = 5 ms\n", 0, 0)
+    assert res.unknown_service == 1 and res.fed == 0 and recs[0]["service_id"] == _capi.NO_SERVICE
+    eng.close()
+
+
+def test_packed_entry_point_rejects_a_negative_base():
+    from apmbackend_b200._capi import ApmError
+    sp, _ = _mirror()
+    with pytest.raises(ApmError, match="base_ts_ms"):
+        sp.engine.process_host_packed(np.zeros(1, np.uint32), np.zeros(1, np.uint32), np.zeros(1, np.uint32), -1)
+    sp.engine.close()
