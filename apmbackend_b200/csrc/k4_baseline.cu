@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(K4_THREADS) baseline_kernel(const BaselinePara
 constexpr int K4T_COLS = 32;
 constexpr int K4T_ROWS = 16;
 constexpr uint32_t K4T_STAGE_BYTES = K4T_COLS * K4T_ROWS * sizeof(double);
-constexpr int K4T_DEEP_STAGES = 24;
+constexpr int K4T_DEEP_STAGES = 12;  // x 2 boxes of 4 KB = the same 96 KB in flight per CTA
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -197,18 +197,21 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
         ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(r0), "r"(smem_u32(bar)), "l"(policy) : "memory");
 }
 
-template <int K4T_STAGES>
+// MULT: 16-slot boxes per stage.  The bandwidth-bound instance (many CTAs per SM) uses one; the instance for a
+// few hundred lists, where one warp per SM is paced by per-chunk overhead, uses two.
+template <int K4T_STAGES, int MULT>
 struct __align__(128) K4TSmem {
-    double buf[K4T_STAGES][K4T_ROWS][K4T_COLS];
+    double buf[K4T_STAGES][K4T_ROWS * MULT][K4T_COLS];
     uint64_t bar[K4T_STAGES];
 };
 
-template <int K4T_STAGES>
+template <int K4T_STAGES, int MULT>
 __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant__ CUtensorMap tmap, const BaselineParams p) {
+    constexpr int ROWS = K4T_ROWS * MULT;
     // dynamic shared memory: the deep-pipeline instance (few columns, long lists) needs more than 48 KB
     // (no static shared memory in this kernel, so the dynamic window starts at offset 0 and is 128-byte aligned)
     extern __shared__ __align__(128) unsigned char k4t_smem_raw[];
-    K4TSmem<K4T_STAGES>& sm = *reinterpret_cast<K4TSmem<K4T_STAGES>*>(k4t_smem_raw);
+    K4TSmem<K4T_STAGES, MULT>& sm = *reinterpret_cast<K4TSmem<K4T_STAGES, MULT>*>(k4t_smem_raw);
     const int lane = threadIdx.x;
     const uint32_t col0 = blockIdx.x * K4T_COLS, col = col0 + lane;
     const bool in_range = col < 3u * p.K;
@@ -222,13 +225,13 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
     uint32_t cnt = 0;
     if (__any_sync(0xffffffffu, full)) {
         const uint64_t policy = l2_evict_first_policy();
-        // oldest first: rows head .. L-1, then 0 .. head-1, in chunks of K4T_ROWS slots
-        const uint32_t nA = (p.L - p.head + K4T_ROWS - 1) / K4T_ROWS, nB = (p.head + K4T_ROWS - 1) / K4T_ROWS;
+        // oldest first: rows head .. L-1, then 0 .. head-1, in chunks of ROWS slots
+        const uint32_t nA = (p.L - p.head + ROWS - 1) / ROWS, nB = (p.head + ROWS - 1) / ROWS;
         const uint32_t n = nA + nB;
-        auto row0_of = [&](uint32_t c) { return c < nA ? p.head + c * K4T_ROWS : (c - nA) * K4T_ROWS; };
+        auto row0_of = [&](uint32_t c) { return c < nA ? p.head + c * ROWS : (c - nA) * ROWS; };
         auto rows_of = [&](uint32_t c) {
             const uint32_t r0 = row0_of(c), end = c < nA ? p.L : p.head;
-            return end - r0 < (uint32_t)K4T_ROWS ? end - r0 : (uint32_t)K4T_ROWS;
+            return end - r0 < (uint32_t)ROWS ? end - r0 : (uint32_t)ROWS;
         };
         if (lane == 0) {
 #pragma unroll
@@ -239,46 +242,48 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
         __syncwarp();
         if (lane == 0) {
             for (uint32_t c = 0; c < n && c < (uint32_t)K4T_STAGES; ++c) {
-                mbar_expect_tx(&sm.bar[c], K4T_STAGE_BYTES);  // rows past the end are zero-filled but still counted
-                tma_load_2d(&sm.buf[c][0][0], &tmap, (int)col0, (int)row0_of(c), &sm.bar[c], policy);
+                mbar_expect_tx(&sm.bar[c], K4T_STAGE_BYTES * MULT);  // rows past the end are zero-filled but still counted
+#pragma unroll
+                for (int m = 0; m < MULT; ++m)
+                    tma_load_2d(&sm.buf[c][m * (ROWS / MULT)][0], &tmap, (int)col0, (int)row0_of(c) + m * (ROWS / MULT), &sm.bar[c], policy);
             }
         }
         // Software pipeline over the chunks: the values of chunk c + 1 are pulled from shared memory
         // into registers before the dependent adds of chunk c run, so with one warp per SM (few
         // lists) the walk is paced by the add chain, not by barrier and shared-memory latency.
-        double v[K4T_ROWS], vn[K4T_ROWS];
+        double v[ROWS], vn[ROWS];
         mbar_wait(&sm.bar[0], 0);
 #pragma unroll
-        for (int r = 0; r < K4T_ROWS; ++r) v[r] = sm.buf[0][r][lane];
+        for (int r = 0; r < ROWS; ++r) v[r] = sm.buf[0][r][lane];
         for (uint32_t c = 0; c < n; ++c) {
             const uint32_t s = c % K4T_STAGES;
             if (c + 1 < n) {
                 const uint32_t s1 = (c + 1) % K4T_STAGES, parity1 = ((c + 1) / K4T_STAGES) & 1u;
                 mbar_wait(&sm.bar[s1], parity1);
 #pragma unroll
-                for (int r = 0; r < K4T_ROWS; ++r) vn[r] = sm.buf[s1][r][lane];
+                for (int r = 0; r < ROWS; ++r) vn[r] = sm.buf[s1][r][lane];
             }
             const uint32_t rows = rows_of(c);
-            if (rows == (uint32_t)K4T_ROWS) {
+            if (rows == (uint32_t)ROWS) {
                 if (full) {
                     // Sixteen bare adds, validity checked once on the result: a NaN entry (a tick
                     // the key had no data for) poisons t, and only then is the chunk redone entry
                     // by entry from the saved sum.  Without a NaN the adds are the same sequence.
                     double t = sum;
 #pragma unroll
-                    for (int r = 0; r < K4T_ROWS; ++r) t = __dadd_rn(t, v[r]);
+                    for (int r = 0; r < ROWS; ++r) t = __dadd_rn(t, v[r]);
                     if (t == t) {
                         sum = t;
-                        cnt += K4T_ROWS;
+                        cnt += ROWS;
                     } else {
 #pragma unroll
-                        for (int r = 0; r < K4T_ROWS; ++r) accumulate(v[r], sum, cnt);
+                        for (int r = 0; r < ROWS; ++r) accumulate(v[r], sum, cnt);
                     }
                 }
-                last = v[K4T_ROWS - 1];
+                last = v[ROWS - 1];
             } else {
 #pragma unroll
-                for (int r = 0; r < K4T_ROWS; ++r)
+                for (int r = 0; r < ROWS; ++r)
                     if ((uint32_t)r < rows) {
                         if (full) accumulate(v[r], sum, cnt);
                         last = v[r];
@@ -286,11 +291,13 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
             }
             __syncwarp();  // every lane has consumed chunk c from registers: its stage may be overwritten
             if (lane == 0 && c + K4T_STAGES < n) {
-                mbar_expect_tx(&sm.bar[s], K4T_STAGE_BYTES);
-                tma_load_2d(&sm.buf[s][0][0], &tmap, (int)col0, (int)row0_of(c + K4T_STAGES), &sm.bar[s], policy);
+                mbar_expect_tx(&sm.bar[s], K4T_STAGE_BYTES * MULT);
+#pragma unroll
+                for (int m = 0; m < MULT; ++m)
+                    tma_load_2d(&sm.buf[s][m * (ROWS / MULT)][0], &tmap, (int)col0, (int)row0_of(c + K4T_STAGES) + m * (ROWS / MULT), &sm.bar[s], policy);
             }
 #pragma unroll
-            for (int r = 0; r < K4T_ROWS; ++r) v[r] = vn[r];
+            for (int r = 0; r < ROWS; ++r) v[r] = vn[r];
         }
     }
     if (!in_range) return;
@@ -683,8 +690,8 @@ apm_status apm_baseline_make_tmaps(apm_ctx* c) {
                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return apm_fail(c, APM_E_DEVICE, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
     }
-    CUDA_TRY(c, cudaFuncSetAttribute(baseline_tma_kernel<K4T_DEEP_STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)sizeof(K4TSmem<K4T_DEEP_STAGES>) + 128));
+    CUDA_TRY(c, cudaFuncSetAttribute(baseline_tma_kernel<K4T_DEEP_STAGES, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sizeof(K4TSmem<K4T_DEEP_STAGES, 2>) + 128));
     c->ring_tmap_ok = true;
     return APM_OK;
 }
@@ -716,13 +723,13 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
         // Below two CTAs per SM the deep instance (24 stages, 96 KB in flight per CTA) is used.
         int stages = c->k4_stages;
         if (stages == 0) stages = g <= 2 * APM_NUM_SMS ? K4T_DEEP_STAGES : 4;
-#define APM_K4T_LAUNCH(NS) baseline_tma_kernel<NS><<<g, 32, sizeof(K4TSmem<NS>) + 128, st>>>(c->ring_tmap[l], p)
+#define APM_K4T_LAUNCH(NS, M) baseline_tma_kernel<NS, M><<<g, 32, sizeof(K4TSmem<NS, M>) + 128, st>>>(c->ring_tmap[l], p)
         switch (stages) {
-            case 2: APM_K4T_LAUNCH(2); break;
-            case 3: APM_K4T_LAUNCH(3); break;
-            case 6: APM_K4T_LAUNCH(6); break;
-            case K4T_DEEP_STAGES: APM_K4T_LAUNCH(K4T_DEEP_STAGES); break;
-            default: APM_K4T_LAUNCH(4); break;
+            case 2: APM_K4T_LAUNCH(2, 1); break;
+            case 3: APM_K4T_LAUNCH(3, 1); break;
+            case 6: APM_K4T_LAUNCH(6, 1); break;
+            case K4T_DEEP_STAGES: APM_K4T_LAUNCH(K4T_DEEP_STAGES, 2); break;
+            default: APM_K4T_LAUNCH(4, 1); break;
         }
 #undef APM_K4T_LAUNCH
     } else {
