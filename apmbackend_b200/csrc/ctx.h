@@ -135,7 +135,7 @@ struct apm_ctx {
     apm_counters counters;
     uint64_t launches = 0;
     uint32_t k1_tiles_per_cta = 3;  // tuning knob (APM_K1_TPC)
-    int k4_stages = 0;              // APM_K4_STAGES: bulk-tensor loads in flight per CTA (2, 3, 4, 6, or 12 = the two-box instance for few lists); 0 = by grid size
+    int k4_stages = 0;              // APM_K4_STAGES: bulk-tensor loads in flight per CTA (2, 3, 4, 6, or 8 = the three-box instance for few lists); 0 = by grid size
     bool k4_force_ldg = false;      // APM_K4_LDG=1: register-pipelined loads instead of TMA (A/B measurements)
 
     // log feeder (k6_logparse.cu), created by the first apm_dict_set / apm_parse_log_host

@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(K4_THREADS) baseline_kernel(const BaselinePara
 constexpr int K4T_COLS = 32;
 constexpr int K4T_ROWS = 16;
 constexpr uint32_t K4T_STAGE_BYTES = K4T_COLS * K4T_ROWS * sizeof(double);
-constexpr int K4T_DEEP_STAGES = 12;  // x 2 boxes of 4 KB = the same 96 KB in flight per CTA
+constexpr int K4T_DEEP_STAGES = 8;   // x 3 boxes of 4 KB = the same 96 KB in flight per CTA
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -198,7 +198,7 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
 }
 
 // MULT: 16-slot boxes per stage.  The bandwidth-bound instance (many CTAs per SM) uses one; the instance for a
-// few hundred lists, where one warp per SM is paced by per-chunk overhead, uses two.
+// few hundred lists, where one warp per SM is paced by per-chunk overhead, uses three.
 template <int K4T_STAGES, int MULT>
 struct __align__(128) K4TSmem {
     double buf[K4T_STAGES][K4T_ROWS * MULT][K4T_COLS];
@@ -690,8 +690,8 @@ apm_status apm_baseline_make_tmaps(apm_ctx* c) {
                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return apm_fail(c, APM_E_DEVICE, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
     }
-    CUDA_TRY(c, cudaFuncSetAttribute(baseline_tma_kernel<K4T_DEEP_STAGES, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)sizeof(K4TSmem<K4T_DEEP_STAGES, 2>) + 128));
+    CUDA_TRY(c, cudaFuncSetAttribute(baseline_tma_kernel<K4T_DEEP_STAGES, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sizeof(K4TSmem<K4T_DEEP_STAGES, 3>) + 128));
     c->ring_tmap_ok = true;
     return APM_OK;
 }
@@ -728,7 +728,7 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
             case 2: APM_K4T_LAUNCH(2, 1); break;
             case 3: APM_K4T_LAUNCH(3, 1); break;
             case 6: APM_K4T_LAUNCH(6, 1); break;
-            case K4T_DEEP_STAGES: APM_K4T_LAUNCH(K4T_DEEP_STAGES, 2); break;
+            case K4T_DEEP_STAGES: APM_K4T_LAUNCH(K4T_DEEP_STAGES, 3); break;
             default: APM_K4T_LAUNCH(4, 1); break;
         }
 #undef APM_K4T_LAUNCH
