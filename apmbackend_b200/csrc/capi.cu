@@ -393,7 +393,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFree(c->pk[0]); cudaFree(c->pk[1]);
     cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
     free_columns_device(&c->dev[0]); free_columns_device(&c->dev[1]);
-    cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
+    cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->d_alert_blocks); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
     for (int l = 0; l < APM_MAX_LAGS; ++l) { cudaFree(c->ring[l]); cudaFree(c->ring_len[l]); cudaFree(c->ring_next[l]);
         cudaFree(c->inc_sum[l]); cudaFree(c->inc_comp[l]); cudaFree(c->inc_cnt[l]); cudaFree(c->inc_nz[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
     cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->d_gather);
@@ -534,6 +534,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
             if (cfg->max_alerts_per_tick == 0) { c->err = "max_alerts_per_tick must be > 0 with APM_F_ALERTS"; return fail(APM_E_INVALID); }
             TRY_CREATE(dalloc(&c->d_alerts, (size_t)cfg->out_ticks * cfg->max_alerts_per_tick));
             TRY_CREATE(dalloc(&c->d_alert_count, (size_t)cfg->out_ticks));
+            TRY_CREATE(dalloc(&c->d_alert_blocks, (size_t)K * cfg->num_lags / 256 + 2));
             TRY_CREATE(cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * cfg->out_ticks, c->s_main));
         }
         c->ring_pitch = (3 * K + 31) & ~(size_t)31;

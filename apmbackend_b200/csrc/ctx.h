@@ -86,6 +86,7 @@ struct apm_ctx {
     apm_fs_record* d_fs = nullptr;       // [out_ticks][num_lags][K]
     apm_fs_record* d_alerts = nullptr;   // [out_ticks][max_alerts_per_tick]
     unsigned int* d_alert_count = nullptr;  // [out_ticks]
+    uint32_t* d_alert_blocks = nullptr;     // [ceil(K * num_lags / 256)] hits per CTA of the ordered compaction
     double* zin[2] = {nullptr, nullptr};     // double-buffered [4][K]: tpm', val0, val1, val2 (quantised)
     uint8_t* emit[2] = {nullptr, nullptr};   // [K] key emitted a StatEntry this tick (snapshot of `seen`)
     // optional: fs records stream to a caller-owned pinned buffer as each tick's baseline finishes

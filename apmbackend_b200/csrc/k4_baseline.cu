@@ -626,46 +626,66 @@ __global__ void __launch_bounds__(256) alert_counter_kernel(const AlertParams p)
 }
 
 // Copies the fs records that carry a signal into the tick's compact alert block, in the order of the fs
-// block itself ((lag, key)-ascending): one CTA walks the tick's records 1024 at a time and ranks the hits with
-// a block scan, so the block needs no sorting afterwards and no counter has to be zeroed beforehand.
-constexpr int CA_THREADS = 1024;
+// block itself ((lag, key)-ascending), so the block needs no sorting afterwards: every CTA counts the hits among
+// its 256 records (pass 1), then adds up the counts of the CTAs before it, ranks its hits with a ballot and copies
+// them (pass 2).  No counter has to be zeroed beforehand; the last CTA stores the total.
+constexpr int CA_THREADS = 256;
+
+__device__ __forceinline__ bool ca_hit(const apm_fs_record* fs, uint32_t i, uint32_t n, int by_trigger) {
+    if (i >= n) return false;
+    const apm_fs_record* r = fs + i;
+    if (!(r->flags & 1)) return false;
+    return by_trigger ? (r->flags & 2) != 0 : (r->signal[0] | r->signal[1] | r->signal[2]) != 0;
+}
+
+__global__ void __launch_bounds__(CA_THREADS) count_alerts_kernel(const apm_fs_record* __restrict__ fs, uint32_t n, int by_trigger,
+                                                                  uint32_t* __restrict__ block_counts) {
+    const uint32_t c = __syncthreads_count(ca_hit(fs, blockIdx.x * CA_THREADS + threadIdx.x, n, by_trigger));
+    if (threadIdx.x == 0) block_counts[blockIdx.x] = c;
+}
+
 __global__ void __launch_bounds__(CA_THREADS) compact_alerts_kernel(const apm_fs_record* __restrict__ fs, uint32_t n,
                                                                     apm_fs_record* __restrict__ alerts,
-                                                                    unsigned int* __restrict__ count, uint32_t cap, int by_trigger) {
+                                                                    unsigned int* __restrict__ count, uint32_t cap, int by_trigger,
+                                                                    const uint32_t* __restrict__ block_counts) {
     __shared__ uint32_t s_warp[CA_THREADS / 32];
     __shared__ uint32_t s_base;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    if (tid == 0) s_base = 0;
+    // hits in the CTAs before this one
+    uint32_t part = 0;
+    for (uint32_t j = tid; j < blockIdx.x; j += CA_THREADS) part += block_counts[j];
+    part = __reduce_add_sync(0xffffffffu, part);
+    if (lane == 0) s_warp[w] = part;
     __syncthreads();
-    for (uint32_t i0 = 0; i0 < n; i0 += CA_THREADS) {
-        const uint32_t i = i0 + tid;
-        bool hit = false;
-        if (i < n) {
-            const apm_fs_record* r = fs + i;
-            if (r->flags & 1) hit = by_trigger ? (r->flags & 2) != 0 : (r->signal[0] | r->signal[1] | r->signal[2]) != 0;
-        }
-        const uint32_t bal = __ballot_sync(0xffffffffu, hit);
-        if (lane == 0) s_warp[w] = __popc(bal);
-        __syncthreads();
-        uint32_t before = 0, total = 0;
+    if (tid == 0) {
+        uint32_t t = 0;
 #pragma unroll
-        for (int j = 0; j < CA_THREADS / 32; ++j) {
-            const uint32_t c = s_warp[j];
-            if (j < w) before += c;
-            total += c;
-        }
-        const uint32_t k = s_base + before + __popc(bal & ((1u << lane) - 1u));
-        if (hit && k < cap) {
-            const uint4* src = reinterpret_cast<const uint4*>(fs + i);
-            uint4* dst = reinterpret_cast<uint4*>(alerts + k);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) dst[j] = src[j];
-        }
-        __syncthreads();
-        if (tid == 0) s_base += total;
-        __syncthreads();
+        for (int j = 0; j < CA_THREADS / 32; ++j) t += s_warp[j];
+        s_base = t;
     }
-    if (tid == 0) *count = s_base;
+    __syncthreads();
+    const uint32_t base = s_base;
+    __syncthreads();
+    const uint32_t i = blockIdx.x * CA_THREADS + tid;
+    const bool hit = ca_hit(fs, i, n, by_trigger);
+    const uint32_t bal = __ballot_sync(0xffffffffu, hit);
+    if (lane == 0) s_warp[w] = __popc(bal);
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int j = 0; j < CA_THREADS / 32; ++j) {
+        const uint32_t c = s_warp[j];
+        if (j < w) before += c;
+        total += c;
+    }
+    const uint32_t k = base + before + __popc(bal & ((1u << lane) - 1u));
+    if (hit && k < cap) {
+        const uint4* src = reinterpret_cast<const uint4*>(fs + i);
+        uint4* dst = reinterpret_cast<uint4*>(alerts + k);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dst[j] = src[j];
+    }
+    if (blockIdx.x == gridDim.x - 1 && tid == 0) *count = base + total;
 }
 
 }  // namespace
@@ -775,10 +795,13 @@ apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t aler
     ProfScope prof_scope_(c, APM_PG_ALERTS, st);
     if (!c->d_alerts || !c->d_fs) return APM_OK;
     const uint32_t n = c->K * (uint32_t)c->cfg.num_lags;
-    compact_alerts_kernel<<<1, CA_THREADS, 0, st>>>(
-        c->d_fs + (size_t)fs_slot * c->cfg.num_lags * c->K, n,
-        c->d_alerts + (size_t)alert_slot * c->cfg.max_alerts_per_tick, c->d_alert_count + alert_slot,
-        c->cfg.max_alerts_per_tick, c->alert_rules.enabled);
+    const unsigned g = (n + CA_THREADS - 1) / CA_THREADS;
+    const apm_fs_record* fs = c->d_fs + (size_t)fs_slot * c->cfg.num_lags * c->K;
+    count_alerts_kernel<<<g, CA_THREADS, 0, st>>>(fs, n, c->alert_rules.enabled, c->d_alert_blocks);
+    compact_alerts_kernel<<<g, CA_THREADS, 0, st>>>(fs, n, c->d_alerts + (size_t)alert_slot * c->cfg.max_alerts_per_tick,
+                                                    c->d_alert_count + alert_slot, c->cfg.max_alerts_per_tick, c->alert_rules.enabled,
+                                                    c->d_alert_blocks);
+    c->launches += 2;
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;
