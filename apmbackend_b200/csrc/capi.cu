@@ -180,7 +180,7 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
     }
     if (with_pct(c)) {
         // sort the window's value logs that grew since their last sort; their lengths come from the chunk's
-        // segment table (apm_launch_seg_hist), not from the device, so nothing here waits for the GPU
+        // segment table (the chunk's pre-pass), not from the device, so nothing here waits for the GPU
         for (int i = 0; i < w.n; ++i) {
             const int slot = w.slot[i];
             const uint64_t count = c->host_count[slot];
@@ -219,37 +219,32 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
     return APM_OK;
 }
 
-// What segment i of the current chunk appends to the value logs, by bucket age under the latestBucket in
-// force (c->latest): keeps host_count equal to the device's SlotMeta.count.
-void apply_seg_counts(apm_ctx* c, unsigned int i) {
-    const uint32_t* row = c->h_seg_counts + (size_t)i * (c->keep + 1);
+// What segment i of a chunk appends to the value logs, by bucket age under the latestBucket in force
+// (c->latest): keeps host_count equal to the device's SlotMeta.count.
+void apply_seg_counts(apm_ctx* c, const apm_ctx::PrePass& pp, unsigned int i) {
+    const uint32_t* row = pp.h_seg_counts + (size_t)i * (c->keep + 1);
     for (int age = 0; age <= c->keep; ++age)
         if (row[age]) c->host_count[(c->latest - age) % c->S] += row[age];
 }
 
-apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n, apm_tick_result* res) {
-    unsigned int nt = 0;
-    // The baseline of the last tick is normally launched behind the next segment's ingest kernel.  At a chunk
-    // boundary the host is about to block on the tick marks and the segment table: launch it now (it sits behind
-    // the previous chunk's tail segment), or the baseline stream idles for those round trips.
-    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
-    apm_status st = apm_launch_find_ticks(c, d.end_ts_ms, n, &nt);
-    if (st) return st;
+// latestBucket after a chunk whose pre-pass has finished: the label of its last tick
+int64_t latest_after(const apm_ctx::PrePass& pp) { return pp.nt ? pp.h_ticks[pp.nt - 1].label : pp.latest0; }
+
+// The ticks of one chunk, queued without waiting for the device: everything the loop needs from the data (where the
+// ticks are, what each segment appends to each bucket) is in the chunk's finished pre-pass.
+apm_status run_chunk(apm_ctx* c, const apm_tx_columns& d, uint64_t n, const apm_ctx::PrePass& pp, apm_tick_result* res) {
+    const unsigned int nt = pp.nt;
+    if (pp.latest0 != c->latest) return apm_fail(c, APM_E_STATE, "internal: a chunk's pre-pass was made for another latestBucket");
     const bool keep_any = c->cfg.flags & (APM_F_KEEP_STATS | APM_F_KEEP_FS | APM_F_ALERTS);
     if (keep_any && c->ticks_buffered + nt > c->cfg.out_ticks)
         return apm_fail(c, APM_E_WOULDBLOCK, "chunk holds more ticks than the output ring has room for: fetch results or raise out_ticks");
-    std::sort(c->h_ticks, c->h_ticks + nt, [](const TickMark& a, const TickMark& b) { return a.pos < b.pos; });
     const bool logs = with_pct(c);
-    if (logs) {
-        st = apm_launch_seg_hist(c, d, n, nt);
-        if (st) return st;
-        if (c->seg_max > c->known_max_value) c->known_max_value = c->seg_max;
-    }
-    auto account = [&](unsigned int i) { if (logs) apply_seg_counts(c, i); };
+    if (logs && pp.seg_max > c->known_max_value) c->known_max_value = pp.seg_max;
+    apm_status st;
     uint64_t pos = 0;
     for (unsigned int i = 0; i < nt; ++i) {
-        const TickMark tm = c->h_ticks[i];
-        account(i);
+        const TickMark tm = pp.h_ticks[i];
+        if (logs) apply_seg_counts(c, pp, i);
         st = apm_launch_reduce(c, d, pos, tm.pos);  // everything that arrived before the trigger
         if (st) return st;
         st = apm_pt_append(c, d, pos, tm.pos);
@@ -259,7 +254,7 @@ apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n,
         if (st) return st;
         pos = tm.pos;
     }
-    account(nt);
+    if (logs) apply_seg_counts(c, pp, nt);
     st = apm_launch_reduce(c, d, pos, n);
     if (st) return st;
     st = apm_pt_append(c, d, pos, n);
@@ -267,6 +262,19 @@ apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n,
     c->pt_seq += n - pos;
     if (res) res->ticks += nt;
     return APM_OK;
+}
+
+// one chunk, pre-pass and ticks on the ingest stream (callers that have a single chunk)
+apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n, apm_tick_result* res) {
+    // The baseline of the last tick is normally launched behind the next segment's ingest kernel.  The host is
+    // about to block on the tick marks and the segment table: launch it now, or the baseline stream idles.
+    { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
+    apm_ctx::PrePass& pp = c->pre[0];
+    apm_status st = apm_prepass_begin(c, pp, d, n, c->latest, c->s_main);
+    if (st) return st;
+    st = apm_prepass_finish(c, pp, d, n, c->s_main);
+    if (st) return st;
+    return run_chunk(c, d, n, pp, res);
 }
 
 // Copies the valid records of the buffered ticks to the caller, tick-major / key-ascending.
@@ -321,7 +329,9 @@ apm_status process_host_chunks(apm_ctx* c, uint64_t n, apm_tick_result* res, Cop
         static int top_div = 0;
         if (!top_div) { const char* e = getenv("APM_CHUNK_TOP_DIV"); top_div = e ? atoi(e) : 4; if (top_div < 1) top_div = 1; }
         const uint64_t top = n > B ? std::max<uint64_t>(B / top_div, 1) : B;
-        uint64_t off = 0, len = n > B ? std::max<uint64_t>(B / 16, 1) : B;
+        static int first_div = 0;
+        if (!first_div) { const char* e = getenv("APM_CHUNK_FIRST_DIV"); first_div = e ? atoi(e) : 16; if (first_div < 1) first_div = 1; }
+        uint64_t off = 0, len = n > B ? std::max<uint64_t>(B / first_div, 1) : B;
         while (off < n) {
             const uint64_t m = std::min<uint64_t>(n - off, len);
             chunks.emplace_back(off, m);
@@ -338,15 +348,35 @@ apm_status process_host_chunks(apm_ctx* c, uint64_t n, apm_tick_result* res, Cop
         CUDA_TRY(c, cudaEventRecord(c->ev_copied[b], c->s_copy));
         return APM_OK;
     };
-    if (nchunks) { apm_status st = copy(0); if (st) return st; }
+    if (nchunks == 0) return finish_result(c, before, res);
+    // Pipeline: while the ticks of chunk i are queued and run (ingest stream), chunk i + 1 is copied (copy stream)
+    // and its pre-pass - tick finder, segment table, their host round trips - runs on the pre-pass stream.
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_pre));
+    apm_status st = copy(0);
+    if (st) return st;
+    CUDA_TRY(c, cudaStreamWaitEvent(c->s_pre, c->ev_copied[0], 0));
+    st = apm_prepass_begin(c, c->pre[0], c->dev[0], chunks[0].second, c->latest, c->s_pre);
+    if (st) return st;
+    if (nchunks > 1) { st = copy(1); if (st) return st; }
+    st = apm_prepass_finish(c, c->pre[0], c->dev[0], chunks[0].second, c->s_pre);
+    if (st) return st;
     for (uint64_t ci = 0; ci < nchunks; ++ci) {
         const int b = (int)(ci & 1);
-        // the next chunk's copy overlaps this chunk's kernels
-        if (ci + 1 < nchunks) { apm_status st = copy(ci + 1); if (st) return st; }
+        const bool more = ci + 1 < nchunks;
+        if (more) {  // the next chunk's tick finder starts as soon as its copy has landed
+            CUDA_TRY(c, cudaStreamWaitEvent(c->s_pre, c->ev_copied[b ^ 1], 0));
+            st = apm_prepass_begin(c, c->pre[b ^ 1], c->dev[b ^ 1], chunks[ci + 1].second, latest_after(c->pre[b]), c->s_pre);
+            if (st) return st;
+        }
         CUDA_TRY(c, cudaStreamWaitEvent(c->s_main, c->ev_copied[b], 0));
-        apm_status st = process_chunk_device(c, c->dev[b], chunks[ci].second, res);
+        st = run_chunk(c, c->dev[b], chunks[ci].second, c->pre[b], res);
         if (st) return st;
         CUDA_TRY(c, cudaEventRecord(c->ev_consumed[b], c->s_main));
+        if (ci + 2 < nchunks) { st = copy(ci + 2); if (st) return st; }  // into the buffer this chunk has just released
+        if (more) {
+            st = apm_prepass_finish(c, c->pre[b ^ 1], c->dev[b ^ 1], chunks[ci + 1].second, c->s_pre);
+            if (st) return st;
+        }
     }
     return finish_result(c, before, res);
 }
@@ -383,12 +413,17 @@ void apm_ctx_destroy(apm_ctx* c) {
     c->pending.valid = false;
     if (c->s_base) cudaStreamSynchronize(c->s_base);
     if (c->s_copy) cudaStreamSynchronize(c->s_copy);
+    if (c->s_pre) cudaStreamSynchronize(c->s_pre);
     cudaFree(c->acc_raw); cudaFree(c->seen); cudaFree(c->slot_meta);
     for (int i = 0; i <= c->S && i <= APM_MAX_SLOTS; ++i) cudaFree(c->log_buf[i]);
     cudaFree(c->d_log_ptrs); cudaFree(c->sort_hist); cudaFree(c->sort_base); cudaFree(c->sort_scratch);
-    cudaFree(c->tf_tile_max); cudaFree(c->tf_tile_prefix); cudaFree(c->d_ticks); cudaFree(c->d_nticks);
-    cudaFreeHost(c->h_ticks); cudaFreeHost(c->h_nticks);
-    cudaFree(c->d_seg_counts); cudaFreeHost(c->h_seg_counts);
+    for (int i = 0; i < 2; ++i) {
+        apm_ctx::PrePass& pp = c->pre[i];
+        cudaFree(pp.tf_tile_max); cudaFree(pp.tf_tile_prefix); cudaFree(pp.d_ticks); cudaFree(pp.d_nticks);
+        cudaFreeHost(pp.h_ticks); cudaFreeHost(pp.h_nticks);
+        cudaFree(pp.d_seg_counts); cudaFreeHost(pp.h_seg_counts);
+        if (pp.ev) cudaEventDestroy(pp.ev);
+    }
     apm_lp_destroy(c);
     cudaFree(c->pk[0]); cudaFree(c->pk[1]);
     cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
@@ -407,6 +442,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     if (c->s_base) cudaStreamDestroy(c->s_base);
     if (c->s_main) cudaStreamDestroy(c->s_main);
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
+    if (c->s_pre) cudaStreamDestroy(c->s_pre);
     apm_comm_destroy_internal(c);
     for (auto& sp : c->prof_spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : c->prof_pool) cudaEventDestroy(e);
@@ -449,6 +485,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
         TRY_CREATE(cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_hi));
         TRY_CREATE(cudaStreamCreateWithPriority(&c->s_copy, cudaStreamNonBlocking, prio_hi));
         TRY_CREATE(cudaStreamCreateWithPriority(&c->s_base, cudaStreamNonBlocking, prio_lo));
+        TRY_CREATE(cudaStreamCreateWithPriority(&c->s_pre, cudaStreamNonBlocking, prio_hi));
     }
     for (int i = 0; i < 4; ++i) {
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_stats[i], cudaEventDisableTiming));
@@ -509,18 +546,20 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     }
     TRY_CREATE(cudaMemcpyAsync(c->d_log_ptrs, c->log_buf, sizeof(uint64_t*) * APM_MAX_SLOTS, cudaMemcpyHostToDevice, c->s_main));
     c->tf_tiles_cap = (cfg->max_batch + 4095) / 4096;
-    TRY_CREATE(dalloc(&c->tf_tile_max, (size_t)c->tf_tiles_cap));
-    TRY_CREATE(dalloc(&c->tf_tile_prefix, (size_t)c->tf_tiles_cap));
-    TRY_CREATE(dalloc(&c->d_ticks, (size_t)c->max_ticks_per_chunk));
-    TRY_CREATE(dalloc(&c->d_nticks, (size_t)1));
-    TRY_CREATE(cudaMallocHost((void**)&c->h_ticks, sizeof(TickMark) * c->max_ticks_per_chunk));
-    TRY_CREATE(cudaMallocHost((void**)&c->h_nticks, sizeof(unsigned int)));
-    {
+    for (int i = 0; i < 2; ++i) {
+        apm_ctx::PrePass& pp = c->pre[i];
         const size_t cells = (size_t)(c->max_ticks_per_chunk + 1) * (c->keep + 1) + 1;
-        TRY_CREATE(dalloc(&c->d_seg_counts, cells));
-        TRY_CREATE(cudaMallocHost((void**)&c->h_seg_counts, sizeof(uint32_t) * cells));
-        for (int s = 0; s < APM_MAX_SLOTS; ++s) c->host_count[s] = c->host_sorted[s] = 0;
+        TRY_CREATE(dalloc(&pp.tf_tile_max, (size_t)c->tf_tiles_cap));
+        TRY_CREATE(dalloc(&pp.tf_tile_prefix, (size_t)c->tf_tiles_cap));
+        TRY_CREATE(dalloc(&pp.d_ticks, (size_t)c->max_ticks_per_chunk));
+        TRY_CREATE(dalloc(&pp.d_nticks, (size_t)1));
+        TRY_CREATE(cudaMallocHost((void**)&pp.h_ticks, sizeof(TickMark) * c->max_ticks_per_chunk));
+        TRY_CREATE(cudaMallocHost((void**)&pp.h_nticks, sizeof(unsigned int)));
+        TRY_CREATE(dalloc(&pp.d_seg_counts, cells));
+        TRY_CREATE(cudaMallocHost((void**)&pp.h_seg_counts, sizeof(uint32_t) * cells));
+        TRY_CREATE(cudaEventCreateWithFlags(&pp.ev, cudaEventDisableTiming));
     }
+    for (int s = 0; s < APM_MAX_SLOTS; ++s) c->host_count[s] = c->host_sorted[s] = 0;
     for (int i = 0; i < 2; ++i) {
         TRY_CREATE(dalloc(&c->zin[i], 4 * K));
         TRY_CREATE(dalloc(&c->emit[i], K));
@@ -615,10 +654,10 @@ apm_status apm_ingest_commit(apm_ctx* c, uint64_t n) {
     c->counters.h2d_bytes += n * 20;
     apm_status st;
     if (with_pct(c)) {  // one segment under the current latestBucket
-        st = apm_launch_seg_hist(c, d, n, 0);
+        st = apm_prepass_segment(c, c->pre[0], d, n, c->latest, c->s_main);
         if (st) return st;
-        if (c->seg_max > c->known_max_value) c->known_max_value = c->seg_max;
-        apply_seg_counts(c, 0);
+        if (c->pre[0].seg_max > c->known_max_value) c->known_max_value = c->pre[0].seg_max;
+        apply_seg_counts(c, c->pre[0], 0);
     }
     st = apm_launch_reduce(c, d, 0, n);
     if (st) return st;
@@ -645,13 +684,42 @@ apm_status apm_process_device(apm_ctx* c, const apm_tx_columns* cols, uint64_t n
     if (!c || !cols) return APM_E_INVALID;
     if (res) memset(res, 0, sizeof *res);
     const apm_counters before = c->counters;
-    uint64_t off = 0;
-    while (off < n) {
-        const uint64_t m = std::min<uint64_t>(n - off, c->cfg.max_batch);
-        apm_tx_columns d = {cols->service_id + off, cols->jvm_id + off, cols->end_ts_ms + off, cols->elapsed_ms + off};
-        apm_status st = process_chunk_device(c, d, m, res);
+    const uint64_t B = c->cfg.max_batch;
+    if (n <= B) {
+        if (n) { apm_status st = process_chunk_device(c, *cols, n, res); if (st) return st; }
+        return finish_result(c, before, res);
+    }
+    // several chunks: the pre-pass of chunk i + 1 runs on its own stream while the ticks of chunk i are queued
+    auto chunk = [&](uint64_t ci, uint64_t* m) {
+        const uint64_t off = ci * B;
+        *m = std::min<uint64_t>(n - off, B);
+        return apm_tx_columns{cols->service_id + off, cols->jvm_id + off, cols->end_ts_ms + off, cols->elapsed_ms + off};
+    };
+    const uint64_t nchunks = (n + B - 1) / B;
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_pre));
+    uint64_t m = 0, m1 = 0;
+    apm_tx_columns d = chunk(0, &m);
+    apm_status st = apm_prepass_begin(c, c->pre[0], d, m, c->latest, c->s_pre);
+    if (st) return st;
+    st = apm_prepass_finish(c, c->pre[0], d, m, c->s_pre);
+    if (st) return st;
+    for (uint64_t ci = 0; ci < nchunks; ++ci) {
+        const int b = (int)(ci & 1);
+        const bool more = ci + 1 < nchunks;
+        apm_tx_columns d1 = d;
+        if (more) {
+            d1 = chunk(ci + 1, &m1);
+            st = apm_prepass_begin(c, c->pre[b ^ 1], d1, m1, latest_after(c->pre[b]), c->s_pre);
+            if (st) return st;
+        }
+        st = run_chunk(c, d, m, c->pre[b], res);
         if (st) return st;
-        off += m;
+        if (more) {
+            st = apm_prepass_finish(c, c->pre[b ^ 1], d1, m1, c->s_pre);
+            if (st) return st;
+            d = d1;
+            m = m1;
+        }
     }
     return finish_result(c, before, res);
 }

@@ -57,20 +57,29 @@ struct apm_ctx {
     size_t sort_scratch_bytes = 0;
     bool sort_legacy = false;               // APM_SORT_LEGACY=1: three-kernel-per-pass sort (A/B measurements)
 
-    // --- tick finder scratch
-    long long* tf_tile_max = nullptr;
-    long long* tf_tile_prefix = nullptr;
+    // --- per-chunk pre-pass (tick finder + segment table).  Two sets: while the ticks of chunk i are being queued,
+    //     the pre-pass of chunk i + 1 runs on its own stream (s_pre), so a chunk boundary costs the ingest / sort
+    //     chain neither the pre-pass kernels nor the host round trips.
+    struct PrePass {
+        long long* tf_tile_max = nullptr;
+        long long* tf_tile_prefix = nullptr;
+        TickMark* d_ticks = nullptr;
+        unsigned int* d_nticks = nullptr;
+        TickMark* h_ticks = nullptr;        // pinned; sorted by position once the pre-pass has finished
+        unsigned int* h_nticks = nullptr;   // pinned
+        // log entries per (segment, bucket age): from it the host knows the exact length of every bucket's value
+        // log, so the tick loop never waits for the device
+        uint32_t* d_seg_counts = nullptr;   // [(max_ticks_per_chunk + 1)][keep + 1] + 1 (largest duration of the chunk)
+        uint32_t* h_seg_counts = nullptr;   // pinned
+        uint32_t seg_max = 0;
+        unsigned int nt = 0;                // ticks inside the chunk
+        int64_t latest0 = 0;                // latestBucket before the chunk
+        cudaEvent_t ev = nullptr;           // the tick marks are on the host
+    };
+    PrePass pre[2];
+    cudaStream_t s_pre = nullptr;
     uint64_t tf_tiles_cap = 0;
-    TickMark* d_ticks = nullptr;
-    unsigned int* d_nticks = nullptr;
-    TickMark* h_ticks = nullptr;       // pinned
-    unsigned int* h_nticks = nullptr;  // pinned
     uint32_t max_ticks_per_chunk = 4096;
-    // per-chunk table of log entries per (segment, bucket age) and what the host derives from it: the
-    // exact length of every bucket's value log, so the tick loop never waits for the device
-    uint32_t* d_seg_counts = nullptr;  // [(max_ticks_per_chunk + 1)][keep + 1] + 1 (largest duration of the chunk)
-    uint32_t* h_seg_counts = nullptr;  // pinned
-    uint32_t seg_max = 0;
     uint64_t host_count[APM_MAX_SLOTS];   // log entries per slot (== SlotMeta.count)
     uint64_t host_sorted[APM_MAX_SLOTS];  // entries that were in place at the slot's last sort
     uint32_t known_max_value = 0;         // largest duration appended to any log so far
@@ -177,11 +186,12 @@ struct ProfScope {
 };
 
 // k1_ingest.cu
-apm_status apm_launch_find_ticks(apm_ctx* c, const int64_t* d_ts, uint64_t n, unsigned int* n_ticks_out);
+apm_status apm_prepass_begin(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_columns& d, uint64_t n, int64_t latest0, cudaStream_t st);
+apm_status apm_prepass_finish(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_columns& d, uint64_t n, cudaStream_t st);
+apm_status apm_prepass_segment(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_columns& d, uint64_t n, int64_t latest0, cudaStream_t st);
 apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin, uint64_t end);
 // k3_sort.cu
 apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value);
-apm_status apm_launch_seg_hist(apm_ctx* c, const apm_tx_columns& d, uint64_t n, unsigned int nt);
 uint64_t* apm_radix_sort_words(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t n, uint32_t* hist, uint32_t* totals,
                                int vbits, int kbits, uint64_t* launches);
 uint64_t apm_radix_sort_tiles(uint64_t n);

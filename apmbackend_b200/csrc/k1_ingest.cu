@@ -3,6 +3,7 @@
 // Replaces, for a whole batch at once, what consumeMsg does per message
 // (stream_calc_stats.js:331-371): generateBucketLabel (:89-91), the
 // `bucketLabel > latestBucket` test (:348) and addData (:115-134).
+#include <algorithm>
 #include <cstddef>
 #include <cstring>
 
@@ -527,63 +528,85 @@ __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReducePa
 
 }  // namespace
 
-apm_status apm_launch_find_ticks(apm_ctx* c, const int64_t* d_ts, uint64_t n, unsigned int* n_ticks_out) {
-    ProfScope prof_scope_(c, APM_PG_TICKFIND);
-    *n_ticks_out = 0;
-    if (n == 0) return APM_OK;
+// ---- the pre-pass of a chunk: where its ticks are and what every segment appends to every bucket ------------
+// begin:  tick finder on `st`, count + first slice of the marks on their way to the host, pp.ev recorded behind them.
+// finish: waits for pp.ev, sorts the marks by position, runs the segment table kernel and brings it back.
+// Between the two the host is free to queue other work (the ticks of the previous chunk).
+constexpr unsigned int PP_FIRST_MARKS = 256;
+
+apm_status apm_prepass_begin(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_columns& d, uint64_t n, int64_t latest0, cudaStream_t st) {
+    ProfScope prof_scope_(c, APM_PG_TICKFIND, st);
+    pp.nt = 0;
+    pp.seg_max = 0;
+    pp.latest0 = latest0;
+    *pp.h_nticks = 0;
+    if (n == 0) { CUDA_TRY(c, cudaEventRecord(pp.ev, st)); return APM_OK; }
     const uint64_t ntiles = (n + TF_TILE - 1) / TF_TILE;
     if (ntiles > c->tf_tiles_cap) return apm_fail(c, APM_E_CAPACITY, "chunk larger than max_batch");
-    CUDA_TRY(c, cudaMemsetAsync(c->d_nticks, 0, sizeof(unsigned int), c->s_main));
-    tf_tile_max_kernel<<<(unsigned)ntiles, TF_THREADS, 0, c->s_main>>>(d_ts, n, c->cfg.bucket_ms, c->inv_bucket,
-                                                                      c->tf_tile_max);
-    tf_scan_kernel<<<1, 1024, 0, c->s_main>>>(c->tf_tile_max, ntiles, c->latest, c->tf_tile_prefix);
-    tf_emit_kernel<<<(unsigned)ntiles, TF_THREADS, 0, c->s_main>>>(d_ts, n, c->cfg.bucket_ms, c->inv_bucket,
-                                                                  c->tf_tile_max, c->tf_tile_prefix, c->d_ticks,
-                                                                  c->d_nticks, c->max_ticks_per_chunk);
+    CUDA_TRY(c, cudaMemsetAsync(pp.d_nticks, 0, sizeof(unsigned int), st));
+    tf_tile_max_kernel<<<(unsigned)ntiles, TF_THREADS, 0, st>>>(d.end_ts_ms, n, c->cfg.bucket_ms, c->inv_bucket, pp.tf_tile_max);
+    tf_scan_kernel<<<1, 1024, 0, st>>>(pp.tf_tile_max, ntiles, latest0, pp.tf_tile_prefix);
+    tf_emit_kernel<<<(unsigned)ntiles, TF_THREADS, 0, st>>>(d.end_ts_ms, n, c->cfg.bucket_ms, c->inv_bucket, pp.tf_tile_max,
+                                                           pp.tf_tile_prefix, pp.d_ticks, pp.d_nticks, c->max_ticks_per_chunk);
     c->launches += 3;
     CUDA_TRY(c, cudaGetLastError());
     // the count and a first slice of the marks come back in one round trip; only a chunk with more ticks than
     // the slice holds pays a second one
-    const unsigned int first = c->max_ticks_per_chunk < 256u ? c->max_ticks_per_chunk : 256u;
-    CUDA_TRY(c, cudaMemcpyAsync(c->h_nticks, c->d_nticks, sizeof(unsigned int), cudaMemcpyDeviceToHost, c->s_main));
-    CUDA_TRY(c, cudaMemcpyAsync(c->h_ticks, c->d_ticks, first * sizeof(TickMark), cudaMemcpyDeviceToHost, c->s_main));
-    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-    unsigned int nt = *c->h_nticks;
-    if (nt > c->max_ticks_per_chunk) return apm_fail(c, APM_E_CAPACITY, "too many ticks in one chunk");
-    if (nt > first) {
-        CUDA_TRY(c, cudaMemcpyAsync(c->h_ticks + first, c->d_ticks + first, (nt - first) * sizeof(TickMark), cudaMemcpyDeviceToHost, c->s_main));
-        CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-    }
-    c->counters.d2h_bytes += sizeof(unsigned int) + (nt > first ? nt : first) * sizeof(TickMark);
-    *n_ticks_out = nt;
+    const unsigned int first = c->max_ticks_per_chunk < PP_FIRST_MARKS ? c->max_ticks_per_chunk : PP_FIRST_MARKS;
+    CUDA_TRY(c, cudaMemcpyAsync(pp.h_nticks, pp.d_nticks, sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(c, cudaMemcpyAsync(pp.h_ticks, pp.d_ticks, first * sizeof(TickMark), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(c, cudaEventRecord(pp.ev, st));
     return APM_OK;
 }
 
-// Uploads the chunk's tick marks (sorted by position, in c->h_ticks), counts the log entries of every
-// (segment, bucket age) pair and brings the table back: c->h_seg_counts[(nt + 1)][keep + 1], c->seg_max.
-apm_status apm_launch_seg_hist(apm_ctx* c, const apm_tx_columns& d, uint64_t n, unsigned int nt) {
-    ProfScope prof_scope_(c, APM_PG_TICKFIND);
+// the segment table of a chunk whose (sorted) marks are in pp.h_ticks[0 .. pp.nt): pp.h_seg_counts, pp.seg_max
+static apm_status seg_table(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_columns& d, uint64_t n, cudaStream_t st) {
+    ProfScope prof_scope_(c, APM_PG_TICKFIND, st);
+    const unsigned int nt = pp.nt;
     const size_t cells = (size_t)(nt + 1) * (c->keep + 1);
-    memset(c->h_seg_counts, 0, cells * sizeof(uint32_t));
-    c->seg_max = 0;
+    memset(pp.h_seg_counts, 0, cells * sizeof(uint32_t));
+    pp.seg_max = 0;
     if (n == 0) return APM_OK;
-    if (nt) CUDA_TRY(c, cudaMemcpyAsync(c->d_ticks, c->h_ticks, nt * sizeof(TickMark), cudaMemcpyHostToDevice, c->s_main));
-    CUDA_TRY(c, cudaMemsetAsync(c->d_seg_counts, 0, (cells + 1) * sizeof(uint32_t), c->s_main));
+    if (nt) CUDA_TRY(c, cudaMemcpyAsync(pp.d_ticks, pp.h_ticks, nt * sizeof(TickMark), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(c, cudaMemsetAsync(pp.d_seg_counts, 0, (cells + 1) * sizeof(uint32_t), st));
     SegHistParams p;
     p.svc = d.service_id; p.jvm = d.jvm_id; p.ts = d.end_ts_ms; p.el = d.elapsed_ms; p.n = n;
-    p.bucket_ms = c->cfg.bucket_ms; p.inv_bucket = c->inv_bucket; p.latest0 = c->latest; p.keep = c->keep;
+    p.bucket_ms = c->cfg.bucket_ms; p.inv_bucket = c->inv_bucket; p.latest0 = pp.latest0; p.keep = c->keep;
     p.num_services = c->cfg.num_services; p.num_jvms = c->cfg.num_jvms;
-    p.ticks = c->d_ticks; p.nt = nt;
-    p.counts = c->d_seg_counts; p.max_value = c->d_seg_counts + cells;  // the chunk maximum rides behind the table
-    seg_hist_kernel<<<(unsigned)((n + SH_TILE - 1) / SH_TILE), SH_THREADS, 0, c->s_main>>>(p);
+    p.ticks = pp.d_ticks; p.nt = nt;
+    p.counts = pp.d_seg_counts; p.max_value = pp.d_seg_counts + cells;  // the chunk maximum rides behind the table
+    seg_hist_kernel<<<(unsigned)((n + SH_TILE - 1) / SH_TILE), SH_THREADS, 0, st>>>(p);
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
-    CUDA_TRY(c, cudaMemcpyAsync(c->h_seg_counts, c->d_seg_counts, (cells + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->s_main));
-    CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
-    c->seg_max = c->h_seg_counts[cells];
+    CUDA_TRY(c, cudaMemcpyAsync(pp.h_seg_counts, pp.d_seg_counts, (cells + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(c, cudaStreamSynchronize(st));
+    pp.seg_max = pp.h_seg_counts[cells];
     c->counters.d2h_bytes += (cells + 1) * sizeof(uint32_t);
     c->counters.h2d_bytes += nt * sizeof(TickMark);
     return APM_OK;
+}
+
+apm_status apm_prepass_finish(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_columns& d, uint64_t n, cudaStream_t st) {
+    CUDA_TRY(c, cudaEventSynchronize(pp.ev));
+    const unsigned int nt = *pp.h_nticks;
+    if (nt > c->max_ticks_per_chunk) return apm_fail(c, APM_E_CAPACITY, "too many ticks in one chunk");
+    const unsigned int first = c->max_ticks_per_chunk < PP_FIRST_MARKS ? c->max_ticks_per_chunk : PP_FIRST_MARKS;
+    if (nt > first) {
+        CUDA_TRY(c, cudaMemcpyAsync(pp.h_ticks + first, pp.d_ticks + first, (nt - first) * sizeof(TickMark), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(c, cudaStreamSynchronize(st));
+    }
+    c->counters.d2h_bytes += sizeof(unsigned int) + (nt > first ? nt : first) * sizeof(TickMark);
+    pp.nt = nt;
+    std::sort(pp.h_ticks, pp.h_ticks + nt, [](const TickMark& a, const TickMark& b) { return a.pos < b.pos; });
+    if ((c->cfg.flags & APM_F_PERCENTILES) && c->cfg.num_percentiles > 0) return seg_table(c, pp, d, n, st);
+    return APM_OK;
+}
+
+// a batch that is known to hold no tick (apm_ingest_commit): one segment under latest0
+apm_status apm_prepass_segment(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_columns& d, uint64_t n, int64_t latest0, cudaStream_t st) {
+    pp.nt = 0;
+    pp.latest0 = latest0;
+    return seg_table(c, pp, d, n, st);
 }
 
 apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin, uint64_t end) {

@@ -49,7 +49,10 @@ for s in range(3):
     el = p[3].array.view(np.uint32)
     pk = [syn.PinnedArray(np.uint32, n) for _ in range(3)]
     pk[0].array[:] = key; pk[1].array[:] = dtv; pk[2].array[:] = el
+    eng.profile_read(); eng.profile_enable(True)
     t0 = time.perf_counter(); eng.process_host_packed(pk[0].array, pk[1].array, pk[2].array, base); t1 = time.perf_counter()
+    prof = eng.profile_read(); eng.profile_enable(False)
+    print("   spans ms:", {g: round(v["ms"], 2) for g, v in prof.items() if v["ms"] > 0.05})
     fs = eng.fetch_fs(pinned=True); t2 = time.perf_counter()
     al = eng.fetch_alerts(pinned=True); t3 = time.perf_counter()
     eng.release_ticks(); t4 = time.perf_counter()
