@@ -282,7 +282,7 @@ apm_status apm_state_load(apm_ctx* ctx, const char* path);
 /* ---- optional device timing (no reference counterpart; the reference only times its DB
  * inserts, stream_insert_db.js:295-308).  When enabled, every launch group is bracketed by
  * CUDA events on the context's stream; read sums them per group and resets.
- * groups: 0 tick finder, 1 keyed reduce, 2 slot clear, 3 radix sort, 4 window/percentiles,
+ * groups: 0 chunk pre-pass (tick finder + segment table), 1 keyed reduce, 2 slot clear, 3 radix sort, 4 window/percentiles,
  *         5 rolling baseline, 6 alert compaction, 7 lag-list realignment, 8 transaction passthrough. */
 #define APM_KT_GROUPS 12
 typedef struct apm_kernel_times {
