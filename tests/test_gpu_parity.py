@@ -310,3 +310,33 @@ def test_packed_transactions_give_the_same_records():
     assert a.fetch_stats().tobytes() == b.fetch_stats().tobytes() and a.fetch_fs().tobytes() == b.fetch_fs().tobytes()
     a.close()
     b.close()
+
+
+def test_full_output_ring_refuses_the_chunk_and_leaves_the_state_untouched():
+    """APM_E_WOULDBLOCK (the `pause` path of stream_calc_stats.js:270-276): a chunk with more ticks than the
+    output ring has room for is refused before anything of it is ingested; fed in smaller pieces with a
+    fetch in between, the same stream gives the oracle's records."""
+    from apmbackend_b200 import Engine
+    from apmbackend_b200._capi import ApmError
+    from oracle import capi as ocapi
+    from tests.gpu_util import engine_config, oracle_config
+    c = dict(CASES[2], out_ticks=6)
+    svc, jvm, ts, el = stream_for(c)
+    eng = Engine(engine_config(c))
+    with pytest.raises(ApmError) as e:
+        eng.process_host(svc, jvm, ts, el)            # ~40 ticks, room for 6
+    assert e.value.status == 4 and eng.counters().ticks == 0 and eng.counters().tx_ingested == 0
+    orc = ocapi.Pipeline(oracle_config(c), fast=True)
+    orc.consume(svc, jvm, ts, el)
+    st_parts, fs_parts = [], []
+    step = svc.size // 40
+    for a in range(0, svc.size, step):
+        b = min(svc.size, a + step)
+        eng.process_host(svc[a:b], jvm[a:b], ts[a:b], el[a:b])
+        if eng.ticks_buffered >= 3:
+            st_parts.append(eng.fetch_stats().copy()); fs_parts.append(eng.fetch_fs().copy())
+            eng.release_ticks()
+    st_parts.append(eng.fetch_stats().copy()); fs_parts.append(eng.fetch_fs().copy())
+    assert_stats_equal(np.concatenate(st_parts), orc.stats())
+    assert_fs_equal(np.concatenate(fs_parts), orc.fs())
+    eng.close()
