@@ -370,6 +370,7 @@ apm_status process_host_chunks(apm_ctx* c, uint64_t n, apm_tick_result* res, Cop
         }
         CUDA_TRY(c, cudaStreamWaitEvent(c->s_main, c->ev_copied[b], 0));
         st = run_chunk(c, c->dev[b], chunks[ci].second, c->pre[b], res);
+        if (st == APM_E_WOULDBLOCK) { finish_result(c, before, res); return st; }  // res: what the earlier chunks consumed
         if (st) return st;
         CUDA_TRY(c, cudaEventRecord(c->ev_consumed[b], c->s_main));
         if (ci + 2 < nchunks) { st = copy(ci + 2); if (st) return st; }  // into the buffer this chunk has just released
@@ -713,6 +714,7 @@ apm_status apm_process_device(apm_ctx* c, const apm_tx_columns* cols, uint64_t n
             if (st) return st;
         }
         st = run_chunk(c, d, m, c->pre[b], res);
+        if (st == APM_E_WOULDBLOCK) { finish_result(c, before, res); return st; }  // res: what the earlier chunks consumed
         if (st) return st;
         if (more) {
             st = apm_prepass_finish(c, c->pre[b ^ 1], d1, m1, c->s_pre);

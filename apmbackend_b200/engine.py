@@ -98,9 +98,11 @@ class Engine:
     def __exit__(self, *a):
         self.close()
 
-    def _check(self, st):
+    def _check(self, st, res=None):
         if st != _capi.OK:
-            raise ApmError(st, (self._lib.apm_last_error(self._h) or b"").decode())
+            err = ApmError(st, (self._lib.apm_last_error(self._h) or b"").decode())
+            err.result = res  # APM_E_WOULDBLOCK: what the chunks before the refused one consumed
+            raise err
 
     @property
     def handle(self):
@@ -112,7 +114,7 @@ class Engine:
         s, j, t, e = _cols(service_id, jvm_id, end_ts_ms, elapsed_ms)
         cols = TxColumns(s.ctypes.data, j.ctypes.data, t.ctypes.data, e.ctypes.data)
         res = TickResult()
-        self._check(self._lib.apm_process_host(self._h, C.byref(cols), s.size, C.byref(res)))
+        self._check(self._lib.apm_process_host(self._h, C.byref(cols), s.size, C.byref(res)), res)
         return res
 
     def process_host_packed(self, key, end_ts_delta_ms, elapsed_ms, base_ts_ms: int) -> TickResult:

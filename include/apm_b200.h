@@ -199,7 +199,10 @@ apm_status apm_tick(apm_ctx* ctx, int64_t latest_bucket, apm_tick_result* res);
 /* ---- stream chunk: replaces a run of consumeMsg calls (:331-371) over n
  * transactions in arrival order, ticks found on the device.  *_host takes
  * host columns (pageable or pinned) and includes the H2D copies; *_device
- * takes device-resident columns. res may be NULL. */
+ * takes device-resident columns. res may be NULL.  A call longer than max_batch goes through in
+ * chunks; when a chunk holds more ticks than the output ring has room for, the call stops there with
+ * APM_E_WOULDBLOCK and res counts what the chunks before it consumed: after a fetch + apm_release_ticks
+ * the caller resubmits from transaction tx_ingested + tx_dropped + tx_invalid on. */
 apm_status apm_process_host(apm_ctx* ctx, const apm_tx_columns* host_cols, uint64_t n, apm_tick_result* res);
 apm_status apm_process_device(apm_ctx* ctx, const apm_tx_columns* dev_cols, uint64_t n, apm_tick_result* res);
 

@@ -340,3 +340,33 @@ def test_full_output_ring_refuses_the_chunk_and_leaves_the_state_untouched():
     assert_stats_equal(np.concatenate(st_parts), orc.stats())
     assert_fs_equal(np.concatenate(fs_parts), orc.fs())
     eng.close()
+
+
+def test_refused_chunk_in_the_middle_of_a_long_call_reports_what_was_consumed():
+    from apmbackend_b200 import Engine
+    from apmbackend_b200._capi import ApmError
+    from oracle import capi as ocapi
+    from tests.gpu_util import engine_config, oracle_config
+    c = dict(CASES[2], out_ticks=12, max_batch=256)     # chunks of 16 .. 64 transactions, ~40 ticks in the stream
+    svc, jvm, ts, el = stream_for(c)
+    orc = ocapi.Pipeline(oracle_config(c), fast=True)
+    orc.consume(svc, jvm, ts, el)
+    eng = Engine(engine_config(c))
+    st_parts, fs_parts, off, refusals = [], [], 0, 0
+    while off < svc.size:
+        try:
+            eng.process_host(svc[off:], jvm[off:], ts[off:], el[off:])
+            off = svc.size
+        except ApmError as e:
+            assert e.status == 4
+            r = e.result
+            used = r.tx_ingested + r.tx_dropped + r.tx_invalid
+            assert used > 0 or eng.ticks_buffered > 0
+            off += used
+            refusals += 1
+        st_parts.append(eng.fetch_stats().copy()); fs_parts.append(eng.fetch_fs().copy())
+        eng.release_ticks()
+    assert refusals >= 2
+    assert_stats_equal(np.concatenate(st_parts), orc.stats())
+    assert_fs_equal(np.concatenate(fs_parts), orc.fs())
+    eng.close()
