@@ -370,3 +370,26 @@ def test_refused_chunk_in_the_middle_of_a_long_call_reports_what_was_consumed():
     assert_stats_equal(np.concatenate(st_parts), orc.stats())
     assert_fs_equal(np.concatenate(fs_parts), orc.fs())
     eng.close()
+
+
+def test_capacity_errors_name_the_limit():
+    """A bucket with more transactions than max_tx_per_bucket and a batch above max_batch are APM_E_CAPACITY with the limit's name in the message - never silent truncation."""
+    from apmbackend_b200 import Engine
+    from apmbackend_b200._capi import ApmError
+    from tests.gpu_util import engine_config
+    c = dict(CASES[2])
+    svc, jvm, ts, el = stream_for(c)
+    eng = Engine(engine_config(dict(c, log_cap=16)))            # ~60 transactions per bucket, room for 16
+    with pytest.raises(ApmError, match="max_tx_per_bucket") as e:
+        eng.process_host(svc, jvm, ts, el)
+    assert e.value.status == 3
+    eng.close()
+    eng = Engine(engine_config(dict(c, max_batch=64)))
+    import ctypes
+    from apmbackend_b200._capi import TxColumns
+    pin = TxColumns()
+    assert eng._lib.apm_ingest_acquire(eng._h, 64, ctypes.byref(pin)) == 0
+    with pytest.raises(ApmError, match="max_batch") as e:
+        eng._check(eng._lib.apm_ingest_acquire(eng._h, 65, ctypes.byref(pin)))
+    assert e.value.status == 3
+    eng.close()
