@@ -336,7 +336,10 @@ apm_status process_host_chunks(apm_ctx* c, uint64_t n, apm_tick_result* res, Cop
             const uint64_t m = std::min<uint64_t>(n - off, len);
             chunks.emplace_back(off, m);
             off += m;
-            len = std::min<uint64_t>(len * 2, top);
+            static int growth = 0;  // APM_CHUNK_GROWTH_PCT: size of a chunk relative to the one before it (the link is
+                                    // barely faster than the device: doubling chunks starve it during the ramp)
+            if (!growth) { const char* e = getenv("APM_CHUNK_GROWTH_PCT"); growth = e ? atoi(e) : 150; if (growth < 100) growth = 100; }
+            len = std::min<uint64_t>(len * growth / 100, top);
         }
     }
     const uint64_t nchunks = chunks.size();
