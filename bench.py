@@ -50,6 +50,13 @@ WORKLOADS = {
                        influences=(0.0,), zscore=True, pct=True, seed=3,
                        desc="one of 8 key-hash shards of 1B transactions / 1M keys: 125M transactions, 125k keys, "
                             "p50/p95/p99 + z-score vs 10080-bucket baseline (30 GB of rings)"),
+    # BASELINE.json configs[4]: heavy skew - the top 10 services carry 80 % of the traffic; cfg3's shape otherwise
+    # (what one rank sees when all hot keys land in its shard)
+    "cfg5": dict(n=100_000_000, services=10_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
+                 percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
+                 influences=(0.0,), zscore=True, pct=True, seed=5, hot=(10, 0.8), log_cap_factor=1.5,
+                 desc="100M transactions, 10k service keys, top 10 services = 80% of the traffic, p50/p95/p99 + z-score vs "
+                      "10080-bucket baseline (pre-filled), exact-order baseline"),
     # BASELINE.json configs[1]
     "cfg2": dict(n=100_000_000, services=10_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
                  percentiles=(), z_series_pct=(0, 1), lags=(), thresholds=(), influences=(), zscore=False, pct=False,
@@ -306,7 +313,7 @@ def main():
 
     nsteps = args.warmup + args.steps
     spec = syn.StreamSpec(seed=wl["seed"] + 1000 * rank, n=wl["n"], num_services=wl["services"], num_jvms=wl["jvms"],
-                          span_ms=span_ms, shift_mod=97)
+                          span_ms=span_ms, shift_mod=97, hot=wl.get("hot"))
     stream = syn.SynthStream(spec, device=True)
     ring_seed = 77 + rank
     if wl["zscore"] and wl.get("prefill", True):
@@ -547,7 +554,7 @@ def run_reference(args, wl, rank, world, config, span_ms):
         return
     from apmbackend_b200 import synthetic as syn
     spec = syn.StreamSpec(seed=wl["seed"], n=wl["n"], num_services=wl["services"], num_jvms=wl["jvms"], span_ms=span_ms,
-                          shift_mod=97)
+                          shift_mod=97, hot=wl.get("hot"))
     hs = syn.SynthStream(spec, device=False)
     threads = os.cpu_count() or 1
     (svc, jvm, ts, el), n_s = sample_for_cpu(wl, hs, ticks=6)
