@@ -57,6 +57,19 @@ WORKLOADS = {
                  influences=(0.0,), zscore=True, pct=True, seed=5, hot=(10, 0.8), log_cap_factor=1.5,
                  desc="100M transactions, 10k service keys, top 10 services = 80% of the traffic, p50/p95/p99 + z-score vs "
                       "10080-bucket baseline (pre-filled), exact-order baseline"),
+    # configs[4] as BASELINE.json states it (1 B transactions, 10 k keys, 8 GPUs), seen from one rank: splitmix64 ownership
+    # gives the heaviest rank 1316 keys with 2 of the 10 hot services = 18.6 % of the transactions (ideal 12.5 %) ...
+    "cfg5_rank8_heavy": dict(n=186_000_000, services=1316, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
+                             percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
+                             influences=(0.0,), zscore=True, pct=True, seed=5, hot=(2, 0.86), log_cap_factor=1.5,
+                             desc="heaviest of 8 key-hash shards of 1B transactions / 10k keys with top 10 = 80%: 186M "
+                                  "transactions, 1316 keys, 2 hot services = 86% of the shard"),
+    # ... and an even shard of the same job (1250 keys, 125 M transactions, one hot service)
+    "cfg5_rank8_even": dict(n=125_000_000, services=1250, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
+                            percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
+                            influences=(0.0,), zscore=True, pct=True, seed=5, hot=(1, 0.64), log_cap_factor=1.5,
+                            desc="an even 1/8 shard of 1B transactions / 10k keys with top 10 = 80%: 125M transactions, "
+                                 "1250 keys, 1 hot service = 64% of the shard"),
     # BASELINE.json configs[1]
     "cfg2": dict(n=100_000_000, services=10_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
                  percentiles=(), z_series_pct=(0, 1), lags=(), thresholds=(), influences=(), zscore=False, pct=False,
