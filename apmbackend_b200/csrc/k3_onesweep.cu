@@ -10,6 +10,7 @@
 // Only the significant bits are sorted: the logical word is the low `vbits` of the value
 // field with the key field packed directly above it, cut into equal digits of 8 bits (up to 11 on request).
 #include <cstdlib>
+#include <type_traits>
 
 #include "ctx.h"
 
@@ -21,6 +22,9 @@ constexpr int OS_ITEMS = 16;
 constexpr int OS_TILE = OS_THREADS * OS_ITEMS;  // 4096 words
 constexpr int OS_MAX_BITS = 11;
 constexpr int OS_MAX_PASSES = 6;
+#ifndef OS_NARROW_CTAS
+#define OS_NARROW_CTAS 4  // resident CTAs per SM the u32 pass is compiled for
+#endif
 constexpr uint32_t OS_FLAG_AGG = 1u << 30, OS_FLAG_PREFIX = 1u << 31, OS_COUNT_MASK = (1u << 30) - 1u;
 
 struct OsPlan {
@@ -93,19 +97,29 @@ __global__ void __launch_bounds__(1024) os_scan_kernel(uint32_t* __restrict__ gh
 }
 
 // ---- one digit: rank, look back, scatter ----------------------------------------------------------
+// NARROW (the logical word fits 32 bits - e.g. 10 k keys x durations below 131 s = 31 bits): the words travel
+// between the passes as packed u32 `key << vbits | value`; the first pass packs the log's u64 words while it
+// reads them and the last one unpacks while it writes, so the middle passes move half the bytes, hold half
+// the registers and shared memory, and a digit is one shift and one mask.
+template <bool NARROW>
 struct OsSmemLayout {
-    // [items u64 x 4096][wcnt u16 x 8 x bins][tile_cnt u32 x bins][gbase u32 x bins]
-    static size_t bytes(int bins) { return (size_t)OS_TILE * 8 + (size_t)OS_WARPS * bins * 2 + (size_t)bins * 4 * 2 + 64; }
+    // [items x 4096][wcnt u16 x 8 x bins][tile_cnt u32 x bins][gbase u32 x bins][misc]
+    static constexpr size_t item_bytes = NARROW ? 4 : 8;
+    static size_t bytes(int bins) { return (size_t)OS_TILE * item_bytes + (size_t)OS_WARPS * bins * 2 + (size_t)bins * 4 * 2 + 64; }
 };
 
-__global__ void __launch_bounds__(OS_THREADS, 3) os_pass_kernel(const uint64_t* __restrict__ src, uint64_t* __restrict__ dst, uint64_t n,
-                                                             int vbits, int shift, int bits, const uint32_t* __restrict__ gbase,
-                                                             volatile uint32_t* status /* [tiles][bins] */, uint32_t* ticket) {
+template <bool NARROW>
+__global__ void __launch_bounds__(OS_THREADS, NARROW ? OS_NARROW_CTAS : 3)
+os_pass_kernel(const void* __restrict__ src_v, void* __restrict__ dst_v, uint64_t n, int vbits, int shift, int bits, int first, int last,
+               const uint32_t* __restrict__ gbase, volatile uint32_t* status /* [tiles][bins] */, uint32_t* ticket) {
+    using T = typename std::conditional<NARROW, uint32_t, uint64_t>::type;
     extern __shared__ __align__(16) unsigned char os_raw[];
     const int bins = 1 << bits;
-    uint64_t* s_items = reinterpret_cast<uint64_t*>(os_raw);
-    uint16_t* s_wcnt = reinterpret_cast<uint16_t*>(os_raw + (size_t)OS_TILE * 8);          // [warp][bin]
-    uint32_t* s_cnt = reinterpret_cast<uint32_t*>(os_raw + (size_t)OS_TILE * 8 + (size_t)OS_WARPS * bins * 2);  // tile count, then local start
+    const uint32_t dmask = (uint32_t)bins - 1u;
+    constexpr size_t IB = OsSmemLayout<NARROW>::item_bytes;
+    T* s_items = reinterpret_cast<T*>(os_raw);
+    uint16_t* s_wcnt = reinterpret_cast<uint16_t*>(os_raw + (size_t)OS_TILE * IB);          // [warp][bin]
+    uint32_t* s_cnt = reinterpret_cast<uint32_t*>(os_raw + (size_t)OS_TILE * IB + (size_t)OS_WARPS * bins * 2);  // tile count, then local start
     uint32_t* s_gbase = s_cnt + bins;
     uint32_t* s_misc = s_gbase + bins;  // [0] tile id, [1..8] scan scratch
 
@@ -116,27 +130,34 @@ __global__ void __launch_bounds__(OS_THREADS, 3) os_pass_kernel(const uint64_t* 
     const uint32_t tile = s_misc[0];
     const uint64_t tile_base = (uint64_t)tile * OS_TILE;
     const uint64_t base = tile_base + (uint64_t)w * (32 * OS_ITEMS);
+    const bool in64 = !NARROW || first, out64 = !NARROW || last;
 
-    uint64_t item[OS_ITEMS];
-    uint16_t rank[OS_ITEMS];
+    T item[OS_ITEMS];
+    uint32_t dr[OS_ITEMS];  // digit | rank inside the warp's share of the bin << 16
 #pragma unroll
     for (int i = 0; i < OS_ITEMS; ++i) {
         const uint64_t idx = base + (uint64_t)i * 32 + lane;
-        item[i] = idx < n ? __ldcs(src + idx) : ~0ull;
+        if (in64) {
+            const uint64_t x = idx < n ? __ldcs(reinterpret_cast<const uint64_t*>(src_v) + idx) : ~0ull;
+            item[i] = NARROW ? (T)os_logical(x, vbits) : (T)x;
+        } else {
+            item[i] = idx < n ? (T)__ldcs(reinterpret_cast<const uint32_t*>(src_v) + idx) : (T)~0u;
+        }
     }
     uint16_t* my_wcnt = s_wcnt + (size_t)w * bins;
 #pragma unroll
     for (int i = 0; i < OS_ITEMS; ++i) {
         const uint64_t idx = base + (uint64_t)i * 32 + lane;
         const bool ok = idx < n;
-        const uint32_t d = os_digit(item[i], vbits, shift, bits);
+        const uint32_t d = NARROW ? (((uint32_t)item[i] >> shift) & dmask) : os_digit((uint64_t)item[i], vbits, shift, bits);
+        // eight ballots: __match_any_sync gives the same mask in one instruction but was measured slower here (142 vs 122 us per sort)
         const uint32_t peers = os_match(d, bits) & __ballot_sync(0xffffffffu, ok);
         uint32_t before = 0;
         if (ok) before = my_wcnt[d];
         __syncwarp();
         if (ok && lane == (__ffs(peers) - 1)) my_wcnt[d] = (uint16_t)(before + __popc(peers));
         __syncwarp();
-        rank[i] = (uint16_t)(before + __popc(peers & ((1u << lane) - 1u)));
+        dr[i] = d | ((before + __popc(peers & ((1u << lane) - 1u))) << 16);
     }
     __syncthreads();
 
@@ -156,6 +177,7 @@ __global__ void __launch_bounds__(OS_THREADS, 3) os_pass_kernel(const uint64_t* 
     // decoupled look-back: add the predecessors' counts until one of them carries an inclusive prefix
     for (int d = tid; d < bins; d += OS_THREADS) {
         uint32_t excl = 0;
+#ifndef OS_MICRO_NO_LOOKBACK  // scripts/micro_sort.cu: the cost of the chain
         if (tile != 0) {
             for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
                 volatile uint32_t* prev = status + (size_t)t * bins + d;
@@ -166,6 +188,7 @@ __global__ void __launch_bounds__(OS_THREADS, 3) os_pass_kernel(const uint64_t* 
             }
             status[(size_t)tile * bins + d] = (excl + s_cnt[d]) | OS_FLAG_PREFIX;
         }
+#endif
         s_gbase[d] = gbase[d] + excl;
     }
     __syncthreads();
@@ -197,16 +220,20 @@ __global__ void __launch_bounds__(OS_THREADS, 3) os_pass_kernel(const uint64_t* 
     for (int i = 0; i < OS_ITEMS; ++i) {
         const uint64_t idx = base + (uint64_t)i * 32 + lane;
         if (idx < n) {
-            const uint32_t d = os_digit(item[i], vbits, shift, bits);
-            s_items[s_cnt[d] + my_wcnt[d] + rank[i]] = item[i];
+            const uint32_t d = dr[i] & 0xffffu;
+            s_items[s_cnt[d] + my_wcnt[d] + (dr[i] >> 16)] = item[i];
         }
     }
     __syncthreads();
     const uint32_t in_tile = tile_base >= n ? 0u : (uint32_t)((n - tile_base) < (uint64_t)OS_TILE ? (n - tile_base) : OS_TILE);
+    const uint32_t vmask = vbits >= 32 ? 0xffffffffu : ((1u << vbits) - 1u);
     for (uint32_t j = tid; j < in_tile; j += OS_THREADS) {
-        const uint64_t x = s_items[j];
-        const uint32_t d = os_digit(x, vbits, shift, bits);
-        dst[(uint64_t)s_gbase[d] + (j - s_cnt[d])] = x;
+        const T x = s_items[j];
+        const uint32_t d = NARROW ? (((uint32_t)x >> shift) & dmask) : os_digit((uint64_t)x, vbits, shift, bits);
+        const uint64_t pos = (uint64_t)s_gbase[d] + (j - s_cnt[d]);
+        if (!NARROW) reinterpret_cast<uint64_t*>(dst_v)[pos] = (uint64_t)x;
+        else if (out64) reinterpret_cast<uint64_t*>(dst_v)[pos] = ((uint64_t)((uint32_t)x >> vbits) << 32) | ((uint32_t)x & vmask);
+        else reinterpret_cast<uint32_t*>(dst_v)[pos] = (uint32_t)x;
     }
 }
 
@@ -250,9 +277,17 @@ uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t 
     uint32_t* tickets = reinterpret_cast<uint32_t*>(scratch);
     uint32_t* ghist = reinterpret_cast<uint32_t*>(scratch + 64);
     uint32_t* status = reinterpret_cast<uint32_t*>(scratch + head);
+    // 32 significant bits or fewer: the passes work on packed u32 words (APM_SORT_NARROW=0 keeps the u64 form)
+    static int narrow_ok = -1;
+    if (narrow_ok < 0) {
+        const char* e = getenv("APM_SORT_NARROW");
+        narrow_ok = e ? atoi(e) != 0 : 1;
+    }
+    const bool narrow = narrow_ok && vbits + kbits <= 32 && vbits < 32;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(os_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout::bytes(2048));
+        cudaFuncSetAttribute(os_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<false>::bytes(2048));
+        cudaFuncSetAttribute(os_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<true>::bytes(2048));
         cudaFuncSetAttribute(os_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_MAX_PASSES * 2048 * 4);
         attr_set = true;
     }
@@ -265,9 +300,15 @@ uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t 
     uint64_t* src = a;
     uint64_t* dst = b;
     for (int p = 0; p < plan.npass; ++p) {
-        os_pass_kernel<<<(unsigned)tiles, OS_THREADS, OsSmemLayout::bytes(bins), st>>>(
-            src, dst, n, plan.vbits, plan.shift[p], plan.bits[p], ghist + ((size_t)p << OS_MAX_BITS),
-            status + (size_t)p * tiles * bins, tickets + p);
+        const int first = p == 0, last = p == plan.npass - 1;
+        if (narrow)
+            os_pass_kernel<true><<<(unsigned)tiles, OS_THREADS, OsSmemLayout<true>::bytes(bins), st>>>(
+                src, dst, n, plan.vbits, plan.shift[p], plan.bits[p], first, last, ghist + ((size_t)p << OS_MAX_BITS),
+                status + (size_t)p * tiles * bins, tickets + p);
+        else
+            os_pass_kernel<false><<<(unsigned)tiles, OS_THREADS, OsSmemLayout<false>::bytes(bins), st>>>(
+                src, dst, n, plan.vbits, plan.shift[p], plan.bits[p], first, last, ghist + ((size_t)p << OS_MAX_BITS),
+                status + (size_t)p * tiles * bins, tickets + p);
         uint64_t* t = src; src = dst; dst = t;
     }
     if (launches) *launches += 2 + plan.npass;
