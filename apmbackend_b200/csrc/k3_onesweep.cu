@@ -22,9 +22,6 @@ constexpr int OS_ITEMS = 16;
 constexpr int OS_TILE = OS_THREADS * OS_ITEMS;  // 4096 words
 constexpr int OS_MAX_BITS = 11;
 constexpr int OS_MAX_PASSES = 6;
-#ifndef OS_NARROW_CTAS
-#define OS_NARROW_CTAS 4  // resident CTAs per SM the u32 pass is compiled for
-#endif
 constexpr uint32_t OS_FLAG_AGG = 1u << 30, OS_FLAG_PREFIX = 1u << 31, OS_COUNT_MASK = (1u << 30) - 1u;
 
 struct OsPlan {
@@ -58,8 +55,19 @@ __global__ void __launch_bounds__(OS_THREADS) os_hist_kernel(const uint64_t* __r
     const int nb = plan.npass << OS_MAX_BITS;
     for (int i = threadIdx.x; i < nb; i += OS_THREADS) s_hist[i] = 0;
     __syncthreads();
+    // four independent loads in flight per thread: the loop is bound by the load latency, not by the atomics
     const uint64_t stride = (uint64_t)gridDim.x * OS_THREADS;
-    for (uint64_t i = (uint64_t)blockIdx.x * OS_THREADS + threadIdx.x; i < n; i += stride) {
+    uint64_t i = (uint64_t)blockIdx.x * OS_THREADS + threadIdx.x;
+    for (; i + 3 * stride < n; i += 4 * stride) {
+        uint64_t x[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) x[u] = __ldg(src + i + (uint64_t)u * stride);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            for (int p = 0; p < plan.npass; ++p)
+                atomicAdd(&s_hist[(p << OS_MAX_BITS) + os_digit(x[u], plan.vbits, plan.shift[p], plan.bits[p])], 1u);
+    }
+    for (; i < n; i += stride) {
         const uint64_t x = __ldg(src + i);
         for (int p = 0; p < plan.npass; ++p)
             atomicAdd(&s_hist[(p << OS_MAX_BITS) + os_digit(x, plan.vbits, plan.shift[p], plan.bits[p])], 1u);
@@ -108,12 +116,28 @@ struct OsSmemLayout {
     static size_t bytes(int bins) { return (size_t)OS_TILE * item_bytes + (size_t)OS_WARPS * bins * 2 + (size_t)bins * 4 * 2 + 64; }
 };
 
-template <bool NARROW>
-__global__ void __launch_bounds__(OS_THREADS, NARROW ? OS_NARROW_CTAS : 3)
-os_pass_kernel(const void* __restrict__ src_v, void* __restrict__ dst_v, uint64_t n, int vbits, int shift, int bits, int first, int last,
+// BITS: digit width known at compile time (the planner's default, 8), 0 = taken from the argument.  The ballots of
+// the ranking loop and the per-bin loops unroll only then; with run-time bits the kernel executes twice the instructions.
+template <int BITS>
+__device__ __forceinline__ uint32_t os_match_t(uint32_t d, int bits_rt) {
+    if (BITS == 0) return os_match(d, bits_rt);
+    uint32_t peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < (BITS ? BITS : 1); ++b) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? bal : ~bal;
+    }
+    return peers;
+}
+
+template <bool NARROW, int BITS>
+__global__ void __launch_bounds__(OS_THREADS, 3)
+os_pass_kernel(const void* __restrict__ src_v, void* __restrict__ dst_v, uint32_t n, int vbits, int shift, int bits_rt, int first, int last,
                const uint32_t* __restrict__ gbase, volatile uint32_t* status /* [tiles][bins] */, uint32_t* ticket) {
     using T = typename std::conditional<NARROW, uint32_t, uint64_t>::type;
     extern __shared__ __align__(16) unsigned char os_raw[];
+    const int bits = BITS ? BITS : bits_rt;
     const int bins = 1 << bits;
     const uint32_t dmask = (uint32_t)bins - 1u;
     constexpr size_t IB = OsSmemLayout<NARROW>::item_bytes;
@@ -123,47 +147,48 @@ os_pass_kernel(const void* __restrict__ src_v, void* __restrict__ dst_v, uint64_
     uint32_t* s_gbase = s_cnt + bins;
     uint32_t* s_misc = s_gbase + bins;  // [0] tile id, [1..8] scan scratch
 
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     if (tid == 0) s_misc[0] = atomicAdd(ticket, 1u);  // tiles start in index order: a predecessor is always running or done
-    for (int i = tid; i < OS_WARPS * bins / 2; i += OS_THREADS) reinterpret_cast<uint32_t*>(s_wcnt)[i] = 0;
+    for (uint32_t i = tid; i < (uint32_t)(OS_WARPS * bins / 2); i += OS_THREADS) reinterpret_cast<uint32_t*>(s_wcnt)[i] = 0;
     __syncthreads();
     const uint32_t tile = s_misc[0];
-    const uint64_t tile_base = (uint64_t)tile * OS_TILE;
-    const uint64_t base = tile_base + (uint64_t)w * (32 * OS_ITEMS);
+    const uint32_t tile_base = tile * OS_TILE;  // n < 2^30
+    const uint32_t in_tile = tile_base >= n ? 0u : (n - tile_base < (uint32_t)OS_TILE ? n - tile_base : (uint32_t)OS_TILE);
+    const uint32_t lbase = w * (32 * OS_ITEMS) + lane;  // this thread's first word inside the tile
     const bool in64 = !NARROW || first, out64 = !NARROW || last;
 
+    // Words past the end are all ones: top bin of every digit, behind every real word of the (last) tile, so they are
+    // ranked like real words - no validity test in the ranking loop - and simply not written out at the end.
     T item[OS_ITEMS];
-    uint32_t dr[OS_ITEMS];  // digit | rank inside the warp's share of the bin << 16
 #pragma unroll
     for (int i = 0; i < OS_ITEMS; ++i) {
-        const uint64_t idx = base + (uint64_t)i * 32 + lane;
+        const uint32_t li = lbase + i * 32;
         if (in64) {
-            const uint64_t x = idx < n ? __ldcs(reinterpret_cast<const uint64_t*>(src_v) + idx) : ~0ull;
+            const uint64_t x = li < in_tile ? __ldcs(reinterpret_cast<const uint64_t*>(src_v) + tile_base + li) : ~0ull;
             item[i] = NARROW ? (T)os_logical(x, vbits) : (T)x;
         } else {
-            item[i] = idx < n ? (T)__ldcs(reinterpret_cast<const uint32_t*>(src_v) + idx) : (T)~0u;
+            item[i] = li < in_tile ? (T)__ldcs(reinterpret_cast<const uint32_t*>(src_v) + tile_base + li) : (T)~0u;
         }
     }
     uint16_t* my_wcnt = s_wcnt + (size_t)w * bins;
+    const uint32_t lanes_below = (1u << lane) - 1u;
+    uint16_t rank[OS_ITEMS];  // position inside the warp's share of the bin
 #pragma unroll
     for (int i = 0; i < OS_ITEMS; ++i) {
-        const uint64_t idx = base + (uint64_t)i * 32 + lane;
-        const bool ok = idx < n;
         const uint32_t d = NARROW ? (((uint32_t)item[i] >> shift) & dmask) : os_digit((uint64_t)item[i], vbits, shift, bits);
         // eight ballots: __match_any_sync gives the same mask in one instruction but was measured slower here (142 vs 122 us per sort)
-        const uint32_t peers = os_match(d, bits) & __ballot_sync(0xffffffffu, ok);
-        uint32_t before = 0;
-        if (ok) before = my_wcnt[d];
+        const uint32_t peers = os_match_t<BITS>(d, bits);
+        const uint32_t before = my_wcnt[d];
         __syncwarp();
-        if (ok && lane == (__ffs(peers) - 1)) my_wcnt[d] = (uint16_t)(before + __popc(peers));
+        if ((peers & lanes_below) == 0) my_wcnt[d] = (uint16_t)(before + __popc(peers));  // the lowest lane of the group
         __syncwarp();
-        dr[i] = d | ((before + __popc(peers & ((1u << lane) - 1u))) << 16);
+        rank[i] = (uint16_t)(before + __popc(peers & lanes_below));
     }
     __syncthreads();
 
     // per bin: offsets of the warps inside the bin and the tile's count, published at once so that
     // successor tiles can already look back through this tile
-    for (int d = tid; d < bins; d += OS_THREADS) {
+    for (uint32_t d = tid; d < (uint32_t)bins; d += OS_THREADS) {
         uint32_t run = 0;
 #pragma unroll
         for (int j = 0; j < OS_WARPS; ++j) {
@@ -175,11 +200,11 @@ os_pass_kernel(const void* __restrict__ src_v, void* __restrict__ dst_v, uint64_
         status[(size_t)tile * bins + d] = run | (tile == 0 ? OS_FLAG_PREFIX : OS_FLAG_AGG);
     }
     // decoupled look-back: add the predecessors' counts until one of them carries an inclusive prefix
-    for (int d = tid; d < bins; d += OS_THREADS) {
+    for (uint32_t d = tid; d < (uint32_t)bins; d += OS_THREADS) {
         uint32_t excl = 0;
 #ifndef OS_MICRO_NO_LOOKBACK  // scripts/micro_sort.cu: the cost of the chain
         if (tile != 0) {
-            for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
+            for (int32_t t = (int32_t)tile - 1; t >= 0; --t) {
                 volatile uint32_t* prev = status + (size_t)t * bins + d;
                 uint32_t s;
                 while ((s = *prev) == 0) { /* the predecessor holds a ticket, so it is resident and will publish */ }
@@ -195,42 +220,44 @@ os_pass_kernel(const void* __restrict__ src_v, void* __restrict__ dst_v, uint64_
 
     // exclusive scan of the tile counts over the bins -> first local position of each bin
     {
-        const int per = bins / OS_THREADS > 0 ? bins / OS_THREADS : 1;  // bins >= 256 is guaranteed by the planner
+        constexpr int PER_CT = BITS ? ((1 << BITS) / OS_THREADS > 0 ? (1 << BITS) / OS_THREADS : 1) : 0;
+        const int per = BITS ? PER_CT : (bins / OS_THREADS > 0 ? bins / OS_THREADS : 1);  // bins >= 256 is guaranteed by the planner
         const int d0 = tid * per;
         uint32_t local[8];
         uint32_t sum = 0;
-        for (int j = 0; j < per; ++j) { local[j] = s_cnt[d0 + j]; sum += local[j]; }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (j < per) { local[j] = s_cnt[d0 + j]; sum += local[j]; }
         uint32_t v = sum;
+#pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t y = __shfl_up_sync(0xffffffffu, v, o);
-            if (lane >= o) v += y;
+            if (lane >= (uint32_t)o) v += y;
         }
         if (lane == 31) s_misc[1 + w] = v;
         __syncthreads();
         uint32_t woff = 0;
 #pragma unroll
         for (int j = 0; j < OS_WARPS; ++j)
-            if (j < w) woff += s_misc[1 + j];
+            if ((uint32_t)j < w) woff += s_misc[1 + j];
         uint32_t run = woff + v - sum;
-        for (int j = 0; j < per; ++j) { s_cnt[d0 + j] = run; run += local[j]; }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (j < per) { s_cnt[d0 + j] = run; run += local[j]; }
     }
     __syncthreads();
 
 #pragma unroll
     for (int i = 0; i < OS_ITEMS; ++i) {
-        const uint64_t idx = base + (uint64_t)i * 32 + lane;
-        if (idx < n) {
-            const uint32_t d = dr[i] & 0xffffu;
-            s_items[s_cnt[d] + my_wcnt[d] + (dr[i] >> 16)] = item[i];
-        }
+        const uint32_t d = NARROW ? (((uint32_t)item[i] >> shift) & dmask) : os_digit((uint64_t)item[i], vbits, shift, bits);
+        s_items[s_cnt[d] + my_wcnt[d] + rank[i]] = item[i];
     }
     __syncthreads();
-    const uint32_t in_tile = tile_base >= n ? 0u : (uint32_t)((n - tile_base) < (uint64_t)OS_TILE ? (n - tile_base) : OS_TILE);
     const uint32_t vmask = vbits >= 32 ? 0xffffffffu : ((1u << vbits) - 1u);
-    for (uint32_t j = tid; j < in_tile; j += OS_THREADS) {
+    for (uint32_t j = tid; j < in_tile; j += OS_THREADS) {  // the padding sits behind in_tile
         const T x = s_items[j];
         const uint32_t d = NARROW ? (((uint32_t)x >> shift) & dmask) : os_digit((uint64_t)x, vbits, shift, bits);
-        const uint64_t pos = (uint64_t)s_gbase[d] + (j - s_cnt[d]);
+        const uint32_t pos = s_gbase[d] + (j - s_cnt[d]);
         if (!NARROW) reinterpret_cast<uint64_t*>(dst_v)[pos] = (uint64_t)x;
         else if (out64) reinterpret_cast<uint64_t*>(dst_v)[pos] = ((uint64_t)((uint32_t)x >> vbits) << 32) | ((uint32_t)x & vmask);
         else reinterpret_cast<uint32_t*>(dst_v)[pos] = (uint32_t)x;
@@ -286,8 +313,10 @@ uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t 
     const bool narrow = narrow_ok && vbits + kbits <= 32 && vbits < 32;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(os_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<false>::bytes(2048));
-        cudaFuncSetAttribute(os_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<true>::bytes(2048));
+        cudaFuncSetAttribute(os_pass_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<false>::bytes(2048));
+        cudaFuncSetAttribute(os_pass_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<true>::bytes(2048));
+        cudaFuncSetAttribute(os_pass_kernel<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<false>::bytes(256));
+        cudaFuncSetAttribute(os_pass_kernel<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<true>::bytes(256));
         cudaFuncSetAttribute(os_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_MAX_PASSES * 2048 * 4);
         attr_set = true;
     }
@@ -301,14 +330,12 @@ uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t 
     uint64_t* dst = b;
     for (int p = 0; p < plan.npass; ++p) {
         const int first = p == 0, last = p == plan.npass - 1;
-        if (narrow)
-            os_pass_kernel<true><<<(unsigned)tiles, OS_THREADS, OsSmemLayout<true>::bytes(bins), st>>>(
-                src, dst, n, plan.vbits, plan.shift[p], plan.bits[p], first, last, ghist + ((size_t)p << OS_MAX_BITS),
-                status + (size_t)p * tiles * bins, tickets + p);
-        else
-            os_pass_kernel<false><<<(unsigned)tiles, OS_THREADS, OsSmemLayout<false>::bytes(bins), st>>>(
-                src, dst, n, plan.vbits, plan.shift[p], plan.bits[p], first, last, ghist + ((size_t)p << OS_MAX_BITS),
-                status + (size_t)p * tiles * bins, tickets + p);
+        auto kernel = narrow ? (per == 8 ? os_pass_kernel<true, 8> : os_pass_kernel<true, 0>)
+                             : (per == 8 ? os_pass_kernel<false, 8> : os_pass_kernel<false, 0>);
+        const size_t smem = narrow ? OsSmemLayout<true>::bytes(bins) : OsSmemLayout<false>::bytes(bins);
+        kernel<<<(unsigned)tiles, OS_THREADS, smem, st>>>(src, dst, (uint32_t)n, plan.vbits, plan.shift[p], plan.bits[p], first, last,
+                                                          ghist + ((size_t)p << OS_MAX_BITS), status + (size_t)p * tiles * bins,
+                                                          tickets + p);
         uint64_t* t = src; src = dst; dst = t;
     }
     if (launches) *launches += 2 + plan.npass;
