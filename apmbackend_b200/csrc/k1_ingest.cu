@@ -277,6 +277,7 @@ struct ReduceParams {
     double inv_bucket;
     int64_t latest;
     int keep, S;
+    int slot_latest;       // latest % S: slots are found from the bucket's age, not with a 64-bit modulo per transaction
     uint32_t num_services, num_jvms, K;
     AccSoA acc;
     uint8_t* seen;
@@ -300,11 +301,9 @@ constexpr int K1_SLOT_SHIFT = 26;         // tag = slot << 26 | key  (K <= 2^26)
 
 struct K1Smem {
     // used by both variants
-    unsigned long long base;  // reserved log position of the current (tile, slot) group
     unsigned long long c[5];
-    uint32_t warp_scan[K1_THREADS / 32];
-    uint32_t pick;            // (first pending index << 8 | slot) of the current log group
     uint32_t vmax;
+    uint32_t pad_;
     // the hash table: only the stats-only variant allocates it
     uint32_t tag[K1_TABLE], sum[K1_TABLE], sq_lo[K1_TABLE], cnt_hi[K1_TABLE], mn[K1_TABLE], mx[K1_TABLE];
 };
@@ -358,7 +357,7 @@ template <bool TABLE>
 __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReduceParams p) {
     extern __shared__ __align__(16) unsigned char k1_raw[];
     K1Smem& sm = *reinterpret_cast<K1Smem*>(k1_raw);
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     if (TABLE) k1_table_init(sm, tid);
     if (tid < 5) sm.c[tid] = 0;
     if (tid == 0) sm.vmax = 0;
@@ -421,7 +420,8 @@ __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReducePa
             // the key is emitted from now on even if this transaction is too old to count
             if (!p.seen[k]) p.seen[k] = 1;
             if (lab < p.latest - p.keep) { n_drop++; continue; }
-            const int sl = (int)(lab % p.S);
+            int sl = p.slot_latest - (int)(p.latest - lab);  // lab % S for latest - keep <= lab <= latest (keep < S)
+            if (sl < 0) sl += p.S;
             const uint32_t v = (uint32_t)el[j];
             slot[j] = sl;
             key[j] = k;
@@ -452,55 +452,44 @@ __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReducePa
             if (!done) k1_global_update(p, sl, k, v);
         }
 
-        if (p.with_log) {
-            // append (key, value) words to their bucket's log: one reservation per (tile, slot)
-            bool pending[4];
+        if (!TABLE) {
+            // Append (key, value) words to their bucket's log.  Every warp reserves its own stretch of the log - one
+            // atomicAdd per (warp, slot), normally one per 128 transactions - and writes it as 1 KB of consecutive
+            // words, so the tile loop has no block barrier and no warp waits for another one's reservation.
+            uint32_t pend = 0;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) pending[j] = slot[j] >= 0;
-            bool any = pending[0] | pending[1] | pending[2] | pending[3];
-            while (__syncthreads_or(any)) {
-                if (tid == 0) sm.pick = 0xFFFFFFFFu;
-                __syncthreads();
+            for (int j = 0; j < 4; ++j) pend |= slot[j] >= 0 ? (1u << j) : 0u;
+            for (;;) {
                 uint32_t mine = 0xFFFFFFFFu;
 #pragma unroll
                 for (int j = 3; j >= 0; --j)
-                    if (pending[j]) mine = ((uint32_t)(tid * 4 + j) << 8) | (uint32_t)slot[j];
+                    if (pend & (1u << j)) mine = ((uint32_t)(lane * 4 + j) << 8) | (uint32_t)slot[j];
                 const uint32_t wmin = __reduce_min_sync(0xffffffffu, mine);
-                if (lane == 0 && wmin != 0xFFFFFFFFu) atomicMin(&sm.pick, wmin);
-                __syncthreads();
-                const int gslot = (int)(sm.pick & 0xFFu);
+                if (wmin == 0xFFFFFFFFu) break;
+                const int gslot = (int)(wmin & 0xFFu);
                 uint32_t c = 0;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) c += (pending[j] && slot[j] == gslot) ? 1u : 0u;
+                for (int j = 0; j < 4; ++j) c += ((pend >> j) & 1u) && slot[j] == gslot ? 1u : 0u;
                 uint32_t incl = c;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
                     const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
                     if (lane >= o) incl += y;
                 }
-                if (lane == 31) sm.warp_scan[wid] = incl;
-                __syncthreads();
-                uint32_t woff = 0, total = 0;
-#pragma unroll
-                for (int w = 0; w < K1_THREADS / 32; ++w) {
-                    const uint32_t x = sm.warp_scan[w];
-                    if (w < wid) woff += x;
-                    total += x;
-                }
-                if (tid == 0) sm.base = atomicAdd(&p.slot_meta[gslot].count, (unsigned long long)total);
-                __syncthreads();
-                unsigned long long pos = sm.base + woff + incl - c;
+                const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(&p.slot_meta[gslot].count, (unsigned long long)total);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                unsigned long long pos = base + incl - c;
                 uint64_t* lg = p.logs[gslot];
-                any = false;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    if (pending[j] && slot[j] == gslot) {
+                    if (((pend >> j) & 1u) && slot[j] == gslot) {
                         if (pos < p.log_cap) lg[pos] = ((uint64_t)key[j] << 32) | (uint32_t)el[j];
                         else n_ovf++;
                         ++pos;
-                        pending[j] = false;
+                        pend &= ~(1u << j);
                     }
-                    any |= pending[j];
                 }
             }
         }
@@ -510,11 +499,16 @@ __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReducePa
     if (TABLE) k1_table_flush(p, sm, tid);
     my_max = __reduce_max_sync(0xffffffffu, my_max);
     if (lane == 0 && my_max) atomicMax(&sm.vmax, my_max);
-    if (n_ing) atomicAdd(&sm.c[0], n_ing);
-    if (n_drop) atomicAdd(&sm.c[1], n_drop);
-    if (n_inv) atomicAdd(&sm.c[2], n_inv);
-    if (n_fut) atomicAdd(&sm.c[3], n_fut);
-    if (n_ovf) atomicAdd(&sm.c[4], n_ovf);
+    {
+        // per-warp totals first: a 64-bit shared atomicAdd is a compare-and-swap loop on sm_100a, and 512 threads spinning on
+        // one word were 45 % of this kernel's stall samples
+        const unsigned long long mine[5] = {n_ing, n_drop, n_inv, n_fut, n_ovf};
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+            const uint32_t wsum = __reduce_add_sync(0xffffffffu, (uint32_t)mine[q]);  // a thread sees < 2^32 transactions
+            if (lane == 0 && wsum) atomicAdd(&sm.c[q], (unsigned long long)wsum);
+        }
+    }
     __syncthreads();
     if (tid == 0) {
         if (sm.c[0]) atomicAdd(&p.counters->ingested, sm.c[0]);
@@ -617,6 +611,7 @@ apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin
     p.begin = begin; p.end = end;
     p.bucket_ms = c->cfg.bucket_ms; p.inv_bucket = c->inv_bucket; p.latest = c->latest;
     p.keep = c->keep; p.S = c->S;
+    p.slot_latest = (int)(c->latest % c->S);
     p.num_services = c->cfg.num_services; p.num_jvms = c->cfg.num_jvms; p.K = c->K;
     p.acc = c->acc; p.seen = c->seen; p.slot_meta = c->slot_meta; p.logs = c->d_log_ptrs; p.log_cap = c->log_cap;
     p.counters = c->d_counters;
