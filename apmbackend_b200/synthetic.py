@@ -103,7 +103,8 @@ def zipf_cdf(num_services: int, s: float = 1.0, hot=None) -> np.ndarray:
     if hot:
         h, mass = hot
         w[:h] = mass / h
-        w[h:] *= (1.0 - mass) / w[h:].sum()
+        if h < num_services:
+            w[h:] *= (1.0 - mass) / w[h:].sum()
     c = np.cumsum(w / w.sum())
     cdf = np.minimum(np.floor(c * 4294967296.0), 4294967295.0).astype(np.uint64).astype(np.uint32)
     cdf[-1] = 0xFFFFFFFF

@@ -70,6 +70,29 @@ WORKLOADS = {
                             influences=(0.0,), zscore=True, pct=True, seed=5, hot=(1, 0.64), log_cap_factor=1.5,
                             desc="an even 1/8 shard of 1B transactions / 10k keys with top 10 = 80%: 125M transactions, "
                                  "1250 keys, 1 hot service = 64% of the shard"),
+    # the same job with count-aware key placement (sharding.balanced_owner_table): two ranks hold two hot services each
+    # and nothing else (16 % of the transactions), six hold one hot service and a sixth of the other keys (11.3 %)
+    "cfg5_lpt8_hot": dict(n=160_000_000, services=2, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
+                          percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
+                          influences=(0.0,), zscore=True, pct=True, seed=5, hot=(2, 1.0), log_cap_factor=1.5,
+                          desc="count-aware placement of 1B transactions / 10k keys with top 10 = 80% on 8 ranks, a rank "
+                               "that holds two hot services only: 160M transactions, 2 keys"),
+    "cfg5_lpt8_rest": dict(n=113_300_000, services=1667, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
+                           percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
+                           influences=(0.0,), zscore=True, pct=True, seed=5, hot=(1, 0.706), log_cap_factor=1.5,
+                           desc="count-aware placement of 1B transactions / 10k keys with top 10 = 80% on 8 ranks, a rank "
+                                "with one hot service and a sixth of the other keys: 113M transactions, 1667 keys"),
+    # ... and with a key's own cost in the balance (balanced_owner_table(key_cost=160e3)): the two-hot ranks keep 917 keys
+    "cfg5_cost8_two_hot": dict(n=178_300_000, services=917, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
+                               percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
+                               influences=(0.0,), zscore=True, pct=True, seed=5, hot=(2, 0.897), log_cap_factor=1.5,
+                               desc="key-cost-aware placement of 1B transactions / 10k keys with top 10 = 80% on 8 ranks, a rank "
+                                    "with two hot services: 178M transactions, 917 keys"),
+    "cfg5_cost8_one_hot": dict(n=107_200_000, services=1361, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
+                               percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
+                               influences=(0.0,), zscore=True, pct=True, seed=5, hot=(1, 0.746), log_cap_factor=1.5,
+                               desc="key-cost-aware placement of 1B transactions / 10k keys with top 10 = 80% on 8 ranks, a rank "
+                                    "with one hot service: 107M transactions, 1361 keys"),
     # BASELINE.json configs[1]
     "cfg2": dict(n=100_000_000, services=10_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
                  percentiles=(), z_series_pct=(0, 1), lags=(), thresholds=(), influences=(), zscore=False, pct=False,

@@ -98,3 +98,45 @@ def test_global_tick_labels():
     p = _pipeline()
     p.consume(svc, jvm, ts, el)
     assert labs.size == p.ticks and labs[-1] == p.latest
+
+
+def test_count_aware_placement_evens_out_a_two_tier_skew():
+    """BASELINE config 5 (top 10 of 10 000 services = 80 % of the traffic) on 8 ranks: the hash puts up to 18.6 % of the
+    transactions on one rank, the count-aware table 16 % - two hot services, the least a rank holding two of ten can have."""
+    K = 10000
+    counts = np.full(K, 0.2e9 / (K - 10))
+    counts[:10] = 0.08e9
+    for n in (2, 4, 8):
+        hashed = np.bincount(sharding.owner_of_keys(np.arange(K), n), weights=counts, minlength=n)
+        table = sharding.balanced_owner_table(counts, n)
+        assert table.shape == (K,) and table.max() < n
+        load = np.bincount(table, weights=counts, minlength=n)
+        assert load.max() <= hashed.max()
+        assert load.max() <= max(counts.sum() / n, 2 * counts[0]) * 1.001
+    # with a per-key cost in the balance the ranks that hold two hot services keep fewer of the light keys
+    t0 = sharding.balanced_owner_table(counts, 8)
+    t1 = sharding.balanced_owner_table(counts, 8, key_cost=160e3)
+    two_hot = np.flatnonzero(np.bincount(t1[:10], minlength=8) == 2)
+    keys0, keys1 = np.bincount(t0, minlength=8), np.bincount(t1, minlength=8)
+    assert two_hot.size == 2 and np.all(keys1[two_hot] > keys0[two_hot]) and np.all(keys1[two_hot] < keys1.max())
+    cost = np.bincount(t1, weights=counts + 160e3, minlength=8)
+    assert cost.max() / cost.mean() < 1.01
+    # light keys stay with their hash owner wherever that rank has room
+    uniform = np.full(K, 100.0)
+    t = sharding.balanced_owner_table(uniform, 4)
+    assert np.mean(t == sharding.owner_of_keys(np.arange(K), 4)) > 0.95
+    assert np.array_equal(sharding.balanced_owner_table(np.zeros(16), 4), sharding.owner_of_keys(np.arange(16), 4))
+
+
+def test_partition_with_an_owner_table_is_still_a_disjoint_cover():
+    svc, jvm, ts, el = _stream()
+    K = CFG["S"] * CFG["J"]
+    key = jvm.astype(np.int64) * CFG["S"] + svc
+    table = sharding.balanced_owner_table(np.bincount(key, minlength=K), 3)
+    parts = sharding.partition_columns(svc, jvm, ts, el, CFG["S"], 3, owner_table=table)
+    assert sum(p[0].size for p in parts) == svc.size
+    for r, p in enumerate(parts):
+        assert np.all(table[p[1].astype(np.int64) * CFG["S"] + p[0]] == r)
+    sizes = np.array([p[0].size for p in parts])
+    hashed = np.array([p[0].size for p in sharding.partition_columns(svc, jvm, ts, el, CFG["S"], 3)])
+    assert sizes.max() <= hashed.max()
