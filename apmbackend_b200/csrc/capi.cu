@@ -1053,6 +1053,45 @@ uint32_t apm_owner_of_key(uint64_t k, uint32_t nranks) {
     return nranks ? (uint32_t)(k % nranks) : 0;
 }
 
+// Count-aware placement (host arithmetic only; the same algorithm as sharding.balanced_owner_table): keys that alone
+// exceed 1 / (8 nranks) of the load go longest-first to the least loaded rank, the light ones keep their hash owner
+// unless that rank is already above the mean.  load(key) = count + key_cost.
+apm_status apm_owner_table_build(const uint64_t* key_counts, uint32_t num_keys, uint32_t nranks, uint64_t key_cost,
+                                 uint32_t* owner_out) {
+    if ((!key_counts || !owner_out) && num_keys) return apm_fail(nullptr, APM_E_INVALID, "apm_owner_table_build: null argument");
+    const uint32_t n = nranks ? nranks : 1;
+    double total = 0.0;
+    std::vector<double> w(num_keys);
+    for (uint32_t k = 0; k < num_keys; ++k) {
+        w[k] = (double)key_counts[k] + (double)key_cost;
+        total += w[k];
+        owner_out[k] = apm_owner_of_key(k, n);
+    }
+    if (n == 1 || !(total > 0.0)) return APM_OK;
+    std::vector<double> load(n, 0.0);
+    auto least = [&]() { return (uint32_t)(std::min_element(load.begin(), load.end()) - load.begin()); };
+    const double heavy_above = total / (8.0 * n), mean = total / n;
+    std::vector<uint32_t> heavy, light;
+    for (uint32_t k = 0; k < num_keys; ++k) (w[k] > heavy_above ? heavy : light).push_back(k);
+    auto by_load = [&](uint32_t a, uint32_t b) { return w[a] > w[b]; };
+    std::stable_sort(heavy.begin(), heavy.end(), by_load);
+    std::stable_sort(light.begin(), light.end(), by_load);
+    for (uint32_t k : heavy) {
+        const uint32_t r = least();
+        owner_out[k] = r;
+        load[r] += w[k];
+    }
+    for (uint32_t k : light) {
+        uint32_t r = owner_out[k];
+        if (load[r] + w[k] > mean) {
+            r = least();
+            owner_out[k] = r;
+        }
+        load[r] += w[k];
+    }
+    return APM_OK;
+}
+
 }  // extern "C"
 
 // Device-side stopwatch on the context's stream (what bench.py brackets its timed region with).

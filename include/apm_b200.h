@@ -352,6 +352,14 @@ apm_status apm_sorted_percentiles_noalloc(int32_t device, const int32_t* d_value
 /* ---- multi-GPU: keys are hash-sharded by the host; each rank owns its keys.
  * The only exchange is an all-gather of the compact alert block per tick. */
 uint32_t apm_owner_of_key(uint64_t global_key, uint32_t nranks);
+/* Placement for skewed traffic (BASELINE config 5; no counterpart in the reference, whose stages are single processes):
+ * owner_out[key] for the dense key ids 0 .. num_keys-1 from the transactions each key had in an earlier interval.
+ * load(key) = count + key_cost (what holding a key costs per interval, in transactions: the exact-order baseline walks
+ * every key's lists each tick whatever its traffic; 0 balances transactions only).  Heavy keys go longest-first to the
+ * least loaded rank, light keys keep apm_owner_of_key unless that rank is above the mean; a key is never split and rings
+ * do not migrate - choose the table when a deployment starts.  Pure host arithmetic, no device needed. */
+apm_status apm_owner_table_build(const uint64_t* key_counts, uint32_t num_keys, uint32_t nranks, uint64_t key_cost,
+                                 uint32_t* owner_out);
 apm_status apm_comm_unique_id(void* out128);                 /* ncclGetUniqueId */
 apm_status apm_comm_init(apm_ctx* ctx, int32_t rank, int32_t nranks, const void* unique_id128);
 /* Collective: every rank calls it at the same point of the stream.  Gathers the

@@ -140,3 +140,17 @@ def test_partition_with_an_owner_table_is_still_a_disjoint_cover():
     sizes = np.array([p[0].size for p in parts])
     hashed = np.array([p[0].size for p in sharding.partition_columns(svc, jvm, ts, el, CFG["S"], 3)])
     assert sizes.max() <= hashed.max()
+
+
+def test_owner_table_of_the_c_abi_equals_the_host_helper():
+    lib = _capi.lib()
+    rng = np.random.default_rng(7)
+    cases = [(np.r_[np.full(10, 80_000_000), np.full(9990, 20_020)].astype(np.uint64), 8, 160_000),
+             (np.r_[np.full(10, 80_000_000), np.full(9990, 20_020)].astype(np.uint64), 8, 0),
+             (rng.zipf(1.3, 5000).astype(np.uint64), 3, 0), (rng.integers(0, 1000, 777).astype(np.uint64), 5, 50),
+             (np.zeros(16, np.uint64), 4, 0), (np.array([5], np.uint64), 2, 0)]
+    for counts, n, cost in cases:
+        out = np.empty(counts.size, np.uint32)
+        assert lib.apm_owner_table_build(counts.ctypes.data, counts.size, n, cost, out.ctypes.data) == 0
+        assert np.array_equal(out, sharding.balanced_owner_table(counts, n, key_cost=cost)), (n, cost)
+    assert lib.apm_owner_table_build(None, 4, 2, 0, None) != 0
