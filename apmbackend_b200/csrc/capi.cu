@@ -22,6 +22,28 @@ apm_status apm_fail_cuda(apm_ctx* ctx, cudaError_t e, const char* what, const ch
     return APM_E_DEVICE;
 }
 
+int apm_sm_count() {
+    static int cached[APM_MAX_DEVICES];  // 0 = not asked yet
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= APM_MAX_DEVICES) return 148;
+    int n = cached[dev];
+    if (n <= 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return n;
+}
+
+bool apm_first_on_device(unsigned long long* done) {
+    static std::mutex mu;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= APM_MAX_DEVICES) return true;
+    std::lock_guard<std::mutex> lock(mu);
+    if (*done & (1ull << dev)) return false;
+    *done |= 1ull << dev;
+    return true;
+}
+
 namespace {
 
 template <typename T>
@@ -391,6 +413,7 @@ apm_status process_host_chunks(apm_ctx* c, uint64_t n, apm_tick_result* res, Cop
 // kernel and after everything queued on the ingest stream so far.
 apm_status apm_flush_pending(apm_ctx* c) {
     if (!c->pending.valid) return APM_OK;
+    APM_ENTER(c);
     const PendingBaseline pb = c->pending;
     c->pending.valid = false;
     CUDA_TRY(c, cudaStreamWaitEvent(c->s_base, c->ev_stats[pb.ev], 0));
@@ -412,7 +435,7 @@ double apm_quantize(double x, int32_t digits) { return apm_quantize_fixed(x, dig
 
 void apm_ctx_destroy(apm_ctx* c) {
     if (!c) return;
-    cudaSetDevice(c->cfg.device);
+    APM_ENTER(c);
     if (c->s_main) cudaStreamSynchronize(c->s_main);
     c->pending.valid = false;
     if (c->s_base) cudaStreamSynchronize(c->s_base);
@@ -481,7 +504,9 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     for (int i = 0; i < cfg->num_percentiles; ++i) c->pfrac[i] = cfg->percentiles[i] / 100.0;  // util_methods.js:129
     auto fail = [&](apm_status s) { g_create_error = c->err; apm_ctx_destroy(c); return s; };
 #define TRY_CREATE(expr) do { cudaError_t e2_ = (expr); if (e2_ != cudaSuccess) { apm_fail_cuda(c, e2_, #expr, __FILE__, __LINE__); return fail(APM_E_DEVICE); } } while (0)
+    APM_ENTER(c);  // the caller's current device is restored when create returns
     TRY_CREATE(cudaSetDevice(cfg->device));
+    c->num_sms = apm_sm_count();
     {
         // the ingest / sort chain is the latency-critical one: its CTAs go first when both streams have work
         int prio_lo = 0, prio_hi = 0;
@@ -628,11 +653,13 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
 
 apm_status apm_sync(apm_ctx* c) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     return sync_all(c);
 }
 
 apm_status apm_ingest_acquire(apm_ctx* c, uint64_t n, apm_tx_columns* out) {
     if (!c || !out) return APM_E_INVALID;
+    APM_ENTER(c);
     if (n > c->cfg.max_batch) return apm_fail(c, APM_E_CAPACITY, "acquire larger than max_batch");
     // the previous commit's copy must have left the pinned slices
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
@@ -643,6 +670,7 @@ apm_status apm_ingest_acquire(apm_ctx* c, uint64_t n, apm_tx_columns* out) {
 
 apm_status apm_ingest_commit(apm_ctx* c, uint64_t n) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     if (n > c->acquired) return apm_fail(c, APM_E_STATE, "commit without a matching acquire");
     c->acquired = 0;
     if (n == 0) return APM_OK;
@@ -674,6 +702,7 @@ apm_status apm_ingest_commit(apm_ctx* c, uint64_t n) {
 
 apm_status apm_tick(apm_ctx* c, int64_t latest_bucket, apm_tick_result* res) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     apm_status st = do_tick(c, latest_bucket);
     if (st) return st;
     if (res) {
@@ -686,6 +715,7 @@ apm_status apm_tick(apm_ctx* c, int64_t latest_bucket, apm_tick_result* res) {
 
 apm_status apm_process_device(apm_ctx* c, const apm_tx_columns* cols, uint64_t n, apm_tick_result* res) {
     if (!c || !cols) return APM_E_INVALID;
+    APM_ENTER(c);
     if (res) memset(res, 0, sizeof *res);
     const apm_counters before = c->counters;
     const uint64_t B = c->cfg.max_batch;
@@ -731,6 +761,7 @@ apm_status apm_process_device(apm_ctx* c, const apm_tx_columns* cols, uint64_t n
 
 apm_status apm_process_host(apm_ctx* c, const apm_tx_columns* h, uint64_t n, apm_tick_result* res) {
     if (!c || !h) return APM_E_INVALID;
+    APM_ENTER(c);
     return process_host_chunks(c, n, res, [&](uint64_t off, uint64_t m, int b) -> apm_status {
         apm_tx_columns& d = c->dev[b];
         CUDA_TRY(c, cudaMemcpyAsync(d.service_id, h->service_id + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
@@ -744,6 +775,7 @@ apm_status apm_process_host(apm_ctx* c, const apm_tx_columns* h, uint64_t n, apm
 
 apm_status apm_process_host_packed(apm_ctx* c, const apm_tx_packed* h, int64_t base_ts_ms, uint64_t n, apm_tick_result* res) {
     if (!c || !h) return APM_E_INVALID;
+    APM_ENTER(c);
     if (base_ts_ms < 0) return apm_fail(c, APM_E_INVALID, "process_host_packed: base_ts_ms must not be negative");
     if (!c->pk[0]) {  // 12-byte staging, one third of the wide staging, created at the first packed call
         for (int i = 0; i < 2; ++i) CUDA_TRY(c, cudaMalloc((void**)&c->pk[i], c->cfg.max_batch * 3 * sizeof(uint32_t)));
@@ -764,6 +796,7 @@ apm_status apm_process_host_packed(apm_ctx* c, const apm_tx_packed* h, int64_t b
 
 apm_status apm_set_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, int32_t l, const double* thr, const double* infl) {
     if (!c || !thr || !infl) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || (uint64_t)key_lo + n > c->K) return apm_fail(c, APM_E_INVALID, "set_key_params: range");
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
@@ -775,6 +808,7 @@ apm_status apm_set_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, int32_t l
 
 apm_status apm_set_alert_rules(apm_ctx* c, const apm_alert_rules* r) {
     if (!c || !r) return APM_E_INVALID;
+    APM_ENTER(c);
     if (r->struct_size != sizeof(apm_alert_rules)) return apm_fail(c, APM_E_INVALID, "apm_alert_rules.struct_size mismatch");
     if (!with_z(c)) return apm_fail(c, APM_E_STATE, "alert rules need APM_F_ZSCORE and at least one lag");
     if (r->enabled && !(c->cfg.flags & (APM_F_KEEP_FS | APM_F_ALERTS))) return apm_fail(c, APM_E_STATE, "alert rules need APM_F_KEEP_FS or APM_F_ALERTS");
@@ -786,6 +820,7 @@ apm_status apm_set_alert_rules(apm_ctx* c, const apm_alert_rules* r) {
 
 apm_status apm_set_alert_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, const double* hard_max_ms, const uint8_t* suppressed) {
     if (!c || !hard_max_ms || !suppressed) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!with_z(c) || (uint64_t)key_lo + n > c->K) return apm_fail(c, APM_E_INVALID, "set_alert_key_params: range");
     apm_status st = sync_all(c);
     if (st) return st;
@@ -796,6 +831,7 @@ apm_status apm_set_alert_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, con
 
 apm_status apm_drop_lag(apm_ctx* c, int32_t l) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags) return apm_fail(c, APM_E_INVALID, "drop_lag: index");
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
@@ -807,6 +843,7 @@ apm_status apm_drop_lag(apm_ctx* c, int32_t l) {
 
 apm_status apm_fetch_stats(apm_ctx* c, apm_stat_record* out, uint64_t cap, uint64_t* n) {
     if (!c || !n) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!(c->cfg.flags & APM_F_KEEP_STATS)) return apm_fail(c, APM_E_STATE, "stat records are not retained (APM_F_KEEP_STATS)");
     apm_status st = fetch_dense(c, c->d_stats, c->K, out, cap, n);
     if (!st) c->counters.stat_records += *n;
@@ -815,6 +852,7 @@ apm_status apm_fetch_stats(apm_ctx* c, apm_stat_record* out, uint64_t cap, uint6
 
 apm_status apm_fetch_fs(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64_t* n) {
     if (!c || !n) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!(c->cfg.flags & APM_F_KEEP_FS) || !with_z(c)) return apm_fail(c, APM_E_STATE, "fs records are not retained (APM_F_KEEP_FS | APM_F_ZSCORE)");
     const size_t per_tick = (size_t)c->K * c->cfg.num_lags, total = (size_t)c->ticks_buffered * per_tick;
     if (out && out == c->h_fs_bound && total <= c->h_fs_bound_cap) {
@@ -845,6 +883,7 @@ apm_status apm_fetch_fs(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64_t* 
 
 apm_status apm_bind_fs_output(apm_ctx* c, apm_fs_record* pinned, uint64_t cap_records) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     apm_status st = sync_all(c);
     if (st) return st;
     if (pinned) {
@@ -862,6 +901,7 @@ apm_status apm_bind_fs_output(apm_ctx* c, apm_fs_record* pinned, uint64_t cap_re
 
 apm_status apm_fetch_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64_t* n) {
     if (!c || !n) return APM_E_INVALID;
+    APM_ENTER(c);
     *n = 0;
     if (!c->d_alerts) return apm_fail(c, APM_E_STATE, "alerts are not compacted (APM_F_ALERTS | APM_F_ZSCORE)");
     if (c->ticks_buffered == 0) return APM_OK;
@@ -892,6 +932,7 @@ apm_status apm_fetch_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64
 
 apm_status apm_release_ticks(apm_ctx* c) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     if (c->d_alert_count) {
         { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
         CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
@@ -906,6 +947,7 @@ apm_status apm_release_ticks(apm_ctx* c) {
 
 apm_status apm_ring_load(apm_ctx* c, uint32_t key, int32_t l, int32_t series, const double* values, uint32_t len) {
     if (!c || (!values && len)) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || series < 0 || series >= APM_NUM_SERIES || key >= c->K) return apm_fail(c, APM_E_INVALID, "ring_load: index");
     const uint32_t L = (uint32_t)c->cfg.lags[l];
     if (len > L) return apm_fail(c, APM_E_INVALID, "ring_load: list longer than its lag");
@@ -930,6 +972,7 @@ apm_status apm_ring_load(apm_ctx* c, uint32_t key, int32_t l, int32_t series, co
 
 apm_status apm_ring_load_all(apm_ctx* c, int32_t l, const double* values, uint32_t len, int32_t on_device) {
     if (!c || (!values && len)) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags) return apm_fail(c, APM_E_INVALID, "ring_load_all: index");
     const uint32_t L = (uint32_t)c->cfg.lags[l];
     if (len > L) return apm_fail(c, APM_E_INVALID, "ring_load_all: lists longer than the lag");
@@ -953,6 +996,7 @@ apm_status apm_ring_load_all(apm_ctx* c, int32_t l, const double* values, uint32
 
 apm_status apm_ring_read(apm_ctx* c, uint32_t key, int32_t l, int32_t series, double* values, uint32_t cap, uint32_t* len_out) {
     if (!c || !len_out) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!with_z(c) || l < 0 || l >= c->cfg.num_lags || series < 0 || series >= APM_NUM_SERIES || key >= c->K) return apm_fail(c, APM_E_INVALID, "ring_read: index");
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
@@ -977,6 +1021,7 @@ int64_t apm_latest(const apm_ctx* c) { return c ? c->latest : 0; }
 
 apm_status apm_set_latest(apm_ctx* c, int64_t latest) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     if (latest <= 0) return apm_fail(c, APM_E_INVALID, "set_latest: label must be positive");
     apm_status st = sync_all(c);
     if (st) return st;
@@ -997,6 +1042,7 @@ apm_status apm_set_latest(apm_ctx* c, int64_t latest) {
 
 apm_status apm_mark_seen(apm_ctx* c, uint32_t key_lo, uint32_t n) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     if ((uint64_t)key_lo + n > c->K) return apm_fail(c, APM_E_INVALID, "mark_seen: range");
     apm_status st = sync_all(c);
     if (st) return st;
@@ -1006,6 +1052,7 @@ apm_status apm_mark_seen(apm_ctx* c, uint32_t key_lo, uint32_t n) {
 
 apm_status apm_log_read(apm_ctx* c, int64_t label, uint64_t* out, uint64_t cap, uint64_t* n) {
     if (!c || !n) return APM_E_INVALID;
+    APM_ENTER(c);
     *n = 0;
     if (!c->log_cap) return apm_fail(c, APM_E_STATE, "value logs are only kept with APM_F_PERCENTILES");
     apm_status st = sync_all(c);
@@ -1025,6 +1072,7 @@ apm_status apm_log_read(apm_ctx* c, int64_t label, uint64_t* out, uint64_t cap, 
 
 apm_status apm_get_counters(apm_ctx* c, apm_counters* out) {
     if (!c || !out) return APM_E_INVALID;
+    APM_ENTER(c);
     apm_status st = refresh_counters(c);
     // keys_seen: count on the host (called rarely)
     std::vector<uint8_t> seen(c->K);
@@ -1038,6 +1086,7 @@ apm_status apm_get_counters(apm_ctx* c, apm_counters* out) {
 
 apm_status apm_reset_counters(apm_ctx* c) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     CUDA_TRY(c, cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->s_main));
     memset(&c->counters, 0, sizeof c->counters);
     c->launches = 0;
@@ -1097,6 +1146,7 @@ apm_status apm_owner_table_build(const uint64_t* key_counts, uint32_t num_keys, 
 // Device-side stopwatch on the context's stream (what bench.py brackets its timed region with).
 extern "C" apm_status apm_timer_start(apm_ctx* c) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!c->timer[0]) { CUDA_TRY(c, cudaEventCreate(&c->timer[0])); CUDA_TRY(c, cudaEventCreate(&c->timer[1])); }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
@@ -1107,6 +1157,7 @@ extern "C" apm_status apm_timer_start(apm_ctx* c) {
 
 extern "C" apm_status apm_timer_stop(apm_ctx* c, double* ms) {
     if (!c || !ms) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!c->timer[0]) return apm_fail(c, APM_E_STATE, "timer_stop without timer_start");
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
@@ -1121,12 +1172,14 @@ extern "C" apm_status apm_timer_stop(apm_ctx* c, double* ms) {
 
 extern "C" apm_status apm_profile_enable(apm_ctx* c, int32_t on) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     c->prof_on = on != 0;
     return APM_OK;
 }
 
 extern "C" apm_status apm_profile_read(apm_ctx* c, apm_kernel_times* out) {
     if (!c || !out) return APM_E_INVALID;
+    APM_ENTER(c);
     memset(out, 0, sizeof *out);
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
@@ -1147,6 +1200,7 @@ extern "C" apm_status apm_profile_read(apm_ctx* c, apm_kernel_times* out) {
 // Run the rolling baseline on its own stream under the next tick's ingest/sort (default), or in line.
 extern "C" apm_status apm_set_overlap(apm_ctx* c, int32_t on) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     apm_status st = sync_all(c);
     if (st) return st;
     c->overlap = on != 0;

@@ -79,10 +79,10 @@ apm_status apm_comm_unique_id(void* out128) {
 
 apm_status apm_comm_init(apm_ctx* c, int32_t rank, int32_t nranks, const void* unique_id128) {
     if (!c || !unique_id128 || nranks < 1 || rank < 0 || rank >= nranks) return APM_E_INVALID;
+    APM_ENTER(c);
     if (!c->d_alerts) return apm_fail(c, APM_E_STATE, "comm_init needs APM_F_ALERTS | APM_F_ZSCORE");
     NcclApi& a = nccl();
     if (!a.error.empty()) return apm_fail(c, APM_E_COMM, a.error);
-    CUDA_TRY(c, cudaSetDevice(c->cfg.device));
     nccl_unique_id id;
     memcpy(&id, unique_id128, 128);
     nccl_comm_t comm = nullptr;
@@ -100,6 +100,7 @@ apm_status apm_comm_init(apm_ctx* c, int32_t rank, int32_t nranks, const void* u
 
 apm_status apm_gather_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint64_t* n) {
     if (!c || !n) return APM_E_INVALID;
+    APM_ENTER(c);
     *n = 0;
     if (!c->nccl_comm) return apm_fail(c, APM_E_STATE, "apm_comm_init has not been called");
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }

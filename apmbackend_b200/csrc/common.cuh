@@ -8,7 +8,29 @@
 #include "../../include/apm_b200.h"
 
 #define APM_MAX_SLOTS 64  // window + buffer + 1 must not exceed this
-#define APM_NUM_SMS 148   // B200
+#define APM_MAX_DEVICES 64
+
+// SMs of the current device (148 on B200), asked once per device ordinal: grids are sized in multiples of it.
+int apm_sm_count();
+// True exactly once per device ordinal and `done` mask: kernel attributes such as the dynamic shared-memory
+// limit belong to the device that is current when they are set, so a process that holds contexts on several
+// GPUs has to set them on each.
+bool apm_first_on_device(unsigned long long* done);
+
+// Makes `device` current for the duration of an entry point and restores the caller's device afterwards:
+// one host process may drive a context per GPU (the reference stage is one process, apm_manager.js:329-347).
+struct ApmDeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    explicit ApmDeviceGuard(int device) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; cudaGetLastError(); }
+        if (prev != device) switched = cudaSetDevice(device) == cudaSuccess;
+    }
+    ~ApmDeviceGuard() { if (switched && prev >= 0) cudaSetDevice(prev); }
+    ApmDeviceGuard(const ApmDeviceGuard&) = delete;
+    ApmDeviceGuard& operator=(const ApmDeviceGuard&) = delete;
+};
+#define APM_ENTER(ctx) ApmDeviceGuard apm_device_guard_((ctx)->cfg.device)
 
 // (key, bucket-slot) accumulators: everything addData (stream_calc_stats.js:115-134) would
 // have appended to buckets[label], reduced to order-independent integers.  Structure of

@@ -24,6 +24,7 @@ struct PendingBaseline {
 struct apm_ctx {
     apm_config cfg;
     uint32_t K = 0;       // keys = num_services * num_jvms
+    int num_sms = 148;    // SMs of cfg.device
     int S = 0;            // bucket slots = window + buffer + 1 (labels latest-keep .. latest)
     int keep = 0;         // NUM_KEEP_INTERVALS = window + buffer (stream_calc_stats.js:233)
     int64_t latest = 0;   // latestBucket (:42)

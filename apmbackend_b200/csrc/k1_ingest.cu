@@ -624,18 +624,17 @@ apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin
     p.tiles = (uint32_t)tiles;
     // every CTA flushes its table once: give each at least k1_tiles_per_cta tiles, cap at 2 CTAs per SM
     uint64_t blocks = (tiles + c->k1_tiles_per_cta - 1) / c->k1_tiles_per_cta;
-    const uint64_t max_blocks = (uint64_t)APM_NUM_SMS * 2;
+    const uint64_t max_blocks = (uint64_t)c->num_sms * 2;
     if (blocks > max_blocks) blocks = max_blocks;
     if (blocks < 1) blocks = 1;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static unsigned long long attr_done = 0;  // per device: the limit belongs to the device that is current when it is set
+    if (apm_first_on_device(&attr_done)) {
         CUDA_TRY(c, cudaFuncSetAttribute(reduce_kernel_v3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem)));
         CUDA_TRY(c, cudaFuncSetAttribute(reduce_kernel_v3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem)));
-        attr_set = true;
     }
     if (p.with_log) {
         // append-only: no table in shared memory and none to flush, so the tiles spread over every SM (2 CTAs each: 64 registers per thread)
-        const uint64_t cap4 = (uint64_t)APM_NUM_SMS * 2;
+        const uint64_t cap4 = (uint64_t)c->num_sms * 2;
         uint64_t b2 = tiles < cap4 ? tiles : cap4;
         reduce_kernel_v3<false><<<(unsigned)b2, K1_THREADS, K1_SMEM_APPEND_ONLY, c->s_main>>>(p);
     } else {

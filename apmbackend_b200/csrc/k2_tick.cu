@@ -331,7 +331,7 @@ apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask) {
     ProfScope prof_scope_(c, APM_PG_CLEAR);
     if (!slot_mask) return APM_OK;
     unsigned gx = (c->K + 255) / 256;
-    if (gx > APM_NUM_SMS * 4) gx = APM_NUM_SMS * 4;
+    if (gx > (unsigned)c->num_sms * 4) gx = (unsigned)c->num_sms * 4;
     clear_slots_kernel<<<dim3(gx, c->S), 256, 0, c->s_main>>>(c->acc, c->slot_meta, c->K, slot_mask);
     c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());

@@ -311,19 +311,20 @@ uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t 
         narrow_ok = e ? atoi(e) != 0 : 1;
     }
     const bool narrow = narrow_ok && vbits + kbits <= 32 && vbits < 32;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(os_pass_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<false>::bytes(2048));
-        cudaFuncSetAttribute(os_pass_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<true>::bytes(2048));
-        cudaFuncSetAttribute(os_pass_kernel<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<false>::bytes(256));
-        cudaFuncSetAttribute(os_pass_kernel<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<true>::bytes(256));
-        cudaFuncSetAttribute(os_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_MAX_PASSES * 2048 * 4);
-        attr_set = true;
+    static unsigned long long attr_done = 0;  // per device ordinal
+    if (apm_first_on_device(&attr_done)) {
+        cudaError_t ea = cudaFuncSetAttribute(os_pass_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<false>::bytes(2048));
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(os_pass_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<true>::bytes(2048));
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(os_pass_kernel<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<false>::bytes(256));
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(os_pass_kernel<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OsSmemLayout<true>::bytes(256));
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(os_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OS_MAX_PASSES * 2048 * 4);
+        if (ea != cudaSuccess) { attr_done = 0; *err = ea; return nullptr; }
     }
     *err = cudaMemsetAsync(scratch, 0, head + status_bytes, st);
     if (*err != cudaSuccess) return nullptr;
     unsigned hg = (unsigned)((n + OS_THREADS * 16 - 1) / (OS_THREADS * 16));
-    if (hg > 148 * 4) hg = 148 * 4;
+    const unsigned hg_cap = (unsigned)apm_sm_count() * 4;
+    if (hg > hg_cap) hg = hg_cap;
     os_hist_kernel<<<hg, OS_THREADS, (size_t)plan.npass * 2048 * 4, st>>>(a, n, plan, ghist);
     os_scan_kernel<<<plan.npass, 1024, 0, st>>>(ghist);
     uint64_t* src = a;

@@ -96,7 +96,7 @@ apm_status run_percentiles(unsigned char* scratch, const int32_t* d_values, uint
         // the scratch keeps the previous call's contents: the one word that is accumulated into is cleared
         CUDA_TRY(nullptr, cudaMemsetAsync(dmax, 0, sizeof(uint32_t), st));
         const unsigned g = (n + 255) / 256;
-        max_kernel<<<g < 1184 ? g : 1184, 256, 0, st>>>(d_values, n, dmax);
+        max_kernel<<<g < (unsigned)apm_sm_count() * 8 ? g : (unsigned)apm_sm_count() * 8, 256, 0, st>>>(d_values, n, dmax);
         widen_kernel<<<g, 256, 0, st>>>(d_values, a, n);
         uint32_t hmax = 0;
         CUDA_TRY(nullptr, cudaMemcpyAsync(&hmax, dmax, sizeof hmax, cudaMemcpyDeviceToHost, st));

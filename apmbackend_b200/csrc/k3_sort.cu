@@ -386,7 +386,7 @@ apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value)
 apm_status apm_acc_from_sorted(apm_ctx* c, int slot, uint64_t n) {
     ProfScope prof_scope_(c, APM_PG_REDUCE);
     unsigned g = (c->K + 255) / 256;
-    clear_planes_kernel<<<g < 592 ? g : 592, 256, 0, c->s_main>>>(c->acc, c->K, slot, c->slot_meta, n);
+    clear_planes_kernel<<<g < (unsigned)c->num_sms * 4 ? g : (unsigned)c->num_sms * 4, 256, 0, c->s_main>>>(c->acc, c->K, slot, c->slot_meta, n);
     c->launches += 1;
     if (n) {
         const uint64_t per_block = (uint64_t)AS_THREADS * AS_ITEMS;

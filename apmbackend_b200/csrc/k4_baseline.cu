@@ -747,7 +747,7 @@ apm_status apm_launch_baseline(apm_ctx* c, int l, int64_t tick_ts, uint32_t tick
         // flight with 4 x 4 KB stages: the list walk is then bound by load latency, not by HBM.
         // Below two CTAs per SM the deep instance (24 stages, 96 KB in flight per CTA) is used.
         int stages = c->k4_stages;
-        if (stages == 0) stages = g <= 2 * APM_NUM_SMS ? K4T_DEEP_STAGES : 4;
+        if (stages == 0) stages = g <= 2u * (unsigned)c->num_sms ? K4T_DEEP_STAGES : 4;
 #define APM_K4T_LAUNCH(NS, M) baseline_tma_kernel<NS, M><<<g, 32, sizeof(K4TSmem<NS, M>) + 128, st>>>(c->ring_tmap[l], p)
         switch (stages) {
             case 2: APM_K4T_LAUNCH(2, 1); break;
@@ -807,7 +807,6 @@ apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t aler
                                                     c->d_alert_count + alert_slot, c->cfg.max_alerts_per_tick, c->alert_rules.enabled,
                                                     c->d_alert_blocks);
     c->launches += 2;
-    c->launches += 1;
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;
 }

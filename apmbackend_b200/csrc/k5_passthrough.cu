@@ -167,6 +167,7 @@ apm_status apm_pt_tick(apm_ctx* c, int64_t edge_ts, uint32_t tick_slot) {
 extern "C" apm_status apm_fetch_passthrough(apm_ctx* c, int64_t* end_ts, uint32_t* seq, uint64_t cap, uint64_t* n, uint32_t* tick_counts,
                                             uint32_t tick_cap, uint32_t* nticks) {
     if (!c || !n) return APM_E_INVALID;
+    APM_ENTER(c);
     *n = 0;
     if (nticks) *nticks = 0;
     if (!c->pt_pend[0]) return apm_fail(c, APM_E_STATE, "passthrough is off (APM_F_PASSTHROUGH)");

@@ -640,6 +640,7 @@ uint64_t apm_name_hash(const char* s, uint64_t len) {
 
 apm_status apm_dict_set(apm_ctx* c, const uint64_t* name_hashes, const uint32_t* service_ids, uint32_t n) {
     if (!c || (n && (!name_hashes || !service_ids))) return APM_E_INVALID;
+    APM_ENTER(c);
     LogParseState* s = lp_state(c);
     uint32_t size = 16;
     while (size < 2u * n + 2u) size <<= 1;
@@ -670,6 +671,7 @@ apm_status apm_parse_log_host(apm_ctx* c, const char* text, uint64_t nbytes, uin
                               const apm_tz_rule* tz, uint32_t num_tz, apm_log_record* out, uint64_t cap, uint64_t* n_out,
                               apm_parse_result* result) {
     if (!c || (nbytes && !text) || (num_tz && !tz)) return APM_E_INVALID;
+    APM_ENTER(c);
     if (n_out) *n_out = 0;
     if (result) memset(result, 0, sizeof *result);
     if (num_tz > APM_MAX_TZ_RULES) return apm_fail(c, APM_E_INVALID, "parse_log: more than APM_MAX_TZ_RULES zone rules");
@@ -864,6 +866,7 @@ apm_status apm_parse_log_host(apm_ctx* c, const char* text, uint64_t nbytes, uin
 
 apm_status apm_feed_parsed(apm_ctx* c, apm_tick_result* result) {
     if (!c) return APM_E_INVALID;
+    APM_ENTER(c);
     if (result) memset(result, 0, sizeof *result);
     if (!c->lp) return apm_fail(c, APM_E_STATE, "feed_parsed: nothing was parsed");
     LogParseState* s = static_cast<LogParseState*>(c->lp);

@@ -54,6 +54,7 @@ extern "C" {
 
 apm_status apm_state_save(apm_ctx* c, const char* path) {
     if (!c || !path) return APM_E_INVALID;
+    APM_ENTER(c);
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
@@ -97,6 +98,7 @@ apm_status apm_state_save(apm_ctx* c, const char* path) {
 
 apm_status apm_state_load(apm_ctx* c, const char* path) {
     if (!c || !path) return APM_E_INVALID;
+    APM_ENTER(c);
     CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
