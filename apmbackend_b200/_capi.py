@@ -100,6 +100,19 @@ class TxPacked(C.Structure):
     _fields_ = [("key", C.c_void_p), ("end_ts_delta_ms", C.c_void_p), ("elapsed_ms", C.c_void_p)]
 
 
+class TickMark(C.Structure):
+    """apm_tick_mark: the tick for bucket `label` fires before transaction `pos` of the next process_* call."""
+    _fields_ = [("pos", C.c_uint64), ("label", C.c_int64)]
+
+
+MARK_DTYPE = np.dtype([("pos", "<u8"), ("label", "<i8")])
+
+
+class PartitionOut(C.Structure):
+    _fields_ = [("cols", TxColumns), ("cap", C.c_uint64), ("n", C.c_uint64), ("marks", C.c_void_p),
+                ("marks_cap", C.c_uint32), ("num_marks", C.c_uint32)]
+
+
 class ParseResult(C.Structure):
     _fields_ = [("lines", C.c_uint64), ("records", C.c_uint64), ("exits", C.c_uint64), ("fed", C.c_uint64),
                 ("unknown_service", C.c_uint64), ("malformed", C.c_uint64)]
@@ -163,6 +176,11 @@ SYMBOLS = {
     "apm_parse_log_host": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
                                        C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(ParseResult)]),
     "apm_feed_parsed": (C.c_int32, [C.c_void_p, C.POINTER(TickResult)]),
+    "apm_comm_set_capacity": (C.c_int32, [C.c_void_p, C.c_uint32]),
+    "apm_bind_gather_output": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "apm_set_tick_marks": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32]),
+    "apm_partition_host": (C.c_int32, [C.POINTER(TxColumns), C.c_uint64, C.c_int64, C.c_int64, C.c_uint32, C.c_uint32,
+                                       C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64)]),
 }
 
 

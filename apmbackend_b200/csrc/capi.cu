@@ -148,6 +148,10 @@ apm_status launch_baseline_group(apm_ctx* c, const PendingBaseline& pb, cudaStre
     if (c->cfg.flags & APM_F_ALERTS) {
         st = apm_launch_compact_alerts(c, pb.fslot, pb.tslot, sb);
         if (st) return st;
+        if (c->h_gather_bound) {  // all-gathered while the next ticks run
+            st = apm_comm_tick_gather(c, pb.tslot, sb);
+            if (st) return st;
+        }
     }
     if (c->h_fs_bound && (c->cfg.flags & APM_F_KEEP_FS)) {
         // this tick's records go to the bound pinned buffer on their own stream, under the following ticks
@@ -162,6 +166,12 @@ apm_status launch_baseline_group(apm_ctx* c, const PendingBaseline& pb, cudaStre
     }
     return APM_OK;
 }
+
+// host-located ticks are consumed by one process_* call, whether it succeeds or not
+struct ExtMarksScope {
+    apm_ctx* c;
+    ~ExtMarksScope() { c->ext_armed = false; c->ext_marks.clear(); c->ext_next = 0; }
+};
 
 // The tick itself: everything consumeMsg does inside `if (bucketLabel > latestBucket)`
 // (stream_calc_stats.js:348-367) and, behind it, processData for each emitted StatEntry.
@@ -286,12 +296,28 @@ apm_status run_chunk(apm_ctx* c, const apm_tx_columns& d, uint64_t n, const apm_
     return APM_OK;
 }
 
+// A call without transactions that still carries host-located ticks (a key shard that is silent while the global
+// stream ticks, stream_calc_stats.js:348: the tick is triggered by ANY transaction): run them.
+apm_status run_marks_only(apm_ctx* c, apm_tick_result* res) {
+    if (!c->ext_armed) return APM_OK;
+    for (; c->ext_next < c->ext_marks.size(); ++c->ext_next) {
+        const TickMark& m = c->ext_marks[c->ext_next];
+        if (m.pos != 0) return apm_fail(c, APM_E_INVALID, "tick mark beyond the call's transactions");
+        apm_status st = do_tick(c, m.label);
+        if (st) return st;
+        if (res) res->ticks += 1;
+    }
+    return APM_OK;
+}
+
 // one chunk, pre-pass and ticks on the ingest stream (callers that have a single chunk)
 apm_status process_chunk_device(apm_ctx* c, const apm_tx_columns& d, uint64_t n, apm_tick_result* res) {
     // The baseline of the last tick is normally launched behind the next segment's ingest kernel.  The host is
     // about to block on the tick marks and the segment table: launch it now, or the baseline stream idles.
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     apm_ctx::PrePass& pp = c->pre[0];
+    c->ext_off = 0;
+    c->ext_last = true;
     apm_status st = apm_prepass_begin(c, pp, d, n, c->latest, c->s_main);
     if (st) return st;
     st = apm_prepass_finish(c, pp, d, n, c->s_main);
@@ -327,6 +353,8 @@ static apm_status fetch_dense(apm_ctx* c, const R* d_src, size_t per_tick, R* ou
 // surfaces a value-log overflow as APM_E_CAPACITY
 static apm_status finish_result(apm_ctx* c, const apm_counters& before, apm_tick_result* res) {
     apm_status st = refresh_counters(c);
+    if (!st && c->ext_armed && c->ext_next < c->ext_marks.size())
+        st = apm_fail(c, APM_E_INVALID, "tick mark beyond the call's transactions");
     if (res) {
         res->tx_ingested = c->counters.tx_ingested - before.tx_ingested;
         res->tx_dropped = c->counters.tx_dropped - before.tx_dropped;
@@ -373,13 +401,19 @@ apm_status process_host_chunks(apm_ctx* c, uint64_t n, apm_tick_result* res, Cop
         CUDA_TRY(c, cudaEventRecord(c->ev_copied[b], c->s_copy));
         return APM_OK;
     };
-    if (nchunks == 0) return finish_result(c, before, res);
+    if (nchunks == 0) {
+        apm_status st0 = run_marks_only(c, res);  // a shard that is silent for the whole call still ticks
+        if (st0) return st0;
+        return finish_result(c, before, res);
+    }
     // Pipeline: while the ticks of chunk i are queued and run (ingest stream), chunk i + 1 is copied (copy stream)
     // and its pre-pass - tick finder, segment table, their host round trips - runs on the pre-pass stream.
     CUDA_TRY(c, cudaStreamSynchronize(c->s_pre));
     apm_status st = copy(0);
     if (st) return st;
     CUDA_TRY(c, cudaStreamWaitEvent(c->s_pre, c->ev_copied[0], 0));
+    c->ext_off = 0;
+    c->ext_last = nchunks == 1;
     st = apm_prepass_begin(c, c->pre[0], c->dev[0], chunks[0].second, c->latest, c->s_pre);
     if (st) return st;
     if (nchunks > 1) { st = copy(1); if (st) return st; }
@@ -390,6 +424,8 @@ apm_status process_host_chunks(apm_ctx* c, uint64_t n, apm_tick_result* res, Cop
         const bool more = ci + 1 < nchunks;
         if (more) {  // the next chunk's tick finder starts as soon as its copy has landed
             CUDA_TRY(c, cudaStreamWaitEvent(c->s_pre, c->ev_copied[b ^ 1], 0));
+            c->ext_off = chunks[ci + 1].first;
+            c->ext_last = ci + 2 == nchunks;
             st = apm_prepass_begin(c, c->pre[b ^ 1], c->dev[b ^ 1], chunks[ci + 1].second, latest_after(c->pre[b]), c->s_pre);
             if (st) return st;
         }
@@ -458,7 +494,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->d_alert_blocks); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
     for (int l = 0; l < APM_MAX_LAGS; ++l) { cudaFree(c->ring[l]); cudaFree(c->ring_len[l]); cudaFree(c->ring_next[l]);
         cudaFree(c->inc_sum[l]); cudaFree(c->inc_comp[l]); cudaFree(c->inc_cnt[l]); cudaFree(c->inc_nz[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
-    cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->d_gather);
+    cudaFree(c->d_counters); cudaFreeHost(c->h_counters);
     cudaFree(c->alert_count); cudaFree(c->alert_hard_max); cudaFree(c->alert_suppressed);
     cudaFree(c->pt_pend[0]); cudaFree(c->pt_pend[1]); cudaFree(c->pt_emit); cudaFree(c->pt_tmp); cudaFree(c->pt_out); cudaFree(c->pt_cursors);
     for (int i = 0; i < 2; ++i) { if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); if (c->ev_consumed[i]) cudaEventDestroy(c->ev_consumed[i]); }
@@ -716,11 +752,13 @@ apm_status apm_tick(apm_ctx* c, int64_t latest_bucket, apm_tick_result* res) {
 apm_status apm_process_device(apm_ctx* c, const apm_tx_columns* cols, uint64_t n, apm_tick_result* res) {
     if (!c || !cols) return APM_E_INVALID;
     APM_ENTER(c);
+    ExtMarksScope ext_scope_{c};
     if (res) memset(res, 0, sizeof *res);
     const apm_counters before = c->counters;
     const uint64_t B = c->cfg.max_batch;
     if (n <= B) {
-        if (n) { apm_status st = process_chunk_device(c, *cols, n, res); if (st) return st; }
+        apm_status st = n ? process_chunk_device(c, *cols, n, res) : run_marks_only(c, res);
+        if (st) return st;
         return finish_result(c, before, res);
     }
     // several chunks: the pre-pass of chunk i + 1 runs on its own stream while the ticks of chunk i are queued
@@ -733,6 +771,8 @@ apm_status apm_process_device(apm_ctx* c, const apm_tx_columns* cols, uint64_t n
     CUDA_TRY(c, cudaStreamSynchronize(c->s_pre));
     uint64_t m = 0, m1 = 0;
     apm_tx_columns d = chunk(0, &m);
+    c->ext_off = 0;
+    c->ext_last = false;
     apm_status st = apm_prepass_begin(c, c->pre[0], d, m, c->latest, c->s_pre);
     if (st) return st;
     st = apm_prepass_finish(c, c->pre[0], d, m, c->s_pre);
@@ -743,6 +783,8 @@ apm_status apm_process_device(apm_ctx* c, const apm_tx_columns* cols, uint64_t n
         apm_tx_columns d1 = d;
         if (more) {
             d1 = chunk(ci + 1, &m1);
+            c->ext_off = (ci + 1) * B;
+            c->ext_last = ci + 2 == nchunks;
             st = apm_prepass_begin(c, c->pre[b ^ 1], d1, m1, latest_after(c->pre[b]), c->s_pre);
             if (st) return st;
         }
@@ -762,6 +804,7 @@ apm_status apm_process_device(apm_ctx* c, const apm_tx_columns* cols, uint64_t n
 apm_status apm_process_host(apm_ctx* c, const apm_tx_columns* h, uint64_t n, apm_tick_result* res) {
     if (!c || !h) return APM_E_INVALID;
     APM_ENTER(c);
+    ExtMarksScope ext_scope_{c};
     return process_host_chunks(c, n, res, [&](uint64_t off, uint64_t m, int b) -> apm_status {
         apm_tx_columns& d = c->dev[b];
         CUDA_TRY(c, cudaMemcpyAsync(d.service_id, h->service_id + off, m * 4, cudaMemcpyHostToDevice, c->s_copy));
@@ -776,6 +819,7 @@ apm_status apm_process_host(apm_ctx* c, const apm_tx_columns* h, uint64_t n, apm
 apm_status apm_process_host_packed(apm_ctx* c, const apm_tx_packed* h, int64_t base_ts_ms, uint64_t n, apm_tick_result* res) {
     if (!c || !h) return APM_E_INVALID;
     APM_ENTER(c);
+    ExtMarksScope ext_scope_{c};
     if (base_ts_ms < 0) return apm_fail(c, APM_E_INVALID, "process_host_packed: base_ts_ms must not be negative");
     if (!c->pk[0]) {  // 12-byte staging, one third of the wide staging, created at the first packed call
         for (int i = 0; i < 2; ++i) CUDA_TRY(c, cudaMalloc((void**)&c->pk[i], c->cfg.max_batch * 3 * sizeof(uint32_t)));
@@ -792,6 +836,26 @@ apm_status apm_process_host_packed(apm_ctx* c, const apm_tx_packed* h, int64_t b
         c->counters.h2d_bytes += m * 12;
         return APM_OK;
     });
+}
+
+apm_status apm_set_tick_marks(apm_ctx* c, const apm_tick_mark* marks, uint32_t n) {
+    if (!c || (!marks && n)) return APM_E_INVALID;
+    c->ext_marks.clear();
+    c->ext_next = 0;
+    int64_t prev = c->latest;
+    uint64_t pos = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        if (marks[i].pos < pos || marks[i].label <= prev) {
+            c->ext_armed = false;
+            c->ext_marks.clear();
+            return apm_fail(c, APM_E_INVALID, "tick marks must be ascending in position and strictly ascending in label, above latestBucket");
+        }
+        pos = marks[i].pos;
+        prev = marks[i].label;
+        c->ext_marks.push_back(TickMark{(unsigned long long)marks[i].pos, (long long)marks[i].label});
+    }
+    c->ext_armed = true;  // even with n == 0: the next call then runs without any tick
+    return APM_OK;
 }
 
 apm_status apm_set_key_params(apm_ctx* c, uint32_t key_lo, uint32_t n, int32_t l, const double* thr, const double* infl) {
@@ -936,6 +1000,7 @@ apm_status apm_release_ticks(apm_ctx* c) {
     if (c->d_alert_count) {
         { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
         CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
+        { apm_status cr_ = apm_comm_release(c); if (cr_) return cr_; }  // the gather stream still reads the alert blocks
         CUDA_TRY(c, cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * c->cfg.out_ticks, c->s_main));
         CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
     }
@@ -1138,6 +1203,50 @@ apm_status apm_owner_table_build(const uint64_t* key_counts, uint32_t num_keys, 
         }
         load[r] += w[k];
     }
+    return APM_OK;
+}
+
+// Host binning for key-sharded deployments (pure host arithmetic).  One pass over the arrival-ordered global stream:
+// every valid transaction goes to the rank that owns its key, arrival order kept inside a rank, and every rank learns
+// where the GLOBAL stream ticks - the running maximum of the bucket label over all transactions, whoever owns them
+// (stream_calc_stats.js:348) - as the number of its own transactions that precede the trigger.
+apm_status apm_partition_host(const apm_tx_columns* cols, uint64_t n, int64_t bucket_ms, int64_t latest_bucket,
+                              uint32_t num_services, uint32_t num_jvms, uint32_t nranks, const uint32_t* owner_table,
+                              const uint32_t* local_id, apm_partition_out* out, int64_t* latest_out) {
+    if ((!cols && n) || !out || nranks == 0 || bucket_ms <= 0 || num_services == 0 || num_jvms == 0)
+        return apm_fail(nullptr, APM_E_INVALID, "apm_partition_host: bad argument");
+    for (uint32_t r = 0; r < nranks; ++r) { out[r].n = 0; out[r].num_marks = 0; }
+    int64_t latest = latest_bucket;
+    for (uint64_t i = 0; i < n; ++i) {
+        const uint32_t sv = cols->service_id[i], jv = cols->jvm_id[i];
+        const int64_t ts = cols->end_ts_ms[i];
+        const int64_t lab = ts >= 0 ? ts / bucket_ms : -1;
+        if (lab > latest) {  // the tick fires before this transaction is added, on every rank
+            latest = lab;
+            for (uint32_t r = 0; r < nranks; ++r) {
+                apm_partition_out& o = out[r];
+                if (o.num_marks >= o.marks_cap) return apm_fail(nullptr, APM_E_CAPACITY, "apm_partition_host: marks_cap too small");
+                o.marks[o.num_marks].pos = o.n;
+                o.marks[o.num_marks].label = lab;
+                o.num_marks++;
+            }
+        }
+        uint32_t r = 0, s_out = sv, j_out = jv;
+        if (sv < num_services && jv < num_jvms) {
+            const uint64_t key = (uint64_t)jv * num_services + sv;
+            r = owner_table ? owner_table[key] : apm_owner_of_key(key, nranks);
+            if (r >= nranks) return apm_fail(nullptr, APM_E_INVALID, "apm_partition_host: owner_table entry out of range");
+            if (local_id) { s_out = local_id[key]; j_out = 0; }
+        }  // else: an invalid transaction; rank 0 counts it
+        apm_partition_out& o = out[r];
+        if (o.n >= o.cap) return apm_fail(nullptr, APM_E_CAPACITY, "apm_partition_host: a rank's output columns are full");
+        o.cols.service_id[o.n] = s_out;
+        o.cols.jvm_id[o.n] = j_out;
+        o.cols.end_ts_ms[o.n] = ts;
+        o.cols.elapsed_ms[o.n] = cols->elapsed_ms[i];
+        o.n++;
+    }
+    if (latest_out) *latest_out = latest;
     return APM_OK;
 }
 

@@ -74,6 +74,7 @@ struct apm_ctx {
         uint32_t* h_seg_counts = nullptr;   // pinned
         uint32_t seg_max = 0;
         unsigned int nt = 0;                // ticks inside the chunk
+        bool external = false;              // the marks came from the host (apm_set_tick_marks), not from the tick finder
         int64_t latest0 = 0;                // latestBucket before the chunk
         cudaEvent_t ev = nullptr;           // the tick marks are on the host
     };
@@ -81,6 +82,13 @@ struct apm_ctx {
     cudaStream_t s_pre = nullptr;
     uint64_t tf_tiles_cap = 0;
     uint32_t max_ticks_per_chunk = 4096;
+    // ticks the host has already located (apm_set_tick_marks; key-sharded deployments, where a tick is a property of the
+    // global stream): they replace the tick finder for the next process_* call, which consumes them chunk by chunk
+    std::vector<TickMark> ext_marks;
+    bool ext_armed = false;
+    size_t ext_next = 0;        // first mark not yet handed to a chunk
+    uint64_t ext_off = 0;       // offset, inside the call, of the chunk whose pre-pass is being started
+    bool ext_last = false;      // ... and whether it is the call's last chunk (takes the marks at pos == n)
     uint64_t host_count[APM_MAX_SLOTS];   // log entries per slot (== SlotMeta.count)
     uint64_t host_sorted[APM_MAX_SLOTS];  // entries that were in place at the slot's last sort
     uint32_t known_max_value = 0;         // largest duration appended to any log so far
@@ -154,7 +162,17 @@ struct apm_ctx {
     // multi-GPU
     void* nccl_comm = nullptr;
     int rank = 0, nranks = 1;
-    apm_fs_record* d_gather = nullptr;  // [nranks][1 + max_alerts_per_tick * out_ticks] blocks
+    // alert all-gather (comm.cu): one fixed-size block {header, records[gather_cap]} per rank and collective
+    uint32_t gather_cap = 0;
+    apm_fs_record* d_gather_send = nullptr;   // [1 + gather_cap]
+    apm_fs_record* d_gather_recv = nullptr;   // [nranks][1 + gather_cap]
+    apm_fs_record* d_gather_stage = nullptr;  // [nranks * gather_cap]: unpacked records for callers without a pinned buffer
+    void* d_gather_state = nullptr;           // GatherState: records appended so far, error bits
+    void* h_gather_state = nullptr;           // pinned copy, refreshed behind every collective
+    cudaStream_t s_comm = nullptr;            // pack -> ncclAllGather -> unpack, beside the baseline stream
+    cudaEvent_t ev_comm = nullptr;
+    apm_fs_record* h_gather_bound = nullptr;  // apm_bind_gather_output: every tick's alerts are gathered as the tick finishes
+    uint64_t h_gather_bound_cap = 0;
 
     // optional per-kernel-group timing (CUDA events on s_main around each launch)
     bool prof_on = false;
@@ -217,5 +235,7 @@ apm_status apm_pt_tick(apm_ctx* c, int64_t edge_ts, uint32_t tick_slot);
 void apm_lp_destroy(apm_ctx* c);
 // comm.cu
 void apm_comm_destroy_internal(apm_ctx* c);
+apm_status apm_comm_tick_gather(apm_ctx* c, uint32_t alert_slot, cudaStream_t after);  // bound mode: this tick's alerts
+apm_status apm_comm_release(apm_ctx* c);
 // capi.cu
 apm_status apm_flush_pending(apm_ctx* c);

@@ -533,7 +533,31 @@ apm_status apm_prepass_begin(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_colu
     pp.nt = 0;
     pp.seg_max = 0;
     pp.latest0 = latest0;
+    pp.external = false;
     *pp.h_nticks = 0;
+    if (c->ext_armed) {
+        // The host has located the ticks: this chunk takes the marks that fall inside it (the call's last chunk also the
+        // ones behind its last transaction), rebased to the chunk.  No tick finder runs.
+        pp.external = true;
+        unsigned int k = 0;
+        const uint64_t lo = c->ext_off, hi = c->ext_off + n;
+        int64_t prev = latest0;
+        while (c->ext_next < c->ext_marks.size()) {
+            const TickMark& m = c->ext_marks[c->ext_next];
+            if (m.pos > hi || (m.pos == hi && !c->ext_last)) break;
+            if (m.pos < lo || m.label <= prev)
+                return apm_fail(c, APM_E_INVALID, "tick marks must be ascending in position and strictly ascending in label, above latestBucket");
+            if (k >= c->max_ticks_per_chunk) return apm_fail(c, APM_E_CAPACITY, "too many ticks in one chunk");
+            pp.h_ticks[k].pos = m.pos - lo;
+            pp.h_ticks[k].label = m.label;
+            prev = m.label;
+            ++k;
+            ++c->ext_next;
+        }
+        *pp.h_nticks = k;
+        CUDA_TRY(c, cudaEventRecord(pp.ev, st));
+        return APM_OK;
+    }
     if (n == 0) { CUDA_TRY(c, cudaEventRecord(pp.ev, st)); return APM_OK; }
     const uint64_t ntiles = (n + TF_TILE - 1) / TF_TILE;
     if (ntiles > c->tf_tiles_cap) return apm_fail(c, APM_E_CAPACITY, "chunk larger than max_batch");
@@ -584,14 +608,16 @@ apm_status apm_prepass_finish(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_col
     CUDA_TRY(c, cudaEventSynchronize(pp.ev));
     const unsigned int nt = *pp.h_nticks;
     if (nt > c->max_ticks_per_chunk) return apm_fail(c, APM_E_CAPACITY, "too many ticks in one chunk");
-    const unsigned int first = c->max_ticks_per_chunk < PP_FIRST_MARKS ? c->max_ticks_per_chunk : PP_FIRST_MARKS;
-    if (nt > first) {
-        CUDA_TRY(c, cudaMemcpyAsync(pp.h_ticks + first, pp.d_ticks + first, (nt - first) * sizeof(TickMark), cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(c, cudaStreamSynchronize(st));
-    }
-    c->counters.d2h_bytes += sizeof(unsigned int) + (nt > first ? nt : first) * sizeof(TickMark);
     pp.nt = nt;
-    std::sort(pp.h_ticks, pp.h_ticks + nt, [](const TickMark& a, const TickMark& b) { return a.pos < b.pos; });
+    if (!pp.external) {
+        const unsigned int first = c->max_ticks_per_chunk < PP_FIRST_MARKS ? c->max_ticks_per_chunk : PP_FIRST_MARKS;
+        if (nt > first) {
+            CUDA_TRY(c, cudaMemcpyAsync(pp.h_ticks + first, pp.d_ticks + first, (nt - first) * sizeof(TickMark), cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(c, cudaStreamSynchronize(st));
+        }
+        c->counters.d2h_bytes += sizeof(unsigned int) + (nt > first ? nt : first) * sizeof(TickMark);
+        std::sort(pp.h_ticks, pp.h_ticks + nt, [](const TickMark& a, const TickMark& b) { return a.pos < b.pos; });
+    }
     if ((c->cfg.flags & APM_F_PERCENTILES) && c->cfg.num_percentiles > 0) return seg_table(c, pp, d, n, st);
     return APM_OK;
 }

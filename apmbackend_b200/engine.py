@@ -134,6 +134,13 @@ class Engine:
         self._check(self._lib.apm_process_device(self._h, C.byref(cols), n, C.byref(res)))
         return res
 
+    def set_tick_marks(self, marks):
+        """apm_set_tick_marks: the next process_* call ticks where the host says (key-sharded deployments; ticks are
+        global, stream_calc_stats.js:348).  marks: structured array (pos u64, label i64) or a sequence of pairs."""
+        m = np.ascontiguousarray(marks, dtype=_capi.MARK_DTYPE) if isinstance(marks, np.ndarray) else \
+            np.array([tuple(x) for x in marks], dtype=_capi.MARK_DTYPE)
+        self._check(self._lib.apm_set_tick_marks(self._h, m.ctypes.data if m.size else None, m.size))
+
     # ---- log feeder (SURVEY 8 f-3)
     @staticmethod
     def name_hash(name) -> int:
@@ -362,6 +369,14 @@ class Engine:
 
     def comm_init(self, rank: int, nranks: int, unique_id: bytes):
         self._check(self._lib.apm_comm_init(self._h, rank, nranks, unique_id))
+
+    def comm_set_capacity(self, records_per_block: int):
+        self._check(self._lib.apm_comm_set_capacity(self._h, int(records_per_block)))
+
+    def bind_gather_output(self, cap: int):
+        """Every tick's alerts are all-gathered as the tick finishes; gather_alerts(cap, pinned=True) then returns them."""
+        out = self._out_buffer("gather", _capi.FS_DTYPE, cap, True)
+        self._check(self._lib.apm_bind_gather_output(self._h, out.ctypes.data, out.size))
 
     def gather_alerts(self, cap: int, pinned: bool = False) -> np.ndarray:
         out = self._out_buffer("gather", _capi.FS_DTYPE, cap, pinned)

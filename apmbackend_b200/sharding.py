@@ -78,6 +78,67 @@ def tick_labels(end_ts_ms, bucket_ms: int, latest: int = 0) -> np.ndarray:
     return np.unique(run[1:][run[1:] > run[:-1]])
 
 
+def tick_marks(service_id, jvm_id, end_ts_ms, bucket_ms: int, num_services: int, nranks: int, latest: int = 0,
+               owner_table=None):
+    """Per rank, where the GLOBAL ticks fall inside that rank's sub-stream: a structured (pos, label) array per rank for
+    Engine.set_tick_marks.  pos = the rank's transactions that precede the trigger (numpy mirror of apm_partition_host;
+    assumes every transaction passes the apm_tx_columns preconditions)."""
+    from ._capi import MARK_DTYPE
+    ts = np.asarray(end_ts_ms, dtype=np.int64)
+    lab = np.where(ts >= 0, ts // bucket_ms, -1)
+    run = np.maximum.accumulate(np.concatenate([[latest], lab]))
+    trig = np.flatnonzero(run[1:] > run[:-1])          # global positions of the triggers
+    key = np.asarray(jvm_id, dtype=np.uint64) * np.uint64(num_services) + np.asarray(service_id, dtype=np.uint64)
+    own = owner_of_keys(key, nranks) if owner_table is None else np.asarray(owner_table, dtype=np.uint32)[key]
+    out = []
+    for r in range(nranks):
+        before = np.concatenate([[0], np.cumsum(own == r)])  # before[i] = rank-r transactions among the first i
+        m = np.zeros(trig.size, dtype=MARK_DTYPE)
+        m["pos"] = before[trig]
+        m["label"] = lab[trig]
+        out.append(m)
+    return out
+
+
+def partition_native(service_id, jvm_id, end_ts_ms, elapsed_ms, bucket_ms: int, num_services: int, num_jvms: int,
+                     nranks: int, latest: int = 0, owner_table=None, local_id=None):
+    """apm_partition_host through the C ABI: [(columns, marks)] per rank and latestBucket after the stream."""
+    import ctypes as C
+    from . import _capi
+    svc = np.ascontiguousarray(service_id, dtype=np.uint32)
+    jvm = np.ascontiguousarray(jvm_id, dtype=np.uint32)
+    ts = np.ascontiguousarray(end_ts_ms, dtype=np.int64)
+    el = np.ascontiguousarray(elapsed_ms, dtype=np.int32)
+    n = svc.size
+    lab = ts // bucket_ms
+    marks_cap = int(np.unique(lab).size) + 1
+    outs = (_capi.PartitionOut * nranks)()
+    bufs = []
+    for r in range(nranks):
+        b = (np.empty(n, np.uint32), np.empty(n, np.uint32), np.empty(n, np.int64), np.empty(n, np.int32),
+             np.zeros(marks_cap, _capi.MARK_DTYPE))
+        bufs.append(b)
+        outs[r].cols = _capi.TxColumns(b[0].ctypes.data, b[1].ctypes.data, b[2].ctypes.data, b[3].ctypes.data)
+        outs[r].cap = n
+        outs[r].marks = b[4].ctypes.data
+        outs[r].marks_cap = marks_cap
+    ot = None if owner_table is None else np.ascontiguousarray(owner_table, dtype=np.uint32)
+    li = None if local_id is None else np.ascontiguousarray(local_id, dtype=np.uint32)
+    cols = _capi.TxColumns(svc.ctypes.data, jvm.ctypes.data, ts.ctypes.data, el.ctypes.data)
+    latest_out = C.c_int64(0)
+    st = _capi.lib().apm_partition_host(C.byref(cols), n, int(bucket_ms), int(latest), int(num_services), int(num_jvms),
+                                        int(nranks), ot.ctypes.data if ot is not None else None,
+                                        li.ctypes.data if li is not None else None, outs, C.byref(latest_out))
+    if st != _capi.OK:
+        raise _capi.ApmError(st, (_capi.lib().apm_last_error(None) or b"").decode())
+    res = []
+    for r in range(nranks):
+        k, m = int(outs[r].n), int(outs[r].num_marks)
+        b = bufs[r]
+        res.append(((b[0][:k].copy(), b[1][:k].copy(), b[2][:k].copy(), b[3][:k].copy()), b[4][:m].copy()))
+    return res, int(latest_out.value)
+
+
 def merge_alerts(per_rank_alerts):
     """What the all-gather delivers: rank-major concatenation, (tick, lag, key)-sorted inside a rank."""
     parts = []

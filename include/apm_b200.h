@@ -129,7 +129,7 @@ typedef struct apm_fs_record {
     double ub[APM_NUM_SERIES];
     int8_t signal[APM_NUM_SERIES];
     uint8_t flags;               /* bit0: record valid; bit1: triggerAlert (alert rules on) */
-    uint8_t pad_[4];             /* with alert rules on: [0] causes (APM_CAUSE_*), [1] bad-interval count (<= 255) */
+    uint8_t pad_[4];             /* with alert rules on: [0] causes (APM_CAUSE_*), [1] bad-interval count (<= 255); gathered records: [2] sending rank */
 } apm_fs_record;
 
 /* causes of an alert, in the order processFSEntry tests them (stream_process_alerts.js:398-423) */
@@ -218,6 +218,22 @@ typedef struct apm_tx_packed {
 } apm_tx_packed;
 apm_status apm_process_host_packed(apm_ctx* ctx, const apm_tx_packed* host_cols, int64_t base_ts_ms, uint64_t n,
                                    apm_tick_result* res);
+
+/* ---- ticks located by the host: replaces, for the NEXT apm_process_host / _host_packed / _device call only,
+ * the `bucketLabel > data.latestBucket` test of consumeMsg (stream_calc_stats.js:348).  In a key-sharded
+ * deployment a tick is a property of the GLOBAL stream - any transaction with a larger bucket label triggers
+ * it, whichever rank owns its key - so the host that bins the transactions by owner (apm_partition_host)
+ * tells every rank where the ticks fall in its own sub-stream; a rank then ticks even while its shard is silent.
+ * marks[i]: the tick for bucket `label` fires before the transaction at index `pos` of the next call
+ * (pos == n: behind its last transaction).  Ascending in pos, strictly ascending in label, above latestBucket.
+ * With marks set the device does not look for ticks itself; n == 0 arms a call without any tick.  The marks are
+ * consumed by that call whether it succeeds or not (after APM_E_WOULDBLOCK: set the remaining ones again,
+ * rebased, before resubmitting). */
+typedef struct apm_tick_mark {
+    uint64_t pos;
+    int64_t label;
+} apm_tick_mark;
+apm_status apm_set_tick_marks(apm_ctx* ctx, const apm_tick_mark* marks, uint32_t n);
 
 /* ---- per-key z-score settings: replaces updateServiceSettings
  * (stream_calc_z_score.js:134-150); thr/infl hold n values for keys
@@ -349,8 +365,9 @@ apm_status apm_sorted_percentiles(int32_t device, const int32_t* d_values, uint3
 apm_status apm_sorted_percentiles_noalloc(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts,
                                           int32_t npct, double* out_pct, int32_t* d_sorted);
 
-/* ---- multi-GPU: keys are hash-sharded by the host; each rank owns its keys.
- * The only exchange is an all-gather of the compact alert block per tick. */
+/* ---- multi-GPU: keys are sharded by the host (hash or placement table); each rank owns its keys' buckets and
+ * baselines outright.  The only exchange is an all-gather of the compact alert records (per tick with
+ * apm_bind_gather_output, or on demand). */
 uint32_t apm_owner_of_key(uint64_t global_key, uint32_t nranks);
 /* Placement for skewed traffic (BASELINE config 5; no counterpart in the reference, whose stages are single processes):
  * owner_out[key] for the dense key ids 0 .. num_keys-1 from the transactions each key had in an earlier interval.
@@ -360,11 +377,46 @@ uint32_t apm_owner_of_key(uint64_t global_key, uint32_t nranks);
  * do not migrate - choose the table when a deployment starts.  Pure host arithmetic, no device needed. */
 apm_status apm_owner_table_build(const uint64_t* key_counts, uint32_t num_keys, uint32_t nranks, uint64_t key_cost,
                                  uint32_t* owner_out);
+/* Host binning for a key-sharded deployment (no counterpart in the reference, whose stats stage is one process that
+ * sees every transaction; it keeps what makes sharding legal - no statistic has a cross-key term,
+ * stream_calc_stats.js:159-202, stream_calc_z_score.js:197-308 - and what makes it subtle: ticks are triggered by ANY
+ * transaction, :348).  Splits n arrival-ordered transactions into one sub-stream per rank (arrival order kept) and
+ * gives every rank the global ticks as marks for apm_set_tick_marks.  owner_table[key] (apm_owner_table_build) or NULL
+ * for apm_owner_of_key; local_id[key] (optional) is the dense id the key has on its owner - the sub-stream then carries
+ * service_id = local_id, jvm_id = 0 for a context sized to the rank's own keys.  Transactions that fail the
+ * apm_tx_columns preconditions go to rank 0 unchanged (it counts them as invalid); like on the device their
+ * timestamp still ticks.  latest_bucket: latestBucket before these transactions; *latest_out: after.
+ * Pure host arithmetic, no device needed. */
+typedef struct apm_partition_out {
+    apm_tx_columns cols;   /* caller-owned host columns, capacity `cap` transactions */
+    uint64_t cap;
+    uint64_t n;            /* out: transactions routed to this rank */
+    apm_tick_mark* marks;  /* caller-owned, capacity marks_cap */
+    uint32_t marks_cap;
+    uint32_t num_marks;    /* out */
+} apm_partition_out;
+apm_status apm_partition_host(const apm_tx_columns* cols, uint64_t n, int64_t bucket_ms, int64_t latest_bucket,
+                              uint32_t num_services, uint32_t num_jvms, uint32_t nranks, const uint32_t* owner_table,
+                              const uint32_t* local_id, apm_partition_out* out /* [nranks] */, int64_t* latest_out);
 apm_status apm_comm_unique_id(void* out128);                 /* ncclGetUniqueId */
 apm_status apm_comm_init(apm_ctx* ctx, int32_t rank, int32_t nranks, const void* unique_id128);
-/* Collective: every rank calls it at the same point of the stream.  Gathers the
- * alerts of this rank's retained ticks from all ranks (rank-major, then
- * tick, lag, key): first the counts, then the records padded to the largest count. */
+/* Collective: every rank calls it at the same point of its stream of calls (ranks tick in step: ticks are global).
+ * Gathers, from all ranks, the alerts of the retained ticks that have not been gathered yet.  Each rank contributes
+ * one fixed-size block {count, records[capacity]}: the alert blocks of its ticks packed on the device, ONE
+ * ncclAllGather, and a kernel that appends the valid prefix of every rank's block to `out` - page-locked host memory
+ * (apm_host_alloc) is written directly, pageable memory through a device staging area.  The call waits once, at its
+ * end.  Order: one block per rank (rank-ascending), inside it (tick, lag, key)-ascending.  Capacity: records per
+ * block, default max_alerts_per_tick (one tick always fits); a host that lets many ticks pile up raises it with
+ * apm_comm_set_capacity.  A block or tick that overflows is reported by every rank alike (APM_E_CAPACITY): the
+ * headers travel with the blocks, so no rank is left waiting in a collective the others skipped.  Every gathered
+ * record carries its sending rank in pad_[2] (ranks below 256): with dense per-rank key ids the key alone does not
+ * say whose key it is. */
+apm_status apm_comm_set_capacity(apm_ctx* ctx, uint32_t records_per_block);
+/* Streams the gather: with a bound buffer (page-locked, cap_records) every tick's alerts are all-gathered on their own
+ * stream as soon as that tick's baseline has finished, under the following ticks' work, and appended tick by tick
+ * (tick-major, then rank, lag, key); apm_gather_alerts(ctx, pinned, ...) then only waits for the last one and returns
+ * the count; the buffer is appended to from 0 again afterwards.  NULL unbinds.  All ranks bind, or none. */
+apm_status apm_bind_gather_output(apm_ctx* ctx, apm_fs_record* pinned, uint64_t cap_records);
 apm_status apm_gather_alerts(apm_ctx* ctx, apm_fs_record* out, uint64_t cap, uint64_t* n);
 
 /* ------------------------------------------------------------------------------------------------

@@ -154,3 +154,80 @@ def test_owner_table_of_the_c_abi_equals_the_host_helper():
         assert lib.apm_owner_table_build(counts.ctypes.data, counts.size, n, cost, out.ctypes.data) == 0
         assert np.array_equal(out, sharding.balanced_owner_table(counts, n, key_cost=cost)), (n, cost)
     assert lib.apm_owner_table_build(None, 4, 2, 0, None) != 0
+
+
+def _local_ids(table_or_none, K, nranks):
+    """Dense id of every key on its owner, in key order."""
+    own = sharding.owner_of_keys(np.arange(K), nranks) if table_or_none is None else np.asarray(table_or_none)
+    local = np.zeros(K, np.uint32)
+    for r in range(nranks):
+        idx = np.flatnonzero(own == r)
+        local[idx] = np.arange(idx.size, dtype=np.uint32)
+    return own, local
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 3, 8])
+def test_native_partitioner_equals_the_numpy_mirror(nranks):
+    """apm_partition_host (host arithmetic of the C ABI) against sharding.partition_columns + sharding.tick_marks."""
+    svc, jvm, ts, el = make_stream(41, 5000, CFG["S"], CFG["J"], CFG["bucket_ms"], 120, late_frac=0.05, gap_at=(40, 47))
+    K = CFG["S"] * CFG["J"]
+    key = jvm.astype(np.int64) * CFG["S"] + svc
+    for table in (None, sharding.balanced_owner_table(np.bincount(key, minlength=K), nranks)):
+        parts = sharding.partition_columns(svc, jvm, ts, el, CFG["S"], nranks, owner_table=table)
+        marks = sharding.tick_marks(svc, jvm, ts, CFG["bucket_ms"], CFG["S"], nranks, latest=0, owner_table=table)
+        got, latest = sharding.partition_native(svc, jvm, ts, el, CFG["bucket_ms"], CFG["S"], CFG["J"], nranks,
+                                                owner_table=table)
+        assert latest == int((ts // CFG["bucket_ms"]).max())
+        for r in range(nranks):
+            for a, b in zip(got[r][0], parts[r]):
+                assert np.array_equal(a, b)
+            assert got[r][1].tobytes() == marks[r].tobytes()
+            # every rank ticks at every global label, also while its shard is silent
+            assert np.array_equal(got[r][1]["label"], sharding.tick_labels(ts, CFG["bucket_ms"]))
+            assert np.all(np.diff(got[r][1]["pos"].astype(np.int64)) >= 0) and got[r][1]["pos"].max() <= parts[r][0].size
+        # dense per-owner ids: service = the key's rank among its owner's keys, jvm = 0
+        own, local = _local_ids(table, K, nranks)
+        got2, _ = sharding.partition_native(svc, jvm, ts, el, CFG["bucket_ms"], CFG["S"], CFG["J"], nranks,
+                                            owner_table=table, local_id=local)
+        for r in range(nranks):
+            pk = parts[r][1].astype(np.int64) * CFG["S"] + parts[r][0]
+            assert np.array_equal(got2[r][0][0], local[pk]) and not got2[r][0][1].any()
+            assert np.array_equal(got2[r][0][2], parts[r][2]) and np.array_equal(got2[r][0][3], parts[r][3])
+
+
+def test_native_partitioner_carries_latest_and_routes_invalid_rows_to_rank_0():
+    svc, jvm, ts, el = make_stream(43, 2000, CFG["S"], CFG["J"], CFG["bucket_ms"], 60)
+    svc = svc.copy(); ts = ts.copy()
+    svc[100] = CFG["S"] + 5          # service id out of range
+    ts[200] = -1                     # negative timestamp: never ticks
+    half = 1000
+    a, latest = sharding.partition_native(svc[:half], jvm[:half], ts[:half], el[:half], CFG["bucket_ms"], CFG["S"], CFG["J"], 4)
+    b, latest2 = sharding.partition_native(svc[half:], jvm[half:], ts[half:], el[half:], CFG["bucket_ms"], CFG["S"], CFG["J"], 4,
+                                           latest=latest)
+    whole, latest3 = sharding.partition_native(svc, jvm, ts, el, CFG["bucket_ms"], CFG["S"], CFG["J"], 4)
+    assert latest2 == latest3
+    for r in range(4):
+        for i in range(4):
+            assert np.array_equal(np.concatenate([a[r][0][i], b[r][0][i]]), whole[r][0][i])
+        # marks of the second call are relative to it and continue above the first call's latestBucket
+        joined = np.concatenate([a[r][1]["label"], b[r][1]["label"]])
+        assert np.array_equal(joined, whole[r][1]["label"])
+        assert np.array_equal(np.concatenate([a[r][1]["pos"], b[r][1]["pos"] + a[r][0][0].size]), whole[r][1]["pos"])
+    assert (CFG["S"] + 5) in whole[0][0][0]                    # no key, no owner: rank 0 counts it as invalid
+    assert sum(int((-1 == whole[r][0][2]).sum()) for r in range(4)) == 1  # a bad timestamp stays with its key's owner
+    for r in range(1, 4):
+        assert (CFG["S"] + 5) not in whole[r][0][0]
+
+
+def test_native_partitioner_reports_full_outputs():
+    import ctypes as C
+    svc, jvm, ts, el = make_stream(44, 100, 4, 1, 10000, 10)
+    outs = (_capi.PartitionOut * 2)()
+    bufs = [(np.empty(10, np.uint32), np.empty(10, np.uint32), np.empty(10, np.int64), np.empty(10, np.int32),
+             np.zeros(64, _capi.MARK_DTYPE)) for _ in range(2)]
+    for r, b in enumerate(bufs):
+        outs[r].cols = _capi.TxColumns(*(x.ctypes.data for x in b[:4]))
+        outs[r].cap, outs[r].marks, outs[r].marks_cap = 10, b[4].ctypes.data, 64
+    cols = _capi.TxColumns(svc.ctypes.data, jvm.ctypes.data, ts.ctypes.data, el.ctypes.data)
+    st = _capi.lib().apm_partition_host(C.byref(cols), svc.size, 10000, 0, 4, 1, 2, None, None, outs, None)
+    assert st == _capi.E_CAPACITY and b"full" in _capi.lib().apm_last_error(None)
