@@ -31,7 +31,7 @@ def _rank_thread(r, world, uid, c, part, local_count, mode, calls, out, errs):
         bounds = np.linspace(0, n, calls + 1).astype(int)
         for a, b in zip(bounds[:-1], bounds[1:]):
             m = marks[(marks["pos"] >= a) & ((marks["pos"] < b) | (b == n))].copy()
-            m["pos"] -= a
+            m["pos"] -= np.uint64(a)
             eng.set_tick_marks(m)
             eng.process_host(svc[a:b], jvm[a:b], ts[a:b], el[a:b])
             try:
