@@ -106,6 +106,7 @@ class TickMark(C.Structure):
 
 
 MARK_DTYPE = np.dtype([("pos", "<u8"), ("label", "<i8")])
+ESCAPE_DTYPE = np.dtype([("index", "<u4"), ("elapsed_ms", "<i4")])
 
 
 class PartitionOut(C.Structure):
@@ -176,6 +177,8 @@ SYMBOLS = {
     "apm_parse_log_host": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
                                        C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(ParseResult)]),
     "apm_feed_parsed": (C.c_int32, [C.c_void_p, C.POINTER(TickResult)]),
+    "apm_process_host_packed8": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int64, C.c_uint64,
+                                             C.POINTER(TickResult)]),
     "apm_comm_set_capacity": (C.c_int32, [C.c_void_p, C.c_uint32]),
     "apm_bind_gather_output": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64]),
     "apm_set_tick_marks": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32]),
@@ -227,6 +230,11 @@ def synth():
         S.synth_ring_fill_host.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint32, C.c_uint32,
                                            C.c_void_p, C.c_uint64]
         S.synth_ring_fill_host.restype = None
+        S.synth_shard_tiles.argtypes = [C.c_uint64]
+        S.synth_shard_tiles.restype = C.c_int
+        S.synth_shard_count_device.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_int64, C.c_void_p, C.c_void_p]
+        S.synth_shard_emit_device.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int64, C.c_void_p,
+                                              C.c_void_p, C.c_void_p, C.POINTER(TxColumns), C.c_void_p, C.c_void_p, C.c_uint32]
         _synth = S
     return _synth
 

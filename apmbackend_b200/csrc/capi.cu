@@ -65,6 +65,33 @@ __global__ void __launch_bounds__(256) widen_tx_kernel(const uint32_t* __restric
     d.elapsed_ms[i] = (int32_t)__ldcs(el + i);
 }
 
+// 8-byte transactions (apm_process_host_packed8) -> the same columns.  A word whose elapsed field is all ones looks its
+// duration up in the call's escape list (sorted by transaction index, a handful of entries at most).
+__global__ void __launch_bounds__(256) widen_tx8_kernel(const uint64_t* __restrict__ tx, const apm_tx_escape* __restrict__ esc, uint32_t num_esc,
+                                                        uint64_t first_index, int64_t base, uint64_t n, uint32_t num_services,
+                                                        apm_tx_columns d) {
+    const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t w = __ldcs(tx + i);
+    const uint32_t key = (uint32_t)(w >> 48), dt = (uint32_t)(w >> 24) & 0xFFFFFFu;
+    uint32_t el = (uint32_t)w & 0xFFFFFFu;
+    if (el == 0xFFFFFFu) {
+        // not in the list: the field stands for itself (a duration of exactly 16 777 215 ms)
+        const uint64_t idx = first_index + i;
+        uint32_t lo = 0, hi = num_esc;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if ((uint64_t)esc[mid].index < idx) lo = mid + 1; else hi = mid;
+        }
+        if (lo < num_esc && (uint64_t)esc[lo].index == idx) el = (uint32_t)esc[lo].elapsed_ms;
+    }
+    // key -> (jvm, service): a key at or above num_services * num_jvms becomes a jvm id out of range, i.e. an invalid transaction
+    d.service_id[i] = key % num_services;
+    d.jvm_id[i] = key / num_services;
+    d.end_ts_ms[i] = base + (int64_t)dt;
+    d.elapsed_ms[i] = (int32_t)el;
+}
+
 apm_status alloc_columns_device(apm_ctx* c, apm_tx_columns* d, uint64_t n) {
     CUDA_TRY(c, dalloc(&d->service_id, n));
     CUDA_TRY(c, dalloc(&d->jvm_id, n));
@@ -488,7 +515,7 @@ void apm_ctx_destroy(apm_ctx* c) {
         if (pp.ev) cudaEventDestroy(pp.ev);
     }
     apm_lp_destroy(c);
-    cudaFree(c->pk[0]); cudaFree(c->pk[1]);
+    cudaFree(c->pk[0]); cudaFree(c->pk[1]); cudaFree(c->esc[0]); cudaFree(c->esc[1]);
     cudaFreeHost(c->pin.service_id); cudaFreeHost(c->pin.jvm_id); cudaFreeHost(c->pin.end_ts_ms); cudaFreeHost(c->pin.elapsed_ms);
     free_columns_device(&c->dev[0]); free_columns_device(&c->dev[1]);
     cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->d_alert_blocks); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
@@ -834,6 +861,41 @@ apm_status apm_process_host_packed(apm_ctx* c, const apm_tx_packed* h, int64_t b
         c->launches += 1;
         CUDA_TRY(c, cudaGetLastError());
         c->counters.h2d_bytes += m * 12;
+        return APM_OK;
+    });
+}
+
+apm_status apm_process_host_packed8(apm_ctx* c, const uint64_t* tx, const apm_tx_escape* escapes, uint32_t num_escapes,
+                                    int64_t base_ts_ms, uint64_t n, apm_tick_result* res) {
+    if (!c || (!tx && n) || (!escapes && num_escapes)) return APM_E_INVALID;
+    APM_ENTER(c);
+    ExtMarksScope ext_scope_{c};
+    if (base_ts_ms < 0) return apm_fail(c, APM_E_INVALID, "process_host_packed8: base_ts_ms must not be negative");
+    if (n > 0xFFFFFFFFull) return apm_fail(c, APM_E_CAPACITY, "process_host_packed8: at most 2^32 - 1 transactions per call (escape indices are 32-bit)");
+    for (uint32_t i = 1; i < num_escapes; ++i)
+        if (escapes[i].index <= escapes[i - 1].index) return apm_fail(c, APM_E_INVALID, "process_host_packed8: escapes must be ascending by index");
+    if (!c->pk[0]) {  // shared with the 12-byte form: [3][max_batch] u32 holds max_batch u64 words
+        for (int i = 0; i < 2; ++i) CUDA_TRY(c, cudaMalloc((void**)&c->pk[i], c->cfg.max_batch * 3 * sizeof(uint32_t)));
+    }
+    return process_host_chunks(c, n, res, [&](uint64_t off, uint64_t m, int b) -> apm_status {
+        uint64_t* p = reinterpret_cast<uint64_t*>(c->pk[b]);
+        CUDA_TRY(c, cudaMemcpyAsync(p, tx + off, m * 8, cudaMemcpyHostToDevice, c->s_copy));
+        // the chunk's slice of the escape list
+        const apm_tx_escape* lo = std::lower_bound(escapes, escapes + num_escapes, off, [](const apm_tx_escape& e, uint64_t v) { return e.index < v; });
+        const apm_tx_escape* hi = std::lower_bound(lo, escapes + num_escapes, off + m, [](const apm_tx_escape& e, uint64_t v) { return e.index < v; });
+        const uint32_t ne = (uint32_t)(hi - lo);
+        if (ne > c->esc_cap[b]) {
+            CUDA_TRY(c, cudaStreamSynchronize(c->s_copy));
+            cudaFree(c->esc[b]);
+            c->esc[b] = nullptr;
+            c->esc_cap[b] = std::max<uint32_t>(2 * ne, 1024);
+            CUDA_TRY(c, cudaMalloc((void**)&c->esc[b], (size_t)c->esc_cap[b] * sizeof(apm_tx_escape)));
+        }
+        if (ne) CUDA_TRY(c, cudaMemcpyAsync(c->esc[b], lo, (size_t)ne * sizeof(apm_tx_escape), cudaMemcpyHostToDevice, c->s_copy));
+        widen_tx8_kernel<<<(unsigned)((m + 255) / 256), 256, 0, c->s_copy>>>(p, c->esc[b], ne, off, base_ts_ms, m, c->cfg.num_services, c->dev[b]);
+        c->launches += 1;
+        CUDA_TRY(c, cudaGetLastError());
+        c->counters.h2d_bytes += m * 8 + (uint64_t)ne * sizeof(apm_tx_escape);
         return APM_OK;
     });
 }

@@ -97,7 +97,9 @@ struct apm_ctx {
     apm_tx_columns pin = {nullptr, nullptr, nullptr, nullptr};
     apm_tx_columns dev[2] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
     uint64_t acquired = 0;
-    uint32_t* pk[2] = {nullptr, nullptr};  // staging of 12-byte transactions: [3][max_batch] each (apm_process_host_packed)
+    uint32_t* pk[2] = {nullptr, nullptr};  // staging of 12-byte / 8-byte transactions: [3][max_batch] u32 each (apm_process_host_packed, _packed8)
+    apm_tx_escape* esc[2] = {nullptr, nullptr};  // a chunk's slice of the 8-byte form's escape list
+    uint32_t esc_cap[2] = {0, 0};
 
     // --- tick outputs
     apm_stat_record* d_stats = nullptr;  // [out_ticks][K]

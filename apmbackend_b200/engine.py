@@ -64,6 +64,34 @@ def _cols(service_id, jvm_id, end_ts_ms, elapsed_ms):
     return s, j, t, e
 
 
+def pack8(service_id, jvm_id, end_ts_ms, elapsed_ms, num_services: int, num_jvms: int, base_ts_ms: int, out=None):
+    """Host columns -> the 8-byte form of apm_process_host_packed8: (words u64, escapes).  Rows with an id out of range
+    get key 0xFFFF (needs fewer than 65 535 keys), durations that do not fit 24 bits (or are negative) go to the escape
+    list.  `out`: optional uint64 array to fill (e.g. page-locked memory)."""
+    s, j, t, e = _cols(service_id, jvm_id, end_ts_ms, elapsed_ms)
+    K = num_services * num_jvms
+    if K > 65536:
+        raise ValueError("the 8-byte form carries 16-bit key ids")
+    bad = (s >= num_services) | (j >= num_jvms)
+    if bad.any() and K > 65535:
+        raise ValueError("no spare key code for rows with ids out of range")
+    dt = t - np.int64(base_ts_ms)
+    if dt.size and (dt.min() < 0 or dt.max() >= (1 << 24)):
+        raise ValueError("endTs - base must fit 24 bits (0 .. 4.6 h)")
+    key = np.where(bad, 0xFFFF, j.astype(np.uint64) * np.uint64(num_services) + s.astype(np.uint64)).astype(np.uint64)
+    esc_rows = np.flatnonzero((e < 0) | (e >= 0xFFFFFF))
+    el = e.astype(np.int64)
+    el[esc_rows] = 0xFFFFFF
+    w = out if out is not None else np.empty(s.size, np.uint64)
+    np.left_shift(key, np.uint64(48), out=w)
+    w |= dt.astype(np.uint64) << np.uint64(24)
+    w |= el.astype(np.uint64)
+    esc = np.zeros(esc_rows.size, _capi.ESCAPE_DTYPE)
+    esc["index"] = esc_rows
+    esc["elapsed_ms"] = e[esc_rows]
+    return w, esc
+
+
 class Engine:
     def __init__(self, cfg: EngineConfig):
         self.cfg = cfg
@@ -127,6 +155,15 @@ class Engine:
         cols = _capi.TxPacked(k.ctypes.data, t.ctypes.data, e.ctypes.data)
         res = TickResult()
         self._check(self._lib.apm_process_host_packed(self._h, C.byref(cols), int(base_ts_ms), k.size, C.byref(res)))
+        return res
+
+    def process_host_packed8(self, words, escapes, base_ts_ms: int) -> TickResult:
+        """apm_process_host_packed8: one u64 per transaction (key:16 | endTs - base:24 | elapsed:24) + the escape list."""
+        w = np.ascontiguousarray(words, dtype=np.uint64)
+        e = np.ascontiguousarray(escapes, dtype=_capi.ESCAPE_DTYPE) if escapes is not None else np.zeros(0, _capi.ESCAPE_DTYPE)
+        res = TickResult()
+        self._check(self._lib.apm_process_host_packed8(self._h, w.ctypes.data if w.size else None, e.ctypes.data if e.size else None,
+                                                       e.size, int(base_ts_ms), w.size, C.byref(res)))
         return res
 
     def process_device(self, cols: TxColumns, n: int) -> TickResult:

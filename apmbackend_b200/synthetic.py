@@ -210,11 +210,87 @@ class SynthStream:
             b.free()
 
 
-def ring_fill_device(buf: DeviceBuffer, rows: int, stream: "SynthStream", seed: int):
-    """Fills buf as [rows][3][K] with a plausible baseline history for `stream`'s services."""
+def ring_fill_device(buf: DeviceBuffer, rows: int, stream: "SynthStream", seed: int, base_dev=None, num_keys=None):
+    """Fills buf as [rows][3][K] with a plausible baseline history for `stream`'s services (or, for a key shard, for
+    the `num_keys` local keys whose duration scales are in the device table `base_dev`)."""
     sp = stream.spec
-    K = sp.num_services * sp.num_jvms
-    _chk(_capi.synth().synth_ring_fill_device(buf.ptr, rows, 3 * K, seed, stream._dev[1].ptr, sp.num_services, K), "ring_fill")
+    if base_dev is None:
+        K = sp.num_services * sp.num_jvms
+        _chk(_capi.synth().synth_ring_fill_device(buf.ptr, rows, 3 * K, seed, stream._dev[1].ptr, sp.num_services, K), "ring_fill")
+    else:
+        _chk(_capi.synth().synth_ring_fill_device(buf.ptr, rows, 3 * num_keys, seed, base_dev, num_keys, num_keys), "ring_fill")
+
+
+class ShardPlan:
+    """Placement of a global key space on `nranks` ranks: owner[key], the dense id each key has on its owner, and
+    per rank the global keys in local-id order.  owner=None: apm_owner_of_key (splitmix64 hash)."""
+
+    def __init__(self, num_keys: int, nranks: int, owner=None):
+        from . import sharding
+        self.num_keys, self.nranks = int(num_keys), int(nranks)
+        self.owner = (sharding.owner_of_keys(np.arange(num_keys, dtype=np.uint64), nranks) if owner is None
+                      else np.ascontiguousarray(owner, dtype=np.uint32))
+        order = np.argsort(self.owner, kind="stable")
+        counts = np.bincount(self.owner, minlength=nranks)
+        starts = np.concatenate([[0], np.cumsum(counts)])
+        self.local_id = np.empty(num_keys, np.uint32)
+        self.local_id[order] = (np.arange(num_keys) - starts[self.owner[order]]).astype(np.uint32)
+        self.keys_of = [order[starts[r]:starts[r + 1]] for r in range(nranks)]
+        self.counts = counts
+        self._dev = None
+
+    def device(self):
+        if self._dev is None:
+            self._dev = (DeviceBuffer(self.owner.nbytes).upload(self.owner), DeviceBuffer(self.local_id.nbytes).upload(self.local_id))
+        return self._dev
+
+    def free(self):
+        for b in self._dev or []:
+            b.free()
+        self._dev = None
+
+
+def expected_key_counts(stream: "SynthStream") -> np.ndarray:
+    """Expected transactions per key (jvm * num_services + service) of the whole stream, from its popularity table."""
+    sp = stream.spec
+    c = stream.cdf.astype(np.float64)
+    p = np.diff(np.concatenate([[-1.0], c])) / 4294967296.0
+    return np.tile(p * sp.n / sp.num_jvms, sp.num_jvms)
+
+
+def generate_shard_device(stream: "SynthStream", plan: ShardPlan, rank: int, cols: DeviceColumns, bucket_ms: int, latest: int,
+                          t0_ms=None, seed=None):
+    """One rank's shard of the global stream into `cols` (arrival order, dense local ids, jvm 0).  Returns
+    (transactions written, tick marks of the GLOBAL stream as (pos in the shard, label), latestBucket afterwards)."""
+    S = _capi.synth()
+    sp = stream.spec
+    n = sp.n
+    p = stream._params(0, True, t0_ms, seed)
+    tiles = int(S.synth_shard_tiles(n))
+    owner_d, local_d = plan.device()
+    tc, tm = DeviceBuffer(tiles * 4), DeviceBuffer(tiles * 8)
+    _chk(S.synth_shard_count_device(C.byref(p), n, owner_d.ptr, rank, bucket_ms, tc.ptr, tm.ptr), "shard_count")
+    cnt = tc.download(np.uint32, tiles).astype(np.uint64)
+    mx = tm.download(np.int64, tiles)
+    prefix = np.concatenate([[0], np.cumsum(cnt)[:-1]]).astype(np.uint64)
+    carry = np.maximum.accumulate(np.concatenate([[latest], mx]))[:-1].astype(np.int64)
+    total = int(cnt.sum())
+    if total > cols.n:
+        raise RuntimeError(f"shard of {total} transactions does not fit the {cols.n} allocated")
+    tp, tcar = DeviceBuffer(tiles * 8).upload(prefix), DeviceBuffer(tiles * 8).upload(carry)
+    cap = 1 << 14
+    marks_d, nm = DeviceBuffer(cap * 16), DeviceBuffer(4).upload(np.zeros(1, np.uint32))
+    c = cols.columns()
+    _chk(S.synth_shard_emit_device(C.byref(p), n, owner_d.ptr, local_d.ptr, rank, bucket_ms, tp.ptr, tcar.ptr, tm.ptr, C.byref(c),
+                                   marks_d.ptr, nm.ptr, cap), "shard_emit")
+    k = int(nm.download(np.uint32, 1)[0])
+    if k > cap:
+        raise RuntimeError("too many ticks in one synthetic step")
+    marks = marks_d.download(_capi.MARK_DTYPE, k)
+    marks = marks[np.argsort(marks["label"], kind="stable")]
+    for b in (tc, tm, tp, tcar, marks_d, nm):
+        b.free()
+    return total, marks, int(max(latest, mx.max() if tiles else latest))
 
 
 def ring_fill_host(rows: int, stream: "SynthStream", seed: int, cols) -> np.ndarray:

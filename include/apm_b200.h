@@ -219,7 +219,23 @@ typedef struct apm_tx_packed {
 apm_status apm_process_host_packed(apm_ctx* ctx, const apm_tx_packed* host_cols, int64_t base_ts_ms, uint64_t n,
                                    apm_tick_result* res);
 
-/* ---- ticks located by the host: replaces, for the NEXT apm_process_host / _host_packed / _device call only,
+/* The same run once more from 8-byte transactions, for hosts that feed several GPUs through one PCIe root / memory
+ * system: one word per transaction,
+ *     bits 63..48  key = jvm_id * num_services + service_id (below 65536; a value >= the context's key count is the
+ *                  invalid transaction an out-of-range id is in the wide form)
+ *     bits 47..24  endTs - base_ts_ms in ms (the call spans less than 2^24 ms = 4.6 h)
+ *     bits 23..0   elapsed in ms; 0xFFFFFF = "look it up": the transaction's index (inside this call) is in `escapes`,
+ *                  ascending by index, which carries the full int32 (a duration of 16 777 215 ms or more, or a negative,
+ *                  i.e. invalid, one).  An all-ones field without a list entry stands for 16 777 215 ms itself.
+ * Widened on the device, then identical to apm_process_host: same ticks, same records, same counters. */
+typedef struct apm_tx_escape {
+    uint32_t index;
+    int32_t elapsed_ms;
+} apm_tx_escape;
+apm_status apm_process_host_packed8(apm_ctx* ctx, const uint64_t* tx, const apm_tx_escape* escapes, uint32_t num_escapes,
+                                    int64_t base_ts_ms, uint64_t n, apm_tick_result* res);
+
+/* ---- ticks located by the host: replaces, for the NEXT apm_process_host / _host_packed / _host_packed8 / _device call only,
  * the `bucketLabel > data.latestBucket` test of consumeMsg (stream_calc_stats.js:348).  In a key-sharded
  * deployment a tick is a property of the GLOBAL stream - any transaction with a larger bucket label triggers
  * it, whichever rank owns its key - so the host that bins the transactions by owner (apm_partition_host)
