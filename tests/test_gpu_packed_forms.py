@@ -132,7 +132,7 @@ def test_narrow_forms_at_baseline_size_100m_transactions():
             eng.process_host_packed8(words, esc, base)
         results.append(_results(eng))
         eng.close()
-    assert results[0][1][3] == span_buckets + 1 - 1 or results[0][1][3] >= span_buckets - 1
+    assert results[0][1][3] >= span_buckets - 1
     assert results[0][1][2] >= 1000
     _same(results[1], results[0])
     _same(results[2], results[0])
