@@ -179,6 +179,7 @@ SYMBOLS = {
     "apm_feed_parsed": (C.c_int32, [C.c_void_p, C.POINTER(TickResult)]),
     "apm_process_host_packed8": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int64, C.c_uint64,
                                              C.POINTER(TickResult)]),
+    "apm_preload_kernels": (C.c_int32, [C.c_int32]),
     "apm_comm_set_capacity": (C.c_int32, [C.c_void_p, C.c_uint32]),
     "apm_bind_gather_output": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64]),
     "apm_set_tick_marks": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32]),

@@ -488,7 +488,32 @@ apm_status apm_flush_pending(apm_ctx* c) {
     return APM_OK;
 }
 
+cudaError_t apm_preload_capi(); cudaError_t apm_preload_comm(); cudaError_t apm_preload_k1_ingest(); cudaError_t apm_preload_k2_tick();
+cudaError_t apm_preload_k3_onesweep(); cudaError_t apm_preload_k3_percentile_op(); cudaError_t apm_preload_k3_sort();
+cudaError_t apm_preload_k4_baseline(); cudaError_t apm_preload_k5_passthrough(); cudaError_t apm_preload_k6_logparse();
+
 extern "C" {
+
+// CUDA loads a kernel when it is first launched, and that load can need the device to drain.  A kernel that spins on
+// another GPU's progress (an NCCL collective waiting for its peer) never drains, so two ranks that each meet a
+// not-yet-loaded kernel while the other's collective is in flight wait for each other for ever.  Loading every kernel
+// up front removes the first-use loads from the steady state (apm_comm_init does it for its device).
+apm_status apm_preload_kernels(int32_t device) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+        return apm_fail(nullptr, APM_E_DEVICE, "apm_preload_kernels: no such CUDA device");
+    ApmDeviceGuard guard(device);
+    static unsigned long long done = 0;
+    if (!apm_first_on_device(&done)) return APM_OK;
+    cudaError_t (*const parts[])() = {apm_preload_capi, apm_preload_comm, apm_preload_k1_ingest, apm_preload_k2_tick, apm_preload_k3_onesweep,
+                                      apm_preload_k3_percentile_op, apm_preload_k3_sort, apm_preload_k4_baseline,
+                                      apm_preload_k5_passthrough, apm_preload_k6_logparse};
+    for (auto part : parts) {
+        const cudaError_t e = part();
+        if (e != cudaSuccess) { done = 0; return apm_fail_cuda(nullptr, e, "cudaFuncGetAttributes (kernel preload)", __FILE__, __LINE__); }
+    }
+    return APM_OK;
+}
 
 uint32_t apm_abi_version(void) { return APM_ABI_VERSION; }
 
@@ -1392,3 +1417,15 @@ extern "C" void apm_host_free(void* p) {
 }
 
 extern "C" uint32_t apm_ticks_buffered(const apm_ctx* c) { return c ? c->ticks_buffered : 0; }
+
+// Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
+cudaError_t apm_preload_capi() {
+    const void* fns[] = {(const void*)widen_tx8_kernel, (const void*)widen_tx_kernel};
+    cudaError_t first = cudaSuccess;
+    for (const void* f : fns) {
+        cudaFuncAttributes a;
+        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        if (e != cudaSuccess && first == cudaSuccess) first = e;
+    }
+    return first;
+}

@@ -184,7 +184,21 @@ apm_status enqueue_gather(apm_ctx* c, uint32_t tick0, uint32_t nticks, apm_fs_re
     return APM_OK;
 }
 
-apm_status alloc_gather(apm_ctx* c, uint32_t cap) {
+// Every rank must send blocks of the same size, whatever it asked for (ranks own different numbers of keys): the
+// ranks exchange their requests and all take the largest.  A collective in itself - every rank calls it.
+apm_status alloc_gather(apm_ctx* c, uint32_t want) {
+    uint32_t* d_req = nullptr;
+    CUDA_TRY(c, cudaMalloc((void**)&d_req, sizeof(uint32_t) * 4 * ((size_t)c->nranks + 1)));
+    const uint32_t mine[4] = {want, 0, 0, 0};
+    CUDA_TRY(c, cudaMemcpyAsync(d_req, mine, sizeof mine, cudaMemcpyHostToDevice, c->s_comm));
+    nccl_result_t r = nccl().AllGather(d_req, d_req + 4, sizeof mine, NCCL_INT8, (nccl_comm_t)c->nccl_comm, c->s_comm);
+    if (r) { cudaFree(d_req); return nccl_fail(c, r, "ncclAllGather (block capacity)"); }
+    std::vector<uint32_t> all((size_t)c->nranks * 4);
+    CUDA_TRY(c, cudaMemcpyAsync(all.data(), d_req + 4, all.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->s_comm));
+    CUDA_TRY(c, cudaStreamSynchronize(c->s_comm));
+    cudaFree(d_req);
+    uint32_t cap = want;
+    for (int rk = 0; rk < c->nranks; ++rk) cap = std::max(cap, all[(size_t)rk * 4]);
     cudaFree(c->d_gather_send); cudaFree(c->d_gather_recv); cudaFree(c->d_gather_stage);
     c->d_gather_send = c->d_gather_recv = c->d_gather_stage = nullptr;
     c->gather_cap = cap;
@@ -258,6 +272,10 @@ apm_status apm_comm_init(apm_ctx* c, int32_t rank, int32_t nranks, const void* u
     if (c->nccl_comm) return apm_fail(c, APM_E_STATE, "comm_init: the context already has a communicator");
     NcclApi& a = nccl();
     if (!a.error.empty()) return apm_fail(c, APM_E_COMM, a.error);
+    {   // no first-use kernel load may happen while a collective is in flight (see apm_preload_kernels)
+        apm_status pl = apm_preload_kernels(c->cfg.device);
+        if (pl) return apm_fail(c, pl, apm_last_error(nullptr));
+    }
     nccl_unique_id id;
     memcpy(&id, unique_id128, 128);
     nccl_comm_t comm = nullptr;
@@ -359,3 +377,15 @@ apm_status apm_gather_alerts(apm_ctx* c, apm_fs_record* out, uint64_t cap, uint6
 }
 
 }  // extern "C"
+
+// Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
+cudaError_t apm_preload_comm() {
+    const void* fns[] = {(const void*)gather_advance_kernel, (const void*)gather_pack_kernel, (const void*)gather_unpack_kernel};
+    cudaError_t first = cudaSuccess;
+    for (const void* f : fns) {
+        cudaFuncAttributes a;
+        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        if (e != cudaSuccess && first == cudaSuccess) first = e;
+    }
+    return first;
+}

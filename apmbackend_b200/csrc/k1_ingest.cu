@@ -670,3 +670,15 @@ apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;
 }
+
+// Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
+cudaError_t apm_preload_k1_ingest() {
+    const void* fns[] = {(const void*)reduce_kernel_v3<true>, (const void*)reduce_kernel_v3<false>, (const void*)seg_hist_kernel, (const void*)tf_emit_kernel, (const void*)tf_scan_kernel, (const void*)tf_tile_max_kernel};
+    cudaError_t first = cudaSuccess;
+    for (const void* f : fns) {
+        cudaFuncAttributes a;
+        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        if (e != cudaSuccess && first == cudaSuccess) first = e;
+    }
+    return first;
+}

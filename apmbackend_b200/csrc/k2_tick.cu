@@ -362,3 +362,15 @@ apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;
 }
+
+// Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
+cudaError_t apm_preload_k2_tick() {
+    const void* fns[] = {(const void*)clear_slots_kernel, (const void*)tick_stats_kernel, (const void*)tick_stats_warp_kernel};
+    cudaError_t first = cudaSuccess;
+    for (const void* f : fns) {
+        cudaFuncAttributes a;
+        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        if (e != cudaSuccess && first == cudaSuccess) first = e;
+    }
+    return first;
+}

@@ -343,3 +343,15 @@ uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t 
     *err = cudaGetLastError();
     return src;
 }
+
+// Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
+cudaError_t apm_preload_k3_onesweep() {
+    const void* fns[] = {(const void*)os_hist_kernel, (const void*)os_scan_kernel, (const void*)os_pass_kernel<false, 0>, (const void*)os_pass_kernel<true, 0>, (const void*)os_pass_kernel<false, 8>, (const void*)os_pass_kernel<true, 8>};
+    cudaError_t first = cudaSuccess;
+    for (const void* f : fns) {
+        cudaFuncAttributes a;
+        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        if (e != cudaSuccess && first == cudaSuccess) first = e;
+    }
+    return first;
+}

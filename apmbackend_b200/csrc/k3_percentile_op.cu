@@ -177,3 +177,15 @@ apm_status apm_sorted_percentiles(int32_t device, const int32_t* d_values, uint3
 }
 
 }  // extern "C"
+
+// Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
+cudaError_t apm_preload_k3_percentile_op() {
+    const void* fns[] = {(const void*)max_kernel, (const void*)narrow_pct_kernel, (const void*)widen_kernel};
+    cudaError_t first = cudaSuccess;
+    for (const void* f : fns) {
+        cudaFuncAttributes a;
+        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        if (e != cudaSuccess && first == cudaSuccess) first = e;
+    }
+    return first;
+}

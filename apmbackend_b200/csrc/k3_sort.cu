@@ -397,3 +397,15 @@ apm_status apm_acc_from_sorted(apm_ctx* c, int slot, uint64_t n) {
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;
 }
+
+// Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
+cudaError_t apm_preload_k3_sort() {
+    const void* fns[] = {(const void*)acc_from_sorted_kernel, (const void*)clear_planes_kernel, (const void*)rs_hist_kernel, (const void*)rs_scan_rows_kernel, (const void*)rs_scatter_kernel, (const void*)small_sort_kernel};
+    cudaError_t first = cudaSuccess;
+    for (const void* f : fns) {
+        cudaFuncAttributes a;
+        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        if (e != cudaSuccess && first == cudaSuccess) first = e;
+    }
+    return first;
+}

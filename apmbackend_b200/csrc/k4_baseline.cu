@@ -810,3 +810,15 @@ apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t aler
     CUDA_TRY(c, cudaGetLastError());
     return APM_OK;
 }
+
+// Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
+cudaError_t apm_preload_k4_baseline() {
+    const void* fns[] = {(const void*)alert_counter_kernel, (const void*)baseline_inc_kernel, (const void*)baseline_kernel, (const void*)baseline_tma_kernel<2, 1>, (const void*)baseline_tma_kernel<3, 1>, (const void*)baseline_tma_kernel<4, 1>, (const void*)baseline_tma_kernel<6, 1>, (const void*)baseline_tma_kernel<K4T_DEEP_STAGES, 3>, (const void*)compact_alerts_kernel, (const void*)count_alerts_kernel, (const void*)inc_init_kernel, (const void*)realign_kernel};
+    cudaError_t first = cudaSuccess;
+    for (const void* f : fns) {
+        cudaFuncAttributes a;
+        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        if (e != cudaSuccess && first == cudaSuccess) first = e;
+    }
+    return first;
+}

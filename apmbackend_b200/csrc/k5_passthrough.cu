@@ -189,3 +189,15 @@ extern "C" apm_status apm_fetch_passthrough(apm_ctx* c, int64_t* end_ts, uint32_
     c->counters.d2h_bytes += words.size() * sizeof(uint64_t);
     return APM_OK;
 }
+
+// Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
+cudaError_t apm_preload_k5_passthrough() {
+    const void* fns[] = {(const void*)pt_append_kernel, (const void*)pt_partition_kernel};
+    cudaError_t first = cudaSuccess;
+    for (const void* f : fns) {
+        cudaFuncAttributes a;
+        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        if (e != cudaSuccess && first == cudaSuccess) first = e;
+    }
+    return first;
+}

@@ -877,3 +877,15 @@ apm_status apm_feed_parsed(apm_ctx* c, apm_tick_result* result) {
 }
 
 }  // extern "C"
+
+// Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
+cudaError_t apm_preload_k6_logparse() {
+    const void* fns[] = {(const void*)lp_count_fed_kernel, (const void*)lp_count_newlines_kernel, (const void*)lp_count_records_kernel, (const void*)lp_finish_kernel, (const void*)lp_gather_fed_kernel, (const void*)lp_gather_records_kernel, (const void*)lp_pair_kernel, (const void*)lp_parse_kernel, (const void*)lp_scan_kernel, (const void*)lp_write_newlines_kernel};
+    cudaError_t first = cudaSuccess;
+    for (const void* f : fns) {
+        cudaFuncAttributes a;
+        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        if (e != cudaSuccess && first == cudaSuccess) first = e;
+    }
+    return first;
+}

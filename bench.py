@@ -421,6 +421,7 @@ def sharded_parity(rank, world, local_rank, dist, Engine, EngineConfig, _capi, s
     latest = 0
     gathered, own_fs, want_fs, want_al = [], [], [], []
     for ci, (a, b) in enumerate(zip(calls[:-1], calls[1:])):
+        note(f"parity call {ci}")
         if ci == 3:
             eng.bind_gather_output(1 << 16)  # second half: the gather is streamed tick by tick
         parts, latest = sharding.partition_native(svc[a:b], jvm[a:b], ts[a:b], el[a:b], bucket_ms, S, 1, world, latest=latest,
@@ -459,9 +460,21 @@ def sharded_parity(rank, world, local_rank, dist, Engine, EngineConfig, _capi, s
     return "ok", int(wa.size)
 
 
+def note(msg):
+    """progress on stderr (APM_BENCH_VERBOSE=1)"""
+    if os.environ.get("APM_BENCH_VERBOSE"):
+        print(f"[bench rank {os.environ.get('RANK', '0')} +{time.perf_counter() - _T0:.1f}s] {msg}", file=sys.stderr, flush=True)
+
+
+_T0 = time.perf_counter()
+
+
 def main():
     global _REAL_STDOUT
     args = parse_args()
+    if os.environ.get("APM_BENCH_WATCHDOG"):  # a hung run dumps every thread's Python stack and exits
+        import faulthandler
+        faulthandler.dump_traceback_later(float(os.environ["APM_BENCH_WATCHDOG"]), exit=True)
     sys.stdout.flush()
     _REAL_STDOUT = os.dup(1)
     os.dup2(2, 1)  # stdout of everything below (C libraries included) joins stderr
@@ -513,7 +526,9 @@ def main():
 
     parity = None
     if world > 1 and wl["zscore"]:
+        note("sharded parity leg")
         parity = sharded_parity(rank, world, local_rank, dist, Engine, EngineConfig, _capi, syn)
+        note(f"sharded parity {parity}")
 
     shard = Shard(args, wl, rank, world, syn, _capi)
     K = shard.K
@@ -550,7 +565,7 @@ def main():
         e = make_engine(wl, shard, flags | extra_flags, local_rank, Engine, EngineConfig)
         if world > 1 and wl["zscore"]:
             e.comm_init(rank, world, broadcast_unique_id(rank, dist, Engine))
-            e.comm_set_capacity(max(K * len(wl["lags"]) // 2, 1024))  # records per rank and tick
+            e.comm_set_capacity(max(int(shard.plan.counts.max()) * len(wl["lags"]) // 2, 1024))  # records per rank and tick
             e.bind_gather_output(gather_out_cap)
         if wl["zscore"] and wl.get("prefill", True) and K:
             shard.prefill(e, ring_seed)
@@ -612,8 +627,11 @@ def main():
         return dict(ms=ms, wall_ms=wall_ms, clk=clk, prof=prof, prof_iso=prof_iso, launches=c1.kernel_launches - c0.kernel_launches,
                     ticks=c1.ticks - c0.ticks, gathered=gather_n[0], inc_fallbacks=c1.inc_fallbacks - c0.inc_fallbacks)
 
+    note(f"{len(dev_steps)} device-resident steps generated")
     eng = setup_engine(inc_flag)
+    note("engine ready")
     main_pass = timed_device_pass(eng, not args.no_profile)
+    note("device pass done")
     ms = main_pass["ms"]
     tx_timed = allreduce(sum(dev_steps[s][1] for s in range(args.warmup, nsteps)), "sum")
     value = tx_timed / (ms / 1e3)
@@ -745,11 +763,13 @@ def main():
         can12 = eng.cfg.num_services < 65536 and eng.cfg.num_jvms < 65536 and span_ms + 4000 < (1 << 32)
         can8 = eng.cfg.num_services * eng.cfg.num_jvms < 65536 and span_ms + 4000 < (1 << 24)
         e2e_all["wide"] = measure_e2e("wide", 0)
+        note("e2e wide done")
         if can12:
             e2e_all["packed12"] = measure_e2e("packed12", 1)
         if can8:
             e2e_all["packed8"] = measure_e2e("packed8", 2)
     eng.close()
+    note("e2e done")
 
     # ---- the guarded incremental baseline on the same device-resident steps (one more timed pass, fresh context)
     inc_pass = None

@@ -344,6 +344,13 @@ apm_status apm_mark_seen(apm_ctx* ctx, uint32_t key_lo, uint32_t n);
 apm_status apm_log_read(apm_ctx* ctx, int64_t label, uint64_t* out, uint64_t cap, uint64_t* n);
 int64_t apm_latest(const apm_ctx* ctx);
 
+/* Loads every kernel of the library (and the static scratch of apm_sorted_percentiles_noalloc) on `device` now
+ * instead of at first launch.  CUDA's default lazy loading makes the first launch of each kernel a module load that
+ * may need device memory and a drained device: a host that reserves all GPU memory for its own pool calls this
+ * first, and a multi-GPU host needs it before collectives are in flight (a load cannot complete while an NCCL
+ * kernel spins on a peer that is itself waiting for a load) - apm_comm_init calls it.  No reference counterpart. */
+apm_status apm_preload_kernels(int32_t device);
+
 apm_status apm_get_counters(apm_ctx* ctx, apm_counters* out);
 apm_status apm_reset_counters(apm_ctx* ctx);
 
@@ -423,7 +430,8 @@ apm_status apm_comm_init(apm_ctx* ctx, int32_t rank, int32_t nranks, const void*
  * (apm_host_alloc) is written directly, pageable memory through a device staging area.  The call waits once, at its
  * end.  Order: one block per rank (rank-ascending), inside it (tick, lag, key)-ascending.  Capacity: records per
  * block, default max_alerts_per_tick (one tick always fits); a host that lets many ticks pile up raises it with
- * apm_comm_set_capacity.  A block or tick that overflows is reported by every rank alike (APM_E_CAPACITY): the
+ * apm_comm_set_capacity (itself a collective: the ranks agree on the largest value any of them asked for, as they do
+ * on the default in apm_comm_init - blocks must have one size).  A block or tick that overflows is reported by every rank alike (APM_E_CAPACITY): the
  * headers travel with the blocks, so no rank is left waiting in a collective the others skipped.  Every gathered
  * record carries its sending rank in pad_[2] (ranks below 256): with dense per-rank key ids the key alone does not
  * say whose key it is. */
