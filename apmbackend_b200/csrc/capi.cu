@@ -491,6 +491,7 @@ apm_status apm_flush_pending(apm_ctx* c) {
 cudaError_t apm_preload_capi(); cudaError_t apm_preload_comm(); cudaError_t apm_preload_k1_ingest(); cudaError_t apm_preload_k2_tick();
 cudaError_t apm_preload_k3_onesweep(); cudaError_t apm_preload_k3_percentile_op(); cudaError_t apm_preload_k3_sort();
 cudaError_t apm_preload_k4_baseline(); cudaError_t apm_preload_k5_passthrough(); cudaError_t apm_preload_k6_logparse();
+cudaError_t apm_preload_k3_groupsort();
 
 extern "C" {
 
@@ -506,7 +507,7 @@ apm_status apm_preload_kernels(int32_t device) {
     static unsigned long long done = 0;
     if (!apm_first_on_device(&done)) return APM_OK;
     cudaError_t (*const parts[])() = {apm_preload_capi, apm_preload_comm, apm_preload_k1_ingest, apm_preload_k2_tick, apm_preload_k3_onesweep,
-                                      apm_preload_k3_percentile_op, apm_preload_k3_sort, apm_preload_k4_baseline,
+                                      apm_preload_k3_percentile_op, apm_preload_k3_sort, apm_preload_k3_groupsort, apm_preload_k4_baseline,
                                       apm_preload_k5_passthrough, apm_preload_k6_logparse};
     for (auto part : parts) {
         const cudaError_t e = part();
@@ -531,7 +532,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     if (c->s_pre) cudaStreamSynchronize(c->s_pre);
     cudaFree(c->acc_raw); cudaFree(c->seen); cudaFree(c->slot_meta);
     for (int i = 0; i <= c->S && i <= APM_MAX_SLOTS; ++i) cudaFree(c->log_buf[i]);
-    cudaFree(c->d_log_ptrs); cudaFree(c->sort_hist); cudaFree(c->sort_base); cudaFree(c->sort_scratch);
+    cudaFree(c->d_log_ptrs); cudaFree(c->sort_hist); cudaFree(c->sort_base); cudaFree(c->sort_scratch); cudaFree(c->gs_scratch);
     for (int i = 0; i < 2; ++i) {
         apm_ctx::PrePass& pp = c->pre[i];
         cudaFree(pp.tf_tile_max); cudaFree(pp.tf_tile_prefix); cudaFree(pp.d_ticks); cudaFree(pp.d_nticks);
@@ -660,6 +661,8 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
         if (c->sort_scratch_bytes <= ((size_t)1 << 30)) TRY_CREATE(cudaMalloc((void**)&c->sort_scratch, c->sort_scratch_bytes));
         else c->sort_scratch_bytes = 0;  // very large logs keep the three-kernel sort
         if (const char* e = getenv("APM_SORT_LEGACY")) c->sort_legacy = atoi(e) != 0;
+        if (const char* e = getenv("APM_SORT_GROUP")) c->sort_group = atoi(e) != 0;
+        TRY_CREATE(cudaMalloc((void**)&c->gs_scratch, apm_groupsort_scratch_bytes(c->K)));
     }
     TRY_CREATE(cudaMemcpyAsync(c->d_log_ptrs, c->log_buf, sizeof(uint64_t*) * APM_MAX_SLOTS, cudaMemcpyHostToDevice, c->s_main));
     c->tf_tiles_cap = (cfg->max_batch + 4095) / 4096;

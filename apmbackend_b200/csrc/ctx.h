@@ -9,6 +9,13 @@
 
 #include "common.cuh"
 
+// k3_groupsort.cu: which of the two plan buffers is current and how many splitters it holds (0: no plan)
+#define APM_GS_MAX_SPLIT 2048
+struct apm_groupsort_state {
+    int cur = 0;
+    uint32_t P = 0;
+};
+
 struct TickMark {
     unsigned long long pos;  // index in the chunk of the transaction that triggers the tick
     long long label;         // its bucket label (the new latestBucket)
@@ -57,6 +64,9 @@ struct apm_ctx {
     unsigned char* sort_scratch = nullptr;  // onesweep: tickets, global histograms, per-tile look-back status
     size_t sort_scratch_bytes = 0;
     bool sort_legacy = false;               // APM_SORT_LEGACY=1: three-kernel-per-pass sort (A/B measurements)
+    bool sort_group = true;                 // APM_SORT_GROUP=0: never take the planned partition + group sort path
+    apm_groupsort_state gs;                 // its plan, built from the last bucket that was sorted
+    unsigned char* gs_scratch = nullptr;
 
     // --- per-chunk pre-pass (tick finder + segment table).  Two sets: while the ticks of chunk i are being queued,
     //     the pre-pass of chunk i + 1 runs on its own stream (s_pre), so a chunk boundary costs the ingest / sort
@@ -221,6 +231,12 @@ uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t 
                             int vbits, int kbits, uint64_t* launches, cudaError_t* err);
 apm_status apm_acc_from_sorted(apm_ctx* c, int slot, uint64_t n);
 int apm_bits_of(uint64_t v);
+// k3_groupsort.cu
+size_t apm_groupsort_scratch_bytes(uint32_t K);
+bool apm_groupsort(cudaStream_t st, apm_groupsort_state* gs, unsigned char* scratch, uint32_t K, uint64_t* src, uint64_t* dst, uint64_t n,
+                   int vbits, uint64_t* launches, cudaError_t* err);
+cudaError_t apm_groupsort_plan_from(cudaStream_t st, apm_groupsort_state* gs, unsigned char* scratch, uint32_t K, const uint64_t* sorted,
+                                    uint64_t n, uint64_t* launches);
 // k2_tick.cu
 apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask);
 apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot, int buf);

@@ -363,7 +363,16 @@ apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value)
     }
     const int vbits = bits_of(max_value), kbits = bits_of(c->K > 1 ? c->K - 1 : 0);
     uint64_t* res = nullptr;
-    if (!c->sort_legacy && c->sort_scratch) {
+    const bool planned = c->sort_group && c->gs_scratch && !c->sort_legacy;
+    if (planned) {
+        // one partition pass + one pass of shared-memory sorts, planned from the last sorted bucket
+        cudaError_t e = cudaSuccess;
+        if (apm_groupsort(c->s_main, &c->gs, c->gs_scratch, c->K, c->log_buf[slot], c->log_buf[c->S], n, vbits, &c->launches, &e))
+            res = c->log_buf[c->S];
+        CUDA_TRY(c, e);
+    }
+    const bool by_plan = res != nullptr;
+    if (!res && !c->sort_legacy && c->sort_scratch) {
         cudaError_t e = cudaSuccess;
         res = apm_onesweep_sort(c->s_main, c->log_buf[slot], c->log_buf[c->S], n, c->sort_scratch, c->sort_scratch_bytes, vbits,
                                 kbits, &c->launches, &e);
@@ -373,6 +382,7 @@ apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value)
         res = apm_radix_sort_words(c->s_main, c->log_buf[slot], c->log_buf[c->S], n, c->sort_hist, c->sort_base, vbits, kbits,
                                    &c->launches);
     CUDA_TRY(c, cudaGetLastError());
+    if (planned && !by_plan) CUDA_TRY(c, apm_groupsort_plan_from(c->s_main, &c->gs, c->gs_scratch, c->K, res, n, &c->launches));
     if (res != c->log_buf[slot]) {  // result sits in the spare buffer: swap roles
         c->log_buf[c->S] = c->log_buf[slot];
         c->log_buf[slot] = res;
