@@ -164,6 +164,8 @@ SYMBOLS = {
     "apm_quantize": (C.c_double, [C.c_double, C.c_int32]),
     "apm_sorted_percentiles": (C.c_int32, [C.c_int32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int32, C.c_void_p,
                                            C.c_void_p]),
+    "apm_sorted_percentiles_host": (C.c_int32, [C.c_int32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int32, C.c_void_p,
+                                                C.c_void_p]),
     "apm_sorted_percentiles_noalloc": (C.c_int32, [C.c_int32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int32,
                                                    C.c_void_p, C.c_void_p]),
     "apm_owner_of_key": (C.c_uint32, [C.c_uint64, C.c_uint32]),

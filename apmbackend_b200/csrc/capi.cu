@@ -1181,6 +1181,7 @@ apm_status apm_set_latest(apm_ctx* c, int64_t latest) {
     apm_status st = sync_all(c);
     if (st) return st;
     c->latest = latest;
+    if (c->pt_cap && c->pt_base_ms == INT64_MIN) c->pt_base_ms = latest * c->cfg.bucket_ms - (1ll << 39);  // as the first tick would
     uint64_t mask = 0;
     for (int s = 0; s < c->S; ++s) c->slot_label[s] = -1;
     for (int64_t lab = std::max<int64_t>(0, latest - c->keep); lab <= latest; ++lab) {

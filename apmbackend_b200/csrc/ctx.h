@@ -64,7 +64,8 @@ struct apm_ctx {
     unsigned char* sort_scratch = nullptr;  // onesweep: tickets, global histograms, per-tile look-back status
     size_t sort_scratch_bytes = 0;
     bool sort_legacy = false;               // APM_SORT_LEGACY=1: three-kernel-per-pass sort (A/B measurements)
-    bool sort_group = true;                 // APM_SORT_GROUP=0: never take the planned partition + group sort path
+    bool sort_group = false;                // APM_SORT_GROUP=1: planned partition + shared-memory group sorts (k3_groupsort.cu;
+                                            // measured no faster than the radix passes, kept as an A/B path)
     apm_groupsort_state gs;                 // its plan, built from the last bucket that was sorted
     unsigned char* gs_scratch = nullptr;
 

@@ -139,6 +139,9 @@ std::mutex g_noalloc_mutex;
 
 extern "C" {
 
+apm_status apm_sorted_percentiles(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts, int32_t npct,
+                                  double* out_pct, int32_t* d_sorted);
+
 apm_status apm_sorted_percentiles_noalloc(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts,
                                           int32_t npct, double* out_pct, int32_t* d_sorted) {
     apm_status st = check_args(d_values, n, pcts, npct, out_pct);
@@ -148,7 +151,7 @@ apm_status apm_sorted_percentiles_noalloc(int32_t device, const int32_t* d_value
                         "apm_sorted_percentiles_noalloc: n exceeds APM_NOALLOC_MAX_VALUES (" + std::to_string(kNoAllocMaxValues) +
                             "); use apm_sorted_percentiles for larger arrays");
     if (device < 0 || device >= kMaxDevices) return apm_fail(nullptr, APM_E_INVALID, "apm_sorted_percentiles_noalloc: device ordinal");
-    CUDA_TRY(nullptr, cudaSetDevice(device));
+    ApmDeviceGuard guard(device);
     unsigned char* scratch;
     {
         std::lock_guard<std::mutex> lock(g_noalloc_mutex);
@@ -164,11 +167,32 @@ apm_status apm_sorted_percentiles_noalloc(int32_t device, const int32_t* d_value
     return run_percentiles(scratch, d_values, n, pcts, npct, out_pct, d_sorted);
 }
 
+// the same operator for an array in host memory (what a JavaScript caller has): copies in, sorts, copies out
+apm_status apm_sorted_percentiles_host(int32_t device, const int32_t* h_values, uint32_t n, const double* pcts, int32_t npct,
+                                       double* out_pct, int32_t* h_sorted) {
+    apm_status st = check_args(h_values, n, pcts, npct, out_pct);
+    if (st) return st;
+    ApmDeviceGuard guard(device);
+    int32_t* d = nullptr;
+    if (n) {
+        CUDA_TRY(nullptr, cudaMalloc((void**)&d, (size_t)n * sizeof(int32_t)));
+        cudaError_t e = cudaMemcpy(d, h_values, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { cudaFree(d); return apm_fail_cuda(nullptr, e, "cudaMemcpy", __FILE__, __LINE__); }
+    }
+    st = apm_sorted_percentiles(device, d, n, pcts, npct, out_pct, h_sorted ? d : nullptr);
+    if (!st && n && h_sorted) {
+        cudaError_t e = cudaMemcpy(h_sorted, d, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) st = apm_fail_cuda(nullptr, e, "cudaMemcpy", __FILE__, __LINE__);
+    }
+    cudaFree(d);
+    return st;
+}
+
 apm_status apm_sorted_percentiles(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts, int32_t npct,
                                   double* out_pct, int32_t* d_sorted) {
     apm_status st = check_args(d_values, n, pcts, npct, out_pct);
     if (st) return st;
-    CUDA_TRY(nullptr, cudaSetDevice(device));
+    ApmDeviceGuard guard(device);
     unsigned char* scratch = nullptr;
     CUDA_TRY(nullptr, cudaMalloc((void**)&scratch, plan_for(n).bytes));
     st = run_percentiles(scratch, d_values, n, pcts, npct, out_pct, d_sorted);

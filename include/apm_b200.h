@@ -310,7 +310,11 @@ apm_status apm_ring_load_all(apm_ctx* ctx, int32_t lag_idx, const double* values
 
 /* ---- checkpoint: replaces saveToResumeFile / resumeFromFileIfExists
  * (stream_calc_stats.js:54-87, stream_calc_z_score.js:37-64) with a compact
- * binary image of the same state. */
+ * binary image of the same state: bucket accumulators and value logs, seen keys, lag lists and per-key
+ * settings, alert counters and - with APM_F_PASSTHROUGH - the transactions still waiting in the device-side
+ * reorder buffer with their sequence numbers (the `minHeap` the reference's stats resume file carries,
+ * :40-52); without that flag the heap is the host's to save.  Load needs a context created with the same
+ * configuration; retained output records are not part of the image (fetch them before saving). */
 apm_status apm_state_save(apm_ctx* ctx, const char* path);
 apm_status apm_state_load(apm_ctx* ctx, const char* path);
 
@@ -365,6 +369,11 @@ double apm_quantize(double x, int32_t digits);
  * allocated and freed inside the call.  Errors are reported through apm_last_error(NULL). */
 apm_status apm_sorted_percentiles(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts, int32_t npct,
                                   double* out_pct, int32_t* d_sorted);
+
+/* The operator for an array in HOST memory (what a JavaScript caller of Array.prototype.calcPercentile has): copied
+ * to the device, sorted there, h_sorted (may be NULL) and out_pct copied back. */
+apm_status apm_sorted_percentiles_host(int32_t device, const int32_t* h_values, uint32_t n, const double* pcts, int32_t npct,
+                                       double* out_pct, int32_t* h_sorted);
 
 /* ---- the same operator for callers that must not allocate.  It has no counterpart in the
  * reference.  Some hosts of this library cannot call cudaMalloc at the point where they need

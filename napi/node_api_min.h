@@ -71,6 +71,9 @@ napi_status napi_create_int64(napi_env env, int64_t value, napi_value* result);
 napi_status napi_create_string_utf8(napi_env env, const char* str, size_t length, napi_value* result);
 napi_status napi_get_undefined(napi_env env, napi_value* result);
 napi_status napi_throw_error(napi_env env, const char* code, const char* msg);
+napi_status napi_create_function(napi_env env, const char* utf8name, size_t length, napi_callback cb, void* data, napi_value* result);
+napi_status napi_create_external_arraybuffer(napi_env env, void* external_data, size_t byte_length, napi_finalize finalize_cb,
+                                             void* finalize_hint, napi_value* result);
 
 #define NAPI_AUTO_LENGTH SIZE_MAX
 

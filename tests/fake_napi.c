@@ -90,6 +90,10 @@ void* fk_new(void* cls, size_t argc, void** argv) {
     inst->cls = V(cls);
     return call(inst, V(cls)->cb, argc, argv) ? inst : NULL;
 }
+void* fk_call_function(void* fn, size_t argc, void** argv) {
+    if (!fn || V(fn)->kind != FK_FUNCTION) { snprintf(g_exception, sizeof g_exception, "not a function"); return NULL; }
+    return call(NULL, V(fn)->cb, argc, argv);
+}
 void* fk_call_method(void* inst, const char* name, size_t argc, void** argv) {
     fk_value* m = V(inst)->cls ? prop_get(V(inst)->cls, name) : NULL;
     if (!m) { snprintf(g_exception, sizeof g_exception, "no method %s", name); return NULL; }
@@ -162,6 +166,12 @@ napi_status napi_create_double(napi_env env, double d, napi_value* r) { (void)en
 napi_status napi_create_int64(napi_env env, int64_t d, napi_value* r) { (void)env; *r = N(fk_number((double)d)); return napi_ok; }
 napi_status napi_create_string_utf8(napi_env env, const char* s, size_t n, napi_value* r) { (void)env; (void)n; *r = N(fk_string(s)); return napi_ok; }
 napi_status napi_get_undefined(napi_env env, napi_value* r) { (void)env; *r = N(mk(FK_UNDEF)); return napi_ok; }
+napi_status napi_create_function(napi_env env, const char* name, size_t len, napi_callback cb, void* data, napi_value* r) {
+    (void)env; (void)name; (void)len; (void)data; fk_value* f = mk(FK_FUNCTION); f->cb = cb; *r = N(f); return napi_ok;
+}
+napi_status napi_create_external_arraybuffer(napi_env env, void* data, size_t n, napi_finalize fin, void* hint, napi_value* r) {
+    (void)env; (void)fin; (void)hint; fk_value* b = mk(FK_BUFFER); b->data = data; b->len = n; *r = N(b); return napi_ok;
+}
 napi_status napi_throw_error(napi_env env, const char* code, const char* msg) {
     (void)env; snprintf(g_exception, sizeof g_exception, "%s: %s", code ? code : "", msg ? msg : ""); return napi_ok;
 }

@@ -75,3 +75,50 @@ def test_passthrough_with_the_commit_tick_protocol_and_invalid_rows():
     due = np.flatnonzero((ts[:start] <= edge) & (np.arange(start) != 100))
     assert sorted(s.tolist()) == due.tolist()
     eng.close()
+
+
+def test_passthrough_survives_save_and_load(tmp_path):
+    """The reference writes `minHeap` into the stats resume file and re-pushes it on resume
+    (stream_calc_stats.js:40-52, 54-61): a context restored from a state image must release the transactions that
+    were still waiting, under their old sequence numbers, exactly as the context that kept running does."""
+    S, J, bucket_ms = 6, 2, 10000
+    svc, jvm, ts, el = make_stream(73, 5000, S, J, bucket_ms, 100, late_frac=0.1, late_ms=120000)
+    flags = _capi.F_KEEP_STATS | _capi.F_PASSTHROUGH
+    mk = lambda: Engine(EngineConfig(num_services=S, num_jvms=J, percentiles=(), lags=(), thresholds=(), influences=(),  # noqa: E731
+                                     flags=flags, max_tx_per_bucket=1 << 14, max_batch=1 << 14, out_ticks=256))
+    half = 2600
+    a = mk()
+    a.process_host(svc[:half], jvm[:half], ts[:half], el[:half])
+    first = a.fetch_passthrough()
+    a.release_ticks()
+    path = str(tmp_path / "pt.state")
+    a.state_save(path)
+    b = mk()
+    b.state_load(path)
+    outs = []
+    for eng in (a, b):
+        eng.process_host(svc[half:], jvm[half:], ts[half:], el[half:])
+        t, s, c = eng.fetch_passthrough()
+        outs.append((t.copy(), s.copy(), c.copy(), eng.fetch_stats().copy()))
+        eng.close()
+    for x, y in zip(outs[0], outs[1]):
+        assert x.tobytes() == y.tobytes()
+    # and the two halves together are what one uninterrupted run releases
+    want = _reference_heap(ts, bucket_ms, 6)
+    got = np.concatenate([first[1], outs[1][1]])
+    assert sorted(got.tolist()) == sorted(i for w in want for _, i in w)
+    assert (outs[1][1] < half).any(), "some transactions of the first half must have been waiting across the checkpoint"
+
+
+def test_set_latest_gives_the_passthrough_its_time_base():
+    """After apm_set_latest (resume from the reference's JSON file) data may arrive before the first tick."""
+    S, bucket_ms = 4, 10000
+    svc, jvm, ts, el = make_stream(74, 400, S, 1, bucket_ms, 12)
+    flags = _capi.F_KEEP_STATS | _capi.F_PASSTHROUGH
+    eng = Engine(EngineConfig(num_services=S, percentiles=(), lags=(), thresholds=(), influences=(), flags=flags,
+                              max_tx_per_bucket=1 << 12, max_batch=1 << 12, out_ticks=64))
+    eng.set_latest(int(ts[0] // bucket_ms))
+    eng.process_host(svc, jvm, ts, el)  # used to fail: "no tick has set the time base yet"
+    t, s, c = eng.fetch_passthrough()
+    assert t.size > 0 and np.all(np.diff(t[:c[0]]) >= 0)
+    eng.close()

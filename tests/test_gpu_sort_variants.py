@@ -1,5 +1,5 @@
-"""Every form of the bucket sort behind the percentiles gives the same records: the planned partition + group sort
-(the default after a context's first bucket), and the radix passes it falls back to - packed 32-bit words (key + value fit
+"""Every form of the bucket sort behind the percentiles gives the same records: the radix passes (the default) and the
+planned partition + group sort (APM_SORT_GROUP=1) - packed 32-bit words (key + value fit
 32 bits) and 64-bit words, the compile-time 8-bit digit and run-time digit widths, the three-kernel fallback.
 The in-process run (default settings) is checked against the oracle; each variant then runs in a child process -
 the sort reads its environment knobs once per process - and must reproduce that run's records bit for bit."""
@@ -26,10 +26,10 @@ CASES = {
     "wide": dict(seed=32, n=70000, S=70000, J=1, bucket_ms=10000, window=2, buffer=0, span=8, lags=(3,), thr=(1.5,),
                  infl=(0.2,), pcts=(50.0, 95.0, 99.0), gap=None, log_cap=1 << 15, max_batch=1 << 17, elapsed_hi=1 << 20),
 }
-# the default build plans every bucket after a context's first from the bucket before it (partition + shared-memory
-# group sorts, k3_groupsort.cu); APM_SORT_GROUP=0 sends every bucket down the radix passes these knobs select
-VARIANTS = [{"APM_SORT_GROUP": "0"}, {"APM_SORT_GROUP": "0", "APM_SORT_NARROW": "0"}, {"APM_SORT_GROUP": "0", "APM_SORT_BITS": "11"},
-            {"APM_SORT_GROUP": "0", "APM_SORT_BITS": "10", "APM_SORT_NARROW": "0"}, {"APM_SORT_LEGACY": "1"}]
+# APM_SORT_GROUP=1: every bucket after a context's first is planned from the bucket before it (partition + shared-memory
+# group sorts, k3_groupsort.cu) instead of going down the radix passes the other knobs select
+VARIANTS = [{"APM_SORT_GROUP": "1"}, {"APM_SORT_NARROW": "0"}, {"APM_SORT_BITS": "11"}, {"APM_SORT_BITS": "10", "APM_SORT_NARROW": "0"},
+            {"APM_SORT_LEGACY": "1"}]
 
 
 def _stream(c):
