@@ -36,6 +36,7 @@ typedef struct {
     uint64_t fs_pinned_cap;
     apm_fs_record* gather_pinned;  /* bindGatherOutput / gatherAlerts */
     uint64_t gather_cap;
+    int32_t comm_ranks;            /* > 0 once commInit ran: every result object then carries `gathered` */
 } addon_obj;
 
 static napi_value undefined(napi_env env) {
@@ -186,7 +187,9 @@ static napi_value AddBatch(napi_env env, napi_callback_info info) {
     return undefined(env);
 }
 
-/* { ticks, latestBucket, stats, fs, alerts } with the records of the retained ticks, then releases them */
+static apm_status gather_buffer(addon_obj* o, uint64_t cap);
+
+/* { ticks, latestBucket, stats, fs, alerts[, gathered][, passthrough] } with the records of the retained ticks, then releases them */
 static napi_value collect(napi_env env, addon_obj* o, const apm_tick_result* res) {
     napi_value out, v;
     void* p;
@@ -227,6 +230,18 @@ static napi_value collect(napi_env env, addon_obj* o, const apm_tick_result* res
             free(tmp);
             napi_set_named_property(env, out, "alerts", v);
         }
+    }
+    if (o->comm_ranks > 0) {
+        /* multi-GPU: the alert records of ALL ranks for the same ticks (every rank calls at the same point of its stream) */
+        uint64_t cap = o->gather_cap;
+        if (!cap) cap = (uint64_t)o->comm_ranks * o->cfg.max_alerts_per_tick * (ticks ? ticks : 1);
+        apm_status st = gather_buffer(o, cap);
+        if (st) return fail(env, NULL, st, "apm_host_alloc");
+        st = apm_gather_alerts(o->ctx, o->gather_pinned, o->gather_cap, &n);
+        if (st) return fail(env, o->ctx, st, "apm_gather_alerts");
+        napi_create_arraybuffer(env, n * sizeof(apm_fs_record), &p, &v);
+        memcpy(p, o->gather_pinned, n * sizeof(apm_fs_record));
+        napi_set_named_property(env, out, "gathered", v);
     }
     if (o->cfg.flags & APM_F_PASSTHROUGH) {
         /* writeHeapToQueue's output of the retained ticks (stream_calc_stats.js:136-155): endTs order, arrival sequence numbers */
@@ -666,6 +681,7 @@ static napi_value CommInit(napi_env env, napi_callback_info info) {
         BAD("commInit(rank, nranks, uniqueId: Uint8Array(128))");
     apm_status st = apm_comm_init(o->ctx, (int32_t)rank, (int32_t)nranks, id);
     if (st) return fail(env, o->ctx, st, "apm_comm_init");
+    o->comm_ranks = (int32_t)nranks;
     return undefined(env);
 }
 static napi_value CommSetCapacity(napi_env env, napi_callback_info info) {

@@ -71,6 +71,7 @@ void* fk_typedarray(int type, void* data, size_t n) {
 }
 int fk_kind_of(void* v) { return v ? (int)V(v)->kind : -1; }
 double fk_number_value(void* v) { return V(v)->num; }
+const char* fk_string_value(void* v) { return V(v)->str ? V(v)->str : ""; }
 void* fk_buffer_data(void* v) { return V(v)->data; }
 size_t fk_buffer_len(void* v) { return V(v)->len; }
 const char* fk_exception(void) { return g_exception; }

@@ -6,7 +6,7 @@ import subprocess
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-U8, U32, I32, BIGI64 = 1, 6, 5, 9  # napi_typedarray_type
+U8, U32, I32, F64, BIGI64, BIGU64 = 1, 6, 5, 8, 9, 10  # napi_typedarray_type
 
 
 def load():
@@ -16,7 +16,7 @@ def load():
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "napi"), "../tests/_fake_napi_addon.so"],
                               stdout=subprocess.DEVNULL)
     L = C.CDLL(so)
-    for name in ("fk_env", "fk_object", "fk_init_module", "fk_get", "fk_new", "fk_call_method", "fk_buffer_data"):
+    for name in ("fk_env", "fk_object", "fk_init_module", "fk_get", "fk_new", "fk_call_method", "fk_call_function", "fk_buffer_data"):
         getattr(L, name).restype = C.c_void_p
     L.fk_number.restype = C.c_void_p
     L.fk_number.argtypes = [C.c_double]
@@ -32,6 +32,7 @@ def load():
     L.fk_get.argtypes = [C.c_void_p, C.c_char_p]
     L.fk_new.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
     L.fk_call_method.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_void_p]
+    L.fk_call_function.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
     L.fk_kind_of.argtypes = [C.c_void_p]
     L.fk_number_value.argtypes = [C.c_void_p]
     L.fk_number_value.restype = C.c_double
@@ -66,7 +67,8 @@ class FakeNode:
         return o
 
     def typed(self, arr: np.ndarray):
-        kind = {np.dtype(np.uint8): U8, np.dtype(np.uint32): U32, np.dtype(np.int32): I32, np.dtype(np.int64): BIGI64}[arr.dtype]
+        kind = {np.dtype(np.uint8): U8, np.dtype(np.uint32): U32, np.dtype(np.int32): I32, np.dtype(np.int64): BIGI64,
+                np.dtype(np.uint64): BIGU64, np.dtype(np.float64): F64}[arr.dtype]
         a = np.ascontiguousarray(arr)
         self._keep.append(a)
         return self.L.fk_typedarray(kind, a.ctypes.data, a.size)
@@ -88,6 +90,18 @@ class FakeNode:
         if not r:
             raise JsError(self.L.fk_exception().decode())
         return r
+
+    def fn(self, name: str, *args):
+        """a module-level function of the addon (exports.name(...))"""
+        r = self.L.fk_call_function(self.L.fk_get(self.exports, name.encode()), len(args), self._args(args))
+        if not r:
+            raise JsError(self.L.fk_exception().decode())
+        return r
+
+    def string_value(self, v) -> str:
+        self.L.fk_string_value.restype = C.c_char_p
+        self.L.fk_string_value.argtypes = [C.c_void_p]
+        return self.L.fk_string_value(v).decode()
 
     def number(self, x):
         return self.L.fk_number(float(x))
