@@ -294,6 +294,7 @@ int64_t latest_after(const apm_ctx::PrePass& pp) { return pp.nt ? pp.h_ticks[pp.
 apm_status run_chunk(apm_ctx* c, const apm_tx_columns& d, uint64_t n, const apm_ctx::PrePass& pp, apm_tick_result* res) {
     const unsigned int nt = pp.nt;
     if (pp.latest0 != c->latest) return apm_fail(c, APM_E_STATE, "internal: a chunk's pre-pass was made for another latestBucket");
+    if (apm_stats_chunk_eligible(c, n, nt)) return apm_stats_chunk(c, d, n, pp, res);  // stats only: the whole chunk in two launches
     const bool keep_any = c->cfg.flags & (APM_F_KEEP_STATS | APM_F_KEEP_FS | APM_F_ALERTS);
     if (keep_any && c->ticks_buffered + nt > c->cfg.out_ticks)
         return apm_fail(c, APM_E_WOULDBLOCK, "chunk holds more ticks than the output ring has room for: fetch results or raise out_ticks");
@@ -491,7 +492,7 @@ apm_status apm_flush_pending(apm_ctx* c) {
 cudaError_t apm_preload_capi(); cudaError_t apm_preload_comm(); cudaError_t apm_preload_k1_ingest(); cudaError_t apm_preload_k2_tick();
 cudaError_t apm_preload_k3_onesweep(); cudaError_t apm_preload_k3_percentile_op(); cudaError_t apm_preload_k3_sort();
 cudaError_t apm_preload_k4_baseline(); cudaError_t apm_preload_k5_passthrough(); cudaError_t apm_preload_k6_logparse();
-cudaError_t apm_preload_k3_groupsort();
+cudaError_t apm_preload_k3_groupsort(); cudaError_t apm_preload_k1_chunk();
 
 extern "C" {
 
@@ -506,7 +507,7 @@ apm_status apm_preload_kernels(int32_t device) {
     ApmDeviceGuard guard(device);
     static unsigned long long done = 0;
     if (!apm_first_on_device(&done)) return APM_OK;
-    cudaError_t (*const parts[])() = {apm_preload_capi, apm_preload_comm, apm_preload_k1_ingest, apm_preload_k2_tick, apm_preload_k3_onesweep,
+    cudaError_t (*const parts[])() = {apm_preload_capi, apm_preload_comm, apm_preload_k1_ingest, apm_preload_k1_chunk, apm_preload_k2_tick, apm_preload_k3_onesweep,
                                       apm_preload_k3_percentile_op, apm_preload_k3_sort, apm_preload_k3_groupsort, apm_preload_k4_baseline,
                                       apm_preload_k5_passthrough, apm_preload_k6_logparse};
     for (auto part : parts) {
@@ -547,7 +548,7 @@ void apm_ctx_destroy(apm_ctx* c) {
     cudaFree(c->d_stats); cudaFree(c->d_fs); cudaFree(c->d_alerts); cudaFree(c->d_alert_count); cudaFree(c->d_alert_blocks); cudaFree(c->zin[0]); cudaFree(c->zin[1]); cudaFree(c->emit[0]); cudaFree(c->emit[1]);
     for (int l = 0; l < APM_MAX_LAGS; ++l) { cudaFree(c->ring[l]); cudaFree(c->ring_len[l]); cudaFree(c->ring_next[l]);
         cudaFree(c->inc_sum[l]); cudaFree(c->inc_comp[l]); cudaFree(c->inc_cnt[l]); cudaFree(c->inc_nz[l]); cudaFree(c->thr[l]); cudaFree(c->infl[l]); }
-    cudaFree(c->d_counters); cudaFreeHost(c->h_counters);
+    cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->chunk_planes); cudaFree(c->chunk_first_seg); cudaFree(c->chunk_desc);
     cudaFree(c->alert_count); cudaFree(c->alert_hard_max); cudaFree(c->alert_suppressed);
     cudaFree(c->pt_pend[0]); cudaFree(c->pt_pend[1]); cudaFree(c->pt_emit); cudaFree(c->pt_tmp); cudaFree(c->pt_out); cudaFree(c->pt_cursors);
     for (int i = 0; i < 2; ++i) { if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]); if (c->ev_consumed[i]) cudaEventDestroy(c->ev_consumed[i]); }
@@ -613,6 +614,9 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     TRY_CREATE(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
     TRY_CREATE(cudaEventCreateWithFlags(&c->ev_d2h, cudaEventDisableTiming));
     if (const char* e = getenv("APM_NO_OVERLAP")) c->overlap = atoi(e) == 0;
+    if (const char* e = getenv("APM_STATS_CHUNK")) c->stats_chunk = atoi(e) != 0;
+    if (const char* e = getenv("APM_STATS_CHUNK_MIN_N")) c->stats_chunk_min_n = strtoull(e, nullptr, 10);
+    if (const char* e = getenv("APM_STATS_CHUNK_MIN_SEG")) c->stats_chunk_min_seg = strtoull(e, nullptr, 10);
     for (int i = 0; i < 2; ++i) {
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_consumed[i], cudaEventDisableTiming));

@@ -162,6 +162,15 @@ struct apm_ctx {
     double* alert_hard_max = nullptr;  // [K] per-key hardMaxMsAlertThreshold, <= 0: default
     uint8_t* alert_suppressed = nullptr;  // [K]
 
+    // stats-only whole-chunk path (k1_chunk.cu): per-segment accumulator planes, first-seen segments, tick descriptors
+    bool stats_chunk = true;               // APM_STATS_CHUNK=0: one reduce / clear / window launch per tick even in stats-only mode
+    uint64_t stats_chunk_min_n = 262144;   // below this many transactions, or this many per segment, the per-tick path is as good
+    uint64_t stats_chunk_min_seg = 8192;   // (APM_STATS_CHUNK_MIN_N / APM_STATS_CHUNK_MIN_SEG: tests lower them)
+    void* chunk_planes = nullptr;
+    size_t chunk_cells = 0;
+    uint32_t* chunk_first_seg = nullptr;
+    void* chunk_desc = nullptr;
+
     DevCounters* d_counters = nullptr;
     DevCounters* h_counters = nullptr;  // pinned mirror
     apm_counters counters;
@@ -222,6 +231,9 @@ apm_status apm_prepass_begin(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_colu
 apm_status apm_prepass_finish(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_columns& d, uint64_t n, cudaStream_t st);
 apm_status apm_prepass_segment(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_columns& d, uint64_t n, int64_t latest0, cudaStream_t st);
 apm_status apm_launch_reduce(apm_ctx* c, const apm_tx_columns& d, uint64_t begin, uint64_t end);
+// k1_chunk.cu
+bool apm_stats_chunk_eligible(const apm_ctx* c, uint64_t n, uint32_t nt);
+apm_status apm_stats_chunk(apm_ctx* c, const apm_tx_columns& d, uint64_t n, const apm_ctx::PrePass& pp, apm_tick_result* res);
 // k3_sort.cu
 apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value);
 uint64_t* apm_radix_sort_words(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t n, uint32_t* hist, uint32_t* totals,

@@ -305,7 +305,8 @@ struct K1Smem {
     uint32_t vmax;
     uint32_t pad_;
     // the hash table: only the stats-only variant allocates it
-    uint32_t tag[K1_TABLE], sum[K1_TABLE], sq_lo[K1_TABLE], cnt_hi[K1_TABLE], mn[K1_TABLE], mx[K1_TABLE];
+    // one word longer than the table each: the fields of an entry then fall into different banks (see k1_chunk.cu)
+    uint32_t tag[K1_TABLE + 1], sum[K1_TABLE + 1], sq_lo[K1_TABLE + 1], cnt_hi[K1_TABLE + 1], mn[K1_TABLE + 1], mx[K1_TABLE + 1];
 };
 constexpr size_t K1_SMEM_APPEND_ONLY = offsetof(K1Smem, tag);
 
@@ -409,6 +410,9 @@ __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReducePa
         uint32_t key[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
+            // lanes that took different paths through the last transaction (probe lengths, table misses) go on together:
+            // left to themselves they stay split for the rest of the tile and the warp executes everything several times
+            if (TABLE) __syncwarp();
             slot[j] = -1;
             key[j] = 0;
             if (!in[j]) continue;
@@ -430,23 +434,27 @@ __global__ void __launch_bounds__(K1_THREADS, 2) reduce_kernel_v3(const ReducePa
             if (!TABLE) continue;  // percentile mode: the accumulators are rebuilt from the sorted log
             bool done = false;
             if (v < 65536u) {
+                // straight-line probing: a loop around the compare-and-swap keeps a split warp from ever rejoining (see k1_chunk.cu)
                 const uint32_t tag = ((uint32_t)sl << K1_SLOT_SHIFT) | k;
                 uint32_t h = k1_hash(tag) & (K1_TABLE - 1);
-#pragma unroll 1
+                int at = -1;
+#pragma unroll
                 for (int pr = 0; pr < K1_PROBES; ++pr) {
-                    uint32_t cur = sm.tag[h];
-                    if (cur != tag) {
+                    if (at < 0) {
+                        uint32_t cur = sm.tag[h];
                         if (cur == K1_EMPTY) cur = atomicCAS(&sm.tag[h], K1_EMPTY, tag);
-                        if (cur != K1_EMPTY && cur != tag) { h = (h + 1) & (K1_TABLE - 1); continue; }
+                        if (cur == tag || cur == K1_EMPTY) at = (int)h;
+                        else h = (h + 1) & (K1_TABLE - 1);
                     }
-                    atomicAdd(&sm.sum[h], v);
+                }
+                if (at >= 0) {
+                    atomicAdd(&sm.sum[at], v);
                     const uint32_t q = v * v;
-                    const uint32_t o = atomicAdd(&sm.sq_lo[h], q);
-                    atomicAdd(&sm.cnt_hi[h], 0x10000u + ((o + q < o) ? 1u : 0u));
-                    if (v < sm.mn[h]) atomicMin(&sm.mn[h], v);
-                    if (v > sm.mx[h]) atomicMax(&sm.mx[h], v);
+                    const uint32_t o = atomicAdd(&sm.sq_lo[at], q);
+                    atomicAdd(&sm.cnt_hi[at], 0x10000u + ((o + q < o) ? 1u : 0u));
+                    if (v < sm.mn[at]) atomicMin(&sm.mn[at], v);
+                    if (v > sm.mx[at]) atomicMax(&sm.mx[at], v);
                     done = true;
-                    break;
                 }
             }
             if (!done) k1_global_update(p, sl, k, v);
@@ -619,6 +627,12 @@ apm_status apm_prepass_finish(apm_ctx* c, apm_ctx::PrePass& pp, const apm_tx_col
         std::sort(pp.h_ticks, pp.h_ticks + nt, [](const TickMark& a, const TickMark& b) { return a.pos < b.pos; });
     }
     if ((c->cfg.flags & APM_F_PERCENTILES) && c->cfg.num_percentiles > 0) return seg_table(c, pp, d, n, st);
+    if (nt && c->stats_chunk) {
+        // the whole-chunk stats path (k1_chunk.cu) reads the marks on the device, in position order
+        CUDA_TRY(c, cudaMemcpyAsync(pp.d_ticks, pp.h_ticks, nt * sizeof(TickMark), cudaMemcpyHostToDevice, st));
+        CUDA_TRY(c, cudaStreamSynchronize(st));
+        c->counters.h2d_bytes += nt * sizeof(TickMark);
+    }
     return APM_OK;
 }
 

@@ -59,16 +59,26 @@ __global__ void __launch_bounds__(GS_THREADS) gs_count_kernel(const uint64_t* __
     extern __shared__ uint32_t gs_smem_hist[];
     for (uint32_t i = threadIdx.x; i < ngroups; i += GS_THREADS) gs_smem_hist[i] = 0;
     __syncthreads();
-    const uint32_t stride = gridDim.x * GS_THREADS;
-    uint32_t i = blockIdx.x * GS_THREADS + threadIdx.x;
-    for (; i + 3 * stride < n; i += 4 * stride) {  // four independent loads in flight
+    // warp-uniform trip counts, and the lanes rejoin after every lookup: a lane that searches a hot key's splitters must
+    // not leave its warp split for the rest of the loop
+    const uint32_t tiles = (n + GS_TILE - 1) / GS_TILE;
+    for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const uint32_t base = tile * GS_TILE;
         uint64_t x[4];
+        for (int it = 0; it < GS_ITEMS; it += 4) {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) x[u] = __ldg(src + i + u * stride);
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t idx = base + (it + u) * GS_THREADS + threadIdx.x;
+                x[u] = idx < n ? __ldg(src + idx) : 0ull;
+            }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) atomicAdd(&gs_smem_hist[gs_classify(x[u], split, tbl)], 1u);
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t idx = base + (it + u) * GS_THREADS + threadIdx.x;
+                if (idx < n) atomicAdd(&gs_smem_hist[gs_classify(x[u], split, tbl)], 1u);
+                __syncwarp();
+            }
+        }
     }
-    for (; i < n; i += stride) atomicAdd(&gs_smem_hist[gs_classify(__ldg(src + i), split, tbl)], 1u);
     __syncthreads();
     for (uint32_t g = threadIdx.x; g < ngroups; g += GS_THREADS) {
         const uint32_t v = gs_smem_hist[g];
@@ -143,6 +153,7 @@ __global__ void __launch_bounds__(GS_THREADS) gs_scatter_kernel(const uint64_t* 
             g[i] = gs_classify(w[i], split, tbl);
             r[i] = (uint16_t)atomicAdd(&gs_smem_cnt[g[i]], 1u);  // any order will do: the group is sorted afterwards
         }
+        __syncwarp();  // lanes that searched a hot key's splitters rejoin the others
     }
     __syncthreads();
     for (uint32_t q = threadIdx.x; q < ngroups; q += GS_THREADS) {
