@@ -200,14 +200,16 @@ __global__ void __launch_bounds__(KC_THREADS, 1) reduce_chunk_kernel(const Chunk
                         seg = kc_marks_le(p.marks, cur_seg, p.nt, idx + j);
                         latest = p.marks[seg - 1].label;
                     }
-                    const int64_t lab = apm_label(ts[j], p.bucket_ms, p.inv_bucket);
+                    // most transactions fall into the segment's latest bucket: two compares instead of the division
+                    const int64_t b0 = latest * p.bucket_ms;
+                    const int64_t lab = (ts[j] >= b0 && ts[j] - b0 < p.bucket_ms) ? (int64_t)latest : apm_label(ts[j], p.bucket_ms, p.inv_bucket);
                     if (lab > latest) {
                         n_fut++;
                     } else {
                         k = jvm[j] * p.num_services + svc[j];
-                        if (p.first_seg[k] > seg) atomicMin(&p.first_seg[k], seg);
                         if (lab < latest - p.keep) {
                             n_drop++;
+                            if (p.first_seg[k] > seg) atomicMin(&p.first_seg[k], seg);  // too old to count, but it names the key (:125-126)
                         } else {
                             age = (uint32_t)(latest - lab);
                             v = (uint32_t)el[j];
@@ -229,7 +231,11 @@ __global__ void __launch_bounds__(KC_THREADS, 1) reduce_chunk_kernel(const Chunk
                 for (int pr = 0; pr < KC_PROBES; ++pr) {
                     if (slot < 0) {
                         uint32_t cur = sm.tag[h];
-                        if (cur == KC_EMPTY) cur = atomicCAS(&sm.tag[h], KC_EMPTY, tag);
+                        if (cur == KC_EMPTY) {
+                            cur = atomicCAS(&sm.tag[h], KC_EMPTY, tag);
+                            // whoever creates the entry names the key for this segment: once per (CTA, segment, key), not per transaction
+                            if (cur == KC_EMPTY && p.first_seg[k] > seg) atomicMin(&p.first_seg[k], seg);
+                        }
                         if (cur == tag || cur == KC_EMPTY) slot = (int)h;
                         else h = h + 1 == KC_TABLE ? 0 : h + 1;
                     }
@@ -246,7 +252,10 @@ __global__ void __launch_bounds__(KC_THREADS, 1) reduce_chunk_kernel(const Chunk
                     done = true;
                 }
             }
-            if (!done) kc_direct(p, seg, age, k, v);
+            if (!done) {
+                kc_direct(p, seg, age, k, v);
+                if (p.first_seg[k] > seg) atomicMin(&p.first_seg[k], seg);
+            }
             __syncwarp();  // lanes that took different paths (probe lengths, misses) go on together
         }
     }
@@ -306,6 +315,133 @@ __device__ __forceinline__ void kc_fold(const ChunkTickParams& p, uint32_t seg, 
         if (mn < p.acc.vmin[ai]) p.acc.vmin[ai] = mn;
         if (mx > p.acc.vmax[ai]) p.acc.vmax[ai] = mx;
     }
+}
+
+// the stat record of one (key, tick) from the window's exact integer moments (generateAllStatsToQueue, :157-203)
+__device__ __forceinline__ void kc_emit(apm_stat_record* rec, long long tick_ts, uint32_t key, double tpm_div, uint64_t cnt, uint64_t sum,
+                                        uint64_t sq_lo, uint64_t sq_hi, uint32_t vmin, uint32_t vmax) {
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    double avg = nan, sd = nan;
+    if (cnt) {
+        avg = __ddiv_rn((double)sum, (double)cnt);  // :181
+        const uint64_t a_lo = cnt * sq_lo, a_hi = __umul64hi(cnt, sq_lo) + cnt * sq_hi;
+        const uint64_t b_lo = sum * sum, b_hi = __umul64hi(sum, sum);
+        const uint64_t d_lo = a_lo - b_lo, d_hi = a_hi - b_hi - (a_lo < b_lo ? 1u : 0u);
+        const double num = __dadd_rn(__dmul_rn((double)d_hi, 18446744073709551616.0), (double)d_lo);
+        sd = __ddiv_rn(__dsqrt_rn(num), (double)cnt);
+    }
+    apm_stat_record r;
+    r.tick_ts = tick_ts;
+    r.key = key;
+    r.flags = 1u | (cnt ? 2u : 0u);
+    r.count = cnt;
+    r.sum = sum;
+    r.tpm = __ddiv_rn((double)cnt, tpm_div);  // :186
+    r.avg = avg;
+#pragma unroll
+    for (int q = 0; q < APM_MAX_PCT; ++q) r.pct[q] = nan;
+    r.min = cnt ? (int32_t)vmin : 0;
+    r.max = (int32_t)vmax;
+    r.stddev = sd;
+    *rec = r;
+}
+
+__device__ __forceinline__ void kc_add_sq(uint64_t& sq_lo, uint64_t& sq_hi, uint64_t lo_part, uint64_t hi_part) {
+    const uint64_t add_lo = lo_part + (hi_part << 32);
+    const uint64_t add_hi = (hi_part >> 32) + (add_lo < lo_part ? 1u : 0u);
+    const uint64_t t = sq_lo + add_lo;
+    sq_hi += add_hi + (t < sq_lo ? 1u : 0u);
+    sq_lo = t;
+}
+
+// Few bucket slots (tumbling or short windows: S <= 4): the key's accumulators stay in registers for the whole chunk and
+// each tick costs ONE round trip - the segment's plane cells of every age are loaded together, unconditionally - instead
+// of the dependent count -> cells -> accumulator read-modify-write chain of the general walk below.
+constexpr int KC_SMALL_S = 4;
+struct KcAcc {
+    uint64_t sum, sq_lo, sq_hi;
+    uint32_t cnt, mn, mx;
+};
+
+__global__ void __launch_bounds__(128) chunk_ticks_small_kernel(const ChunkTickParams p) {
+    const uint32_t key = blockIdx.x * blockDim.x + threadIdx.x;
+    if (key >= p.K) return;
+    KcAcc a[KC_SMALL_S];
+#pragma unroll
+    for (int sl = 0; sl < KC_SMALL_S; ++sl) {
+        a[sl] = KcAcc{0, 0, 0, 0, 0xFFFFFFFFu, 0};
+        if (sl < p.S) {
+            const size_t ai = (size_t)sl * p.K + key;
+            a[sl] = KcAcc{p.acc.sum[ai], p.acc.sq_lo[ai], p.acc.sq_hi[ai], p.acc.cnt[ai], p.acc.vmin[ai], p.acc.vmax[ai]};
+        }
+    }
+    const bool seen_before = p.seen[key] != 0;
+    const uint32_t first = p.first_seg[key];
+    uint32_t unseen = 0;
+    for (uint32_t i = 0; i <= p.nt; ++i) {
+        const bool tail = i == p.nt;   // the transactions behind the last tick are folded, nothing is emitted
+        const int slot_latest = tail ? p.slot_latest_final : p.desc[i].slot_latest_before;
+        // ---- fold segment i (addData of everything that arrived before the trigger, :370)
+        KcAcc c[KC_SMALL_S];
+#pragma unroll
+        for (int age = 0; age < KC_SMALL_S; ++age) {
+            c[age] = KcAcc{0, 0, 0, 0, 0xFFFFFFFFu, 0};
+            if (age <= p.keep) {
+                const size_t ci = ((size_t)i * (size_t)(p.keep + 1) + age) * p.K + key;
+                c[age] = KcAcc{p.planes.sum[ci], p.planes.sq_lo[ci], p.planes.sq_hi[ci], p.planes.cnt[ci], p.planes.vmin[ci], p.planes.vmax[ci]};
+            }
+        }
+#pragma unroll
+        for (int age = 0; age < KC_SMALL_S; ++age) {
+            if (age <= p.keep && c[age].cnt) {
+                int sl = slot_latest - age;
+                if (sl < 0) sl += p.S;
+#pragma unroll
+                for (int s2 = 0; s2 < KC_SMALL_S; ++s2)
+                    if (s2 == sl) {
+                        a[s2].cnt += c[age].cnt; a[s2].sum += c[age].sum; a[s2].sq_lo += c[age].sq_lo; a[s2].sq_hi += c[age].sq_hi;
+                        a[s2].mn = c[age].mn < a[s2].mn ? c[age].mn : a[s2].mn;
+                        a[s2].mx = c[age].mx > a[s2].mx ? c[age].mx : a[s2].mx;
+                    }
+            }
+        }
+        if (tail) break;
+        const TickDesc& d = p.desc[i];
+        // ---- removeOldBuckets (:103-113)
+#pragma unroll
+        for (int s2 = 0; s2 < KC_SMALL_S; ++s2)
+            if ((d.clear >> s2) & 1ull) a[s2] = KcAcc{0, 0, 0, 0, 0xFFFFFFFFu, 0};
+        apm_stat_record* rec = p.stats ? p.stats + (size_t)i * p.K + key : nullptr;
+        if (!(seen_before || first <= i)) {
+            if (rec) rec->flags = 0;
+            ++unseen;
+            continue;
+        }
+        if (!rec) continue;
+        uint64_t cnt = 0, sum = 0, sq_lo = 0, sq_hi = 0;
+        uint32_t vmin = 0xFFFFFFFFu, vmax = 0;
+        for (int w = 0; w < d.nwin; ++w) {
+            const int sl = d.win[w];
+#pragma unroll
+            for (int s2 = 0; s2 < KC_SMALL_S; ++s2)
+                if (s2 == sl && a[s2].cnt) {
+                    cnt += a[s2].cnt; sum += a[s2].sum;
+                    kc_add_sq(sq_lo, sq_hi, a[s2].sq_lo, a[s2].sq_hi);
+                    vmin = a[s2].mn < vmin ? a[s2].mn : vmin;
+                    vmax = a[s2].mx > vmax ? a[s2].mx : vmax;
+                }
+        }
+        kc_emit(rec, d.tick_ts, key, p.tpm_div, cnt, sum, sq_lo, sq_hi, vmin, vmax);
+    }
+#pragma unroll
+    for (int sl = 0; sl < KC_SMALL_S; ++sl)
+        if (sl < p.S) {
+            const size_t ai = (size_t)sl * p.K + key;
+            p.acc.sum[ai] = a[sl].sum; p.acc.sq_lo[ai] = a[sl].sq_lo; p.acc.sq_hi[ai] = a[sl].sq_hi;
+            p.acc.cnt[ai] = a[sl].cnt; p.acc.vmin[ai] = a[sl].mn; p.acc.vmax[ai] = a[sl].mx; p.acc.run_start[ai] = 0;
+        }
+    if (first != KC_NO_SEG && !seen_before) p.seen[key] = 1;
+    if (unseen) atomicAdd(p.unseen_records, unseen);
 }
 
 __global__ void __launch_bounds__(128) chunk_ticks_kernel(const ChunkTickParams p) {
@@ -491,7 +627,8 @@ apm_status apm_stats_chunk(apm_ctx* c, const apm_tx_columns& d, uint64_t n, cons
         tp.tpm_div = c->tpm_div;
         tp.stats = keep_stats ? c->d_stats + (size_t)tslot0 * c->K : nullptr;
         tp.unseen_records = &c->d_counters->unseen_records;
-        chunk_ticks_kernel<<<(c->K + 127) / 128, 128, 0, st>>>(tp);
+        if (c->S <= KC_SMALL_S) chunk_ticks_small_kernel<<<(c->K + 127) / 128, 128, 0, st>>>(tp);
+        else chunk_ticks_kernel<<<(c->K + 127) / 128, 128, 0, st>>>(tp);
         c->launches += 1;
         CUDA_TRY(c, cudaGetLastError());
     }
@@ -500,7 +637,7 @@ apm_status apm_stats_chunk(apm_ctx* c, const apm_tx_columns& d, uint64_t n, cons
 }
 
 cudaError_t apm_preload_k1_chunk() {
-    const void* fns[] = {(const void*)reduce_chunk_kernel, (const void*)chunk_ticks_kernel};
+    const void* fns[] = {(const void*)reduce_chunk_kernel, (const void*)chunk_ticks_kernel, (const void*)chunk_ticks_small_kernel};
     cudaError_t first = cudaSuccess;
     for (const void* f : fns) {
         cudaFuncAttributes a;
