@@ -233,6 +233,7 @@ def synth():
         S.synth_ring_fill_host.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint32, C.c_uint32,
                                            C.c_void_p, C.c_uint64]
         S.synth_ring_fill_host.restype = None
+        S.synth_mem_info.argtypes = [C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         S.synth_shard_tiles.argtypes = [C.c_uint64]
         S.synth_shard_tiles.restype = C.c_int
         S.synth_shard_count_device.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint32, C.c_int64, C.c_void_p, C.c_void_p]

@@ -161,6 +161,12 @@ int synth_free_host(void* p) { return (int)cudaFreeHost(p); }
 int synth_h2d(void* d, const void* h, uint64_t bytes) { return (int)cudaMemcpy(d, h, bytes, cudaMemcpyHostToDevice); }
 int synth_d2h(void* h, const void* d, uint64_t bytes) { return (int)cudaMemcpy(h, d, bytes, cudaMemcpyDeviceToHost); }
 int synth_sync(void) { return (int)cudaDeviceSynchronize(); }
+int synth_mem_info(uint64_t* free_bytes, uint64_t* total_bytes) {
+    size_t f = 0, t = 0;
+    const cudaError_t e = cudaMemGetInfo(&f, &t);
+    *free_bytes = f; *total_bytes = t;
+    return (int)e;
+}
 const char* synth_error_string(int e) { return cudaGetErrorString((cudaError_t)e); }
 
 // tables in p must be device pointers

@@ -97,7 +97,7 @@ WORKLOADS = {
     # (--gpus 4 or 8: 242 GB of lag rings in total)
     "cfg4": dict(n=1_000_000_000, services=1_000_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
                  percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,), influences=(0.0,),
-                 zscore=True, pct=True, seed=3, job=True, min_gpus=4,
+                 zscore=True, pct=True, seed=3, job=True, min_gpus=4, alert_frac=0.6,
                  desc="1B transactions, 1M keys, key-sharded over the ranks with NCCL alert all-gather, p50/p95/p99 + z-score vs "
                       "10080-bucket baseline (242 GB of rings over all ranks), exact-order baseline"),
     # BASELINE.json configs[4] as a job: 1 B transactions, 10 k keys, top 10 services = 80 % of the traffic (load-balance stress)
@@ -481,6 +481,9 @@ def main():
     wl = dict(WORKLOADS[args.workload])
     if args.scale != 1.0:
         wl["n"] = int(wl["n"] * args.scale)
+        if os.environ.get("APM_BENCH_SCALE_KEYS"):  # debug: shrink the key space with the stream (the line says scaled_down)
+            wl["services"] = max(int(wl["services"] * args.scale), 16)
+            wl["min_gpus"] = 1
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -559,13 +562,16 @@ def main():
     def step_t0(s):
         return t0 + s * span_ms
 
-    gather_out_cap = 6 * max(int(shard.plan.counts.max()) if shard.plan else K, 256) * max(len(wl["lags"]), 1) * world
+    # records a step's gather may deliver to every rank: all ranks' keys x lags x ticks x the share of records that alert
+    # (a few % for 10 k busy keys; sparse keys - cfg4's tail sees one transaction per bucket - alert far more often)
+    kmax = int(shard.plan.counts.max()) if shard.plan else K
+    gather_out_cap = max(int(kmax * max(len(wl["lags"]), 1) * (wl["span_buckets"] + 2) * world * wl.get("alert_frac", 0.1)), 4096)
 
     def setup_engine(extra_flags):
         e = make_engine(wl, shard, flags | extra_flags, local_rank, Engine, EngineConfig)
         if world > 1 and wl["zscore"]:
             e.comm_init(rank, world, broadcast_unique_id(rank, dist, Engine))
-            e.comm_set_capacity(max(int(shard.plan.counts.max()) * len(wl["lags"]) // 2, 1024))  # records per rank and tick
+            e.comm_set_capacity(max(kmax * len(wl["lags"]), 1024))  # records per rank and tick: a tick always fits
             e.bind_gather_output(gather_out_cap)
         if wl["zscore"] and wl.get("prefill", True) and K:
             shard.prefill(e, ring_seed)

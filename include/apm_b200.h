@@ -382,17 +382,24 @@ apm_status apm_sorted_percentiles_host(int32_t device, const int32_t* h_values, 
  * cannot absorb the device-wide synchronisation cudaMalloc and cudaFree imply, or a
  * deployment whose policy forbids device allocations after initialisation.  For them the scratch memory
  * (two word buffers, histograms, a few scalars; about 4.3 MB) lives in a fixed array inside
- * the library image, held by every GPU that loads the library until the process exits.
+ * the library image.  A GPU holds those bytes from the moment the library's code is loaded onto it until the
+ * process exits: under CUDA's default lazy loading that moment is the first call on the device (or
+ * apm_preload_kernels(device)), with CUDA_MODULE_LOADING=EAGER it is the creation of the CUDA context.
  *   - n may be at most APM_NOALLOC_MAX_VALUES; larger arrays are refused with APM_E_CAPACITY
  *     (use apm_sorted_percentiles).
  *   - the call itself performs no cudaMalloc / cudaFree and calls no allocating library
  *     routine; inputs (d_values) and outputs (d_sorted on the device, out_pct on the host)
  *     are the caller's.
- *   - the first call on each device looks the array's device address up
- *     (cudaGetSymbolAddress); make that first call before any stream capture starts.
+ *   - the first call on each device looks the array's device address up (cudaGetSymbolAddress) and, under
+ *     lazy loading, is what loads the kernels and the array: it needs a little free device memory and must not
+ *     happen inside a stream capture.  A host that hands all GPU memory to its own pool calls
+ *     apm_preload_kernels(device) - or makes one call with a small n >= 2 - BEFORE it reserves the memory;
+ *     from then on calls leave cudaMemGetInfo's free figure untouched (tests/test_zz_no_alloc.py checks that).
  *   - all calls share the one array, which keeps the previous call's contents (the call
  *     clears the single word it accumulates into).  Two calls that overlap on the same GPU
- *     - from two host threads or processes sharing a context - race on it: serialise them. */
+ *     - from two host threads or processes sharing a context - race on it: serialise them.
+ *   - both this and apm_sorted_percentiles run on the legacy default stream, which also orders them against
+ *     every blocking stream of the process. */
 #define APM_NOALLOC_MAX_VALUES 262144u
 apm_status apm_sorted_percentiles_noalloc(int32_t device, const int32_t* d_values, uint32_t n, const double* pcts,
                                           int32_t npct, double* out_pct, int32_t* d_sorted);

@@ -159,3 +159,69 @@ def test_cfg5_heavy_skew_top10_services_carry_80_percent():
         rows = st[st["tick_ts"] == closing * 60_000]
         assert int(rows["count"].sum()) == int(np.count_nonzero(labels[:tick_pos[i]] == closing))
     eng.close()
+
+
+@pytest.mark.parametrize("mode", ["exact", "incremental"])
+def test_cfg4_shard_size_sampled_keys(mode):
+    """One rank's share of BASELINE configs[3] at 8 GPUs: 125 M transactions over 125 k keys, 10 080-slot lists
+    (30 GB of rings, pre-filled), p50/p95/p99 + z-score.  A 0.4 % key sample is followed record by record by the
+    oracle (ticks stay global: it also sees every tick-triggering transaction); with the exact-order baseline every
+    field is bit-identical, with the guarded incremental one signals and values are, means / bounds within 1e-9."""
+    import bench
+    wl = bench.WORKLOADS["cfg4_shard"]
+    K, n = wl["services"], wl["n"]
+    span_ms = wl["span_buckets"] * wl["bucket_ms"]
+    per_bucket = n // wl["span_buckets"]
+    L = wl["lags"][0]
+    spec = syn.StreamSpec(seed=wl["seed"], n=n, num_services=K, span_ms=span_ms, shift_mod=97)
+    stream = syn.SynthStream(spec, device=True)
+    cols = syn.DeviceColumns(n)
+    stream.generate_device(cols)
+    flags = _capi.F_KEEP_FS | _capi.F_KEEP_STATS | _capi.F_ALERTS | _capi.F_ZSCORE | _capi.F_PERCENTILES
+    if mode == "incremental":
+        flags |= _capi.F_INCREMENTAL
+    eng = Engine(EngineConfig(num_services=K, bucket_ms=wl["bucket_ms"], window=1, buffer=0, percentiles=wl["percentiles"],
+                              z_series_pct=wl["z_series_pct"], lags=wl["lags"], thresholds=wl["thresholds"],
+                              influences=wl["influences"], flags=flags, max_tx_per_bucket=int(per_bucket * 1.5),
+                              max_batch=1 << 25, out_ticks=12, max_alerts_per_tick=K))
+    buf = syn.DeviceBuffer(L * 3 * K * 8)
+    syn.ring_fill_device(buf, L, stream, 77)
+    eng.ring_load_all(0, length=L, device_ptr=buf.ptr)
+    buf.free()
+    sample = np.unique(np.concatenate([np.arange(4), np.random.default_rng(13).choice(K, 500, replace=False)]))
+    st_parts, fs_parts, ticks = [], [], 0
+    step = 8 * per_bucket  # out_ticks is small (records of 125 k keys x 60 ticks would be 1.7 GB): fetch every 8 buckets
+    ing = 0
+    for a in range(0, n, step):
+        m = min(step, n - a)
+        res = eng.process_device(cols.columns(a), m)
+        ticks += res.ticks
+        ing += res.tx_ingested + res.tx_dropped + res.tx_invalid
+        st, fs = eng.fetch_stats(), eng.fetch_fs()
+        st_parts.append(st[np.isin(st["key"], sample)].copy())
+        fs_parts.append(fs[np.isin(fs["key"], sample)].copy())
+        eng.release_ticks()
+    assert ing == n and ticks >= wl["span_buckets"]
+    st, fs = np.concatenate(st_parts), np.concatenate(fs_parts)
+    svc, jvm, ts, el = cols.to_host()
+    cols.free()
+    lab = ts // wl["bucket_ms"]
+    run = np.maximum.accumulate(np.r_[0, lab])
+    keep_rows = np.isin(svc, sample) | (run[1:] > run[:-1])
+    keep = np.zeros(K, np.uint8)
+    keep[sample] = 1
+    oflags = ocapi.F_KEEP_FS | ocapi.F_KEEP_STATS | ocapi.F_ZSCORE | ocapi.F_PERCENTILES
+    orc = ocapi.Pipeline(ocapi.make_config(K, 1, wl["bucket_ms"], 1, 0, wl["percentiles"], wl["z_series_pct"], wl["lags"],
+                                           wl["thresholds"], wl["influences"], flags=oflags), fast=True)
+    orc.set_filter(keep)
+    host_stream = syn.SynthStream(spec, device=False)
+    for s in range(3):
+        vals = syn.ring_fill_host(L, host_stream, 77, s * K + sample)
+        for j, key in enumerate(sample):
+            orc.ring_load(int(key), 0, s, vals[:, j])
+    orc.consume(svc[keep_rows], jvm[keep_rows], ts[keep_rows], el[keep_rows])
+    assert orc.ticks == ticks
+    assert_stats_equal(st, orc.stats())
+    assert_fs_equal(fs, orc.fs(), exact=(mode == "exact"))
+    assert fs.size > 40 * sample.size
+    eng.close()

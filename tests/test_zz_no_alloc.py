@@ -56,3 +56,31 @@ def test_noalloc_rejects_sizes_beyond_its_maximum():
     v = _values(3, array_ops.NOALLOC_MAX_VALUES)  # exactly the maximum is accepted
     got_pct, got_sorted = array_ops.sorted_percentiles_noalloc(v, PCTS)
     assert np.array_equal(got_sorted, np.sort(v))
+
+
+def test_noalloc_call_leaves_the_free_device_memory_untouched():
+    """What the entry point promises: once the library's kernels and its static scratch are on the device
+    (apm_preload_kernels, or simply an earlier call), a call asks the CUDA allocator for nothing - the free memory
+    cudaMemGetInfo reports is the same before and after, also for the second call in a row.  The allocating entry
+    point is measured the same way, to show that the probe would see an allocation that stayed."""
+    from apmbackend_b200.synthetic import DeviceBuffer
+    lib, S = _capi.lib(), _capi.synth()
+    assert lib.apm_preload_kernels(0) == _capi.OK
+    v = _values(7, 150_000)
+    d_in, d_out = DeviceBuffer(v.nbytes).upload(v), DeviceBuffer(v.nbytes)
+    pcts = (C.c_double * 4)(*PCTS)
+    out = (C.c_double * 4)()
+
+    def free_now():
+        S.synth_sync()
+        f, t = C.c_uint64(0), C.c_uint64(0)
+        assert S.synth_mem_info(C.byref(f), C.byref(t)) == 0
+        return f.value
+
+    assert lib.apm_sorted_percentiles_noalloc(0, C.c_void_p(d_in.ptr), v.size, pcts, 4, out, C.c_void_p(d_out.ptr)) == _capi.OK  # warm
+    before = free_now()
+    for _ in range(2):
+        assert lib.apm_sorted_percentiles_noalloc(0, C.c_void_p(d_in.ptr), v.size, pcts, 4, out, C.c_void_p(d_out.ptr)) == _capi.OK
+        assert free_now() == before
+    assert np.array_equal(d_out.download(np.int32, v.size), np.sort(v))
+    d_in.free(); d_out.free()
