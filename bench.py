@@ -97,9 +97,11 @@ WORKLOADS = {
     # (--gpus 4 or 8: 242 GB of lag rings in total)
     "cfg4": dict(n=1_000_000_000, services=1_000_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
                  percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,), influences=(0.0,),
-                 zscore=True, pct=True, seed=3, job=True, min_gpus=4, alert_frac=0.6,
+                 zscore=True, pct=True, seed=3, job=True, min_gpus=4, alert_frac=0.1, alert_rules=True,
                  desc="1B transactions, 1M keys, key-sharded over the ranks with NCCL alert all-gather, p50/p95/p99 + z-score vs "
-                      "10080-bucket baseline (242 GB of rings over all ranks), exact-order baseline"),
+                      "10080-bucket baseline (242 GB of rings over all ranks), alert rules of the reference's stage [4] on "
+                      "(most of the 1M keys see about one transaction per bucket: every other record carries a signal, the "
+                      "rules' tpm / bad-interval gates make them the rare alerts they are in a deployment), exact-order baseline"),
     # BASELINE.json configs[4] as a job: 1 B transactions, 10 k keys, top 10 services = 80 % of the traffic (load-balance stress)
     "cfg5_job": dict(n=1_000_000_000, services=10_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
                      percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,), influences=(0.0,),
@@ -125,8 +127,8 @@ def parse_args():
                     help="exact: left-to-right re-sum of every lag list per tick (bit-identical means, the parity default); "
                          "incremental: guarded running sums (APM_F_INCREMENTAL: signals and lists bit-identical, means to 1e-9)")
     ap.add_argument("--placement", default="auto", choices=["auto", "hash", "table"],
-                    help="N > 1: which rank owns a key. hash: apm_owner_of_key (splitmix64 mod ranks); table: apm_owner_table_build "
-                         "(count- and key-cost-aware, for skewed traffic); auto: table for the skewed workloads, hash otherwise")
+                    help="N > 1: which rank owns a key. hash: apm_owner_of_key (splitmix64 mod ranks) for every key; table (= auto): "
+                         "apm_owner_table_build, the hash for light keys and count- / key-cost-aware placement of the heavy ones")
     ap.add_argument("--no-incremental", action="store_true", help="skip the extra timed pass with APM_F_INCREMENTAL")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -325,7 +327,9 @@ class Shard:
             exp = syn.expected_key_counts(self.stream)
             placement = args.placement
             if placement == "auto":
-                placement = "table" if wl.get("hot") else "hash"
+                # Zipf traffic is not hash-friendly: with 80 k keys the top key alone is 8 % of the stream, as much as a
+                # rank's whole fair share at 8 ranks.  The table keeps the hash for the light keys and places the heavy ones.
+                placement = "table"
             owner = None
             if placement == "table":
                 # count- and key-cost-aware placement (apm_owner_table_build): what a key costs per step, in transactions
@@ -335,7 +339,8 @@ class Shard:
                 st = _capi.lib().apm_owner_table_build(counts.ctypes.data, self.K_total, world, key_cost, owner.ctypes.data)
                 if st != 0:
                     raise SystemExit("apm_owner_table_build failed")
-                self.placement = f"placement table (apm_owner_table_build, key_cost {key_cost} transactions)"
+                self.placement = (f"apm_owner_table_build: key hash (splitmix64 mod ranks) for the light keys, the heavy ones placed "
+                                  f"longest-first on the least loaded rank, a key weighing its transactions + {key_cost}")
             else:
                 self.placement = "key hash (apm_owner_of_key: splitmix64(key) mod ranks)"
             self.plan = syn.ShardPlan(self.K_total, world, owner)
@@ -575,6 +580,10 @@ def main():
             e.bind_gather_output(gather_out_cap)
         if wl["zscore"] and wl.get("prefill", True) and K:
             shard.prefill(e, ring_seed)
+        if wl.get("alert_rules"):
+            # the alert stage's counter core behind every tick, with the reference's own settings
+            # (config/apm_config.json:189-204): the gathered block then holds triggered alerts, not every record with a signal
+            e.set_alert_rules()
         return e
 
     def barrier(e):
