@@ -220,14 +220,6 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
         c->slot_label[slot] = lab;
         c->host_count[slot] = c->host_sorted[slot] = 0;
     }
-    apm_status st = apm_launch_clear_slots(c, mask);
-    if (st) return st;
-    if (c->pt_cap) {  // writeHeapToQueue(edgeTs) comes before generateAllStatsToQueue (:364-366)
-        if (c->pt_base_ms == INT64_MIN) c->pt_base_ms = new_latest * c->cfg.bucket_ms - (1ll << 39);
-        st = apm_pt_tick(c, (new_latest - c->cfg.buffer_buckets - 1) * c->cfg.bucket_ms, keep_any ? c->ticks_buffered : 0);
-        if (st) return st;
-    }
-
     // window = labels in [latest - keep, latest - buffer] (:172)
     WindowSlots w;
     w.n = 0;
@@ -237,20 +229,41 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
         if (c->slot_label[slot] != lab) continue;  // never filled
         w.slot[w.n++] = slot;
     }
+    // the window's value logs that grew since their last sort; their lengths come from the chunk's segment table
+    // (the chunk's pre-pass), not from the device, so nothing here waits for the GPU
+    int grown[APM_MAX_SLOTS], ngrown = 0;
+    uint64_t grown_n[APM_MAX_SLOTS], largest = 0;
     if (with_pct(c)) {
-        // sort the window's value logs that grew since their last sort; their lengths come from the chunk's
-        // segment table (the chunk's pre-pass), not from the device, so nothing here waits for the GPU
         for (int i = 0; i < w.n; ++i) {
             const int slot = w.slot[i];
             const uint64_t count = c->host_count[slot];
             if (count > c->log_cap) return apm_fail(c, APM_E_CAPACITY, "a bucket's value log overflowed max_tx_per_bucket");
             if (count != c->host_sorted[slot]) {
-                st = apm_sort_slot_n(c, slot, count, c->known_max_value);
-                if (st) return st;
-                st = apm_acc_from_sorted(c, slot, count);  // count / sum / sum of squares / min / max from the runs
-                if (st) return st;
-                c->host_sorted[slot] = count;
+                grown[ngrown] = slot; grown_n[ngrown] = count; ++ngrown;
+                largest = std::max(largest, count);
             }
+        }
+    }
+    apm_status st;
+    if (with_pct(c) && !c->pt_cap && apm_small_tick_ok(c, largest)) {
+        // small shapes (the reference's own deployment): slot clear, sorts and accumulator rebuilds are one launch
+        st = apm_small_tick(c, grown, grown_n, ngrown, mask);
+        if (st) return st;
+        for (int i = 0; i < ngrown; ++i) c->host_sorted[grown[i]] = grown_n[i];
+    } else {
+        st = apm_launch_clear_slots(c, mask);
+        if (st) return st;
+        if (c->pt_cap) {  // writeHeapToQueue(edgeTs) comes before generateAllStatsToQueue (:364-366)
+            if (c->pt_base_ms == INT64_MIN) c->pt_base_ms = new_latest * c->cfg.bucket_ms - (1ll << 39);
+            st = apm_pt_tick(c, (new_latest - c->cfg.buffer_buckets - 1) * c->cfg.bucket_ms, keep_any ? c->ticks_buffered : 0);
+            if (st) return st;
+        }
+        for (int i = 0; i < ngrown; ++i) {
+            st = apm_sort_slot_n(c, grown[i], grown_n[i], c->known_max_value);
+            if (st) return st;
+            st = apm_acc_from_sorted(c, grown[i], grown_n[i]);  // count / sum / sum of squares / min / max from the runs
+            if (st) return st;
+            c->host_sorted[grown[i]] = grown_n[i];
         }
     }
     const int64_t tick_ts = (new_latest - c->cfg.buffer_buckets - 1) * c->cfg.bucket_ms;  // edgeTs (:356)
@@ -666,6 +679,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
         else c->sort_scratch_bytes = 0;  // very large logs keep the three-kernel sort
         if (const char* e = getenv("APM_SORT_LEGACY")) c->sort_legacy = atoi(e) != 0;
         if (const char* e = getenv("APM_SORT_GROUP")) c->sort_group = atoi(e) != 0;
+        if (const char* e = getenv("APM_SMALL_TICK")) c->small_tick = atoi(e) != 0;
         TRY_CREATE(cudaMalloc((void**)&c->gs_scratch, apm_groupsort_scratch_bytes(c->K)));
     }
     TRY_CREATE(cudaMemcpyAsync(c->d_log_ptrs, c->log_buf, sizeof(uint64_t*) * APM_MAX_SLOTS, cudaMemcpyHostToDevice, c->s_main));

@@ -64,6 +64,7 @@ struct apm_ctx {
     unsigned char* sort_scratch = nullptr;  // onesweep: tickets, global histograms, per-tile look-back status
     size_t sort_scratch_bytes = 0;
     bool sort_legacy = false;               // APM_SORT_LEGACY=1: three-kernel-per-pass sort (A/B measurements)
+    bool small_tick = true;                 // APM_SMALL_TICK=0: separate clear / sort / rebuild launches also for small shapes
     bool sort_group = false;                // APM_SORT_GROUP=1: planned partition + shared-memory group sorts (k3_groupsort.cu;
                                             // measured no faster than the radix passes, kept as an A/B path)
     apm_groupsort_state gs;                 // its plan, built from the last bucket that was sorted
@@ -243,6 +244,8 @@ size_t apm_onesweep_scratch_bytes(uint64_t max_n);
 uint64_t* apm_onesweep_sort(cudaStream_t st, uint64_t* a, uint64_t* b, uint64_t n, unsigned char* scratch, size_t scratch_bytes,
                             int vbits, int kbits, uint64_t* launches, cudaError_t* err);
 apm_status apm_acc_from_sorted(apm_ctx* c, int slot, uint64_t n);
+bool apm_small_tick_ok(const apm_ctx* c, uint64_t largest);
+apm_status apm_small_tick(apm_ctx* c, const int* slots, const uint64_t* n, int nslots, uint64_t clear_mask);
 int apm_bits_of(uint64_t v);
 // k3_groupsort.cu
 size_t apm_groupsort_scratch_bytes(uint32_t K);

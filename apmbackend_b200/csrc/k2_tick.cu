@@ -38,6 +38,20 @@ __device__ __forceinline__ uint32_t count_le(const Run& r, uint32_t v) {
     return lo;
 }
 
+// the same for a run that was staged in shared memory as plain 32-bit values
+struct RunS {
+    const uint32_t* p;
+    uint32_t n;
+};
+__device__ __forceinline__ uint32_t count_le(const RunS& r, uint32_t v) {
+    uint32_t lo = 0, hi = r.n;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (r.p[mid] <= v) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
 // k-th smallest (0-based) of the union of the runs; also returns how many values are <= it
 __device__ uint32_t select_kth(const Run* runs, int nruns, uint64_t k, uint32_t vmin, uint32_t vmax, uint64_t* n_le) {
     uint32_t lo = vmin, hi = vmax;  // invariant: answer in [lo, hi]
@@ -228,6 +242,8 @@ __device__ __forceinline__ uint64_t warp_sum_u64(uint64_t v) {
     return v;
 }
 
+constexpr int TSW_STAGE = 2560;  // values of one key's window a warp stages in shared memory (4 warps: 40 KB)
+
 __global__ void __launch_bounds__(128) tick_stats_warp_kernel(const TickParams p) {
     const uint32_t key = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -280,6 +296,39 @@ __global__ void __launch_bounds__(128) tick_stats_warp_kernel(const TickParams p
     const int nruns = __popc(__ballot_sync(0xffffffffu, runs[0].n != 0)) + __popc(__ballot_sync(0xffffffffu, runs[1].n != 0));
 
     double avg = nan, sd = nan, pct[APM_MAX_PCT] = {nan, nan, nan, nan};
+    // A window of up to TSW_STAGE values is copied into the warp's shared-memory stretch first: the value bisection below
+    // is a chain of ~17 x 2 x 5 dependent loads per percentile, and out of L2 that chain was the whole kernel (22 us for
+    // the reference's 400 keys x 31 buckets).
+    __shared__ uint32_t s_stage[4][TSW_STAGE];
+    const bool staged = p.with_pct && nruns > 1 && cnt <= (uint64_t)TSW_STAGE;
+    RunS sruns[2] = {{nullptr, 0}, {nullptr, 0}};
+    if (staged) {
+        uint32_t* mine = s_stage[(threadIdx.x >> 5) & 3];
+        const uint32_t len = runs[0].n + runs[1].n;
+        uint32_t incl = len;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        uint32_t at = incl - len;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            sruns[h].p = mine + at;
+            sruns[h].n = runs[h].n;
+            // eight loads in flight per round: one at a time, a hot key's 60-word run cost 60 round trips to L2
+            for (uint32_t i = 0; i < runs[h].n; i += 8) {
+                uint32_t v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = i + u < runs[h].n ? (uint32_t)__ldg(runs[h].p + i + u) : 0u;
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (i + u < runs[h].n) mine[at + i + u] = v[u];
+            }
+            at += runs[h].n;
+        }
+        __syncwarp();
+    }
     if (cnt != 0) {
         key_moments(cnt, sum, sq_lo, sq_hi, &avg, &sd);
         for (int q = 0; q < (p.with_pct ? p.npct : 0); ++q) {
@@ -301,18 +350,20 @@ __global__ void __launch_bounds__(128) tick_stats_warp_kernel(const TickParams p
             uint32_t lo = vmin, hi = vmax;
             while (lo < hi) {
                 const uint32_t mid = lo + ((hi - lo) >> 1);
-                const uint64_t c = warp_sum_u64((uint64_t)count_le(runs[0], mid) + count_le(runs[1], mid));
+                const uint32_t mine_le = staged ? count_le(sruns[0], mid) + count_le(sruns[1], mid) : count_le(runs[0], mid) + count_le(runs[1], mid);
+                const uint64_t c = warp_sum_u64((uint64_t)mine_le);
                 if (c >= i0 + 1) hi = mid; else lo = mid + 1;
             }
             const uint32_t v0 = lo;
             uint32_t v1 = v0;
             if (pair) {
-                const uint32_t c0 = count_le(runs[0], v0), c1 = count_le(runs[1], v0);
+                const uint32_t c0 = staged ? count_le(sruns[0], v0) : count_le(runs[0], v0);
+                const uint32_t c1 = staged ? count_le(sruns[1], v0) : count_le(runs[1], v0);
                 const uint64_t n_le = warp_sum_u64((uint64_t)c0 + c1);
                 if (n_le < i0 + 2) {  // element i0 + 1 is the smallest value above v0
                     uint32_t best = 0xFFFFFFFFu;
-                    if (c0 < runs[0].n) best = (uint32_t)__ldg(runs[0].p + c0);
-                    if (c1 < runs[1].n) { const uint32_t x = (uint32_t)__ldg(runs[1].p + c1); best = x < best ? x : best; }
+                    if (c0 < runs[0].n) best = staged ? sruns[0].p[c0] : (uint32_t)__ldg(runs[0].p + c0);
+                    if (c1 < runs[1].n) { const uint32_t x = staged ? sruns[1].p[c1] : (uint32_t)__ldg(runs[1].p + c1); best = x < best ? x : best; }
                     v1 = __reduce_min_sync(0xffffffffu, best);
                 }
             }

@@ -349,6 +349,105 @@ __global__ void __launch_bounds__(SS_THREADS) small_sort_kernel(uint64_t* __rest
 }  // namespace
 
 
+namespace {
+// ---- small buckets, small key spaces: sort + accumulator rebuild (+ the tick's slot clear) in ONE launch ------------
+// The reference's own deployment shape (a few hundred keys, a few hundred transactions per 10-s bucket) spent its
+// tick in launch latency: slot clear, one-CTA sort, plane clear and accumulator rebuild were four launches of a few
+// microseconds of work each.  Here CTA b < nslots takes bucket slot[b] - load, bitonic sort in shared memory, store,
+// clear the slot's planes, rebuild them from the sorted words (one thread per run start walks its run) - and the CTAs
+// behind them clear the planes of the slots the tick re-labels (removeOldBuckets, stream_calc_stats.js:103-113).
+struct SmallTickParams {
+    int nslots;
+    int slot[APM_MAX_SLOTS];
+    uint32_t n[APM_MAX_SLOTS];
+    unsigned long long clear_mask;   // slots the tick evicts: handled by the CTAs with index >= nslots
+    int S;
+};
+
+__global__ void __launch_bounds__(SS_THREADS) small_tick_kernel(const SmallTickParams p, uint64_t* const* __restrict__ logs, const AccSoA acc,
+                                                                uint32_t K, SlotMeta* __restrict__ meta) {
+    __shared__ uint64_t s[SS_CAP];
+    const uint32_t tid = threadIdx.x;
+    if ((int)blockIdx.x >= p.nslots) {
+        // the evicted slots: every (slot, key) plane entry back to empty, the slot's log length to 0
+        for (int sl = 0; sl < p.S; ++sl) {
+            if (!((p.clear_mask >> sl) & 1ull)) continue;
+            const size_t base = (size_t)sl * K;
+            for (uint32_t i = tid + (blockIdx.x - p.nslots) * SS_THREADS; i < K; i += (gridDim.x - p.nslots) * SS_THREADS) {
+                acc.sum[base + i] = 0; acc.sq_lo[base + i] = 0; acc.sq_hi[base + i] = 0;
+                acc.cnt[base + i] = 0; acc.vmin[base + i] = 0xFFFFFFFFu; acc.vmax[base + i] = 0; acc.run_start[base + i] = 0;
+            }
+            if ((int)blockIdx.x == p.nslots && tid == 0) { meta[sl].count = 0; meta[sl].sorted = 0; meta[sl].max_value = 0; }
+        }
+        return;
+    }
+    const int slot = p.slot[blockIdx.x];
+    const uint32_t n = p.n[blockIdx.x];
+    uint64_t* data = logs[slot];
+    uint32_t m = 2;
+    while (m < n) m <<= 1;
+    for (uint32_t i = tid; i < m; i += SS_THREADS) s[i] = i < n ? data[i] : ~0ull;
+    // this slot's planes start empty (the rebuild below writes every key that has a run)
+    const size_t base = (size_t)slot * K;
+    for (uint32_t i = tid; i < K; i += SS_THREADS) {
+        acc.sum[base + i] = 0; acc.sq_lo[base + i] = 0; acc.sq_hi[base + i] = 0;
+        acc.cnt[base + i] = 0; acc.vmin[base + i] = 0xFFFFFFFFu; acc.vmax[base + i] = 0; acc.run_start[base + i] = 0;
+    }
+    __syncthreads();
+    for (uint32_t k = 2; k <= m; k <<= 1) {
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t t = tid; t < (m >> 1); t += SS_THREADS) {
+                const uint32_t i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), l = i | j;
+                const uint64_t a = s[i], b = s[l];
+                const bool up = (i & k) == 0;
+                if ((a > b) == up) { s[i] = b; s[l] = a; }
+            }
+            __syncthreads();
+        }
+    }
+    for (uint32_t i = tid; i < n; i += SS_THREADS) {
+        const uint64_t x = s[i];
+        data[i] = x;
+        const uint32_t key = (uint32_t)(x >> 32);
+        if (i == 0 || (uint32_t)(s[i - 1] >> 32) != key) {
+            // first word of the key's run: its value is the minimum; walk the run for count, sum, sum of squares, maximum
+            uint32_t c = 0, last = 0;
+            unsigned long long sum = 0, sq_lo = 0, sq_hi = 0;
+            for (uint32_t q = i; q < n && (uint32_t)(s[q] >> 32) == key; ++q) {
+                const unsigned long long v = (uint32_t)s[q], sq = v * v;
+                ++c; sum += v; sq_lo += sq & 0xFFFFFFFFull; sq_hi += sq >> 32;
+                last = (uint32_t)v;
+            }
+            const size_t ai = base + key;
+            acc.cnt[ai] = c; acc.sum[ai] = sum; acc.sq_lo[ai] = sq_lo; acc.sq_hi[ai] = sq_hi;
+            acc.vmin[ai] = (uint32_t)x; acc.vmax[ai] = last; acc.run_start[ai] = i;
+        }
+    }
+    if (tid == 0) meta[slot].sorted = n;
+}
+}  // namespace
+
+// The small-shape tick: every bucket of `slots` (n[i] words each, all at most SS_CAP) sorted and its planes rebuilt,
+// and the slots of `clear_mask` emptied, in one launch.  The caller checks apm_small_tick_ok first.
+bool apm_small_tick_ok(const apm_ctx* c, uint64_t largest) {
+    return !c->sort_legacy && c->small_tick && largest <= (uint64_t)SS_CAP && c->K <= 16384;
+}
+
+apm_status apm_small_tick(apm_ctx* c, const int* slots, const uint64_t* n, int nslots, uint64_t clear_mask) {
+    if (nslots == 0 && !clear_mask) return APM_OK;
+    ProfScope prof_scope_(c, APM_PG_SORT);
+    SmallTickParams p;
+    p.nslots = nslots;
+    for (int i = 0; i < nslots; ++i) { p.slot[i] = slots[i]; p.n[i] = (uint32_t)n[i]; }
+    p.clear_mask = clear_mask;
+    p.S = c->S;
+    const unsigned clear_ctas = clear_mask ? (c->K + SS_THREADS - 1) / SS_THREADS : 0;
+    small_tick_kernel<<<nslots + clear_ctas, SS_THREADS, 0, c->s_main>>>(p, c->d_log_ptrs, c->acc, c->K, c->slot_meta);
+    c->launches += 1;
+    CUDA_TRY(c, cudaGetLastError());
+    return APM_OK;
+}
+
 // Sorts log slot `slot` (entries were appended since its last sort).
 apm_status apm_sort_slot_n(apm_ctx* c, int slot, uint64_t n, uint32_t max_value) {
     ProfScope prof_scope_(c, APM_PG_SORT);
@@ -410,7 +509,7 @@ apm_status apm_acc_from_sorted(apm_ctx* c, int slot, uint64_t n) {
 
 // Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
 cudaError_t apm_preload_k3_sort() {
-    const void* fns[] = {(const void*)acc_from_sorted_kernel, (const void*)clear_planes_kernel, (const void*)rs_hist_kernel, (const void*)rs_scan_rows_kernel, (const void*)rs_scatter_kernel, (const void*)small_sort_kernel};
+    const void* fns[] = {(const void*)small_tick_kernel, (const void*)acc_from_sorted_kernel, (const void*)clear_planes_kernel, (const void*)rs_hist_kernel, (const void*)rs_scan_rows_kernel, (const void*)rs_scatter_kernel, (const void*)small_sort_kernel};
     cudaError_t first = cudaSuccess;
     for (const void* f : fns) {
         cudaFuncAttributes a;

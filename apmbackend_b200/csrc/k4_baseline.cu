@@ -693,6 +693,43 @@ __global__ void __launch_bounds__(CA_THREADS) compact_alerts_kernel(const apm_fs
     if (blockIdx.x == gridDim.x - 1 && tid == 0) *count = base + total;
 }
 
+// The same compaction for a few thousand records (the reference's deployment: 400 keys x 2 lags) in one launch: a
+// single CTA walks the records 1024 at a time with a running base, in record order.
+__global__ void __launch_bounds__(1024) compact_alerts_small_kernel(const apm_fs_record* __restrict__ fs, uint32_t n,
+                                                                    apm_fs_record* __restrict__ alerts, unsigned int* __restrict__ count,
+                                                                    uint32_t cap, int by_trigger) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_base;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (uint32_t i0 = 0; i0 < n; i0 += 1024) {
+        const uint32_t i = i0 + tid;
+        const bool hit = ca_hit(fs, i, n, by_trigger);
+        const uint32_t bal = __ballot_sync(0xffffffffu, hit);
+        if (lane == 0) s_warp[w] = __popc(bal);
+        __syncthreads();
+        uint32_t before = 0, total = 0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const uint32_t c = s_warp[j];
+            if (j < w) before += c;
+            total += c;
+        }
+        const uint32_t k = s_base + before + __popc(bal & ((1u << lane) - 1u));
+        if (hit && k < cap) {
+            const uint4* src = reinterpret_cast<const uint4*>(fs + i);
+            uint4* dst = reinterpret_cast<uint4*>(alerts + k);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dst[j] = src[j];
+        }
+        __syncthreads();
+        if (tid == 0) s_base += total;
+        __syncthreads();
+    }
+    if (tid == 0) *count = s_base;
+}
+
 }  // namespace
 
 apm_status apm_baseline_make_tmaps(apm_ctx* c) {
@@ -802,6 +839,13 @@ apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t aler
     const uint32_t n = c->K * (uint32_t)c->cfg.num_lags;
     const unsigned g = (n + CA_THREADS - 1) / CA_THREADS;
     const apm_fs_record* fs = c->d_fs + (size_t)fs_slot * c->cfg.num_lags * c->K;
+    if (n <= 4096 && c->small_tick) {
+        compact_alerts_small_kernel<<<1, 1024, 0, st>>>(fs, n, c->d_alerts + (size_t)alert_slot * c->cfg.max_alerts_per_tick,
+                                                        c->d_alert_count + alert_slot, c->cfg.max_alerts_per_tick, c->alert_rules.enabled);
+        c->launches += 1;
+        CUDA_TRY(c, cudaGetLastError());
+        return APM_OK;
+    }
     count_alerts_kernel<<<g, CA_THREADS, 0, st>>>(fs, n, c->alert_rules.enabled, c->d_alert_blocks);
     compact_alerts_kernel<<<g, CA_THREADS, 0, st>>>(fs, n, c->d_alerts + (size_t)alert_slot * c->cfg.max_alerts_per_tick,
                                                     c->d_alert_count + alert_slot, c->cfg.max_alerts_per_tick, c->alert_rules.enabled,
@@ -813,7 +857,7 @@ apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t aler
 
 // Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
 cudaError_t apm_preload_k4_baseline() {
-    const void* fns[] = {(const void*)alert_counter_kernel, (const void*)baseline_inc_kernel, (const void*)baseline_kernel, (const void*)baseline_tma_kernel<2, 1>, (const void*)baseline_tma_kernel<3, 1>, (const void*)baseline_tma_kernel<4, 1>, (const void*)baseline_tma_kernel<6, 1>, (const void*)baseline_tma_kernel<K4T_DEEP_STAGES, 3>, (const void*)compact_alerts_kernel, (const void*)count_alerts_kernel, (const void*)inc_init_kernel, (const void*)realign_kernel};
+    const void* fns[] = {(const void*)alert_counter_kernel, (const void*)baseline_inc_kernel, (const void*)baseline_kernel, (const void*)baseline_tma_kernel<2, 1>, (const void*)baseline_tma_kernel<3, 1>, (const void*)baseline_tma_kernel<4, 1>, (const void*)baseline_tma_kernel<6, 1>, (const void*)baseline_tma_kernel<K4T_DEEP_STAGES, 3>, (const void*)compact_alerts_kernel, (const void*)compact_alerts_small_kernel, (const void*)count_alerts_kernel, (const void*)inc_init_kernel, (const void*)realign_kernel};
     cudaError_t first = cudaSuccess;
     for (const void* f : fns) {
         cudaFuncAttributes a;
