@@ -170,6 +170,7 @@ SYMBOLS = {
                                                    C.c_void_p, C.c_void_p]),
     "apm_owner_of_key": (C.c_uint32, [C.c_uint64, C.c_uint32]),
     "apm_owner_table_build": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint64, C.c_void_p]),
+    "apm_owner_table_build_capped": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_double, C.c_void_p]),
     "apm_comm_unique_id": (C.c_int32, [C.c_void_p]),
     "apm_comm_init": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "apm_gather_alerts": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),

@@ -1315,6 +1315,32 @@ apm_status apm_owner_table_build(const uint64_t* key_counts, uint32_t num_keys, 
     return APM_OK;
 }
 
+// Placement that evens out the TRANSACTIONS while every rank keeps (almost) the same number of KEYS: longest-first onto
+// the rank with the fewest transactions among those that still have room for a key.  For Zipf traffic over many keys -
+// one key can be most of a rank's fair share - where a rank's memory and its baseline walk follow the key count and its
+// ingest / sort / PCIe time the transactions.
+apm_status apm_owner_table_build_capped(const uint64_t* key_counts, uint32_t num_keys, uint32_t nranks, double key_slack,
+                                        uint32_t* owner_out) {
+    if ((!key_counts || !owner_out) && num_keys) return apm_fail(nullptr, APM_E_INVALID, "apm_owner_table_build_capped: null argument");
+    const uint32_t n = nranks ? nranks : 1;
+    if (!(key_slack >= 0.0)) key_slack = 0.0;
+    const uint64_t cap = (uint64_t)std::ceil((double)num_keys / n * (1.0 + key_slack));
+    std::vector<uint32_t> order(num_keys);
+    for (uint32_t k = 0; k < num_keys; ++k) order[k] = k;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return key_counts[a] > key_counts[b]; });
+    std::vector<uint64_t> load(n, 0), held(n, 0);
+    for (uint32_t k : order) {
+        uint32_t best = n;
+        for (uint32_t r = 0; r < n; ++r)
+            if (held[r] < cap && (best == n || load[r] < load[best])) best = r;
+        if (best == n) best = 0;  // cannot happen: n * cap >= num_keys
+        owner_out[k] = best;
+        load[best] += key_counts[k];
+        held[best] += 1;
+    }
+    return APM_OK;
+}
+
 // Host binning for key-sharded deployments (pure host arithmetic).  One pass over the arrival-ordered global stream:
 // every valid transaction goes to the rank that owns its key, arrival order kept inside a rank, and every rank learns
 // where the GLOBAL stream ticks - the running maximum of the bucket label over all transactions, whoever owns them

@@ -54,6 +54,27 @@ def balanced_owner_table(key_counts, nranks: int, key_cost: float = 0.0) -> np.n
     return owner
 
 
+def capped_owner_table(key_counts, nranks: int, key_slack: float = 0.01) -> np.ndarray:
+    """apm_owner_table_build_capped: transactions balanced longest-first, every rank's key count within (1 + key_slack) of
+    the mean (its ring memory and baseline walk follow the keys, its ingest / sort / PCIe time the transactions)."""
+    import math
+    counts = np.asarray(key_counts, dtype=np.uint64)
+    n = max(int(nranks), 1)
+    cap = math.ceil(counts.size / n * (1.0 + max(float(key_slack), 0.0)))
+    owner = np.zeros(counts.size, np.uint32)
+    load = [0] * n
+    held = [0] * n
+    for k in np.argsort(-counts.astype(np.int64), kind="stable"):
+        best = -1
+        for r in range(n):
+            if held[r] < cap and (best < 0 or load[r] < load[best]):
+                best = r
+        owner[k] = best
+        load[best] += int(counts[k])
+        held[best] += 1
+    return owner
+
+
 def partition_columns(service_id, jvm_id, end_ts_ms, elapsed_ms, num_services: int, nranks: int, owner_table=None):
     """Splits one arrival-ordered stream into per-rank streams (arrival order kept inside each).
     Returns a list of (service_id, jvm_id, end_ts_ms, elapsed_ms) per rank.  owner_table (balanced_owner_table)

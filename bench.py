@@ -126,9 +126,10 @@ def parse_args():
     ap.add_argument("--baseline", default="exact", choices=["exact", "incremental"],
                     help="exact: left-to-right re-sum of every lag list per tick (bit-identical means, the parity default); "
                          "incremental: guarded running sums (APM_F_INCREMENTAL: signals and lists bit-identical, means to 1e-9)")
-    ap.add_argument("--placement", default="auto", choices=["auto", "hash", "table"],
-                    help="N > 1: which rank owns a key. hash: apm_owner_of_key (splitmix64 mod ranks) for every key; table (= auto): "
-                         "apm_owner_table_build, the hash for light keys and count- / key-cost-aware placement of the heavy ones")
+    ap.add_argument("--placement", default="auto", choices=["auto", "hash", "table", "capped"],
+                    help="N > 1: which rank owns a key. hash: apm_owner_of_key (splitmix64 mod ranks) for every key; capped: "
+                         "apm_owner_table_build_capped, transactions balanced with even key counts; table: apm_owner_table_build, "
+                         "count- and key-cost-aware; auto: table for the two-tier skew of config 5, capped otherwise")
     ap.add_argument("--no-incremental", action="store_true", help="skip the extra timed pass with APM_F_INCREMENTAL")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -329,9 +330,18 @@ class Shard:
             if placement == "auto":
                 # Zipf traffic is not hash-friendly: with 80 k keys the top key alone is 8 % of the stream, as much as a
                 # rank's whole fair share at 8 ranks.  The table keeps the hash for the light keys and places the heavy ones.
-                placement = "table"
+                placement = "table" if wl.get("hot") else "capped"
             owner = None
-            if placement == "table":
+            if placement == "capped":
+                counts = np.ascontiguousarray(np.rint(exp), dtype=np.uint64)
+                owner = np.empty(self.K_total, np.uint32)
+                st = _capi.lib().apm_owner_table_build_capped(counts.ctypes.data, self.K_total, world, 0.01, owner.ctypes.data)
+                if st != 0:
+                    raise SystemExit("apm_owner_table_build_capped failed")
+                self.placement = ("apm_owner_table_build_capped: transactions balanced longest-first, every rank's key count within "
+                                  "1 % of the mean (Zipf traffic: the top key alone is most of a rank's fair share, the hash "
+                                  "would leave one rank with 1.5 x the mean)")
+            elif placement == "table":
                 # count- and key-cost-aware placement (apm_owner_table_build): what a key costs per step, in transactions
                 key_cost = int(wl.get("key_cost", 160_000 if args.baseline == "exact" else 4_000))
                 counts = np.ascontiguousarray(np.rint(exp), dtype=np.uint64)

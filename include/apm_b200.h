@@ -416,6 +416,13 @@ uint32_t apm_owner_of_key(uint64_t global_key, uint32_t nranks);
  * do not migrate - choose the table when a deployment starts.  Pure host arithmetic, no device needed. */
 apm_status apm_owner_table_build(const uint64_t* key_counts, uint32_t num_keys, uint32_t nranks, uint64_t key_cost,
                                  uint32_t* owner_out);
+/* The other placement: balance the transactions, keep the KEY COUNT of every rank within (1 + key_slack) of the mean.
+ * A rank's ring memory and its exact-order baseline walk follow its keys, its ingest / sort / PCIe time its
+ * transactions; with Zipf traffic over many keys (80 k keys at 8 ranks: the top key alone is two thirds of a rank's
+ * fair share) the hash leaves one rank with 1.5 x the mean.  Longest-first onto the rank with the fewest transactions
+ * that still has room for a key.  Pure host arithmetic. */
+apm_status apm_owner_table_build_capped(const uint64_t* key_counts, uint32_t num_keys, uint32_t nranks, double key_slack,
+                                        uint32_t* owner_out);
 /* Host binning for a key-sharded deployment (no counterpart in the reference, whose stats stage is one process that
  * sees every transaction; it keeps what makes sharding legal - no statistic has a cross-key term,
  * stream_calc_stats.js:159-202, stream_calc_z_score.js:197-308 - and what makes it subtle: ticks are triggered by ANY

@@ -838,6 +838,22 @@ static napi_value OwnerTableBuild(napi_env env, napi_callback_info info) {
     free(owner);
     return v;
 }
+/* ownerTableBuildCapped(counts: BigUint64Array, nranks, keySlack) -> ArrayBuffer of uint32 owners */
+static napi_value OwnerTableBuildCapped(napi_env env, napi_callback_info info) {
+    napi_value argv[3];
+    void* c;
+    size_t n;
+    double nranks, slack;
+    if (plain_args(env, info, 3, argv) < 3 || !typed(env, argv[0], napi_biguint64_array, &c, &n) || napi_get_value_double(env, argv[1], &nranks) != napi_ok ||
+        napi_get_value_double(env, argv[2], &slack) != napi_ok)
+        BAD("ownerTableBuildCapped(counts: BigUint64Array, nranks, keySlack)");
+    uint32_t* owner = (uint32_t*)malloc((n ? n : 1) * sizeof *owner);
+    apm_status st = apm_owner_table_build_capped((const uint64_t*)c, (uint32_t)n, (uint32_t)nranks, slack, owner);
+    if (st) { free(owner); return fail(env, NULL, st, "apm_owner_table_build_capped"); }
+    napi_value v = buffer_of(env, owner, n * sizeof *owner);
+    free(owner);
+    return v;
+}
 /* commUniqueId() -> ArrayBuffer(128) for commInit on every rank */
 static napi_value CommUniqueId(napi_env env, napi_callback_info info) {
     (void)info;
@@ -1023,7 +1039,7 @@ napi_value napi_register_module_v1(napi_env env, napi_value exports) {
     napi_create_double(env, (double)apm_abi_version(), &v);
     napi_set_named_property(env, exports, "abiVersion", v);
     const struct { const char* name; napi_callback cb; } fns[] = {
-        {"quantize", Quantize}, {"ownerOfKey", OwnerOfKey}, {"ownerTableBuild", OwnerTableBuild}, {"commUniqueId", CommUniqueId},
+        {"quantize", Quantize}, {"ownerOfKey", OwnerOfKey}, {"ownerTableBuild", OwnerTableBuild}, {"ownerTableBuildCapped", OwnerTableBuildCapped}, {"commUniqueId", CommUniqueId},
         {"preloadKernels", PreloadKernels}, {"nameHash", NameHash}, {"calcPercentiles", CalcPercentiles}, {"partitionColumns", PartitionColumns}};
     for (size_t i = 0; i < sizeof fns / sizeof fns[0]; ++i) {
         napi_create_function(env, fns[i].name, NAPI_AUTO_LENGTH, fns[i].cb, NULL, &v);

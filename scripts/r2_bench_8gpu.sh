@@ -1,5 +1,6 @@
 # the 8-rank jobs of round 2 (one box, 8 x B200): default workload, cfg4 and cfg5 as key-sharded jobs
-run() { name=$1; shift; timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 8 "$@" > gpurun_out/$name.json 2> gpurun_out/$name.err; echo "$name rc=$?"; grep "^\[rank" gpurun_out/$name.err | head -8; python - <<PY
+NP=${NP:-8}
+run() { name=$1; shift; timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NP --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $NP "$@" > gpurun_out/$name.json 2> gpurun_out/$name.err; echo "$name rc=$?"; grep "^\[rank" gpurun_out/$name.err | tr ']' '\n' | grep -o "rank [0-9]*.*step" | head -8; python - <<PY
 import json
 try:
     d=json.load(open('gpurun_out/$name.json'))
@@ -9,6 +10,11 @@ except Exception as e:
 PY
 }
 export APM_BENCH_WATCHDOG=500
-run bench_r2_8gpu --steps 5 --warmup 3 --no-cpu-baseline
-run bench_r2_8gpu_cfg4 --workload cfg4 --steps 3 --warmup 2 --no-cpu-baseline --no-e2e
-run bench_r2_8gpu_cfg5 --workload cfg5_job --steps 3 --warmup 2 --no-cpu-baseline
+for w in "$@"; do
+  case $w in
+    cfg3) run bench_r2_${NP}gpu --steps 5 --warmup 3 --no-cpu-baseline ;;
+    cfg3hash) run bench_r2_${NP}gpu_hash --placement hash --steps 5 --warmup 3 --no-cpu-baseline --no-e2e ;;
+    cfg4) run bench_r2_${NP}gpu_cfg4_job --workload cfg4 --steps 3 --warmup 2 --no-cpu-baseline --no-e2e ;;
+    cfg5) run bench_r2_${NP}gpu_cfg5_job --workload cfg5_job --steps 3 --warmup 2 --no-cpu-baseline ;;
+  esac
+done

@@ -141,12 +141,12 @@ ABI_TO_JS = {
     "apm_log_read": "logRead", "apm_latest": "latest", "apm_get_counters": "counters", "apm_reset_counters": "resetCounters",
     "apm_preload_kernels": "preloadKernels", "apm_quantize": "quantize", "apm_sorted_percentiles": None,
     "apm_sorted_percentiles_host": "calcPercentiles", "apm_sorted_percentiles_noalloc": None, "apm_owner_of_key": "ownerOfKey",
-    "apm_owner_table_build": "ownerTableBuild", "apm_partition_host": "partitionColumns", "apm_comm_unique_id": "commUniqueId",
+    "apm_owner_table_build": "ownerTableBuild", "apm_owner_table_build_capped": "ownerTableBuildCapped", "apm_partition_host": "partitionColumns", "apm_comm_unique_id": "commUniqueId",
     "apm_comm_init": "commInit", "apm_comm_set_capacity": "commSetCapacity", "apm_bind_gather_output": "bindGatherOutput",
     "apm_gather_alerts": "gatherAlerts", "apm_name_hash": "nameHash", "apm_dict_set": "dictSet", "apm_parse_log_host": "parseLog",
     "apm_feed_parsed": "feedParsed",
 }
-MODULE_FUNCTIONS = ("quantize", "ownerOfKey", "ownerTableBuild", "commUniqueId", "preloadKernels", "nameHash", "calcPercentiles",
+MODULE_FUNCTIONS = ("quantize", "ownerOfKey", "ownerTableBuild", "ownerTableBuildCapped", "commUniqueId", "preloadKernels", "nameHash", "calcPercentiles",
                     "partitionColumns")
 
 
@@ -176,6 +176,8 @@ def test_module_level_helpers_equal_the_c_abi():
     counts = np.r_[np.full(10, 80_000_000), np.full(990, 20_020)].astype(np.uint64)
     got = node.buffer(node.fn("ownerTableBuild", node.typed(counts), node.number(8), node.number(160_000)), np.uint32)
     assert np.array_equal(got, sharding.balanced_owner_table(counts, 8, key_cost=160_000))
+    got = node.buffer(node.fn("ownerTableBuildCapped", node.typed(counts), node.number(8), node.number(0.01)), np.uint32)
+    assert np.array_equal(got, sharding.capped_owner_table(counts, 8, 0.01))
     assert node.string_value(node.fn("nameHash", node.string("S:getFoo"))) == str(lib.apm_name_hash(b"S:getFoo", 8))
     # host binning: the same sub-streams and marks as the ctypes path
     svc, jvm, ts, el = make_stream(91, 3000, 12, 2, 10000, 60, late_frac=0.05)

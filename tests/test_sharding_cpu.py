@@ -231,3 +231,27 @@ def test_native_partitioner_reports_full_outputs():
     cols = _capi.TxColumns(svc.ctypes.data, jvm.ctypes.data, ts.ctypes.data, el.ctypes.data)
     st = _capi.lib().apm_partition_host(C.byref(cols), svc.size, 10000, 0, 4, 1, 2, None, None, outs, None)
     assert st == _capi.E_CAPACITY and b"full" in _capi.lib().apm_last_error(None)
+
+
+def test_capped_placement_balances_transactions_with_even_key_counts():
+    """80 k keys of Zipf(1) traffic on 8 ranks: the hash gives one rank 1.55 x the mean; the capped placement evens the
+    transactions out while no rank holds more than 1 % above its share of the keys.  C ABI == numpy mirror."""
+    lib = _capi.lib()
+    K, n = 80_000, 8
+    counts = np.rint(800e6 / (np.arange(1, K + 1) * np.log(K))).astype(np.uint64)
+    out = np.empty(K, np.uint32)
+    assert lib.apm_owner_table_build_capped(counts.ctypes.data, K, n, 0.01, out.ctypes.data) == 0
+    tx = np.bincount(out, weights=counts.astype(np.float64), minlength=n)
+    keys = np.bincount(out, minlength=n)
+    hashed = np.bincount(sharding.owner_of_keys(np.arange(K), n), weights=counts.astype(np.float64), minlength=n)
+    assert hashed.max() / hashed.mean() > 1.4
+    assert tx.max() / tx.mean() < 1.01 and keys.max() <= np.ceil(K / n * 1.01)
+    small = counts[:3000]
+    o2 = np.empty(small.size, np.uint32)
+    assert lib.apm_owner_table_build_capped(small.ctypes.data, small.size, 3, 0.05, o2.ctypes.data) == 0
+    assert np.array_equal(o2, sharding.capped_owner_table(small, 3, 0.05))
+    # two-tier skew (config 5): two ranks must hold two hot services; the cap leaves them the lightest keys
+    c5 = np.r_[np.full(10, 80_000_000), np.full(9990, 20_020)].astype(np.uint64)
+    o5 = np.empty(c5.size, np.uint32)
+    assert lib.apm_owner_table_build_capped(c5.ctypes.data, c5.size, 8, 0.01, o5.ctypes.data) == 0
+    assert np.bincount(o5, minlength=8).max() <= 1263 and sorted(np.bincount(o5[:10], minlength=8).tolist()) == [1] * 6 + [2, 2]
