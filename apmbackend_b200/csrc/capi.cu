@@ -166,9 +166,14 @@ apm_status launch_baseline_group(apm_ctx* c, const PendingBaseline& pb, cudaStre
         st = apm_launch_realign(c, pb.buf, sb);  // lists of keys that were silent re-enter the lock step
         if (st) return st;
     }
-    for (int l = 0; l < c->cfg.num_lags; ++l) {  // Object.entries(lags): ascending (:217)
-        st = apm_launch_baseline(c, l, pb.tick_ts, pb.fslot, pb.buf, sb);
+    if (apm_baseline_few_ok(c)) {  // a few hundred lists: every lag in one launch, loader and adder warps
+        st = apm_launch_baseline_few(c, pb.tick_ts, pb.fslot, pb.buf, sb);
         if (st) return st;
+    } else {
+        for (int l = 0; l < c->cfg.num_lags; ++l) {  // Object.entries(lags): ascending (:217)
+            st = apm_launch_baseline(c, l, pb.tick_ts, pb.fslot, pb.buf, sb);
+            if (st) return st;
+        }
     }
     st = apm_launch_alert_counter(c, pb.fslot, sb);  // processFSEntry's counter, when rules are set
     if (st) return st;
@@ -601,6 +606,8 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     c->inv_bucket = 1.0 / (double)cfg->bucket_ms;
     if (const char* e = getenv("APM_K4_STAGES")) c->k4_stages = atoi(e);
     if (const char* e = getenv("APM_K4_LDG")) c->k4_force_ldg = atoi(e) != 0;
+    if (const char* e = getenv("APM_K4_FEW")) c->k4_few = atoi(e) != 0;
+    if (getenv("APM_SMEM_CARVEOUT")) apm_preload_kernels(c->cfg.device);  // the carve-out preference is applied by the preload
     if (const char* e = getenv("APM_K1_TPC")) { int v = atoi(e); if (v > 0) c->k1_tiles_per_cta = (uint32_t)v; }
     // windowSz * intervalLengthSec / 60.0 (stream_calc_stats.js:186)
     c->tpm_div = (double)cfg->window_buckets * ((double)cfg->bucket_ms / 1000.0) / 60.0;
@@ -1472,7 +1479,7 @@ cudaError_t apm_preload_capi() {
     cudaError_t first = cudaSuccess;
     for (const void* f : fns) {
         cudaFuncAttributes a;
-        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        const cudaError_t e = apm_preload_one(&a, f);
         if (e != cudaSuccess && first == cudaSuccess) first = e;
     }
     return first;

@@ -384,7 +384,7 @@ cudaError_t apm_preload_comm() {
     cudaError_t first = cudaSuccess;
     for (const void* f : fns) {
         cudaFuncAttributes a;
-        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        const cudaError_t e = apm_preload_one(&a, f);
         if (e != cudaSuccess && first == cudaSuccess) first = e;
     }
     return first;

@@ -1,5 +1,6 @@
 // Shared device/host definitions of libapm_b200 (sm_100a only).
 #pragma once
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -16,6 +17,17 @@ int apm_sm_count();
 // limit belong to the device that is current when they are set, so a process that holds contexts on several
 // GPUs has to set them on each.
 bool apm_first_on_device(unsigned long long* done);
+
+// Loads one kernel on the current device (see apm_preload_kernels).  APM_SMEM_CARVEOUT=<percent> additionally gives
+// every kernel of the library the same preferred shared-memory carve-out, for A/B runs of small shapes where kernels
+// with very different shared-memory needs alternate on the same SMs.
+inline cudaError_t apm_preload_one(cudaFuncAttributes* a, const void* f) {
+    const cudaError_t e = cudaFuncGetAttributes(a, f);
+    if (e != cudaSuccess) return e;
+    static const int carveout = [] { const char* v = getenv("APM_SMEM_CARVEOUT"); return v ? atoi(v) : -1; }();
+    if (carveout >= 0) return cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+    return cudaSuccess;
+}
 
 // Makes `device` current for the duration of an entry point and restores the caller's device afterwards:
 // one host process may drive a context per GPU (the reference stage is one process, apm_manager.js:329-347).

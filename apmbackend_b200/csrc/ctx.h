@@ -135,6 +135,7 @@ struct apm_ctx {
     uint32_t* ring_next[APM_MAX_LAGS] = {nullptr, nullptr, nullptr, nullptr}; // [3][K] slot the column's next push belongs in
     size_t ring_pitch = 0;  // doubles per ring row: 3K rounded up to 32 (TMA box width, 256-byte rows)
     CUtensorMap ring_tmap[APM_MAX_LAGS];  // 2-D view [L][ring_pitch] of each ring for the bulk-tensor loads
+    CUtensorMap ring_tmap_few[APM_MAX_LAGS];  // the same view with a 96-slot box (baseline_few_kernel)
     bool ring_tmap_ok = false;
     uint64_t misalign_mark = 0;  // tick_seq at the last list load: the pending count is only meaningful after a later tick
     bool may_misalign = false;  // lists were loaded for keys that may be silent: run the realign kernel until none is left
@@ -179,6 +180,7 @@ struct apm_ctx {
     uint32_t k1_tiles_per_cta = 3;  // tuning knob (APM_K1_TPC)
     int k4_stages = 0;              // APM_K4_STAGES: bulk-tensor loads in flight per CTA (2, 3, 4, 6, or 8 = the three-box instance for few lists); 0 = by grid size
     bool k4_force_ldg = false;      // APM_K4_LDG=1: register-pipelined loads instead of TMA (A/B measurements)
+    bool k4_few = true;             // APM_K4_FEW=0: per-lag launches of baseline_tma_kernel also when all lags' column groups fit the SMs
 
     // log feeder (k6_logparse.cu), created by the first apm_dict_set / apm_parse_log_host
     void* lp = nullptr;
@@ -258,6 +260,8 @@ apm_status apm_launch_clear_slots(apm_ctx* c, uint64_t slot_mask);
 apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_ts, uint32_t tick_slot, int buf);
 // k4_baseline.cu
 apm_status apm_launch_baseline(apm_ctx* c, int lag_idx, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st);
+bool apm_baseline_few_ok(const apm_ctx* c);
+apm_status apm_launch_baseline_few(apm_ctx* c, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st);
 apm_status apm_baseline_make_tmaps(apm_ctx* c);
 apm_status apm_launch_realign(apm_ctx* c, int buf, cudaStream_t st);
 apm_status apm_launch_alert_counter(apm_ctx* c, uint32_t fs_slot, cudaStream_t st);

@@ -641,7 +641,7 @@ cudaError_t apm_preload_k1_chunk() {
     cudaError_t first = cudaSuccess;
     for (const void* f : fns) {
         cudaFuncAttributes a;
-        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        const cudaError_t e = apm_preload_one(&a, f);
         if (e != cudaSuccess && first == cudaSuccess) first = e;
     }
     return first;

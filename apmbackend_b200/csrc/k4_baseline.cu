@@ -10,6 +10,7 @@
 // serves all keys: a list of length n occupies the n slots before `head`, the push goes to
 // `head`, and a full list is summed head, head+1, ... (oldest first) - the same left-to-right
 // order as Array.prototype.reduce, so the fp64 mean has the same bits as the reference's.
+#include <cstring>
 #include <string>
 
 #include "ctx.h"
@@ -197,6 +198,59 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
         ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(r0), "r"(smem_u32(bar)), "l"(policy) : "memory");
 }
 
+// What follows the walk of a column: mean, "stddev", bounds, signal, influence blend, push, fs record
+// (processZScoreStats :75-104 and the shift() + push() of processData :285-306).
+__device__ __forceinline__ void finish_column(const BaselineParams& p, uint32_t col, uint32_t series, uint32_t key, bool seen, bool full,
+                                              uint32_t len, double sum, uint32_t cnt, double last) {
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    apm_fs_record* rec = p.fs ? p.fs + key : nullptr;
+    if (!seen) {
+        if (rec && series == 0) rec->flags = 0;
+        return;
+    }
+    const double new_value = p.zin[(size_t)(1 + series) * p.K + key];
+    const double threshold = p.thr[key], influence = p.infl[key];
+    double infl_value = new_value, avg = nan, lb = nan, ub = nan;
+    int signal = 0;
+    if (full) {
+        if (cnt > 0) {
+            avg = __ddiv_rn(sum, (double)cnt);
+            // standardDeviation() == sqrt(mean): mean == 0 -> undefined, mean < 0 -> NaN (util_methods.js:41-49)
+            double sd = nan;
+            if (avg != 0.0) sd = __dsqrt_rn(avg);
+            if (sd == sd) {
+                const double band = __dmul_rn(threshold, sd);  // (:80-83), product rounded before the add
+                lb = __dsub_rn(avg, band);
+                ub = __dadd_rn(avg, band);
+                if (new_value == new_value && fabs(__dsub_rn(new_value, avg)) > band) {  // (:87-89) strict
+                    signal = new_value > avg ? 1 : -1;
+                    if (last == last)  // (:96-97)
+                        infl_value = __dadd_rn(__dmul_rn(influence, new_value), __dmul_rn(__dsub_rn(1.0, influence), last));
+                }
+            }
+        }
+    } else {
+        p.ring_len[col] = len + 1;
+    }
+    p.ring[(size_t)p.head * p.pitch + col] = infl_value;  // shift() + push() (:285-306)
+    p.ring_next[col] = p.head + 1 == p.L ? 0u : p.head + 1;
+    if (rec) {
+        if (series == 0) {
+            rec->tick_ts = p.tick_ts;
+            rec->key = key;
+            rec->lag = p.lag_value;
+            rec->tpm = p.zin[key];
+            rec->flags = 1;
+            rec->pad_[0] = rec->pad_[1] = rec->pad_[2] = rec->pad_[3] = 0;
+        }
+        rec->val[series] = new_value;
+        rec->avg[series] = avg;
+        rec->lb[series] = lb;
+        rec->ub[series] = ub;
+        rec->signal[series] = (int8_t)signal;
+    }
+}
+
 // MULT: 16-slot boxes per stage.  The bandwidth-bound instance (many CTAs per SM) uses one; the instance for a
 // few hundred lists, where one warp per SM is paced by per-chunk overhead, uses three.
 template <int K4T_STAGES, int MULT>
@@ -306,52 +360,192 @@ __global__ void __launch_bounds__(32) baseline_tma_kernel(const __grid_constant_
         }
     }
     if (!in_range) return;
-    apm_fs_record* rec = p.fs ? p.fs + key : nullptr;
-    if (!seen) {
-        if (rec && series == 0) rec->flags = 0;
+    finish_column(p, col, series, key, seen, full, len, sum, cnt, last);
+}
+
+// ---- the walk for a few hundred lists (the reference's own deployment; small key shards) -------------------------
+// With fewer column groups than SMs every warp has an SM to itself and the walk is no longer a bandwidth problem: it
+// is one chain of dependent DADDs per lane, 8 cycles each (scripts/micro_dadd.cu), i.e. L x 8 cycles whatever else
+// happens.  A single warp that also waits on barriers, moves shared memory to registers and hands stages back spends
+// 20-odd cycles per slot (ncu: the 48 LDS of a chunk issue in front of its 48 DADDs, not under them, and everything
+// between two chunks is serial too).  So the jobs get a warp each:
+//   warp 0, one elected lane: waits for a stage to be empty, arms its `full` barrier, issues ONE bulk-tensor load of
+//           96 slots x 32 columns (24 KB);
+//   warps 1 and 2 take the chunks in turn.  While one runs its chunk's 96 dependent adds - nothing else in its
+//           instruction stream - the other has already pulled the next chunk into registers and polls a 16-byte
+//           mailbox in shared memory for the running {sum, count}; the hand-over costs one shared-memory round trip
+//           per 96 slots.
+// All lags go into ONE launch (CTA ranges per lag, the longest list first): the short walks run beside the long one on
+// other SMs instead of in front of it.
+struct alignas(64) FewParams {
+    CUtensorMap tmap[APM_MAX_LAGS];
+    BaselineParams p[APM_MAX_LAGS];
+    uint32_t cta_end[APM_MAX_LAGS];  // launch order: CTAs [cta_end[i - 1], cta_end[i]) walk lag lag_of[i]
+    int32_t lag_of[APM_MAX_LAGS];
+    int32_t n;
+};
+
+constexpr int K4F_ROWS = 96;   // slots per chunk = per bulk load (box 32 x 96 doubles)
+constexpr int K4F_STAGES = 6;  // two chunks sit in the adders' registers with their stages still held: four in flight
+constexpr uint32_t K4F_STAGE_BYTES = K4T_COLS * K4F_ROWS * sizeof(double);
+
+struct alignas(16) K4FMail {
+    double sum;
+    uint32_t cnt;
+    uint32_t seq;  // chunks folded into sum so far
+};
+
+struct __align__(128) K4FSmem {
+    double buf[K4F_STAGES][K4F_ROWS][K4T_COLS];
+    uint64_t full[K4F_STAGES];
+    uint64_t empty[K4F_STAGES];
+    K4FMail mail[2][32];  // [written by adder w][lane]
+};
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+#ifdef APM_K4_DEBUG
+__device__ unsigned long long apm_k4_dbg[2][16];
+#define K4DBG(i) do { if (dbg) { const long long t_ = clock64(); acc[i] += t_ - tprev; tprev = t_; } } while (0)
+#else
+#define K4DBG(i) do { } while (0)
+#endif
+
+__global__ void __launch_bounds__(96) baseline_few_kernel(const __grid_constant__ FewParams fp) {
+#ifdef APM_K4_DEBUG
+    const long long t_entry = clock64();
+    long long acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = t_entry;
+#endif
+    constexpr int ROWS = K4F_ROWS, STAGES = K4F_STAGES;
+    extern __shared__ __align__(128) unsigned char k4f_smem_raw[];
+    K4FSmem& sm = *reinterpret_cast<K4FSmem*>(k4f_smem_raw);
+    int slot = 0;
+    while (slot + 1 < fp.n && blockIdx.x >= fp.cta_end[slot]) ++slot;
+    const int l = fp.lag_of[slot];
+    const BaselineParams& p = fp.p[l];
+    const CUtensorMap* tmap = &fp.tmap[l];
+    const uint32_t cta = blockIdx.x - (slot ? fp.cta_end[slot - 1] : 0u);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t L = p.L, head = p.head;
+    const uint32_t col0 = cta * K4T_COLS, col = col0 + lane;
+    const bool in_range = col < 3u * p.K;
+    const uint32_t series = in_range ? col / p.K : 0, key = in_range ? col - series * p.K : 0;
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    const bool seen = in_range && p.seen[key];
+    const uint32_t len = seen ? p.ring_len[col] : 0;
+    const bool full = seen && len >= L;  // prevValuesList.length >= lag (:75)
+    const bool any_full = __any_sync(0xffffffffu, full);  // every warp looks at the same 32 columns: the same answer
+
+    if (threadIdx.x < 64) {
+        K4FMail m;
+        m.sum = 0.0; m.cnt = 0; m.seq = 0;
+        sm.mail[threadIdx.x >> 5][lane] = m;
+    }
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&sm.full[s], 1);
+            mbar_init(&sm.empty[s], 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    // oldest first: rows head .. L-1, then 0 .. head-1, in chunks of ROWS slots
+    const uint32_t nA = (L - head + ROWS - 1) / ROWS, nB = (head + ROWS - 1) / ROWS;
+    const uint32_t n = any_full ? nA + nB : 0u;
+
+    if (warp == 0) {  // ---- the loader
+        if (lane != 0) return;
+        const uint64_t policy = l2_evict_first_policy();
+        for (uint32_t c = 0; c < n; ++c) {
+            const uint32_t s = c % STAGES;
+            if (c >= (uint32_t)STAGES) mbar_wait(&sm.empty[s], ((c / STAGES) - 1u) & 1u);
+            mbar_expect_tx(&sm.full[s], K4F_STAGE_BYTES);  // rows past the end are zero-filled but still counted
+            const uint32_t r0 = c < nA ? head + c * ROWS : (c - nA) * ROWS;
+            tma_load_2d(&sm.buf[s][0][0], tmap, (int)col0, (int)r0, &sm.full[s], policy);
+        }
         return;
     }
-    const double new_value = p.zin[(size_t)(1 + series) * p.K + key];
-    const double threshold = p.thr[key], influence = p.infl[key];
-    double infl_value = new_value, avg = nan, lb = nan, ub = nan;
-    int signal = 0;
-    if (full) {
-        if (cnt > 0) {
-            avg = __ddiv_rn(sum, (double)cnt);
-            // standardDeviation() == sqrt(mean): mean == 0 -> undefined, mean < 0 -> NaN (util_methods.js:41-49)
-            double sd = nan;
-            if (avg != 0.0) sd = __dsqrt_rn(avg);
-            if (sd == sd) {
-                const double band = __dmul_rn(threshold, sd);  // (:80-83), product rounded before the add
-                lb = __dsub_rn(avg, band);
-                ub = __dadd_rn(avg, band);
-                if (new_value == new_value && fabs(__dsub_rn(new_value, avg)) > band) {  // (:87-89) strict
-                    signal = new_value > avg ? 1 : -1;
-                    if (last == last)  // (:96-97)
-                        infl_value = __dadd_rn(__dmul_rn(influence, new_value), __dmul_rn(__dsub_rn(1.0, influence), last));
+
+    // ---- the adders: w takes chunks w, w + 2, ...
+    const uint32_t w = (uint32_t)warp - 1u;
+#ifdef APM_K4_DEBUG
+    const bool dbg = blockIdx.x == 0 && lane == 0;
+    K4DBG(0);  // prologue
+#endif
+    double sum = 0.0, last = nan;
+    uint32_t cnt = 0;
+    for (uint32_t c = w; c < n; c += 2) {
+        const uint32_t s = c % STAGES;
+        mbar_wait(&sm.full[s], (c / STAGES) & 1u);
+        K4DBG(1);  // waiting for the stage
+        double v[ROWS];
+#pragma unroll
+        for (int r = 0; r < ROWS; ++r) v[r] = sm.buf[s][r][lane];
+#ifdef APM_K4_DEBUG
+        if (dbg && __double_as_longlong(v[ROWS - 1]) == 0x123456789abcdefll) acc[7]++;  // the loads return in order: wait for the last
+#endif
+        K4DBG(2);  // shared memory -> registers
+        const uint32_t r0 = c < nA ? head + c * ROWS : (c - nA) * ROWS, end = c < nA ? L : head;
+        const uint32_t rows = end - r0 < (uint32_t)ROWS ? end - r0 : (uint32_t)ROWS;
+        if (c > 0) {  // the running sum after chunk c - 1, from the other adder
+            const uint32_t addr = smem_u32(&sm.mail[w ^ 1u][lane]);
+            unsigned long long a, b;
+            do {
+                asm volatile("ld.volatile.shared.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr) : "memory");
+            } while (!__all_sync(0xffffffffu, (uint32_t)(b >> 32) == c));
+            sum = __longlong_as_double((long long)a);
+            cnt = (uint32_t)b;
+        }
+        K4DBG(3);  // waiting for the other adder
+        if (rows == (uint32_t)ROWS) {
+            if (full) {  // bare adds, validity checked once on the result (see baseline_tma_kernel)
+                double t = sum;
+#pragma unroll
+                for (int r = 0; r < ROWS; ++r) t = __dadd_rn(t, v[r]);
+                if (t == t) {
+                    sum = t;
+                    cnt += ROWS;
+                } else {
+#pragma unroll
+                    for (int r = 0; r < ROWS; ++r) accumulate(v[r], sum, cnt);
                 }
             }
+            last = v[ROWS - 1];
+        } else {
+#pragma unroll
+            for (int r = 0; r < ROWS; ++r)
+                if ((uint32_t)r < rows) {
+                    if (full) accumulate(v[r], sum, cnt);
+                    last = v[r];
+                }
         }
-    } else {
-        p.ring_len[col] = len + 1;
-    }
-    p.ring[(size_t)p.head * p.pitch + col] = infl_value;  // shift() + push() (:285-306)
-    p.ring_next[col] = p.head + 1 == p.L ? 0u : p.head + 1;
-    if (rec) {
-        if (series == 0) {
-            rec->tick_ts = p.tick_ts;
-            rec->key = key;
-            rec->lag = p.lag_value;
-            rec->tpm = p.zin[key];
-            rec->flags = 1;
-            rec->pad_[0] = rec->pad_[1] = rec->pad_[2] = rec->pad_[3] = 0;
+        K4DBG(4);  // the chain
+        if (c + 1 < n) {
+            const uint32_t addr = smem_u32(&sm.mail[w][lane]);
+            const unsigned long long a = (unsigned long long)__double_as_longlong(sum), b = ((unsigned long long)(c + 1u) << 32) | cnt;
+            asm volatile("st.volatile.shared.v2.b64 [%0], {%1, %2};" ::"r"(addr), "l"(a), "l"(b) : "memory");
         }
-        rec->val[series] = new_value;
-        rec->avg[series] = avg;
-        rec->lb[series] = lb;
-        rec->ub[series] = ub;
-        rec->signal[series] = (int8_t)signal;
+        // the chunk's values have all been used: its stage may be overwritten
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[s]);
+        K4DBG(5);  // post + release
     }
+#ifdef APM_K4_DEBUG
+    if (dbg) {
+        for (int i = 0; i < 8; ++i) apm_k4_dbg[w][i] = (unsigned long long)acc[i];
+        apm_k4_dbg[w][8] = (unsigned long long)(clock64() - t_entry);
+        apm_k4_dbg[w][9] = n;
+    }
+#endif
+    // the adder that folded the last chunk holds the result (adder 0 when nothing was walked)
+    if (((n ? n - 1u : 0u) & 1u) != w) return;
+    if (!in_range) return;
+    finish_column(p, col, series, key, seen, full, len, sum, cnt, last);
 }
 
 // ---- guarded incremental baseline (APM_F_INCREMENTAL) ------------------------------------------
@@ -754,7 +948,54 @@ apm_status apm_baseline_make_tmaps(apm_ctx* c) {
     }
     CUDA_TRY(c, cudaFuncSetAttribute(baseline_tma_kernel<K4T_DEEP_STAGES, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sizeof(K4TSmem<K4T_DEEP_STAGES, 3>) + 128));
+    for (int l = 0; l < c->cfg.num_lags; ++l) {  // the few-list walk loads 96 slots per request
+        const cuuint64_t gdim[2] = {(cuuint64_t)c->ring_pitch, (cuuint64_t)c->cfg.lags[l]};
+        const cuuint64_t gstride[1] = {(cuuint64_t)(c->ring_pitch * sizeof(double))};
+        const cuuint32_t box[2] = {K4T_COLS, K4F_ROWS};
+        const cuuint32_t estr[2] = {1, 1};
+        CUresult r = ((EncodeTiled)fn)(&c->ring_tmap_few[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, c->ring[l], gdim, gstride, box, estr,
+                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return apm_fail(c, APM_E_DEVICE, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    }
+    CUDA_TRY(c, cudaFuncSetAttribute(baseline_few_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K4FSmem) + 128));
     c->ring_tmap_ok = true;
+    return APM_OK;
+}
+
+// Few lists: every lag's column groups together fit the SMs one CTA each (cfg1: 2 x 38 of 148).
+bool apm_baseline_few_ok(const apm_ctx* c) {
+    if (!c->k4_few || !c->ring_tmap_ok || c->cfg.sd_mode != APM_SD_REFERENCE || c->k4_force_ldg || c->k4_stages != 0) return false;
+    if (c->cfg.flags & APM_F_INCREMENTAL) return false;
+    const unsigned g = (3u * c->K + K4T_COLS - 1) / K4T_COLS;
+    return c->cfg.num_lags > 0 && g * (unsigned)c->cfg.num_lags <= (unsigned)c->num_sms;
+}
+
+// All lags of one tick in one launch (see baseline_few_kernel).
+apm_status apm_launch_baseline_few(apm_ctx* c, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st) {
+    ProfScope prof_scope_(c, APM_PG_BASELINE, st);
+    FewParams fp;
+    memset(&fp, 0, sizeof(fp));
+    const unsigned g = (3u * c->K + K4T_COLS - 1) / K4T_COLS;
+    fp.n = c->cfg.num_lags;
+    for (int l = 0; l < c->cfg.num_lags; ++l) {
+        BaselineParams& p = fp.p[l];
+        fp.tmap[l] = c->ring_tmap_few[l];
+        p.ring = c->ring[l]; p.ring_len = c->ring_len[l]; p.ring_next = c->ring_next[l]; p.zin = c->zin[buf]; p.thr = c->thr[l]; p.infl = c->infl[l];
+        p.seen = c->emit[buf];
+        p.fs = c->d_fs ? c->d_fs + ((size_t)tick_slot * c->cfg.num_lags + l) * c->K : nullptr;
+        p.K = c->K; p.L = (uint32_t)c->cfg.lags[l]; p.head = c->ring_head[l]; p.lag_value = (uint32_t)c->cfg.lags[l];
+        p.pitch = (uint32_t)c->ring_pitch;
+        p.tick_ts = tick_ts;
+        p.sd_mode = c->cfg.sd_mode;
+        // lags are ascending (apm_config): launch order is descending, so the longest walk's CTAs are placed first
+        fp.lag_of[c->cfg.num_lags - 1 - l] = l;
+        fp.cta_end[l] = g * (unsigned)(l + 1);
+    }
+    baseline_few_kernel<<<g * (unsigned)c->cfg.num_lags, 96, sizeof(K4FSmem) + 128, st>>>(fp);
+    c->launches += 1;
+    CUDA_TRY(c, cudaGetLastError());
+    for (int l = 0; l < c->cfg.num_lags; ++l) c->ring_head[l] = (c->ring_head[l] + 1) % (uint32_t)c->cfg.lags[l];
     return APM_OK;
 }
 
@@ -857,12 +1098,18 @@ apm_status apm_launch_compact_alerts(apm_ctx* c, uint32_t fs_slot, uint32_t aler
 
 // Loads this file's kernels on the current device (see apm_preload_kernels in capi.cu).
 cudaError_t apm_preload_k4_baseline() {
-    const void* fns[] = {(const void*)alert_counter_kernel, (const void*)baseline_inc_kernel, (const void*)baseline_kernel, (const void*)baseline_tma_kernel<2, 1>, (const void*)baseline_tma_kernel<3, 1>, (const void*)baseline_tma_kernel<4, 1>, (const void*)baseline_tma_kernel<6, 1>, (const void*)baseline_tma_kernel<K4T_DEEP_STAGES, 3>, (const void*)compact_alerts_kernel, (const void*)compact_alerts_small_kernel, (const void*)count_alerts_kernel, (const void*)inc_init_kernel, (const void*)realign_kernel};
+    const void* fns[] = {(const void*)alert_counter_kernel, (const void*)baseline_inc_kernel, (const void*)baseline_kernel, (const void*)baseline_tma_kernel<2, 1>, (const void*)baseline_tma_kernel<3, 1>, (const void*)baseline_tma_kernel<4, 1>, (const void*)baseline_tma_kernel<6, 1>, (const void*)baseline_tma_kernel<K4T_DEEP_STAGES, 3>, (const void*)baseline_few_kernel, (const void*)compact_alerts_kernel, (const void*)compact_alerts_small_kernel, (const void*)count_alerts_kernel, (const void*)inc_init_kernel, (const void*)realign_kernel};
     cudaError_t first = cudaSuccess;
     for (const void* f : fns) {
         cudaFuncAttributes a;
-        const cudaError_t e = cudaFuncGetAttributes(&a, f);
+        const cudaError_t e = apm_preload_one(&a, f);
         if (e != cudaSuccess && first == cudaSuccess) first = e;
     }
     return first;
 }
+
+#ifdef APM_K4_DEBUG
+extern "C" int apm_debug_k4(unsigned long long* out32) {
+    return (int)cudaMemcpyFromSymbol(out32, apm_k4_dbg, sizeof(apm_k4_dbg));
+}
+#endif

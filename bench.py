@@ -41,9 +41,10 @@ WORKLOADS = {
     # BASELINE.json configs[0]: the reference's own settings (10 s buckets, window 30, buffer 6, p75/p95, lags 360 + 8640)
     "cfg1": dict(n=1_000_000, services=200, jvms=2, bucket_ms=10_000, window=30, buffer=6, span_buckets=2160,
                  percentiles=(75.0, 95.0), z_series_pct=(0, 1), lags=(360, 8640), thresholds=(20.0, 15.0),
-                 influences=(0.1, 0.0), zscore=True, pct=True, seed=0xA9B200, prefill=False,
+                 influences=(0.1, 0.0), zscore=True, pct=True, seed=0xA9B200, cpu_sample_buckets=180,
                  desc="1M transactions, 200 services x 2 JVMs, reference settings (10-s buckets, 31-bucket sliding window, "
-                      "p75/p95, lags 360 and 8640), 2160 ticks per step"),
+                      "p75/p95, lags 360 and 8640, both pre-filled: the steady state of a deployment older than a day), "
+                      "2160 ticks per step"),
     # one rank's share of BASELINE.json configs[3] at 8 GPUs: 1 B transactions / 8, 1 M keys / 8
     "cfg4_shard": dict(n=125_000_000, services=125_000, jvms=1, bucket_ms=60_000, window=1, buffer=0, span_buckets=60,
                        percentiles=(50.0, 95.0, 99.0), z_series_pct=(1, 2), lags=(10080,), thresholds=(15.0,),
@@ -256,12 +257,12 @@ def cpu_reference_run(wl, cols, ring_seed, threads, stream, prefill=True):
         p.set_filter(keep)
         p.keep_outputs(False)
         if prefill and wl["zscore"] and wl.get("prefill", True):
-            L = wl["lags"][0]
             mine = np.arange(t, K, threads)
-            for s in range(3):
-                vals = syn.ring_fill_host(L, stream, ring_seed, s * K + mine)
-                for j, key in enumerate(mine):
-                    p.ring_load(int(key), 0, s, vals[:, j])
+            for li, L in enumerate(wl["lags"]):
+                for s in range(3):
+                    vals = syn.ring_fill_host(L, stream, ring_seed + li, s * K + mine)
+                    for j, key in enumerate(mine):
+                        p.ring_load(int(key), li, s, vals[:, j])
         pipes.append(p)
     t0 = time.perf_counter()
     th = [threading.Thread(target=p.consume, args=(svc, jvm, ts, el)) for p in pipes]
@@ -280,7 +281,8 @@ def sample_for_cpu(wl, stream, ticks=2):
     """A bounded sample of the same workload: the first `ticks` buckets' worth of the stream
     (all 10 k keys, same rates), plus one transaction of the next bucket to close the last tick."""
     per_bucket = wl["n"] // wl["span_buckets"]
-    if wl["n"] <= 2_000_000:
+    ticks = wl.get("cpu_sample_buckets", ticks)
+    if wl["n"] <= 2_000_000 and "cpu_sample_buckets" not in wl:
         return stream.generate_host(first=0, count=wl["n"]), wl["n"]  # small enough to run whole
     n = int(per_bucket * ticks + per_bucket // 50)
     return stream.generate_host(first=0, count=n), n
@@ -381,14 +383,15 @@ class Shard:
         return n, marks
 
     def prefill(self, eng, ring_seed):
-        L = self.wl["lags"][0]
-        buf = self.syn.DeviceBuffer(L * 3 * self.K * 8)
-        if self.world == 1:
-            self.syn.ring_fill_device(buf, L, self.stream, ring_seed)
-        else:
-            self.syn.ring_fill_device(buf, L, self.stream, ring_seed, base_dev=self.base_local_dev.ptr, num_keys=self.K)
-        eng.ring_load_all(0, length=L, device_ptr=buf.ptr)
-        buf.free()
+        # every lag's lists start full, as in a deployment that has run for longer than its longest lag
+        for li, L in enumerate(self.wl["lags"]):
+            buf = self.syn.DeviceBuffer(L * 3 * self.K * 8)
+            if self.world == 1:
+                self.syn.ring_fill_device(buf, L, self.stream, ring_seed + li)
+            else:
+                self.syn.ring_fill_device(buf, L, self.stream, ring_seed + li, base_dev=self.base_local_dev.ptr, num_keys=self.K)
+            eng.ring_load_all(li, length=L, device_ptr=buf.ptr)
+            buf.free()
 
 
 def make_engine(wl, shard, flags, local_rank, Engine, EngineConfig):
@@ -884,7 +887,7 @@ def main():
         threads = 1
         dt, tks = cpu_reference_run(wl, cols, ring_seed, threads, hs)
         line["cpu_baseline"] = {"value": n_s / dt, "unit": "transactions/s", "cores": threads, "kind": "port",
-                                "sample": f"first {n_s} transactions of the same stream (6 of its buckets + the tick "
+                                "sample": f"first {n_s} transactions of the same stream ({wl.get('cpu_sample_buckets', 6)} of its buckets + the tick "
                                           f"that closes the last, all {K} keys, rings pre-filled): {tks} ticks in {dt:.1f} s, "
                                           "reference-structure C++ port, 1 thread (each reference stage is one "
                                           "single-threaded Node process; Node itself is absent on this box)"}
@@ -912,7 +915,7 @@ def run_reference(args, wl, rank, world, config, span_ms):
             times.append(dt); ticks += tk
     total = float(np.sum(times))
     v = n_s * args.steps / total
-    sample = (f"each step = the first {n_s} transactions of the workload's stream (6 of its {wl['span_buckets']} buckets + "
+    sample = (f"each step = the first {n_s} transactions of the workload's stream ({wl.get('cpu_sample_buckets', 6)} of its {wl['span_buckets']} buckets + "
               f"the tick that closes the last, all keys, rings pre-filled), reference-structure C++ port of "
               f"stream_calc_stats.js + stream_calc_z_score.js, keys partitioned over {threads} host threads")
     line = {"impl": "reference", "metric": "transactions/sec aggregated+z-scored", "value": v, "unit": "transactions/s",
