@@ -1435,6 +1435,20 @@ extern "C" apm_status apm_profile_read(apm_ctx* c, apm_kernel_times* out) {
     { apm_status fl_ = apm_flush_pending(c); if (fl_) return fl_; }
     CUDA_TRY(c, cudaStreamSynchronize(c->s_base));
     CUDA_TRY(c, cudaStreamSynchronize(c->s_main));
+    // APM_TIMELINE_FILE=<path>: every span as "group start_us end_us" relative to the first span of this read (where the
+    // streams overlap, where they wait for each other)
+    if (const char* path = getenv("APM_TIMELINE_FILE")) {
+        if (FILE* f = c->prof_spans.empty() ? nullptr : fopen(path, "a")) {
+            const cudaEvent_t base = c->prof_spans.front().a;
+            for (auto& sp : c->prof_spans) {
+                float a_ms = 0, b_ms = 0;
+                if (cudaEventElapsedTime(&a_ms, base, sp.a) == cudaSuccess && cudaEventElapsedTime(&b_ms, base, sp.b) == cudaSuccess)
+                    fprintf(f, "%d %.2f %.2f\n", sp.group, a_ms * 1e3, b_ms * 1e3);
+            }
+            fprintf(f, "-1 0 0\n");
+            fclose(f);
+        }
+    }
     for (auto& sp : c->prof_spans) {
         float ms = 0;
         if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess && sp.group < APM_KT_GROUPS) {

@@ -30,23 +30,25 @@ __global__ void __launch_bounds__(TF_THREADS) tf_tile_max_kernel(const int64_t* 
                                                                  long long* __restrict__ tile_max) {
     __shared__ long long s_max[TF_THREADS / 32];
     const uint64_t base = (uint64_t)blockIdx.x * TF_TILE;
+    // the label is monotonic in the timestamp, so the largest label of a tile is the label of its largest timestamp:
+    // the tile is reduced on the raw 64-bit values (negative = invalid = -1) and labelled once, which leaves this
+    // kernel with one compare per transaction instead of the label arithmetic (it ran at a quarter of HBM speed)
     long long m = -1;
+    int64_t t[TF_ITEMS];
 #pragma unroll
     for (int i = 0; i < TF_ITEMS; ++i) {
-        uint64_t idx = base + (uint64_t)i * TF_THREADS + threadIdx.x;
-        if (idx < n) {
-            int64_t t = __ldg(ts + idx);
-            long long lab = t >= 0 ? apm_label(t, bucket_ms, inv_bucket) : -1;
-            m = lab > m ? lab : m;
-        }
+        const uint64_t idx = base + (uint64_t)i * TF_THREADS + threadIdx.x;
+        t[i] = idx < n ? __ldg(ts + idx) : -1;
     }
+#pragma unroll
+    for (int i = 0; i < TF_ITEMS; ++i) m = t[i] > m ? t[i] : m;
     m = warp_max_ll(m);
     if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = m;
     __syncthreads();
     if (threadIdx.x < 32) {
         long long v = threadIdx.x < TF_THREADS / 32 ? s_max[threadIdx.x] : -1;
         v = warp_max_ll(v);
-        if (threadIdx.x == 0) tile_max[blockIdx.x] = v;
+        if (threadIdx.x == 0) tile_max[blockIdx.x] = v >= 0 ? apm_label(v, bucket_ms, inv_bucket) : -1;
     }
 }
 
