@@ -166,8 +166,13 @@ apm_status launch_baseline_group(apm_ctx* c, const PendingBaseline& pb, cudaStre
         st = apm_launch_realign(c, pb.buf, sb);  // lists of keys that were silent re-enter the lock step
         if (st) return st;
     }
+    bool compacted = false;
     if (apm_baseline_few_ok(c)) {  // a few hundred lists: every lag in one launch, loader and adder warps
-        st = apm_launch_baseline_few(c, pb.tick_ts, pb.fslot, pb.buf, sb);
+        // ... and, when the signalled records themselves are the alerts (no stage-[4] rules), the last CTA to finish
+        // compacts them: one launch less on the baseline stream, which is the tick's critical path at this shape
+        compacted = (c->cfg.flags & APM_F_ALERTS) && !c->alert_rules.enabled && c->d_alerts && c->d_fs && c->k4_done && c->small_tick &&
+                    (uint64_t)c->K * c->cfg.num_lags <= 4096;
+        st = apm_launch_baseline_few(c, pb.tick_ts, pb.fslot, pb.buf, compacted ? (int)pb.tslot : -1, sb);
         if (st) return st;
     } else {
         for (int l = 0; l < c->cfg.num_lags; ++l) {  // Object.entries(lags): ascending (:217)
@@ -178,8 +183,10 @@ apm_status launch_baseline_group(apm_ctx* c, const PendingBaseline& pb, cudaStre
     st = apm_launch_alert_counter(c, pb.fslot, sb);  // processFSEntry's counter, when rules are set
     if (st) return st;
     if (c->cfg.flags & APM_F_ALERTS) {
-        st = apm_launch_compact_alerts(c, pb.fslot, pb.tslot, sb);
-        if (st) return st;
+        if (!compacted) {
+            st = apm_launch_compact_alerts(c, pb.fslot, pb.tslot, sb);
+            if (st) return st;
+        }
         if (c->h_gather_bound) {  // all-gathered while the next ticks run
             st = apm_comm_tick_gather(c, pb.tslot, sb);
             if (st) return st;
@@ -718,7 +725,9 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
             if (cfg->max_alerts_per_tick == 0) { c->err = "max_alerts_per_tick must be > 0 with APM_F_ALERTS"; return fail(APM_E_INVALID); }
             TRY_CREATE(dalloc(&c->d_alerts, (size_t)cfg->out_ticks * cfg->max_alerts_per_tick));
             TRY_CREATE(dalloc(&c->d_alert_count, (size_t)cfg->out_ticks));
-            TRY_CREATE(dalloc(&c->d_alert_blocks, (size_t)K * cfg->num_lags / 256 + 2));
+            TRY_CREATE(dalloc(&c->d_alert_blocks, (size_t)K * cfg->num_lags / 256 + 3));
+            TRY_CREATE(cudaMemsetAsync(c->d_alert_blocks, 0, sizeof(uint32_t) * ((size_t)K * cfg->num_lags / 256 + 3), c->s_main));
+            c->k4_done = c->d_alert_blocks + ((size_t)K * cfg->num_lags / 256 + 2);  // CTAs-finished counter of the few-list walk
             TRY_CREATE(cudaMemsetAsync(c->d_alert_count, 0, sizeof(unsigned int) * cfg->out_ticks, c->s_main));
         }
         c->ring_pitch = (3 * K + 31) & ~(size_t)31;

@@ -119,6 +119,7 @@ struct apm_ctx {
     apm_fs_record* d_alerts = nullptr;   // [out_ticks][max_alerts_per_tick]
     unsigned int* d_alert_count = nullptr;  // [out_ticks]
     uint32_t* d_alert_blocks = nullptr;     // [ceil(K * num_lags / 256)] hits per CTA of the ordered compaction
+    uint32_t* k4_done = nullptr;            // inside d_alert_blocks: CTAs of baseline_few_kernel that have written their records
     double* zin[2] = {nullptr, nullptr};     // double-buffered [4][K]: tpm', val0, val1, val2 (quantised)
     uint8_t* emit[2] = {nullptr, nullptr};   // [K] key emitted a StatEntry this tick (snapshot of `seen`)
     // optional: fs records stream to a caller-owned pinned buffer as each tick's baseline finishes
@@ -261,7 +262,7 @@ apm_status apm_launch_tick_stats(apm_ctx* c, const WindowSlots& w, int64_t tick_
 // k4_baseline.cu
 apm_status apm_launch_baseline(apm_ctx* c, int lag_idx, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st);
 bool apm_baseline_few_ok(const apm_ctx* c);
-apm_status apm_launch_baseline_few(apm_ctx* c, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st);
+apm_status apm_launch_baseline_few(apm_ctx* c, int64_t tick_ts, uint32_t tick_slot, int buf, int alert_slot, cudaStream_t st);
 apm_status apm_baseline_make_tmaps(apm_ctx* c);
 apm_status apm_launch_realign(apm_ctx* c, int buf, cudaStream_t st);
 apm_status apm_launch_alert_counter(apm_ctx* c, uint32_t fs_slot, cudaStream_t st);

@@ -384,6 +384,13 @@ struct alignas(64) FewParams {
     uint32_t cta_end[APM_MAX_LAGS];  // launch order: CTAs [cta_end[i - 1], cta_end[i]) walk lag lag_of[i]
     int32_t lag_of[APM_MAX_LAGS];
     int32_t n;
+    // alert compaction by the last CTA to finish (compact_n = 0: a separate launch does it)
+    uint32_t compact_n;              // records of this tick, [lag][key]
+    uint32_t alert_cap;
+    const apm_fs_record* fs_tick;
+    apm_fs_record* alerts;
+    unsigned int* alert_count;
+    uint32_t* done;                  // CTAs that have written their records; left at 0
 };
 
 constexpr int K4F_ROWS = 96;   // slots per chunk = per bulk load (box 32 x 96 doubles)
@@ -402,6 +409,55 @@ struct __align__(128) K4FSmem {
     uint64_t empty[K4F_STAGES];
     K4FMail mail[2][32];  // [written by adder w][lane]
 };
+
+// The signalled records of one tick, in record order, into the tick's alert block: compact_alerts_small_kernel's
+// result by ONE warp (each lane owns a contiguous stretch of records, so the order survives a lane-level prefix sum).
+// fs was written by other CTAs: read through L2.
+__device__ void compact_by_warp(const apm_fs_record* fs, uint32_t n, apm_fs_record* alerts, unsigned int* count, uint32_t cap, int lane) {
+    // n <= 4096: a lane owns at most 128 records, whose hits it keeps as a bit mask between the two passes
+    const uint32_t per = (n + 31u) / 32u, lo = (uint32_t)lane * per, hi = lo + per < n ? lo + per : n;
+    uint32_t mask[4] = {0u, 0u, 0u, 0u};
+    for (uint32_t b0 = 0; b0 < per; b0 += 16) {
+        uint32_t w[16];
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {  // bytes 120..122: the three signals, byte 123: flags (bit 0 = record present)
+            const uint32_t i = lo + b0 + u;
+            w[u] = i < hi ? __ldcg(reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(fs + i) + 120)) : 0u;
+        }
+        uint32_t bits = 0;
+#pragma unroll
+        for (int u = 0; u < 16; ++u) bits |= ((w[u] & 0x01000000u) && (w[u] & 0x00ffffffu)) ? 1u << u : 0u;
+        mask[b0 >> 5] |= bits << (b0 & 31u);
+    }
+    const uint32_t mine = __popc(mask[0]) + __popc(mask[1]) + __popc(mask[2]) + __popc(mask[3]);
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t other = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += other;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    uint32_t k = incl - mine;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        uint32_t bits = mask[q];
+        while (bits) {
+            const uint32_t i = lo + 32u * q + (uint32_t)__ffs((int)bits) - 1u;
+            bits &= bits - 1u;
+            if (k < cap) {
+                const uint4* src = reinterpret_cast<const uint4*>(fs + i);
+                uint4* dst = reinterpret_cast<uint4*>(alerts + k);
+                uint4 r[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) r[j] = __ldcg(src + j);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) dst[j] = r[j];
+            }
+            ++k;
+        }
+    }
+    if (lane == 0) *count = total;
+}
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -543,8 +599,20 @@ __global__ void __launch_bounds__(96) baseline_few_kernel(const __grid_constant_
 #endif
     // the adder that folded the last chunk holds the result (adder 0 when nothing was walked)
     if (((n ? n - 1u : 0u) & 1u) != w) return;
-    if (!in_range) return;
-    finish_column(p, col, series, key, seen, full, len, sum, cnt, last);
+    if (in_range) finish_column(p, col, series, key, seen, full, len, sum, cnt, last);
+    if (fp.compact_n) {
+        // one finishing warp per CTA: the one that draws the last ticket sees every CTA's records
+        __syncwarp();
+        __threadfence();
+        uint32_t ticket = 0;
+        if (lane == 0) ticket = atomicAdd(fp.done, 1u);
+        ticket = __shfl_sync(0xffffffffu, ticket, 0);
+        if (ticket == gridDim.x - 1u) {
+            if (lane == 0) *fp.done = 0;  // for the next launch (stream-ordered behind this one)
+            __threadfence();
+            compact_by_warp(fp.fs_tick, fp.compact_n, fp.alerts, fp.alert_count, fp.alert_cap, lane);
+        }
+    }
 }
 
 // ---- guarded incremental baseline (APM_F_INCREMENTAL) ------------------------------------------
@@ -971,7 +1039,7 @@ bool apm_baseline_few_ok(const apm_ctx* c) {
 }
 
 // All lags of one tick in one launch (see baseline_few_kernel).
-apm_status apm_launch_baseline_few(apm_ctx* c, int64_t tick_ts, uint32_t tick_slot, int buf, cudaStream_t st) {
+apm_status apm_launch_baseline_few(apm_ctx* c, int64_t tick_ts, uint32_t tick_slot, int buf, int alert_slot, cudaStream_t st) {
     ProfScope prof_scope_(c, APM_PG_BASELINE, st);
     FewParams fp;
     memset(&fp, 0, sizeof(fp));
@@ -990,6 +1058,14 @@ apm_status apm_launch_baseline_few(apm_ctx* c, int64_t tick_ts, uint32_t tick_sl
         // lags are ascending (apm_config): launch order is descending, so the longest walk's CTAs are placed first
         fp.lag_of[c->cfg.num_lags - 1 - l] = l;
         fp.cta_end[l] = g * (unsigned)(l + 1);
+    }
+    if (alert_slot >= 0) {
+        fp.compact_n = c->K * (uint32_t)c->cfg.num_lags;
+        fp.alert_cap = c->cfg.max_alerts_per_tick;
+        fp.fs_tick = c->d_fs + (size_t)tick_slot * c->cfg.num_lags * c->K;
+        fp.alerts = c->d_alerts + (size_t)alert_slot * c->cfg.max_alerts_per_tick;
+        fp.alert_count = c->d_alert_count + alert_slot;
+        fp.done = c->k4_done;
     }
     baseline_few_kernel<<<g * (unsigned)c->cfg.num_lags, 96, sizeof(K4FSmem) + 128, st>>>(fp);
     c->launches += 1;

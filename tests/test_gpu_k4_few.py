@@ -31,16 +31,17 @@ def _engine(c, few):
 
 def _run(eng, cols, calls):
     n = cols[0].size
-    st, fs = [], []
+    st, fs, al = [], [], []
     bounds = np.linspace(0, n, calls + 1).astype(int)
     for a, b in zip(bounds[:-1], bounds[1:]):
         eng.process_host(*(x[a:b] for x in cols))
         st.append(eng.fetch_stats().copy())
         fs.append(eng.fetch_fs().copy())
+        al.append(eng.fetch_alerts().copy())
         eng.release_ticks()
     cnt = eng.counters()
     eng.close()
-    return np.concatenate(st), np.concatenate(fs), cnt.kernel_launches, cnt.ticks
+    return np.concatenate(st), np.concatenate(fs), np.concatenate(al), cnt.kernel_launches, cnt.ticks
 
 
 @pytest.mark.parametrize("S,J,lags,span,calls", [
@@ -61,11 +62,16 @@ def test_few_list_walk_equals_the_oracle_and_the_per_lag_kernels(S, J, lags, spa
     svc = svc.copy()
     svc[quiet] = 5
     cols = (svc, jvm, ts, el)
-    st, fs, launches, ticks = _run(_engine(c, True), cols, calls)
-    st0, fs0, launches0, ticks0 = _run(_engine(c, False), cols, calls)
+    st, fs, al, launches, ticks = _run(_engine(c, True), cols, calls)
+    st0, fs0, al0, launches0, ticks0 = _run(_engine(c, False), cols, calls)
     assert st.tobytes() == st0.tobytes() and fs.tobytes() == fs0.tobytes()
+    # the alert blocks, which the walk's last CTA compacts itself: the signalled records in record order
+    assert al.size > 0 and al.tobytes() == al0.tobytes()
+    sig = fs[(fs["signal"] != 0).any(axis=1)]
+    assert al.size == sig.size and np.array_equal(np.sort(al, order=["tick_ts", "lag", "key"]), np.sort(sig, order=["tick_ts", "lag", "key"]))
     assert ticks == ticks0 > 0
-    assert launches0 - launches == ticks * (len(lags) - 1), (launches0, launches, ticks)  # one walk launch per tick instead of one per lag
+    # one launch per tick instead of one per lag + one for the alert compaction
+    assert launches0 - launches == ticks * len(lags), (launches0, launches, ticks)
     orc = ocapi.Pipeline(oracle_config(c), fast=True)
     orc.consume(*cols)
     assert_stats_equal(st, orc.stats())
