@@ -644,6 +644,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     if (const char* e = getenv("APM_STATS_CHUNK")) c->stats_chunk = atoi(e) != 0;
     if (const char* e = getenv("APM_STATS_CHUNK_MIN_N")) c->stats_chunk_min_n = strtoull(e, nullptr, 10);
     if (const char* e = getenv("APM_STATS_CHUNK_MIN_SEG")) c->stats_chunk_min_seg = strtoull(e, nullptr, 10);
+    if (const char* e = getenv("APM_STATS_CHUNK_DIRECT")) c->stats_chunk_direct = atoi(e) != 0;
     for (int i = 0; i < 2; ++i) {
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
         TRY_CREATE(cudaEventCreateWithFlags(&c->ev_consumed[i], cudaEventDisableTiming));

@@ -169,6 +169,7 @@ struct apm_ctx {
     bool stats_chunk = true;               // APM_STATS_CHUNK=0: one reduce / clear / window launch per tick even in stats-only mode
     uint64_t stats_chunk_min_n = 262144;   // below this many transactions, or this many per segment, the per-tick path is as good
     uint64_t stats_chunk_min_seg = 8192;   // (APM_STATS_CHUNK_MIN_N / APM_STATS_CHUNK_MIN_SEG: tests lower them)
+    bool stats_chunk_direct = true;  // APM_STATS_CHUNK_DIRECT=0: the hashed table also when every key fits shared memory
     void* chunk_planes = nullptr;
     size_t chunk_cells = 0;
     uint32_t* chunk_first_seg = nullptr;

@@ -42,13 +42,31 @@ struct SegPlanes {  // each [segments][keep + 1][K]
 // Each field array is one word longer than the table: field f of entry h then sits in bank (h + f) mod 32.  With arrays
 // of exactly KC_TABLE words (a multiple of 32) all seven words of an entry share ONE bank, and a Zipf-hot key's five
 // atomics per transaction queue behind each other there.
-struct KcSmem {
-    uint32_t tag[KC_TABLE + 1], cnt[KC_TABLE + 1], sum_lo[KC_TABLE + 1], sq_lo[KC_TABLE + 1], carry[KC_TABLE + 1] /* sq: bits 8.., sum: bits 0..7 */,
-        mn[KC_TABLE + 1], mx[KC_TABLE + 1];
+struct KcHead {
     unsigned long long c[4];   // ingested, dropped, invalid, future
     uint32_t cur_seg, next_pos_lo, next_pos_hi, pad_;
     long long cur_latest;
 };
+struct KcSmem {
+    KcHead h;
+    uint32_t tag[KC_TABLE + 1], cnt[KC_TABLE + 1], sum_lo[KC_TABLE + 1], sq_lo[KC_TABLE + 1], carry[KC_TABLE + 1] /* sq: bits 8.., sum: bits 0..7 */,
+        mn[KC_TABLE + 1], mx[KC_TABLE + 1];
+};
+
+// When every key has room in shared memory (K <= KC_DIRECT_KEYS: the reference's 400 keys, BASELINE config 2's 10 000),
+// the table needs no tags, no hash and no probing: entry = key, for the segment's latest bucket (age 0; the few late
+// arrivals go straight to the planes).  20 bytes per key: count, sum, sum of squares (32 bits each, carries counted in a
+// fourth word) and two 16-bit FILTERS for min / max - a duration below the filter (above, for max) goes to the planes'
+// own atomicMin / atomicMax and is stored into the filter with a plain 16-bit store.  A filter is never below the minimum
+// the planes hold (only values that were also sent are stored), so nothing that matters is filtered out; a lost race
+// only lets a few more values through.
+constexpr uint32_t KC_DIRECT_KEYS = 11584;
+struct KcDirect {
+    KcHead h;
+    uint32_t words[1];  // cnt[Kp] sum_lo[Kp] sq_lo[Kp] carry[Kp], then uint16 mn[Kp] mx[Kp];  Kp = K rounded up to 32
+};
+__host__ __device__ inline uint32_t kc_direct_kp(uint32_t K) { return (K + 31u) & ~31u; }
+__host__ __device__ inline size_t kc_direct_bytes(uint32_t K) { return sizeof(KcHead) + (size_t)kc_direct_kp(K) * 20u; }
 
 struct ChunkReduceParams {
     const uint32_t* svc;
@@ -119,48 +137,81 @@ __device__ __forceinline__ void kc_table_flush(const ChunkReduceParams& p, KcSme
     }
 }
 
+template <bool DIRECT>
 __global__ void __launch_bounds__(KC_THREADS, 1) reduce_chunk_kernel(const ChunkReduceParams p) {
     extern __shared__ __align__(16) unsigned char kc_raw[];
     KcSmem& sm = *reinterpret_cast<KcSmem*>(kc_raw);
+    KcHead& hd = *reinterpret_cast<KcHead*>(kc_raw);  // first member of either layout
     const int tid = threadIdx.x, lane = tid & 31;
-    kc_table_init(sm, tid);
-    if (tid < 4) sm.c[tid] = 0;
+    // direct layout (DIRECT only)
+    const uint32_t Kp = kc_direct_kp(p.K);
+    uint32_t* const d_cnt = reinterpret_cast<KcDirect*>(kc_raw)->words;
+    uint32_t* const d_sum = d_cnt + Kp;
+    uint32_t* const d_sq = d_sum + Kp;
+    uint32_t* const d_carry = d_sq + Kp;
+    unsigned short* const d_mn = reinterpret_cast<unsigned short*>(d_carry + Kp);
+    unsigned short* const d_mx = d_mn + Kp;
+    auto table_init = [&]() {
+        if constexpr (DIRECT) {
+            for (uint32_t i = tid; i < Kp; i += KC_THREADS) { d_cnt[i] = 0; d_sum[i] = 0; d_sq[i] = 0; d_carry[i] = 0; d_mn[i] = 0xFFFFu; d_mx[i] = 0; }
+        } else {
+            kc_table_init(sm, tid);
+        }
+    };
+    auto table_flush = [&](uint32_t seg) {
+        if constexpr (DIRECT) {
+            for (uint32_t k = tid; k < p.K; k += KC_THREADS) {
+                const uint32_t c = d_cnt[k];
+                if (!c) continue;
+                const size_t ai = kc_cell(p, seg, 0, k);  // min / max are in the planes already
+                const uint32_t cy = d_carry[k];
+                atomicAdd(&p.planes.cnt[ai], c);
+                atomicAdd(&p.planes.sum[ai], (unsigned long long)d_sum[k] + ((unsigned long long)(cy & 0xFFu) << 32));
+                atomicAdd(&p.planes.sq_lo[ai], (unsigned long long)d_sq[k]);
+                if (cy >> 8) atomicAdd(&p.planes.sq_hi[ai], (unsigned long long)(cy >> 8));
+            }
+        } else {
+            kc_table_flush(p, sm, tid, seg);
+        }
+    };
+    table_init();
+    if (tid < 4) hd.c[tid] = 0;
     // this CTA's contiguous stretch of tiles
     const uint32_t t0 = (uint32_t)(((uint64_t)blockIdx.x * p.tiles) / gridDim.x);
     const uint32_t t1 = (uint32_t)(((uint64_t)(blockIdx.x + 1) * p.tiles) / gridDim.x);
     if (tid == 0) {
         const uint32_t s = kc_marks_le(p.marks, 0, p.nt, (uint64_t)t0 * KC_TILE);
         const unsigned long long np = s < p.nt ? p.marks[s].pos : ~0ull;
-        sm.cur_seg = s;
-        sm.next_pos_lo = (uint32_t)np; sm.next_pos_hi = (uint32_t)(np >> 32);
-        sm.cur_latest = s == 0 ? p.latest0 : p.marks[s - 1].label;
+        hd.cur_seg = s;
+        hd.next_pos_lo = (uint32_t)np; hd.next_pos_hi = (uint32_t)(np >> 32);
+        hd.cur_latest = s == 0 ? p.latest0 : p.marks[s - 1].label;
     }
     __syncthreads();
     unsigned long long n_ing = 0, n_drop = 0, n_inv = 0, n_fut = 0;
     uint32_t since_flush = 0;  // a CTA-uniform count of tiles: the sum carry has 8 bits (2^40 / 2^16 values = 2^24 updates per entry)
     for (uint32_t tile = t0; tile < t1; ++tile) {
         const uint64_t tile_begin = (uint64_t)tile * KC_TILE;
-        unsigned long long next_pos = ((unsigned long long)sm.next_pos_hi << 32) | sm.next_pos_lo;
+        unsigned long long next_pos = ((unsigned long long)hd.next_pos_hi << 32) | hd.next_pos_lo;
         if (tile_begin >= next_pos || since_flush >= 4000u) {
             // the stretch enters a new segment (or the carries near their width): hand the table to the planes of the old one
             __syncthreads();
-            kc_table_flush(p, sm, tid, sm.cur_seg);
+            table_flush(hd.cur_seg);
             __syncthreads();
-            kc_table_init(sm, tid);
+            table_init();
             if (tid == 0) {
-                const uint32_t s = kc_marks_le(p.marks, sm.cur_seg, p.nt, tile_begin);
+                const uint32_t s = kc_marks_le(p.marks, hd.cur_seg, p.nt, tile_begin);
                 const unsigned long long np = s < p.nt ? p.marks[s].pos : ~0ull;
-                sm.cur_seg = s;
-                sm.next_pos_lo = (uint32_t)np; sm.next_pos_hi = (uint32_t)(np >> 32);
-                sm.cur_latest = s == 0 ? p.latest0 : p.marks[s - 1].label;
+                hd.cur_seg = s;
+                hd.next_pos_lo = (uint32_t)np; hd.next_pos_hi = (uint32_t)(np >> 32);
+                hd.cur_latest = s == 0 ? p.latest0 : p.marks[s - 1].label;
             }
             __syncthreads();
-            next_pos = ((unsigned long long)sm.next_pos_hi << 32) | sm.next_pos_lo;
+            next_pos = ((unsigned long long)hd.next_pos_hi << 32) | hd.next_pos_lo;
             since_flush = 0;
         }
         ++since_flush;
-        const uint32_t cur_seg = sm.cur_seg;
-        const long long cur_latest = sm.cur_latest;
+        const uint32_t cur_seg = hd.cur_seg;
+        const long long cur_latest = hd.cur_latest;
         const uint64_t idx = tile_begin + (uint64_t)tid * KC_PER_THREAD;
         uint32_t svc[4], jvm[4];
         int32_t el[4];
@@ -214,14 +265,29 @@ __global__ void __launch_bounds__(KC_THREADS, 1) reduce_chunk_kernel(const Chunk
                             age = (uint32_t)(latest - lab);
                             v = (uint32_t)el[j];
                             n_ing++;
-                            if (seg == cur_seg && v < 65536u) tag = (age << KC_AGE_SHIFT) | k;
+                            if (seg == cur_seg && v < 65536u && (!DIRECT || age == 0)) tag = (age << KC_AGE_SHIFT) | k;
                             else direct = true;
                         }
                     }
                 }
             }
             bool done = tag == KC_EMPTY && !direct;
-            if (tag != KC_EMPTY) {
+            if (DIRECT && tag != KC_EMPTY) {
+                const uint32_t oc = atomicAdd(&d_cnt[k], 1u);
+                const uint32_t os = atomicAdd(&d_sum[k], v);
+                const uint32_t q = v * v;
+                const uint32_t oq = atomicAdd(&d_sq[k], q);
+                const uint32_t cy = ((os + v < os) ? 1u : 0u) | ((oq + q < oq) ? 0x100u : 0u);
+                if (cy) atomicAdd(&d_carry[k], cy);
+                if (oc == 0 || v < d_mn[k] || v > d_mx[k]) {
+                    const size_t ai = kc_cell(p, seg, 0, k);
+                    if (v < d_mn[k]) { atomicMin(&p.planes.vmin[ai], v); d_mn[k] = (unsigned short)v; }
+                    if (v > d_mx[k]) { atomicMax(&p.planes.vmax[ai], v); d_mx[k] = (unsigned short)v; }
+                    // whoever touches the entry first names the key for this segment: once per (CTA, segment, key)
+                    if (oc == 0 && p.first_seg[k] > seg) atomicMin(&p.first_seg[k], seg);
+                }
+                done = true;
+            } else if (tag != KC_EMPTY) {
                 // Straight-line probing (no loop around the compare-and-swap): with a backward branch here the compiler
                 // treats the lanes as possibly waiting for each other and never lets a split warp rejoin - every later
                 // transaction of the tile was then executed once per group of lanes.
@@ -260,19 +326,19 @@ __global__ void __launch_bounds__(KC_THREADS, 1) reduce_chunk_kernel(const Chunk
         }
     }
     __syncthreads();
-    kc_table_flush(p, sm, tid, sm.cur_seg);
+    table_flush(hd.cur_seg);
     const unsigned long long mine[4] = {n_ing, n_drop, n_inv, n_fut};
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         const uint32_t wsum = __reduce_add_sync(0xffffffffu, (uint32_t)mine[q]);
-        if (lane == 0 && wsum) atomicAdd(&sm.c[q], (unsigned long long)wsum);
+        if (lane == 0 && wsum) atomicAdd(&hd.c[q], (unsigned long long)wsum);
     }
     __syncthreads();
     if (tid == 0) {
-        if (sm.c[0]) atomicAdd(&p.counters->ingested, sm.c[0]);
-        if (sm.c[1]) atomicAdd(&p.counters->dropped, sm.c[1]);
-        if (sm.c[2]) atomicAdd(&p.counters->invalid, sm.c[2]);
-        if (sm.c[3]) atomicAdd(&p.counters->future, sm.c[3]);
+        if (hd.c[0]) atomicAdd(&p.counters->ingested, hd.c[0]);
+        if (hd.c[1]) atomicAdd(&p.counters->dropped, hd.c[1]);
+        if (hd.c[2]) atomicAdd(&p.counters->invalid, hd.c[2]);
+        if (hd.c[3]) atomicAdd(&p.counters->future, hd.c[3]);
     }
 }
 
@@ -579,11 +645,17 @@ apm_status apm_stats_chunk(apm_ctx* c, const apm_tx_columns& d, uint64_t n, cons
         const uintptr_t align = (uintptr_t)d.service_id | (uintptr_t)d.jvm_id | (uintptr_t)d.end_ts_ms | (uintptr_t)d.elapsed_ms;
         p.vec_ok = (align & 15) == 0;
         static unsigned long long attr_done = 0;
-        if (apm_first_on_device(&attr_done))
-            CUDA_TRY(c, cudaFuncSetAttribute(reduce_chunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(KcSmem)));
+        if (apm_first_on_device(&attr_done)) {
+            CUDA_TRY(c, cudaFuncSetAttribute(reduce_chunk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(KcSmem)));
+            CUDA_TRY(c, cudaFuncSetAttribute(reduce_chunk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)kc_direct_bytes(KC_DIRECT_KEYS)));
+        }
         unsigned g = (unsigned)c->num_sms;
         if (g > p.tiles) g = p.tiles;
-        reduce_chunk_kernel<<<g, KC_THREADS, sizeof(KcSmem), st>>>(p);
+        if (c->K <= KC_DIRECT_KEYS && c->stats_chunk_direct)  // every key has its own entry: no tags, no probing
+            reduce_chunk_kernel<true><<<g, KC_THREADS, kc_direct_bytes(c->K), st>>>(p);
+        else
+            reduce_chunk_kernel<false><<<g, KC_THREADS, sizeof(KcSmem), st>>>(p);
         c->launches += 1;
         CUDA_TRY(c, cudaGetLastError());
     }
@@ -637,7 +709,7 @@ apm_status apm_stats_chunk(apm_ctx* c, const apm_tx_columns& d, uint64_t n, cons
 }
 
 cudaError_t apm_preload_k1_chunk() {
-    const void* fns[] = {(const void*)reduce_chunk_kernel, (const void*)chunk_ticks_kernel, (const void*)chunk_ticks_small_kernel};
+    const void* fns[] = {(const void*)reduce_chunk_kernel<false>, (const void*)reduce_chunk_kernel<true>, (const void*)chunk_ticks_kernel, (const void*)chunk_ticks_small_kernel};
     cudaError_t first = cudaSuccess;
     for (const void* f : fns) {
         cudaFuncAttributes a;

@@ -2,7 +2,8 @@
 whole chunk in two launches - one keyed reduce into per-segment planes, one kernel that walks the chunk's ticks per
 key (k1_chunk.cu).  Its records must equal the oracle's and those of the per-tick path (APM_STATS_CHUNK=0) bit for
 bit: same ticks, same windows, same first-seen behaviour, also when ticks fall inside a CTA's stretch, when buckets
-are skipped, when keys appear in the middle of a chunk and when durations leave the shared-memory table's range."""
+are skipped, when keys appear in the middle of a chunk and when durations leave the shared-memory table's range -
+with the direct-mapped table (every key fits shared memory) and with the hashed one."""
 import os
 
 import numpy as np
@@ -74,6 +75,9 @@ def test_whole_chunk_path_equals_the_oracle_and_the_per_tick_path(S, J, n, windo
     want, wcnt = _run(_engine(S, J, bucket_ms, window, buffer, PER_TICK, **kw), cols, calls)
     assert got.size == want.size and got.tobytes() == want.tobytes()
     assert cnt == wcnt
+    # up to 11 584 keys every key has its own shared-memory entry (no tags, no probing); the hashed table gives the same
+    hashed, hcnt = _run(_engine(S, J, bucket_ms, window, buffer, dict(CHUNKED, APM_STATS_CHUNK_DIRECT="0"), **kw), cols, calls)
+    assert hashed.tobytes() == want.tobytes() and hcnt == wcnt
     orc = ocapi.Pipeline(ocapi.make_config(S, J, bucket_ms, window, buffer, (), (0, 1), (), (), (), flags=ocapi.F_KEEP_STATS), fast=True)
     orc.consume(*cols)
     assert_stats_equal(got, orc.stats())
