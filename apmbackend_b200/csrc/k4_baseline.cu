@@ -544,17 +544,31 @@ __global__ void __launch_bounds__(96) baseline_few_kernel(const __grid_constant_
         K4DBG(2);  // shared memory -> registers
         const uint32_t r0 = c < nA ? head + c * ROWS : (c - nA) * ROWS, end = c < nA ? L : head;
         const uint32_t rows = end - r0 < (uint32_t)ROWS ? end - r0 : (uint32_t)ROWS;
-        // Still under the other adder's chain: is every entry of the chunk a number?  (The lists hold non-negative
-        // values or NaN; the test is on the exponent field, so anything non-finite takes the careful path.)  Decided
-        // for the warp as a whole, so that the chain below is straight-line code and its result can be posted the
-        // moment the last add retires.
+        // Still under the other adder's chain: the chunk is made safe for BARE adds.  average() skips an undefined entry
+        // (util_methods.js:12-18); adding +0.0 in its place gives the same bits, because the running sum starts at +0.0
+        // and can never be -0.0 - so a NaN entry, and a row past the end of a ragged chunk, becomes +0.0 here and is
+        // left out of the count.  (Whether anything needs replacing is first read off the exponent fields: one integer
+        // max per entry.)  The chain below is then the same 96 adds for every chunk, and its result can be posted the
+        // moment the last one retires.
         uint32_t hi_max = 0;
 #pragma unroll
         for (int r = 0; r < ROWS; ++r) {
             const uint32_t hi = (uint32_t)__double2hiint(v[r]) & 0x7fffffffu;
             hi_max = hi > hi_max ? hi : hi_max;
         }
-        const bool fast = __all_sync(0xffffffffu, !full || hi_max < 0x7ff00000u) && rows == (uint32_t)ROWS;
+        uint32_t nvalid = ROWS;
+        last = sm.buf[s][rows - 1u][lane];  // prevValuesList[length - 1], undefined or not (:96); read from the stage: a
+                                            // run-time index into v[] would move the whole array to local memory
+        if (__any_sync(0xffffffffu, hi_max >= 0x7ff00000u) || rows != (uint32_t)ROWS) {
+            nvalid = 0;
+#pragma unroll
+            for (int r = 0; r < ROWS; ++r) {
+                const bool here = (uint32_t)r < rows;
+                const bool ok = here && v[r] == v[r];
+                nvalid += ok ? 1u : 0u;
+                v[r] = ok ? v[r] : 0.0;
+            }
+        }
         if (c > 0) {  // the running sum after chunk c - 1, from the other adder
             asm volatile("bar.sync %0, 64;" ::"r"(1u + (w ^ 1u)) : "memory");
             const uint32_t addr = smem_u32(&sm.mail[w ^ 1u][lane]);
@@ -564,20 +578,10 @@ __global__ void __launch_bounds__(96) baseline_few_kernel(const __grid_constant_
             cnt = (uint32_t)b;
         }
         K4DBG(3);  // waiting for the other adder
-        if (fast) {
-            // bare adds in every lane (a lane whose list is not full yet computes a sum nobody reads)
+        // (a lane whose list is not full yet computes a sum nobody reads)
 #pragma unroll
-            for (int r = 0; r < ROWS; ++r) sum = __dadd_rn(sum, v[r]);
-            cnt += ROWS;
-            last = v[ROWS - 1];
-        } else {
-#pragma unroll
-            for (int r = 0; r < ROWS; ++r)
-                if ((uint32_t)r < rows) {
-                    if (full) accumulate(v[r], sum, cnt);
-                    last = v[r];
-                }
-        }
+        for (int r = 0; r < ROWS; ++r) sum = __dadd_rn(sum, v[r]);
+        cnt += nvalid;
         if (c + 1 < n) {
             const uint32_t addr = smem_u32(&sm.mail[w][lane]);
             const unsigned long long a = (unsigned long long)__double_as_longlong(sum), b = (unsigned long long)cnt;
