@@ -236,8 +236,30 @@ __global__ void __launch_bounds__(KC_THREADS, 1) reduce_chunk_kernel(const Chunk
                 svc[j] = in[j] ? p.svc[i] : 0; jvm[j] = in[j] ? p.jvm[i] : 0; el[j] = in[j] ? p.el[i] : 0; ts[j] = in[j] ? p.ts[i] : 0;
             }
         }
+        // DIRECT: in a tile without a tick, a transaction of the segment's latest bucket with a 16-bit duration - nearly
+        // all of them - is four compares away from its table entry (3 % on cfg2: the kernel waits for its loads more than
+        // it computes; 512 threads with the next tile's loads in flight were slower, 16 warps do not fill the SM)
+        const bool plain_tile = tile_begin + KC_TILE <= next_pos;
+        const int64_t b0_tile = cur_latest * p.bucket_ms;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
+            if (DIRECT && in[j] && plain_tile && svc[j] < p.num_services && jvm[j] < p.num_jvms && (uint32_t)el[j] < 65536u &&
+                (uint64_t)(ts[j] - b0_tile) < (uint64_t)p.bucket_ms) {
+                const uint32_t k = jvm[j] * p.num_services + svc[j], v = (uint32_t)el[j];
+                n_ing++;
+                const uint32_t oc = atomicAdd(&d_cnt[k], 1u);
+                const uint32_t os = atomicAdd(&d_sum[k], v);
+                const uint32_t q = v * v;
+                const uint32_t oq = atomicAdd(&d_sq[k], q);
+                const uint32_t cy = ((os + v < os) ? 1u : 0u) | ((oq + q < oq) ? 0x100u : 0u);
+                if (cy) atomicAdd(&d_carry[k], cy);
+                if (oc == 0 || v < d_mn[k] || v > d_mx[k]) {
+                    const size_t ai = kc_cell(p, cur_seg, 0, k);
+                    if (v < d_mn[k]) { atomicMin(&p.planes.vmin[ai], v); d_mn[k] = (unsigned short)v; }
+                    if (v > d_mx[k]) { atomicMax(&p.planes.vmax[ai], v); d_mx[k] = (unsigned short)v; }
+                    if (oc == 0 && p.first_seg[k] > cur_seg) atomicMin(&p.first_seg[k], cur_seg);
+                }
+            } else {
             // what becomes of transaction j: nothing (skipped / counted only), a direct update of the planes, or a table update
             uint32_t tag = KC_EMPTY, v = 0, seg = cur_seg, age = 0, k = 0;
             bool direct = false;
@@ -321,6 +343,7 @@ __global__ void __launch_bounds__(KC_THREADS, 1) reduce_chunk_kernel(const Chunk
             if (!done) {
                 kc_direct(p, seg, age, k, v);
                 if (p.first_seg[k] > seg) atomicMin(&p.first_seg[k], seg);
+            }
             }
             __syncwarp();  // lanes that took different paths (probe lengths, misses) go on together
         }
