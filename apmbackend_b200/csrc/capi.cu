@@ -291,7 +291,8 @@ apm_status do_tick(apm_ctx* c, int64_t new_latest) {
         if (c->overlap) {
             // Launched later - behind the next segment's ingest kernel (see apm_flush_pending) - so that the
             // bandwidth-hungry baseline does not start on top of the latency-bound head of the next tick's chain.
-            CUDA_TRY(c, cudaEventRecord(c->ev_stats[ev], c->s_main));
+            // (no event here: apm_flush_pending records one on this stream behind the NEXT segment's ingest kernel, which
+            // follows this tick's window kernel)
             c->pending = pb;
         } else {
             st = launch_baseline_group(c, pb, c->s_main);
@@ -505,7 +506,6 @@ apm_status apm_flush_pending(apm_ctx* c) {
     APM_ENTER(c);
     const PendingBaseline pb = c->pending;
     c->pending.valid = false;
-    CUDA_TRY(c, cudaStreamWaitEvent(c->s_base, c->ev_stats[pb.ev], 0));
     CUDA_TRY(c, cudaEventRecord(c->ev_mid, c->s_main));
     CUDA_TRY(c, cudaStreamWaitEvent(c->s_base, c->ev_mid, 0));
     apm_status st = launch_baseline_group(c, pb, c->s_base);
