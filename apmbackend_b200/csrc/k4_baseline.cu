@@ -1034,12 +1034,14 @@ apm_status apm_baseline_make_tmaps(apm_ctx* c) {
     return APM_OK;
 }
 
-// Few lists: every lag's column groups together fit the SMs one CTA each (cfg1: 2 x 38 of 148).
+// Few lists: every lag's column groups together fit the SMs one CTA each (cfg1: 2 x 38 of 148) - or twice that: the
+// CTAs do not wait for each other, the longest lag's are placed first, and two waves of the latency-bound walk (2 x 50 us
+// for day-long lists) still beat the bandwidth-oriented kernel, whose one warp per CTA takes 113 us for such a list.
 bool apm_baseline_few_ok(const apm_ctx* c) {
     if (!c->k4_few || !c->ring_tmap_ok || c->cfg.sd_mode != APM_SD_REFERENCE || c->k4_force_ldg || c->k4_stages != 0) return false;
     if (c->cfg.flags & APM_F_INCREMENTAL) return false;
     const unsigned g = (3u * c->K + K4T_COLS - 1) / K4T_COLS;
-    return c->cfg.num_lags > 0 && g * (unsigned)c->cfg.num_lags <= (unsigned)c->num_sms;
+    return c->cfg.num_lags > 0 && g * (unsigned)c->cfg.num_lags <= 2u * (unsigned)c->num_sms;
 }
 
 // All lags of one tick in one launch (see baseline_few_kernel).

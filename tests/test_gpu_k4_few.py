@@ -47,8 +47,9 @@ def _run(eng, cols, calls):
 @pytest.mark.parametrize("S,J,lags,span,calls", [
     (40, 2, (5, 130), 420, 3),         # a lag far below one chunk, one of 1.4 chunks; the ring wraps three times
     (200, 2, (96, 192, 333), 700, 2),  # lags of exactly one and two chunks and a ragged one; three lags in one launch
-    (390, 1, (7, 61, 200, 401), 900, 4),  # four lags x 37 column groups = 148 CTAs: the last shape that qualifies
-], ids=["two-lags", "chunk-multiples", "four-lags-148-ctas"])
+    (390, 1, (7, 61, 200, 401), 900, 4),  # four lags x 37 column groups = 148 CTAs: one CTA per SM
+    (1000, 1, (50, 300), 640, 2),      # two lags x 94 column groups = 188 CTAs: more than the SMs, a second wave
+], ids=["two-lags", "chunk-multiples", "four-lags-148-ctas", "two-waves"])
 def test_few_list_walk_equals_the_oracle_and_the_per_lag_kernels(S, J, lags, span, calls):
     c = dict(S=S, J=J, bucket_ms=10000, window=3, buffer=1, pcts=(75.0, 95.0), lags=lags, thr=tuple(1.5 + 0.5 * i for i in range(len(lags))),
              infl=tuple(0.1 * i for i in range(len(lags))), log_cap=1 << 14, max_batch=1 << 15, out_ticks=span + 8)
