@@ -614,6 +614,7 @@ apm_status apm_ctx_create(const apm_config* cfg, apm_ctx** out) {
     if (const char* e = getenv("APM_K4_STAGES")) c->k4_stages = atoi(e);
     if (const char* e = getenv("APM_K4_LDG")) c->k4_force_ldg = atoi(e) != 0;
     if (const char* e = getenv("APM_K4_FEW")) c->k4_few = atoi(e) != 0;
+    if (const char* e = getenv("APM_K4_FEW_WAVES")) c->k4_few_waves = std::max(1, atoi(e));
     if (getenv("APM_SMEM_CARVEOUT")) apm_preload_kernels(c->cfg.device);  // the carve-out preference is applied by the preload
     if (const char* e = getenv("APM_K1_TPC")) { int v = atoi(e); if (v > 0) c->k1_tiles_per_cta = (uint32_t)v; }
     // windowSz * intervalLengthSec / 60.0 (stream_calc_stats.js:186)

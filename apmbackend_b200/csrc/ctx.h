@@ -183,6 +183,7 @@ struct apm_ctx {
     int k4_stages = 0;              // APM_K4_STAGES: bulk-tensor loads in flight per CTA (2, 3, 4, 6, or 8 = the three-box instance for few lists); 0 = by grid size
     bool k4_force_ldg = false;      // APM_K4_LDG=1: register-pipelined loads instead of TMA (A/B measurements)
     bool k4_few = true;             // APM_K4_FEW=0: per-lag launches of baseline_tma_kernel also when all lags' column groups fit the SMs
+    int k4_few_waves = 2;           // APM_K4_FEW_WAVES: the few-list walk is used while its CTAs fit this many waves of one CTA per SM
 
     // log feeder (k6_logparse.cu), created by the first apm_dict_set / apm_parse_log_host
     void* lp = nullptr;

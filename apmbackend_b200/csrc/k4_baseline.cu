@@ -1041,7 +1041,7 @@ bool apm_baseline_few_ok(const apm_ctx* c) {
     if (!c->k4_few || !c->ring_tmap_ok || c->cfg.sd_mode != APM_SD_REFERENCE || c->k4_force_ldg || c->k4_stages != 0) return false;
     if (c->cfg.flags & APM_F_INCREMENTAL) return false;
     const unsigned g = (3u * c->K + K4T_COLS - 1) / K4T_COLS;
-    return c->cfg.num_lags > 0 && g * (unsigned)c->cfg.num_lags <= 2u * (unsigned)c->num_sms;
+    return c->cfg.num_lags > 0 && g * (unsigned)c->cfg.num_lags <= (unsigned)c->k4_few_waves * (unsigned)c->num_sms;
 }
 
 // All lags of one tick in one launch (see baseline_few_kernel).
